@@ -1,0 +1,270 @@
+/*
+ * libscenesubmit — C ABI of the B200-native scene-submission path.
+ *
+ * This header is the drop-in boundary.  The reference (PrakarshPanwar/VulkanEngine) has no FFI for
+ * this path; the seam is a handful of C++ member functions.  Every entry point below names the
+ * reference code it stands in for (paths relative to VulkanCore/src/, "VC/" = VulkanCore/,
+ * "PV/" = Platform/Vulkan/).  INTEGRATION.md shows the C++ binding a maintainer would add behind the
+ * unchanged Scene / SceneRenderer signatures.
+ *
+ * Conventions
+ *   - plain pointers and sizes only; no C++ or torch types cross the boundary;
+ *   - every call returns an ss_status; the library never throws and never aborts the host
+ *     (reference convention on this path is a silent skip, VC/Scene/SceneRenderer.cpp:1128-1136);
+ *   - host pointers passed to ss_set_* / ss_upload_* are copied (or queued from pinned memory and
+ *     fenced) before the call returns: the caller owns them again immediately;
+ *   - device buffers returned by ss_map_outputs stay valid until the same frame slot is reused,
+ *     i.e. for frames_in_flight-1 further ss_frame calls (VC/Renderer/Renderer.h:28, FramesInFlight=3);
+ *   - one context per GPU, single producer thread (VC/Core/Application.cpp:68-69); no global state.
+ *
+ * All floating point is IEEE binary32.  Matrices are column-major float[16] exactly as glm::mat4
+ * lies in memory (m[col*4 + row]); instance rows are TransformData (3 x vec4, row r =
+ * (M[0][r], M[1][r], M[2][r], M[3][r]); VC/Core/Components.h:95-98).
+ */
+#ifndef SCENESUBMIT_H
+#define SCENESUBMIT_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(_WIN32)
+#define SS_API __declspec(dllexport)
+#else
+#define SS_API __attribute__((visibility("default")))
+#endif
+
+#define SS_VERSION_MAJOR 0
+#define SS_VERSION_MINOR 1
+
+#define SS_MAX_VIEWS 8u          /* one visibility byte per instance */
+#define SS_MAX_LEVELS 64u
+#define SS_SLOT_NULL 0xFFFFFFFFu /* instance is dropped (null mesh / null table / zero vertices) */
+#define SS_MATERIAL_TESS_BIT 0x80000000u /* material word: bit 31 = HasDisplacementTexture() */
+
+typedef enum ss_status {
+    SS_OK = 0,
+    SS_ERR_INVALID = 1,   /* bad argument (null pointer, size beyond capacity, malformed table) */
+    SS_ERR_CUDA = 2,      /* a CUDA runtime call failed; see ss_last_error */
+    SS_ERR_CAPACITY = 3,  /* an output list overflowed its configured capacity */
+    SS_ERR_STATE = 4,     /* call order violated (frame before streams were set, bad slot ...) */
+    SS_ERR_NOMEM = 5
+} ss_status;
+
+typedef enum ss_trig_mode {
+    /* sin/cos of the half Euler angles through the explicit polynomial in scenesubmit_dettrig.h:
+       the whole chain (matrices, masks, draw order) is bit-identical to the CPU oracle. */
+    SS_TRIG_DETERMINISTIC = 0,
+    /* CUDA sinf/cosf, as glm::sin/glm::cos call libm (GLM/detail/type_quat.inl:208-217):
+       matrices agree with the reference to 1e-6 relative, masks can differ on borderline boxes. */
+    SS_TRIG_LIBM = 1
+} ss_trig_mode;
+
+typedef enum ss_view_flags {
+    SS_VIEW_DEFAULT = 0,
+    /* shadow cascades: the shadow pipeline clamps depth (VC/Scene/SceneRenderer.cpp:188), so casters
+       in front of the near plane still land in the map: skip the near plane. */
+    SS_VIEW_SKIP_NEAR = 1
+} ss_view_flags;
+
+typedef enum ss_frame_flags {
+    SS_FRAME_DEFAULT = 0,
+    /* stage-wise parity: do not run the transform stage, cull/sort/emit from the world rows given
+       to ss_upload_world_rows */
+    SS_FRAME_WORLD_ROWS_GIVEN = 1,
+    /* run without the CUDA graph even if one is cached for this shape */
+    SS_FRAME_NO_GRAPH = 2
+} ss_frame_flags;
+
+typedef struct ss_ctx ss_ctx;
+
+typedef struct ss_config {
+    uint32_t struct_size;          /* sizeof(ss_config), for ABI growth */
+    int32_t device;                /* CUDA device ordinal */
+    uint32_t max_nodes;            /* transform (entity) stream capacity */
+    uint32_t max_instances;        /* instance (entity x submesh) stream capacity */
+    uint32_t max_submesh_slots;    /* rows of the global submesh table */
+    uint32_t max_views;            /* 1..SS_MAX_VIEWS */
+    uint32_t max_draws_per_view;   /* distinct keys per view; 0 = min(max_instances, 1<<20) */
+    uint32_t frames_in_flight;     /* output slots; 0 = 3 (VC/Renderer/Renderer.h:28) */
+    uint64_t max_visible_per_view; /* compacted list capacity per view; 0 = max_instances */
+    uint32_t trig_mode;            /* ss_trig_mode */
+    uint32_t flags;                /* reserved, 0 */
+} ss_config;
+
+/* One row of the global submesh table: the per-frame facts SubmitMesh reads from Submesh
+   (VC/Mesh/Mesh.h:39-46) plus the bounds the reference lacks. */
+typedef struct ss_submesh {
+    float local[16];        /* Submesh::LocalTransform, glm::mat4 memory; must be affine (row 3 = 0,0,0,1) */
+    float aabb_min[3];      /* over Vertex.Position of [BaseVertex, BaseVertex+VertexCount) */
+    float aabb_max[3];
+    uint32_t index_count;   /* Submesh::IndexCount  -> vkCmdDrawIndexed arg 1 (PV/VulkanRenderer.cpp:628) */
+    uint32_t first_index;   /* Submesh::BaseIndex   -> arg 3 */
+    int32_t vertex_offset;  /* Submesh::BaseVertex  -> arg 4 */
+    uint32_t mesh_rank;     /* rank of Mesh::Handle among the sorted unique mesh handles */
+    uint32_t submesh_index; /* index into MeshSource::GetSubmeshes(), MeshKey::SubmeshIndex */
+    uint32_t reserved;
+} ss_submesh;
+
+typedef struct ss_view {
+    float view_proj[16]; /* P*V (VC/Renderer/EditorCamera.h:45) or CascadeLightMatrices[i]
+                            (VC/Scene/SceneRenderer.cpp:683), glm::mat4 memory */
+    uint32_t flags;      /* ss_view_flags */
+} ss_view;
+
+/* Field for field VkDrawIndexedIndirectCommand; meanings from PV/VulkanRenderer.cpp:628. */
+typedef struct ss_draw_cmd {
+    uint32_t index_count;
+    uint32_t instance_count;
+    uint32_t first_index;
+    int32_t vertex_offset;
+    uint32_t first_instance;
+} ss_draw_cmd;
+
+/* Device pointers of one (slot, view) result; library-owned. */
+typedef struct ss_outputs {
+    const float* instance_rows;   /* [visible][12]  TransformData in draw order */
+    const uint64_t* keys;         /* [visible]      sort key of each compacted instance */
+    const uint32_t* instance_idx; /* [visible]      index into the instance stream (EntityID lookup) */
+    const ss_draw_cmd* draws;     /* [draws]        one per run of equal keys, in MeshKey order */
+    const uint64_t* draw_keys;    /* [draws]        key of each draw (to bind mesh + material) */
+    const uint32_t* counts;       /* device: {visible, draws} of this view */
+    const float* world_rows;      /* [instances][12] every instance's world rows (not per view) */
+    const uint8_t* masks;         /* [instances]    bit v = visible in view v */
+    uint32_t visible;             /* host copies, valid after ss_frame_sync */
+    uint32_t n_draws;
+} ss_outputs;
+
+typedef struct ss_frame_stats {
+    uint32_t n_instances;
+    uint32_t n_views;
+    uint32_t visible[SS_MAX_VIEWS]; /* RendererStats::InstanceCount per pass (PV/VulkanRenderer.h:13-17) */
+    uint32_t draws[SS_MAX_VIEWS];   /* RendererStats::DrawCalls per pass */
+    uint32_t sort_passes_run;       /* radix passes that moved data (others were skipped) */
+    uint32_t overflow;              /* non-zero: a list hit its capacity (results truncated) */
+    float gpu_ms;                   /* CUDA-event time of the frame on the context stream */
+    uint32_t kernel_launches;       /* kernels of this library launched for the frame */
+} ss_frame_stats;
+
+/* ---- lifecycle ------------------------------------------------------------------------------ */
+
+/* Replaces SceneRenderer construction of the draw-list maps (VC/Scene/SceneRenderer.h:252-261):
+   allocates every device stream once, sized from cfg. */
+SS_API ss_status ss_create(const ss_config* cfg, ss_ctx** out);
+SS_API void ss_destroy(ss_ctx* ctx);
+/* Last error text of this context (or of ss_create when ctx is NULL). Never NULL. */
+SS_API const char* ss_last_error(const ss_ctx* ctx);
+SS_API uint32_t ss_version(void);
+
+/* ---- static streams (scene load, SetActiveScene, UpdateMeshInstanceData) --------------------- */
+
+/* Key layout [tess:1][meshRank:mesh_bits][submeshIndex:submesh_bits][materialRank:material_bits],
+   packed right-aligned in a uint64; order-isomorphic to MeshKey::operator<
+   (VC/Scene/SceneRenderer.h:64-85: Mesh, then Submesh, then Material) with the tessellated list
+   after the static one (VC/Scene/SceneRenderer.cpp:1368-1382). Sum of widths <= 63.
+   Default 23/16/24. Narrow widths let the radix sort skip constant digits. */
+SS_API ss_status ss_set_key_layout(ss_ctx* ctx, uint32_t mesh_bits, uint32_t submesh_bits,
+                                   uint32_t material_bits);
+
+/* Replaces the per-frame reads of meshSource->GetSubmeshes()[i] (VC/Scene/SceneRenderer.cpp:1132,1150). */
+SS_API ss_status ss_set_submesh_table(ss_ctx* ctx, const ss_submesh* table, uint32_t count);
+
+/* Transform hierarchy (new step N1; the reference has no parent component).
+   parent[i] < 0 = root, otherwise parent[i] < i and nodes are level-ordered:
+   level l occupies [level_offsets[l], level_offsets[l+1]).  parent may be NULL (all roots, 1 level). */
+SS_API ss_status ss_set_nodes(ss_ctx* ctx, uint32_t n_nodes, const int32_t* parent,
+                              const uint32_t* level_offsets, uint32_t n_levels);
+
+/* Instance stream = what the loops of Scene::OnUpdateGeometry x SubmitMesh enumerate
+   (VC/Scene/Scene.cpp:138-146, VC/Scene/SceneRenderer.cpp:1138), flattened in that order.
+   node[i]          entity whose transform places the instance; NULL = node_base + i
+   submesh_slot[i]  row of the submesh table, or SS_SLOT_NULL to drop (SceneRenderer.cpp:1128-1136)
+   material_word[i] materialRank | SS_MATERIAL_TESS_BIT (fallback to base material already resolved
+                    host-side, SceneRenderer.cpp:1141) */
+SS_API ss_status ss_set_instances(ss_ctx* ctx, uint32_t n_instances, const uint32_t* node,
+                                  uint32_t node_base, const uint32_t* submesh_slot,
+                                  const uint32_t* material_word);
+
+/* Optional per-instance local AABB stream {min.xyz, max.xyz} (synthetic scenes); NULL = use the
+   submesh table's box. */
+SS_API ss_status ss_set_instance_aabbs(ss_ctx* ctx, uint32_t first, uint32_t count,
+                                       const float* minmax6);
+
+/* ---- per-frame inputs ------------------------------------------------------------------------ */
+
+/* Dirty range of TransformComponent {Translation, Rotation(euler xyz, radians), Scale}, 36 B each,
+   exactly the entt pool's memory (VC/Core/Components.h:13-15).  Replaces the GetTransform() call per
+   entity (VC/Scene/Scene.cpp:145).  trs may be pageable or pinned host memory. */
+SS_API ss_status ss_upload_trs(ss_ctx* ctx, uint32_t first, uint32_t count, const float* trs9);
+
+/* Stage-wise parity input: world rows per instance (see SS_FRAME_WORLD_ROWS_GIVEN). */
+SS_API ss_status ss_upload_world_rows(ss_ctx* ctx, uint32_t first, uint32_t count,
+                                      const float* rows12);
+
+/* One frame: transform -> cull -> key -> sort -> compact -> emit, asynchronous on the context
+   stream.  Replaces the body of ShadowPass/GeometryPass submission: Scene::OnUpdateGeometry
+   (VC/Scene/Scene.cpp:135-147) + SubmitMesh (VC/Scene/SceneRenderer.cpp:1124-1167) for every view.
+   *slot_out receives the output slot (frame number modulo frames_in_flight). */
+SS_API ss_status ss_frame(ss_ctx* ctx, const ss_view* views, uint32_t n_views, uint32_t flags,
+                          uint32_t* slot_out);
+
+/* Wait for the slot's frame and fetch its counts (the fence the render thread waits on,
+   VC/Renderer/RenderThread.cpp:71-80). */
+SS_API ss_status ss_frame_sync(ss_ctx* ctx, uint32_t slot, ss_frame_stats* stats_out);
+
+/* ---- outputs --------------------------------------------------------------------------------- */
+
+/* Replaces `for (auto& [mk, dc] : m_MeshDrawList)` (VC/Scene/SceneRenderer.cpp:1336,1368,1381,1429):
+   device pointers for one view of a finished slot. */
+SS_API ss_status ss_map_outputs(ss_ctx* ctx, uint32_t slot, uint32_t view, ss_outputs* out);
+
+/* Host copies for headless consumers and parity tests; any pointer may be NULL. Sizes in elements
+   must be at least the counts reported by ss_frame_sync. */
+SS_API ss_status ss_download_view(ss_ctx* ctx, uint32_t slot, uint32_t view, float* rows12,
+                                  uint64_t* keys, uint32_t* instance_idx, ss_draw_cmd* draws,
+                                  uint64_t* draw_keys);
+SS_API ss_status ss_download_world(ss_ctx* ctx, uint32_t first, uint32_t count, float* rows12);
+SS_API ss_status ss_download_masks(ss_ctx* ctx, uint32_t first, uint32_t count, uint8_t* masks);
+SS_API ss_status ss_download_keys(ss_ctx* ctx, uint32_t first, uint32_t count, uint64_t* keys);
+
+/* The CUDA stream (cudaStream_t) frames run on, so a consumer can order its own work after them. */
+SS_API void* ss_stream(ss_ctx* ctx);
+
+/* ---- the sort on its own ---------------------------------------------------------------------- */
+
+/* Stable LSD radix sort (onesweep) of (uint64 key, uint32 value) pairs on bits [begin_bit, end_bit).
+   Device pointers; a/b are ping-pong buffers of n elements; scratch from ss_sort_scratch_bytes(n).
+   The grouping std::map<MeshKey,...> does on the CPU (VC/Scene/SceneRenderer.h:252-253) is this sort.
+   On return *sorted_in_b (host) tells which buffer pair holds the result.  Synchronous w.r.t. the
+   host only in that it reads one flag word back after the last pass. */
+SS_API size_t ss_sort_scratch_bytes(uint64_t n);
+SS_API ss_status ss_sort_pairs(void* cuda_stream, uint64_t* keys_a, uint32_t* vals_a,
+                               uint64_t* keys_b, uint32_t* vals_b, uint64_t n, int begin_bit,
+                               int end_bit, void* scratch, size_t scratch_bytes, int* sorted_in_b);
+/* Convenience for tests: host arrays in, host arrays out; allocates and frees device memory. */
+SS_API ss_status ss_sort_pairs_host(int device, const uint64_t* keys_in, const uint32_t* vals_in,
+                                    uint64_t* keys_out, uint32_t* vals_out, uint64_t n,
+                                    int begin_bit, int end_bit);
+
+/* ---- host-side view matrices (stay on the host) --------------------------------- */
+
+/* EditorCamera::GetViewProjection for a camera given by position + pitch/yaw
+   (VC/Renderer/EditorCamera.cpp:15-33, EditorCamera.h:45): P = perspectiveRH_ZO, V = inverse(T*R). */
+SS_API ss_status ss_camera_view_proj(float fov_y, float aspect, float z_near, float z_far,
+                                     const float position[3], float pitch, float yaw,
+                                     float view_out[16], float proj_out[16], float view_proj_out[16]);
+
+/* SceneRenderer::UpdateCascadeMap (VC/Scene/SceneRenderer.cpp:579-687) with CascadeOffset = 0:
+   4 split depths (stored negated, :682) and 4 light matrices. */
+SS_API ss_status ss_cascade_matrices(const float view_proj[16], float z_near, float z_far,
+                                     float split_lambda, float near_offset, float far_offset,
+                                     const float light_dir[3], float splits_out[4],
+                                     float light_matrices_out[4][16]);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SCENESUBMIT_H */

@@ -1,0 +1,653 @@
+/*
+ * CPU oracle for libscenesubmit — TEST INFRASTRUCTURE, NOT PRODUCT (see scenesubmit_oracle.h).
+ *
+ * Build: gcc -O2 -ffp-contract=off -fno-fast-math -std=c11 -fPIC -shared -pthread  (oracle/Makefile).
+ * Float op order follows the scalar GLM 0.9.9.9 the reference vendors; no FMA, no reassociation.
+ * Citations: "VC/" = /root/reference/VulkanCore/src/VulkanCore/, "GLM/" = /root/reference/VulkanCore/vendor/glm/glm/.
+ */
+#define _GNU_SOURCE
+#include "scenesubmit_oracle.h"
+
+#include <math.h>
+#include <pthread.h>
+#include <stdlib.h>
+#include <string.h>
+#include <time.h>
+
+#include "../include/scenesubmit_dettrig.h" /* the deterministic sin/cos DEFINITION (spec header) */
+
+/* m[c*4 + r] = glm m[c][r] */
+#define M(m, c, r) ((m)[(c) * 4 + (r)])
+
+void sso_det_sincos(float x, float* s, float* c) { ss_det_sincosf(x, s, c); }
+
+/* GLM/detail/type_mat4x4.inl:630-648: Result[j] = A0*B[j][0] + A1*B[j][1] + A2*B[j][2] + A3*B[j][3],
+   left to right. */
+void sso_mat4_mul(const float a[16], const float b[16], float out[16])
+{
+    float r[16];
+    for (int j = 0; j < 4; ++j) {
+        for (int i = 0; i < 4; ++i) {
+            float t0 = M(a, 0, i) * M(b, j, 0);
+            float t1 = M(a, 1, i) * M(b, j, 1);
+            float t2 = M(a, 2, i) * M(b, j, 2);
+            float t3 = M(a, 3, i) * M(b, j, 3);
+            float s = t0 + t1;
+            s = s + t2;
+            s = s + t3;
+            M(r, j, i) = s;
+        }
+    }
+    memcpy(out, r, sizeof r);
+}
+
+static void mat4_identity(float m[16])
+{
+    memset(m, 0, 16 * sizeof(float));
+    M(m, 0, 0) = M(m, 1, 1) = M(m, 2, 2) = M(m, 3, 3) = 1.0f;
+}
+
+static void sincos_mode(float x, int trig_mode, float* s, float* c)
+{
+    if (trig_mode == SSO_TRIG_DETERMINISTIC) {
+        ss_det_sincosf(x, s, c);
+    } else { /* glm::sin / glm::cos -> std::sin(float) -> libm sinf */
+        *s = sinf(x);
+        *c = cosf(x);
+    }
+}
+
+/* GLM/detail/type_quat.inl:208-217 quat(eulerAngle) and GLM/gtc/quaternion.inl:47-72 mat3_cast. */
+static void euler_to_mat4(const float e[3], int trig_mode, float out[16])
+{
+    float cx, cy, cz, sx, sy, sz;
+    sincos_mode(e[0] * 0.5f, trig_mode, &sx, &cx);
+    sincos_mode(e[1] * 0.5f, trig_mode, &sy, &cy);
+    sincos_mode(e[2] * 0.5f, trig_mode, &sz, &cz);
+
+    float qw = cx * cy * cz + sx * sy * sz;
+    float qx = sx * cy * cz - cx * sy * sz;
+    float qy = cx * sy * cz + sx * cy * sz;
+    float qz = cx * cy * sz - sx * sy * cz;
+
+    float qxx = qx * qx, qyy = qy * qy, qzz = qz * qz;
+    float qxz = qx * qz, qxy = qx * qy, qyz = qy * qz;
+    float qwx = qw * qx, qwy = qw * qy, qwz = qw * qz;
+
+    mat4_identity(out);
+    M(out, 0, 0) = 1.0f - 2.0f * (qyy + qzz);
+    M(out, 0, 1) = 2.0f * (qxy + qwz);
+    M(out, 0, 2) = 2.0f * (qxz - qwy);
+    M(out, 1, 0) = 2.0f * (qxy - qwz);
+    M(out, 1, 1) = 1.0f - 2.0f * (qxx + qzz);
+    M(out, 1, 2) = 2.0f * (qyz + qwx);
+    M(out, 2, 0) = 2.0f * (qxz + qwy);
+    M(out, 2, 1) = 2.0f * (qyz - qwx);
+    M(out, 2, 2) = 1.0f - 2.0f * (qxx + qyy);
+}
+
+/* GLM/ext/matrix_transform.inl:10-15 with m = identity:
+   Result[3] = m[0]*v[0] + m[1]*v[1] + m[2]*v[2] + m[3]. */
+static void mat4_translate_identity(const float v[3], float out[16])
+{
+    float m[16];
+    mat4_identity(m);
+    mat4_identity(out);
+    for (int r = 0; r < 4; ++r) {
+        float s = M(m, 0, r) * v[0] + M(m, 1, r) * v[1];
+        s = s + M(m, 2, r) * v[2];
+        s = s + M(m, 3, r);
+        M(out, 3, r) = s;
+    }
+}
+
+/* GLM/ext/matrix_transform.inl:78-86 with m = identity. */
+static void mat4_scale_identity(const float v[3], float out[16])
+{
+    float m[16];
+    mat4_identity(m);
+    for (int r = 0; r < 4; ++r) {
+        M(out, 0, r) = M(m, 0, r) * v[0];
+        M(out, 1, r) = M(m, 1, r) * v[1];
+        M(out, 2, r) = M(m, 2, r) * v[2];
+        M(out, 3, r) = M(m, 3, r);
+    }
+}
+
+/* VC/Core/Components.h:22-29: translate(I,T) * toMat4(quat(R)) * scale(I,S), left-associated. */
+void sso_trs_to_mat4(const float trs[9], int trig_mode, float out[16])
+{
+    float t[16], r[16], s[16], tr[16];
+    mat4_translate_identity(trs + 0, t);
+    euler_to_mat4(trs + 3, trig_mode, r);
+    mat4_scale_identity(trs + 6, s);
+    sso_mat4_mul(t, r, tr);
+    sso_mat4_mul(tr, s, out);
+}
+
+/* VC/Scene/SceneRenderer.cpp:1151-1153: MRow[r] = (m[0][r], m[1][r], m[2][r], m[3][r]). */
+void sso_pack_rows(const float m[16], float rows[12])
+{
+    for (int r = 0; r < 3; ++r)
+        for (int c = 0; c < 4; ++c) rows[r * 4 + c] = M(m, c, r);
+}
+
+/* N1: world[i] = world[parent[i]] * local[i]; roots: world = local. Nodes are level-ordered so a
+   single forward sweep sees every parent first. */
+void sso_node_worlds(const sso_scene* sc, float* node_world16)
+{
+    for (uint32_t i = 0; i < sc->n_nodes; ++i) {
+        float local[16];
+        sso_trs_to_mat4(sc->trs + (size_t)i * 9, (int)sc->trig_mode, local);
+        int32_t p = sc->parent ? sc->parent[i] : -1;
+        if (p < 0)
+            memcpy(node_world16 + (size_t)i * 16, local, sizeof local);
+        else
+            sso_mat4_mul(node_world16 + (size_t)p * 16, local, node_world16 + (size_t)i * 16);
+    }
+}
+
+static void instance_rows_range(const sso_scene* sc, const float* node_world16, float* rows12,
+                                uint32_t lo, uint32_t hi)
+{
+    for (uint32_t i = lo; i < hi; ++i) {
+        float* rows = rows12 + (size_t)i * 12;
+        uint32_t slot = sc->slot[i];
+        if (slot == SSO_SLOT_NULL) { /* VC/Scene/SceneRenderer.cpp:1128-1136: dropped */
+            memset(rows, 0, 12 * sizeof(float));
+            continue;
+        }
+        uint32_t n = sc->node ? sc->node[i] : sc->node_base + i;
+        float w[16];
+        /* :1150 submeshTransform = transform * submeshData[submeshIndex].LocalTransform */
+        sso_mat4_mul(node_world16 + (size_t)n * 16, sc->slots[slot].local, w);
+        sso_pack_rows(w, rows);
+    }
+}
+
+void sso_instance_rows(const sso_scene* sc, const float* node_world16, float* rows12)
+{
+    instance_rows_range(sc, node_world16, rows12, 0, sc->n_instances);
+}
+
+/* N3: Gribb-Hartmann planes of a zero-to-one-depth clip matrix (GLM_FORCE_DEPTH_ZERO_TO_ONE,
+   /root/reference/VulkanCore/premake5.lua:47).  Row r of VP = (m[0][r], m[1][r], m[2][r], m[3][r]).
+   A point is inside when  -w <= x <= w, -w <= y <= w, 0 <= z <= w
+   (the clip volume the vertex stages feed, VulkanCore/assets/shaders/CorePBR.vert:21-29). */
+void sso_planes_from_view_proj(const float vp[16], float planes[6][4])
+{
+    for (int c = 0; c < 4; ++c) {
+        float r0 = M(vp, c, 0), r1 = M(vp, c, 1), r2 = M(vp, c, 2), r3 = M(vp, c, 3);
+        planes[0][c] = r3 + r0; /* left   */
+        planes[1][c] = r3 - r0; /* right  */
+        planes[2][c] = r3 + r1; /* bottom */
+        planes[3][c] = r3 - r1; /* top    */
+        planes[4][c] = r2;      /* near (z >= 0) */
+        planes[5][c] = r3 - r2; /* far  (z <= w) */
+    }
+}
+
+/* N2 + N4 for one instance; rows = TransformData rows (affine world matrix). */
+static uint8_t cull_one(const float rows[12], const float box[6], float planes[][6][4],
+                        const uint32_t* view_flags, uint32_t n_views)
+{
+    float cl[3], el[3];
+    for (int k = 0; k < 3; ++k) {
+        cl[k] = (box[k] + box[3 + k]) * 0.5f;
+        el[k] = (box[3 + k] - box[k]) * 0.5f;
+    }
+    float cw[3], ew[3];
+    for (int r = 0; r < 3; ++r) {
+        const float* R = rows + r * 4; /* R[c] = m[c][r] */
+        /* centre: GLM mat4*vec4 association (GLM/detail/type_mat4x4.inl:561-572) with w = 1 */
+        float a0 = R[0] * cl[0] + R[1] * cl[1];
+        float a1 = R[2] * cl[2] + R[3];
+        cw[r] = a0 + a1;
+        float e0 = fabsf(R[0]) * el[0] + fabsf(R[1]) * el[1];
+        ew[r] = e0 + fabsf(R[2]) * el[2];
+    }
+    uint8_t mask = 0;
+    for (uint32_t v = 0; v < n_views; ++v) {
+        int inside = 1;
+        for (int p = 0; p < 6; ++p) {
+            if (p == 4 && (view_flags[v] & SSO_VIEW_SKIP_NEAR)) continue;
+            const float* pl = planes[v][p];
+            float s = pl[0] * cw[0] + pl[1] * cw[1];
+            s = s + pl[2] * cw[2];
+            s = s + pl[3];
+            float r = fabsf(pl[0]) * ew[0] + fabsf(pl[1]) * ew[1];
+            r = r + fabsf(pl[2]) * ew[2];
+            if (!(s + r >= 0.0f)) inside = 0;
+        }
+        if (inside) mask |= (uint8_t)(1u << v);
+    }
+    return mask;
+}
+
+static void cull_range(const sso_scene* sc, const float* rows12, const sso_view* views,
+                       uint32_t n_views, uint8_t* masks, uint32_t lo, uint32_t hi)
+{
+    float planes[8][6][4];
+    uint32_t flags[8];
+    for (uint32_t v = 0; v < n_views; ++v) {
+        sso_planes_from_view_proj(views[v].view_proj, planes[v]);
+        flags[v] = views[v].flags;
+    }
+    for (uint32_t i = lo; i < hi; ++i) {
+        uint32_t slot = sc->slot[i];
+        if (slot == SSO_SLOT_NULL) {
+            masks[i] = 0;
+            continue;
+        }
+        float box[6];
+        if (sc->inst_aabb) {
+            memcpy(box, sc->inst_aabb + (size_t)i * 6, sizeof box);
+        } else {
+            memcpy(box, sc->slots[slot].aabb_min, 3 * sizeof(float));
+            memcpy(box + 3, sc->slots[slot].aabb_max, 3 * sizeof(float));
+        }
+        masks[i] = cull_one(rows12 + (size_t)i * 12, box, planes, flags, n_views);
+    }
+}
+
+void sso_cull(const sso_scene* sc, const float* rows12, const sso_view* views, uint32_t n_views,
+              uint8_t* masks)
+{
+    cull_range(sc, rows12, views, n_views, masks, 0, sc->n_instances);
+}
+
+/* N5: [tess][meshRank][submeshIndex][materialRank], right-aligned; isomorphic to
+   MeshKey::operator< (VC/Scene/SceneRenderer.h:64-85), tessellated list after the static one
+   (VC/Scene/SceneRenderer.cpp:1368-1382). */
+static void keys_range(const sso_scene* sc, uint64_t* keys, uint32_t lo, uint32_t hi)
+{
+    const uint32_t mb = sc->material_bits, sb = sc->submesh_bits, hb = sc->mesh_bits;
+    for (uint32_t i = lo; i < hi; ++i) {
+        uint32_t slot = sc->slot[i];
+        if (slot == SSO_SLOT_NULL) {
+            keys[i] = ~0ull;
+            continue;
+        }
+        uint32_t mw = sc->matword[i];
+        uint64_t tess = (mw & SSO_TESS_BIT) ? 1u : 0u;
+        uint64_t mat = mw & ~SSO_TESS_BIT;
+        uint64_t k = mat;
+        k |= (uint64_t)sc->slots[slot].submesh_index << mb;
+        k |= (uint64_t)sc->slots[slot].mesh_rank << (mb + sb);
+        k |= tess << (mb + sb + hb);
+        keys[i] = k;
+    }
+}
+
+void sso_keys(const sso_scene* sc, uint64_t* keys) { keys_range(sc, keys, 0, sc->n_instances); }
+
+typedef struct {
+    uint64_t key;
+    uint32_t idx;
+} key_idx;
+
+static int cmp_key_idx(const void* a, const void* b)
+{
+    const key_idx* x = (const key_idx*)a;
+    const key_idx* y = (const key_idx*)b;
+    if (x->key != y->key) return x->key < y->key ? -1 : 1;
+    if (x->idx != y->idx) return x->idx < y->idx ? -1 : 1;
+    return 0;
+}
+
+/* N6 for one view: what iterating std::map<MeshKey, MeshTransform> yields
+   (VC/Scene/SceneRenderer.cpp:1336-1337,1368-1369), restricted to the visible instances. */
+static void view_list_one(const sso_scene* sc, const float* rows12, const uint8_t* masks,
+                          const uint64_t* keys, uint32_t v, uint32_t* n_visible, uint32_t* n_draws,
+                          uint32_t* out_idx, uint64_t* out_keys, float* out_rows12,
+                          sso_draw_cmd* out_draws, uint64_t* out_draw_keys)
+{
+    uint32_t n = sc->n_instances, m = 0;
+    key_idx* list = (key_idx*)malloc((size_t)(n ? n : 1) * sizeof(key_idx));
+    for (uint32_t i = 0; i < n; ++i) {
+        if (masks[i] & (1u << v)) {
+            list[m].key = keys[i];
+            list[m].idx = i;
+            ++m;
+        }
+    }
+    qsort(list, m, sizeof(key_idx), cmp_key_idx); /* (key, idx) is a total order: stable by construction */
+    uint32_t d = 0;
+    for (uint32_t j = 0; j < m; ++j) {
+        out_idx[j] = list[j].idx;
+        out_keys[j] = list[j].key;
+        if (out_rows12) memcpy(out_rows12 + (size_t)j * 12, rows12 + (size_t)list[j].idx * 12, 48);
+        if (j == 0 || list[j].key != list[j - 1].key) {
+            const sso_submesh* sm = &sc->slots[sc->slot[list[j].idx]];
+            /* VC/../Platform/Vulkan/VulkanRenderer.cpp:628
+               vkCmdDrawIndexed(IndexCount, instanceCount, BaseIndex, BaseVertex, firstInstance) */
+            out_draws[d].index_count = sm->index_count;
+            out_draws[d].instance_count = 0;
+            out_draws[d].first_index = sm->first_index;
+            out_draws[d].vertex_offset = sm->vertex_offset;
+            out_draws[d].first_instance = j;
+            out_draw_keys[d] = list[j].key;
+            ++d;
+        }
+        out_draws[d - 1].instance_count++;
+    }
+    *n_visible = m;
+    *n_draws = d;
+    free(list);
+}
+
+int sso_view_lists(const sso_scene* sc, const float* rows12, const uint8_t* masks,
+                   const uint64_t* keys, uint32_t n_views, uint32_t* n_visible, uint32_t* n_draws,
+                   uint32_t* out_idx, uint64_t* out_keys, float* out_rows12,
+                   sso_draw_cmd* out_draws, uint64_t* out_draw_keys)
+{
+    size_t n = sc->n_instances;
+    for (uint32_t v = 0; v < n_views; ++v)
+        view_list_one(sc, rows12, masks, keys, v, &n_visible[v], &n_draws[v], out_idx + v * n,
+                      out_keys + v * n, out_rows12 ? out_rows12 + v * n * 12 : NULL,
+                      out_draws + v * n, out_draw_keys + v * n);
+    return 0;
+}
+
+/* ---- threaded frame (CPU baseline) ---------------------------------------------------------- */
+
+typedef struct {
+    const sso_scene* sc;
+    const sso_view* views;
+    uint32_t n_views;
+    const float* node_world;
+    float* rows12;
+    uint8_t* masks;
+    uint64_t* keys;
+    uint32_t lo, hi;
+} range_job;
+
+static void* range_worker(void* p)
+{
+    range_job* j = (range_job*)p;
+    instance_rows_range(j->sc, j->node_world, j->rows12, j->lo, j->hi);
+    cull_range(j->sc, j->rows12, j->views, j->n_views, j->masks, j->lo, j->hi);
+    keys_range(j->sc, j->keys, j->lo, j->hi);
+    return NULL;
+}
+
+typedef struct {
+    const sso_scene* sc;
+    const float* rows12;
+    const uint8_t* masks;
+    const uint64_t* keys;
+    uint32_t v;
+    uint32_t *n_visible, *n_draws, *out_idx;
+    uint64_t* out_keys;
+    float* out_rows12;
+    sso_draw_cmd* out_draws;
+    uint64_t* out_draw_keys;
+} view_job;
+
+static void* view_worker(void* p)
+{
+    view_job* j = (view_job*)p;
+    view_list_one(j->sc, j->rows12, j->masks, j->keys, j->v, j->n_visible, j->n_draws, j->out_idx,
+                  j->out_keys, j->out_rows12, j->out_draws, j->out_draw_keys);
+    return NULL;
+}
+
+static double now_s(void)
+{
+    struct timespec ts;
+    clock_gettime(CLOCK_MONOTONIC, &ts);
+    return (double)ts.tv_sec + 1e-9 * (double)ts.tv_nsec;
+}
+
+double sso_frame(const sso_scene* sc, const sso_view* views, uint32_t n_views, int threads,
+                 float* rows12, uint8_t* masks, uint64_t* keys, uint32_t* n_visible,
+                 uint32_t* n_draws, uint32_t* out_idx, uint64_t* out_keys, float* out_rows12,
+                 sso_draw_cmd* out_draws, uint64_t* out_draw_keys)
+{
+    if (threads < 1) threads = 1;
+    if (threads > 256) threads = 256;
+    float* node_world = (float*)malloc((size_t)(sc->n_nodes ? sc->n_nodes : 1) * 16 * sizeof(float));
+    double t0 = now_s();
+    /* the parent chain is a dependent sweep; interior nodes are few (levels above the leaves), so it
+       stays on one thread like the reference's main-thread loop (VC/Scene/Scene.cpp:138-146) */
+    sso_node_worlds(sc, node_world);
+    size_t n = sc->n_instances;
+    if (threads == 1) {
+        range_job j = {sc, views, n_views, node_world, rows12, masks, keys, 0, (uint32_t)n};
+        range_worker(&j);
+        sso_view_lists(sc, rows12, masks, keys, n_views, n_visible, n_draws, out_idx, out_keys,
+                       out_rows12, out_draws, out_draw_keys);
+    } else {
+        pthread_t th[256];
+        range_job jobs[256];
+        for (int t = 0; t < threads; ++t) {
+            jobs[t] = (range_job){sc, views, n_views, node_world, rows12, masks, keys,
+                                  (uint32_t)(n * (size_t)t / (size_t)threads),
+                                  (uint32_t)(n * (size_t)(t + 1) / (size_t)threads)};
+            pthread_create(&th[t], NULL, range_worker, &jobs[t]);
+        }
+        for (int t = 0; t < threads; ++t) pthread_join(th[t], NULL);
+        view_job vj[8];
+        for (uint32_t v = 0; v < n_views; ++v) {
+            vj[v] = (view_job){sc, rows12, masks, keys, v, &n_visible[v], &n_draws[v],
+                               out_idx + v * n, out_keys + v * n,
+                               out_rows12 ? out_rows12 + v * n * 12 : NULL, out_draws + v * n,
+                               out_draw_keys + v * n};
+            pthread_create(&th[v], NULL, view_worker, &vj[v]);
+        }
+        for (uint32_t v = 0; v < n_views; ++v) pthread_join(th[v], NULL);
+    }
+    double t1 = now_s();
+    free(node_world);
+    return t1 - t0;
+}
+
+/* ---- view matrices ---------------------------------------------------------------------------- */
+
+/* GLM/detail/func_matrix.inl:347-403 */
+void sso_mat4_inverse(const float m[16], float out[16])
+{
+    float Coef00 = M(m, 2, 2) * M(m, 3, 3) - M(m, 3, 2) * M(m, 2, 3);
+    float Coef02 = M(m, 1, 2) * M(m, 3, 3) - M(m, 3, 2) * M(m, 1, 3);
+    float Coef03 = M(m, 1, 2) * M(m, 2, 3) - M(m, 2, 2) * M(m, 1, 3);
+    float Coef04 = M(m, 2, 1) * M(m, 3, 3) - M(m, 3, 1) * M(m, 2, 3);
+    float Coef06 = M(m, 1, 1) * M(m, 3, 3) - M(m, 3, 1) * M(m, 1, 3);
+    float Coef07 = M(m, 1, 1) * M(m, 2, 3) - M(m, 2, 1) * M(m, 1, 3);
+    float Coef08 = M(m, 2, 1) * M(m, 3, 2) - M(m, 3, 1) * M(m, 2, 2);
+    float Coef10 = M(m, 1, 1) * M(m, 3, 2) - M(m, 3, 1) * M(m, 1, 2);
+    float Coef11 = M(m, 1, 1) * M(m, 2, 2) - M(m, 2, 1) * M(m, 1, 2);
+    float Coef12 = M(m, 2, 0) * M(m, 3, 3) - M(m, 3, 0) * M(m, 2, 3);
+    float Coef14 = M(m, 1, 0) * M(m, 3, 3) - M(m, 3, 0) * M(m, 1, 3);
+    float Coef15 = M(m, 1, 0) * M(m, 2, 3) - M(m, 2, 0) * M(m, 1, 3);
+    float Coef16 = M(m, 2, 0) * M(m, 3, 2) - M(m, 3, 0) * M(m, 2, 2);
+    float Coef18 = M(m, 1, 0) * M(m, 3, 2) - M(m, 3, 0) * M(m, 1, 2);
+    float Coef19 = M(m, 1, 0) * M(m, 2, 2) - M(m, 2, 0) * M(m, 1, 2);
+    float Coef20 = M(m, 2, 0) * M(m, 3, 1) - M(m, 3, 0) * M(m, 2, 1);
+    float Coef22 = M(m, 1, 0) * M(m, 3, 1) - M(m, 3, 0) * M(m, 1, 1);
+    float Coef23 = M(m, 1, 0) * M(m, 2, 1) - M(m, 2, 0) * M(m, 1, 1);
+
+    float Fac0[4] = {Coef00, Coef00, Coef02, Coef03};
+    float Fac1[4] = {Coef04, Coef04, Coef06, Coef07};
+    float Fac2[4] = {Coef08, Coef08, Coef10, Coef11};
+    float Fac3[4] = {Coef12, Coef12, Coef14, Coef15};
+    float Fac4[4] = {Coef16, Coef16, Coef18, Coef19};
+    float Fac5[4] = {Coef20, Coef20, Coef22, Coef23};
+    float Vec0[4] = {M(m, 1, 0), M(m, 0, 0), M(m, 0, 0), M(m, 0, 0)};
+    float Vec1[4] = {M(m, 1, 1), M(m, 0, 1), M(m, 0, 1), M(m, 0, 1)};
+    float Vec2[4] = {M(m, 1, 2), M(m, 0, 2), M(m, 0, 2), M(m, 0, 2)};
+    float Vec3[4] = {M(m, 1, 3), M(m, 0, 3), M(m, 0, 3), M(m, 0, 3)};
+    static const float SignA[4] = {+1, -1, +1, -1};
+    static const float SignB[4] = {-1, +1, -1, +1};
+    float inv[16];
+    for (int k = 0; k < 4; ++k) {
+        float i0 = Vec1[k] * Fac0[k] - Vec2[k] * Fac1[k];
+        i0 = i0 + Vec3[k] * Fac2[k];
+        float i1 = Vec0[k] * Fac0[k] - Vec2[k] * Fac3[k];
+        i1 = i1 + Vec3[k] * Fac4[k];
+        float i2 = Vec0[k] * Fac1[k] - Vec1[k] * Fac3[k];
+        i2 = i2 + Vec3[k] * Fac5[k];
+        float i3 = Vec0[k] * Fac2[k] - Vec1[k] * Fac4[k];
+        i3 = i3 + Vec2[k] * Fac5[k];
+        M(inv, 0, k) = i0 * SignA[k];
+        M(inv, 1, k) = i1 * SignB[k];
+        M(inv, 2, k) = i2 * SignA[k];
+        M(inv, 3, k) = i3 * SignB[k];
+    }
+    float d0 = M(m, 0, 0) * M(inv, 0, 0), d1 = M(m, 0, 1) * M(inv, 1, 0);
+    float d2 = M(m, 0, 2) * M(inv, 2, 0), d3 = M(m, 0, 3) * M(inv, 3, 0);
+    float det = (d0 + d1) + (d2 + d3);
+    float ood = 1.0f / det;
+    for (int k = 0; k < 16; ++k) out[k] = inv[k] * ood;
+}
+
+/* GLM mat4 * vec4 (GLM/detail/type_mat4x4.inl:561-572) */
+static void mat4_mul_vec4(const float m[16], const float v[4], float out[4])
+{
+    for (int r = 0; r < 4; ++r) {
+        float a0 = M(m, 0, r) * v[0] + M(m, 1, r) * v[1];
+        float a1 = M(m, 2, r) * v[2] + M(m, 3, r) * v[3];
+        out[r] = a0 + a1;
+    }
+}
+
+static float dot3(const float a[3], const float b[3])
+{ /* GLM/detail/func_geometric.inl:48-55 */
+    float t0 = a[0] * b[0], t1 = a[1] * b[1], t2 = a[2] * b[2];
+    return t0 + t1 + t2;
+}
+
+static void cross3(const float x[3], const float y[3], float out[3])
+{ /* GLM/detail/func_geometric.inl:68-79 */
+    out[0] = x[1] * y[2] - y[1] * x[2];
+    out[1] = x[2] * y[0] - y[2] * x[0];
+    out[2] = x[0] * y[1] - y[0] * x[1];
+}
+
+static void normalize3(const float v[3], float out[3])
+{ /* v * inversesqrt(dot(v,v)); inversesqrt = 1/sqrt (GLM/detail/func_exponential.inl:134-139) */
+    float inv = 1.0f / sqrtf(dot3(v, v));
+    out[0] = v[0] * inv;
+    out[1] = v[1] * inv;
+    out[2] = v[2] * inv;
+}
+
+/* VC/Renderer/EditorCamera.cpp:15-33 + EditorCamera.h:45.  The orbit parameters
+   (focal point, distance) only produce m_Position; here the position is given directly. */
+void sso_camera_view_proj(float fov_y, float aspect, float z_near, float z_far,
+                          const float position[3], float pitch, float yaw, float view[16],
+                          float proj[16], float view_proj[16])
+{
+    /* GLM/ext/matrix_clip_space.inl:233-246 perspectiveRH_ZO */
+    float tanHalfFovy = tanf(fov_y / 2.0f);
+    memset(proj, 0, 16 * sizeof(float));
+    M(proj, 0, 0) = 1.0f / (aspect * tanHalfFovy);
+    M(proj, 1, 1) = 1.0f / tanHalfFovy;
+    M(proj, 2, 2) = z_far / (z_near - z_far);
+    M(proj, 2, 3) = -1.0f;
+    M(proj, 3, 2) = -(z_far * z_near) / (z_far - z_near);
+
+    /* GetOrientation: quat(vec3(-pitch, -yaw, 0)) (EditorCamera.cpp:172-175) */
+    float e[3] = {-pitch, -yaw, 0.0f};
+    float rot[16], tr[16], inv_view[16];
+    euler_to_mat4(e, SSO_TRIG_LIBM, rot);
+    mat4_translate_identity(position, tr);
+    sso_mat4_mul(tr, rot, inv_view);
+    sso_mat4_inverse(inv_view, view);
+    sso_mat4_mul(proj, view, view_proj);
+}
+
+/* VC/Scene/SceneRenderer.cpp:579-687 (CascadeOffset == 0 branch). */
+void sso_cascade_matrices(const float view_proj[16], float z_near, float z_far, float lambda,
+                          float near_offset, float far_offset, const float light_dir[3],
+                          float splits[4], float light_matrices[64])
+{
+    float cascadeSplits[4];
+    float clipRange = z_far - z_near;
+    float minZ = z_near;
+    float maxZ = z_near + clipRange;
+    float range = maxZ - minZ;
+    float ratio = maxZ / minZ;
+    for (uint32_t i = 0; i < 4; ++i) {
+        float p = (float)(i + 1) / (float)4;
+        float lg = minZ * powf(ratio, p);
+        float uniform = minZ + range * p;
+        float d = lambda * (lg - uniform) + uniform;
+        cascadeSplits[i] = (d - z_near) / clipRange;
+    }
+
+    float lastSplitDist = 0.0f;
+    for (uint32_t i = 0; i < 4; ++i) {
+        float splitDist = cascadeSplits[i];
+        float corners[8][3] = {{-1.0f, 1.0f, 0.0f}, {1.0f, 1.0f, 0.0f},  {1.0f, -1.0f, 0.0f},
+                               {-1.0f, -1.0f, 0.0f}, {-1.0f, 1.0f, 1.0f}, {1.0f, 1.0f, 1.0f},
+                               {1.0f, -1.0f, 1.0f},  {-1.0f, -1.0f, 1.0f}};
+        float inv[16];
+        sso_mat4_inverse(view_proj, inv);
+        for (int j = 0; j < 8; ++j) {
+            float v4[4] = {corners[j][0], corners[j][1], corners[j][2], 1.0f}, o[4];
+            mat4_mul_vec4(inv, v4, o);
+            corners[j][0] = o[0] / o[3];
+            corners[j][1] = o[1] / o[3];
+            corners[j][2] = o[2] / o[3];
+        }
+        for (int j = 0; j < 4; ++j) {
+            for (int k = 0; k < 3; ++k) {
+                float dist = corners[j + 4][k] - corners[j][k];
+                corners[j + 4][k] = corners[j][k] + (dist * splitDist);
+                corners[j][k] = corners[j][k] + (dist * lastSplitDist);
+            }
+        }
+        float center[3] = {0.0f, 0.0f, 0.0f};
+        for (int j = 0; j < 8; ++j)
+            for (int k = 0; k < 3; ++k) center[k] += corners[j][k];
+        for (int k = 0; k < 3; ++k) center[k] /= 8.0f;
+
+        float radius = 0.0f;
+        for (int j = 0; j < 8; ++j) {
+            float dlt[3] = {corners[j][0] - center[0], corners[j][1] - center[1],
+                            corners[j][2] - center[2]};
+            float distance = sqrtf(dot3(dlt, dlt));
+            radius = radius < distance ? distance : radius; /* glm::max(radius, distance) */
+        }
+        radius = ceilf(radius * 16.0f) / 16.0f;
+
+        float maxE = radius, minE = -radius;
+        float ld[3];
+        normalize3(light_dir, ld);
+        float eye[3];
+        for (int k = 0; k < 3; ++k) eye[k] = center[k] - ld[k] * -minE;
+
+        /* GLM/ext/matrix_transform.inl:99-119 lookAtRH(eye, center, up = (0,1,0)) */
+        float up[3] = {0.0f, 1.0f, 0.0f};
+        float fdir[3] = {center[0] - eye[0], center[1] - eye[1], center[2] - eye[2]};
+        float f[3], s[3], u[3], sc[3];
+        normalize3(fdir, f);
+        cross3(f, up, sc);
+        normalize3(sc, s);
+        cross3(s, f, u);
+        float lv[16];
+        mat4_identity(lv);
+        M(lv, 0, 0) = s[0]; M(lv, 1, 0) = s[1]; M(lv, 2, 0) = s[2];
+        M(lv, 0, 1) = u[0]; M(lv, 1, 1) = u[1]; M(lv, 2, 1) = u[2];
+        M(lv, 0, 2) = -f[0]; M(lv, 1, 2) = -f[1]; M(lv, 2, 2) = -f[2];
+        M(lv, 3, 0) = -dot3(s, eye);
+        M(lv, 3, 1) = -dot3(u, eye);
+        M(lv, 3, 2) = dot3(f, eye);
+
+        /* GLM/ext/matrix_clip_space.inl:42-52 orthoRH_ZO */
+        float left = minE, right = maxE, bottom = minE, top = maxE;
+        float zn = near_offset, zf = maxE - minE + far_offset;
+        float lo[16];
+        mat4_identity(lo);
+        M(lo, 0, 0) = 2.0f / (right - left);
+        M(lo, 1, 1) = 2.0f / (top - bottom);
+        M(lo, 2, 2) = -1.0f / (zf - zn);
+        M(lo, 3, 0) = -(right + left) / (right - left);
+        M(lo, 3, 1) = -(top + bottom) / (top - bottom);
+        M(lo, 3, 2) = -zn / (zf - zn);
+
+        splits[i] = (z_near + splitDist * clipRange) * -1.0f;
+        sso_mat4_mul(lo, lv, light_matrices + i * 16);
+        lastSplitDist = cascadeSplits[i];
+    }
+}
