@@ -1,0 +1,38 @@
+# libscenesubmit — build everything in-tree (the .so files travel to the GPU box with the snapshot).
+#   make            product library  vulkanengine_b200/libscenesubmit.so   (nvcc, sm_100a only)
+#   make oracle     CPU oracle + reference-arithmetic build (test infrastructure)
+#   make host       C++ host mirror demo/test binary
+NVCC     ?= /usr/local/cuda/bin/nvcc
+ARCH     := -gencode arch=compute_100a,code=sm_100a
+# -fmad=false: no FMA contraction anywhere, the float op order is the reference's
+NVFLAGS  := $(ARCH) -O3 -std=c++17 -lineinfo -fmad=false \
+            -Xcompiler -fPIC,-ffp-contract=off,-fno-fast-math,-fvisibility=hidden,-Wall
+CSRC     := vulkanengine_b200/csrc
+OBJDIR   := build
+LIB      := vulkanengine_b200/libscenesubmit.so
+CU       := $(CSRC)/transform_cull.cu $(CSRC)/radix_sort.cu $(CSRC)/emit.cu $(CSRC)/context.cu
+CPP      := $(CSRC)/host_views.cpp
+OBJS     := $(patsubst $(CSRC)/%.cu,$(OBJDIR)/%.o,$(CU)) $(patsubst $(CSRC)/%.cpp,$(OBJDIR)/%.o,$(CPP))
+HDRS     := $(wildcard $(CSRC)/*.h $(CSRC)/*.cuh include/*.h)
+
+all: $(LIB)
+
+$(OBJDIR)/%.o: $(CSRC)/%.cu $(HDRS)
+	@mkdir -p $(OBJDIR)
+	$(NVCC) $(NVFLAGS) -Xptxas -v -c $< -o $@ 2> $(OBJDIR)/$*.ptxas.log || (cat $(OBJDIR)/$*.ptxas.log; false)
+
+$(OBJDIR)/%.o: $(CSRC)/%.cpp $(HDRS)
+	@mkdir -p $(OBJDIR)
+	$(NVCC) $(NVFLAGS) -x cu -c $< -o $@
+
+$(LIB): $(OBJS)
+	$(NVCC) $(ARCH) -shared -o $@ $(OBJS)
+
+oracle:
+	$(MAKE) -C oracle all
+
+clean:
+	rm -rf $(OBJDIR) $(LIB)
+	$(MAKE) -C oracle clean
+
+.PHONY: all oracle clean

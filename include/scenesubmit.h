@@ -164,8 +164,10 @@ SS_API uint32_t ss_version(void);
 /* Key layout [tess:1][meshRank:mesh_bits][submeshIndex:submesh_bits][materialRank:material_bits],
    packed right-aligned in a uint64; order-isomorphic to MeshKey::operator<
    (VC/Scene/SceneRenderer.h:64-85: Mesh, then Submesh, then Material) with the tessellated list
-   after the static one (VC/Scene/SceneRenderer.cpp:1368-1382). Sum of widths <= 63.
-   Default 23/16/24. Narrow widths let the radix sort skip constant digits. */
+   after the static one (VC/Scene/SceneRenderer.cpp:1368-1382).  Sum of widths <= 62: the bit above
+   tess marks dropped instances inside the sort so they collect behind every real key (they are
+   never visible, so that bit never reaches an output).  Default 22/16/24.  Narrow widths let the
+   radix sort skip the constant digits: only ceil((sum+2)/8) passes are even considered. */
 SS_API ss_status ss_set_key_layout(ss_ctx* ctx, uint32_t mesh_bits, uint32_t submesh_bits,
                                    uint32_t material_bits);
 
@@ -197,8 +199,13 @@ SS_API ss_status ss_set_instance_aabbs(ss_ctx* ctx, uint32_t first, uint32_t cou
 
 /* Dirty range of TransformComponent {Translation, Rotation(euler xyz, radians), Scale}, 36 B each,
    exactly the entt pool's memory (VC/Core/Components.h:13-15).  Replaces the GetTransform() call per
-   entity (VC/Scene/Scene.cpp:145).  trs may be pageable or pinned host memory. */
+   entity (VC/Scene/Scene.cpp:145).  Pageable memory is staged before the call returns; PINNED memory
+   is read asynchronously by the copy engine and must stay unchanged until ss_flush_uploads or the
+   ss_frame_sync of the next frame. */
 SS_API ss_status ss_upload_trs(ss_ctx* ctx, uint32_t first, uint32_t count, const float* trs9);
+
+/* Wait until every ss_upload_* issued so far has left host memory. */
+SS_API ss_status ss_flush_uploads(ss_ctx* ctx);
 
 /* Stage-wise parity input: world rows per instance (see SS_FRAME_WORLD_ROWS_GIVEN). */
 SS_API ss_status ss_upload_world_rows(ss_ctx* ctx, uint32_t first, uint32_t count,
@@ -228,7 +235,6 @@ SS_API ss_status ss_download_view(ss_ctx* ctx, uint32_t slot, uint32_t view, flo
                                   uint64_t* draw_keys);
 SS_API ss_status ss_download_world(ss_ctx* ctx, uint32_t first, uint32_t count, float* rows12);
 SS_API ss_status ss_download_masks(ss_ctx* ctx, uint32_t first, uint32_t count, uint8_t* masks);
-SS_API ss_status ss_download_keys(ss_ctx* ctx, uint32_t first, uint32_t count, uint64_t* keys);
 
 /* The CUDA stream (cudaStream_t) frames run on, so a consumer can order its own work after them. */
 SS_API void* ss_stream(ss_ctx* ctx);

@@ -1,0 +1,220 @@
+"""GPU parity: libscenesubmit (through the C ABI) against the CPU oracle on the same seeded inputs.
+Bit-exact for masks, keys, instance order and draws; world rows bit-exact in deterministic-trig mode
+(up to the sign of a zero, hence value comparison) and within 1e-6 relative in libm mode."""
+import numpy as np
+import pytest
+
+import oracle_lib as O
+from vulkanengine_b200 import scenesubmit as S
+from vulkanengine_b200 import synth
+
+pytestmark = pytest.mark.gpu
+
+
+def oracle_views(n_views=5, **kw):
+    return synth.make_views(lambda *a: O.camera_view_proj(*a), lambda *a: O.cascade_matrices(*a), n_views, **kw)
+
+
+def run_gpu(sc, views, trig_mode=S.TRIG_DETERMINISTIC, flags=0, world=None, **cfg):
+    ctx = S.SceneSubmit(sc.n_nodes, max(sc.n_instances, 1), len(sc.slots), max_views=len(views), trig_mode=trig_mode, **cfg)
+    ctx.load_scene(sc)
+    if world is not None:
+        ctx.upload_world_rows(world)
+    slot = ctx.frame(views, flags)
+    st = ctx.frame_sync(slot)
+    out = {"stats": st, "world": ctx.download_world(), "masks": ctx.download_masks(),
+           "views": [ctx.download_view(slot, v, st) for v in range(len(views))]}
+    ctx.close()
+    return out
+
+
+def check_against_oracle(sc, views, got, ref, exact_rows=True):
+    live = sc.slot != synth.SLOT_NULL
+    if exact_rows:
+        assert np.array_equal(got["world"], ref["rows"]), "world rows differ"
+    else:
+        scale = np.maximum(np.abs(ref["rows"]).max(axis=1, keepdims=True), 1e-30)
+        assert (np.abs(got["world"] - ref["rows"]) <= 1e-6 * scale)[live].all(), "world rows beyond 1e-6 relative"
+    assert np.array_equal(got["masks"], ref["masks"]), "visibility masks differ"
+    for v in range(len(views)):
+        g, r = got["views"][v], ref["views"][v]
+        assert int(got["stats"].visible[v]) == len(r["idx"]), f"view {v}: visible count"
+        assert np.array_equal(g["idx"], r["idx"]), f"view {v}: draw order (instance ids)"
+        assert np.array_equal(g["keys"], r["keys"]), f"view {v}: sort keys"
+        assert np.array_equal(g["rows"], got["world"][g["idx"]]), f"view {v}: gathered rows"
+        assert int(got["stats"].draws[v]) == len(r["draws"]), f"view {v}: draw count"
+        assert np.array_equal(g["draws"], r["draws"]), f"view {v}: indirect commands"
+        assert np.array_equal(g["draw_keys"], r["draw_keys"]), f"view {v}: draw keys"
+
+
+@pytest.mark.parametrize("n", [1, 31, 256, 257, 4096, 4097, 100_003])
+def test_flat_bit_exact(n):
+    sc = synth.flat_scene(n, n_keys=512)
+    views = oracle_views(5)
+    ref = O.OracleScene(sc, 0).frame(views)
+    got = run_gpu(sc, views)
+    check_against_oracle(sc, views, got, ref)
+
+
+def test_flat_libm_mode_tolerance():
+    sc = synth.flat_scene(50_000, n_keys=512)
+    views = oracle_views(5)
+    ref = O.OracleScene(sc, 1).frame(views)
+    got = run_gpu(sc, views, trig_mode=S.TRIG_LIBM)
+    live = sc.slot != synth.SLOT_NULL
+    scale = np.maximum(np.abs(ref["rows"]).max(axis=1, keepdims=True), 1e-30)
+    assert (np.abs(got["world"] - ref["rows"]) <= 1e-6 * scale)[live].all()
+    # masks may differ only on borderline boxes: well under 0.1 % of instances
+    assert (got["masks"] != ref["masks"]).mean() < 1e-3
+
+
+def test_stagewise_cull_bit_exact_on_oracle_matrices():
+    """SURVEY §7 hard part 1 (i): feed the oracle's libm-trig matrices, everything after must be bit-exact."""
+    sc = synth.flat_scene(30_000, n_keys=300)
+    views = oracle_views(5)
+    osc = O.OracleScene(sc, 1)
+    ref = osc.frame(views)
+    got = run_gpu(sc, views, trig_mode=S.TRIG_LIBM, flags=S.FRAME_WORLD_ROWS_GIVEN, world=ref["rows"])
+    check_against_oracle(sc, views, got, ref)
+
+
+def test_hierarchy_three_levels():
+    sc = synth.hierarchy_scene(n_roots=16, fan1=8, fan2=32, n_keys=200)
+    views = oracle_views(1)
+    ref = O.OracleScene(sc, 0).frame(views)
+    got = run_gpu(sc, views)
+    check_against_oracle(sc, views, got, ref)
+
+
+def test_hierarchy_mixed_parents_in_warp():
+    sc = synth.hierarchy_scene(n_roots=7, fan1=3, fan2=5, n_keys=64)
+    views = oracle_views(5)
+    ref = O.OracleScene(sc, 0).frame(views)
+    got = run_gpu(sc, views)
+    check_against_oracle(sc, views, got, ref)
+
+
+def test_explicit_node_map():
+    sc = synth.with_explicit_nodes(synth.hierarchy_scene(n_roots=8, fan1=4, fan2=16, n_keys=100))
+    views = oracle_views(5)
+    ref = O.OracleScene(sc, 0).frame(views)
+    got = run_gpu(sc, views)
+    check_against_oracle(sc, views, got, ref)
+
+
+def test_submesh_table_boxes():
+    sc = synth.flat_scene(5000, n_keys=128)
+    sc.inst_aabb = None
+    views = oracle_views(5)
+    ref = O.OracleScene(sc, 0).frame(views)
+    got = run_gpu(sc, views)
+    check_against_oracle(sc, views, got, ref)
+
+
+def test_all_dropped_and_single_key():
+    sc = synth.flat_scene(3000, n_keys=1)
+    views = oracle_views(2)
+    ref = O.OracleScene(sc, 0).frame(views)
+    got = run_gpu(sc, views)
+    check_against_oracle(sc, views, got, ref)
+    sc.slot[:] = synth.SLOT_NULL
+    ref = O.OracleScene(sc, 0).frame(views)
+    got = run_gpu(sc, views)
+    assert got["masks"].sum() == 0 and all(int(got["stats"].visible[v]) == 0 for v in range(2))
+    assert all(int(got["stats"].draws[v]) == 0 for v in range(2))
+
+
+def test_every_key_distinct():
+    """Worst case for run bookkeeping: as many draws as instances."""
+    n = 3000
+    sc = synth.flat_scene(n, n_keys=4096)
+    sc.material_bits = 12
+    sc.matword = (np.arange(n, dtype=np.uint32) % 4096).astype(np.uint32)
+    sc.slot = (np.arange(n, dtype=np.uint32) // 4096 % len(sc.slots)).astype(np.uint32)
+    views = oracle_views(5)
+    ref = O.OracleScene(sc, 0).frame(views)
+    got = run_gpu(sc, views)
+    check_against_oracle(sc, views, got, ref)
+
+
+def test_frames_in_flight_slots_and_reuse():
+    sc = synth.flat_scene(20_000, n_keys=256)
+    views = oracle_views(5)
+    ref = O.OracleScene(sc, 0).frame(views)
+    ctx = S.SceneSubmit(sc.n_nodes, sc.n_instances, len(sc.slots), max_views=5)
+    ctx.load_scene(sc)
+    slots = [ctx.frame(views) for _ in range(5)]
+    assert slots == [0, 1, 2, 0, 1]
+    for slot in (2, 0, 1):
+        st = ctx.frame_sync(slot)
+        for v in range(5):
+            assert np.array_equal(ctx.download_view(slot, v, st)["idx"], ref["views"][v]["idx"])
+    # move everything far away: nothing visible in the camera view
+    trs = sc.trs.copy()
+    trs[:, 2] = 5000.0
+    ctx.upload_trs(trs)
+    st = ctx.frame_sync(ctx.frame(views))
+    assert int(st.visible[0]) == 0 and int(st.draws[0]) == 0
+    ctx.close()
+
+
+def test_capacity_overflow_reports_error():
+    sc = synth.flat_scene(20_000, n_keys=256)
+    views = oracle_views(5)
+    ctx = S.SceneSubmit(sc.n_nodes, sc.n_instances, len(sc.slots), max_views=5, max_visible_per_view=100)
+    ctx.load_scene(sc)
+    slot = ctx.frame(views)
+    with pytest.raises(S.SceneSubmitError) as e:
+        ctx.frame_sync(slot)
+    assert e.value.status == S.SS_ERR_CAPACITY
+    ctx.close()
+
+
+def test_invalid_arguments():
+    with pytest.raises(S.SceneSubmitError):
+        S.SceneSubmit(0, 0, 0)
+    sc = synth.flat_scene(100, n_keys=16)
+    ctx = S.SceneSubmit(sc.n_nodes, sc.n_instances, len(sc.slots), max_views=2)
+    with pytest.raises(S.SceneSubmitError):  # frame before streams
+        ctx.frame(oracle_views(2))
+    ctx.load_scene(sc)
+    with pytest.raises(S.SceneSubmitError):  # too many views
+        ctx.frame(oracle_views(5))
+    bad = sc.slots.copy()
+    bad["local"][0][3] = 1.0  # not affine
+    with pytest.raises(S.SceneSubmitError):
+        ctx.set_submesh_table(bad)
+    ctx.close()
+
+
+# ---- the sort on its own ---------------------------------------------------------------------------
+
+@pytest.mark.parametrize("n", [0, 1, 2, 255, 4096, 4097, 70_001, 1 << 20])
+def test_radix_sort_random_64bit(n):
+    rng = np.random.default_rng(n)
+    keys = rng.integers(0, 2**64, size=n, dtype=np.uint64)
+    vals = np.arange(n, dtype=np.uint32)
+    ko, vo = S.sort_pairs_host(keys, vals)
+    order = np.argsort(keys, kind="stable")
+    assert np.array_equal(ko, keys[order]) and np.array_equal(vo, vals[order])
+
+
+def test_radix_sort_stability_and_digit_skip():
+    rng = np.random.default_rng(5)
+    n = 300_000
+    keys = (rng.integers(0, 37, size=n, dtype=np.uint64) << np.uint64(20)) | np.uint64(0xABC)
+    vals = np.arange(n, dtype=np.uint32)
+    ko, vo = S.sort_pairs_host(keys, vals)
+    order = np.argsort(keys, kind="stable")
+    assert np.array_equal(ko, keys[order]) and np.array_equal(vo, vals[order])
+
+
+def test_radix_sort_bit_range():
+    rng = np.random.default_rng(6)
+    n = 50_000
+    keys = rng.integers(0, 2**64, size=n, dtype=np.uint64)
+    vals = np.arange(n, dtype=np.uint32)
+    ko, vo = S.sort_pairs_host(keys, vals, begin_bit=8, end_bit=29)
+    sub = (keys >> np.uint64(8)) & np.uint64((1 << 21) - 1)
+    order = np.argsort(sub, kind="stable")
+    assert np.array_equal(vo, vals[order]) and np.array_equal(ko, keys[order])

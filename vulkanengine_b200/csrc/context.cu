@@ -1,0 +1,740 @@
+// libscenesubmit C ABI: context, device streams, frame orchestration.  See include/scenesubmit.h for the
+// contract and the reference code each entry point replaces.
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <new>
+#include <string>
+#include <vector>
+
+#include "ss_kernels.h"
+
+using namespace ss;
+
+namespace {
+
+thread_local std::string g_create_error;
+
+struct Slot {
+    ViewOut out[SS_MAX_VIEWS];
+    uint32_t* counts_dev = nullptr;   // [max_views][2]
+    cudaEvent_t done = nullptr, start = nullptr;
+    bool pending = false;
+    uint32_t n_views = 0, n_instances = 0;
+    int launches = 0;
+    // pinned host mirror
+    uint32_t* h_counts = nullptr;     // [max_views][2] + overflow + passes_run
+};
+
+}  // namespace
+
+struct ss_ctx {
+    ss_config cfg{};
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    std::string err;
+    std::vector<void*> allocs;
+
+    // static streams
+    float* d_trs = nullptr;
+    int32_t* d_parent = nullptr;
+    float4* d_node_world = nullptr;
+    uint32_t* d_node = nullptr;
+    uint32_t* d_slot = nullptr;
+    uint32_t* d_matword = nullptr;
+    float* d_inst_aabb = nullptr;
+    SlotDev* d_slots = nullptr;
+    // per-frame products
+    float4* d_world = nullptr;
+    uint8_t* d_mask = nullptr;
+    uint64_t *d_keys_a = nullptr, *d_keys_b = nullptr;
+    uint32_t *d_vals_a = nullptr, *d_vals_b = nullptr;
+    void* d_sort_scratch = nullptr;
+    // emit scratch: [lookback | ticket | totals] is zeroed every frame with one memset
+    unsigned char* d_emit_zero = nullptr;
+    size_t emit_zero_bytes = 0;
+    uint32_t* d_lookback = nullptr;
+    uint32_t* d_ticket = nullptr;
+    uint32_t* d_totals = nullptr;
+    uint32_t* d_overflow = nullptr;
+    uint32_t* d_seg_count = nullptr;
+    uint64_t* d_seg_key = nullptr;
+    uint32_t* d_seg_inst = nullptr;
+
+    std::vector<Slot> slots;
+    uint64_t frame_no = 0;
+
+    // host state
+    uint32_t n_nodes = 0, n_instances = 0, n_slots = 0, n_levels = 0;
+    std::vector<uint32_t> level_offsets;
+    bool has_parent = false, has_node_map = false, has_inst_aabb = false, world_uploaded = false;
+    uint32_t node_base = 0;
+    uint32_t mesh_bits = 22, submesh_bits = 16, material_bits = 24;
+    std::vector<ss_submesh> host_table;
+    uint32_t max_draws = 0;
+    uint32_t cap_visible = 0;
+
+    ss_status fail(ss_status st, const char* fmt, ...)
+    {
+        char buf[512];
+        va_list ap;
+        va_start(ap, fmt);
+        vsnprintf(buf, sizeof buf, fmt, ap);
+        va_end(ap);
+        err = buf;
+        return st;
+    }
+};
+
+#define SS_CUDA(ctx, call)                                                                              \
+    do {                                                                                                \
+        cudaError_t e__ = (call);                                                                       \
+        if (e__ != cudaSuccess)                                                                         \
+            return (ctx)->fail(SS_ERR_CUDA, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e__),    \
+                               __FILE__, __LINE__);                                                     \
+    } while (0)
+
+namespace {
+
+template <class T>
+cudaError_t dev_alloc(ss_ctx* c, T** p, size_t count)
+{
+    void* q = nullptr;
+    cudaError_t e = cudaMalloc(&q, std::max<size_t>(count * sizeof(T), 256));
+    if (e == cudaSuccess) {
+        c->allocs.push_back(q);
+        *p = static_cast<T*>(q);
+    }
+    return e;
+}
+
+ss_status upload_table(ss_ctx* c)
+{
+    std::vector<SlotDev> dev(c->n_slots);
+    for (uint32_t i = 0; i < c->n_slots; ++i) {
+        const ss_submesh& s = c->host_table[i];
+        SlotDev& d = dev[i];
+        const float* m = s.local;  // m[col*4 + row]
+        d.r0 = make_float4(m[0], m[4], m[8], m[12]);
+        d.r1 = make_float4(m[1], m[5], m[9], m[13]);
+        d.r2 = make_float4(m[2], m[6], m[10], m[14]);
+        for (int k = 0; k < 3; ++k) {
+            d.mn[k] = s.aabb_min[k];
+            d.mx[k] = s.aabb_max[k];
+        }
+        d.index_count = s.index_count;
+        d.first_index = s.first_index;
+        d.vertex_offset = s.vertex_offset;
+        d.pad = 0;
+        d.key_hi = ((uint64_t)s.mesh_rank << (c->material_bits + c->submesh_bits)) |
+                   ((uint64_t)s.submesh_index << c->material_bits);
+    }
+    if (c->n_slots)
+        SS_CUDA(c, cudaMemcpyAsync(c->d_slots, dev.data(), dev.size() * sizeof(SlotDev), cudaMemcpyHostToDevice,
+                                   c->stream));
+    SS_CUDA(c, cudaStreamSynchronize(c->stream));
+    return SS_OK;
+}
+
+// N3: Gribb-Hartmann planes of a zero-to-one depth clip matrix, L R B T N F; plain adds, same as the oracle.
+void planes_from_view_proj(const float* vp, ViewPlanes& out)
+{
+    float pl[6][4];
+    for (int col = 0; col < 4; ++col) {
+        const float r0 = vp[col * 4 + 0], r1 = vp[col * 4 + 1], r2 = vp[col * 4 + 2], r3 = vp[col * 4 + 3];
+        pl[0][col] = r3 + r0;
+        pl[1][col] = r3 - r0;
+        pl[2][col] = r3 + r1;
+        pl[3][col] = r3 - r1;
+        pl[4][col] = r2;
+        pl[5][col] = r3 - r2;
+    }
+    for (int p = 0; p < 6; ++p) {
+        out.pl[p] = make_float4(pl[p][0], pl[p][1], pl[p][2], pl[p][3]);
+        out.ab[p] = make_float4(fabsf(pl[p][0]), fabsf(pl[p][1]), fabsf(pl[p][2]), 0.f);
+    }
+}
+
+}  // namespace
+
+extern "C" {
+
+SS_API uint32_t ss_version(void) { return (SS_VERSION_MAJOR << 16) | SS_VERSION_MINOR; }
+
+SS_API const char* ss_last_error(const ss_ctx* ctx) { return ctx ? ctx->err.c_str() : g_create_error.c_str(); }
+
+SS_API void ss_destroy(ss_ctx* c)
+{
+    if (!c) return;
+    cudaSetDevice(c->device);
+    if (c->stream) cudaStreamSynchronize(c->stream);
+    for (Slot& s : c->slots) {
+        if (s.done) cudaEventDestroy(s.done);
+        if (s.start) cudaEventDestroy(s.start);
+        if (s.h_counts) cudaFreeHost(s.h_counts);
+    }
+    for (void* p : c->allocs) cudaFree(p);
+    if (c->stream) cudaStreamDestroy(c->stream);
+    delete c;
+}
+
+SS_API ss_status ss_create(const ss_config* cfg, ss_ctx** out)
+{
+    if (!cfg || !out) {
+        g_create_error = "ss_create: null argument";
+        return SS_ERR_INVALID;
+    }
+    *out = nullptr;
+    if (cfg->struct_size != sizeof(ss_config) || cfg->max_views < 1 || cfg->max_views > SS_MAX_VIEWS ||
+        cfg->max_instances == 0 || cfg->max_nodes == 0 || cfg->max_submesh_slots == 0 ||
+        cfg->max_instances >= (1u << 30) || cfg->trig_mode > SS_TRIG_LIBM) {
+        g_create_error = "ss_create: invalid ss_config (struct_size, capacities 1..2^30-1, max_views 1..8, trig_mode)";
+        return SS_ERR_INVALID;
+    }
+    int n_dev = 0;
+    cudaError_t e = cudaGetDeviceCount(&n_dev);
+    if (e != cudaSuccess || n_dev == 0 || cfg->device < 0 || cfg->device >= n_dev) {
+        // No CPU fallback exists: without a CUDA device the library refuses to run.
+        g_create_error = std::string("ss_create: no usable CUDA device (") +
+                         (e != cudaSuccess ? cudaGetErrorString(e) : "bad device ordinal") + ")";
+        return SS_ERR_CUDA;
+    }
+    ss_ctx* c = new (std::nothrow) ss_ctx();
+    if (!c) {
+        g_create_error = "ss_create: out of host memory";
+        return SS_ERR_NOMEM;
+    }
+    c->cfg = *cfg;
+    c->device = cfg->device;
+    const uint32_t fif = cfg->frames_in_flight ? cfg->frames_in_flight : 3;
+    c->max_draws = cfg->max_draws_per_view ? cfg->max_draws_per_view : std::min<uint32_t>(cfg->max_instances, 1u << 20);
+    c->cap_visible = cfg->max_visible_per_view
+                         ? (uint32_t)std::min<uint64_t>(cfg->max_visible_per_view, cfg->max_instances)
+                         : cfg->max_instances;
+    const size_t N = cfg->max_instances, NN = cfg->max_nodes, V = cfg->max_views;
+
+    auto bail = [&](cudaError_t err, const char* what) {
+        g_create_error = std::string("ss_create: ") + what + ": " + cudaGetErrorString(err);
+        ss_destroy(c);
+        return err == cudaErrorMemoryAllocation ? SS_ERR_NOMEM : SS_ERR_CUDA;
+    };
+#define TRY(call)                                  \
+    do {                                           \
+        cudaError_t e2 = (call);                   \
+        if (e2 != cudaSuccess) return bail(e2, #call); \
+    } while (0)
+
+    TRY(cudaSetDevice(c->device));
+    TRY(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+    TRY(dev_alloc(c, &c->d_trs, NN * 9));
+    TRY(dev_alloc(c, &c->d_parent, NN));
+    TRY(dev_alloc(c, &c->d_node_world, NN * 3));
+    TRY(dev_alloc(c, &c->d_node, N));
+    TRY(dev_alloc(c, &c->d_slot, N));
+    TRY(dev_alloc(c, &c->d_matword, N));
+    TRY(dev_alloc(c, &c->d_inst_aabb, N * 6));
+    TRY(dev_alloc(c, &c->d_slots, (size_t)cfg->max_submesh_slots));
+    TRY(dev_alloc(c, &c->d_world, N * 3));
+    TRY(dev_alloc(c, &c->d_mask, N));
+    TRY(dev_alloc(c, &c->d_keys_a, N));
+    TRY(dev_alloc(c, &c->d_keys_b, N));
+    TRY(dev_alloc(c, &c->d_vals_a, N));
+    TRY(dev_alloc(c, &c->d_vals_b, N));
+    TRY(dev_alloc(c, reinterpret_cast<unsigned char**>(&c->d_sort_scratch), sort_scratch_bytes(N)));
+
+    const size_t lb_bytes = (emit_lookback_bytes(N) + 255) & ~size_t(255);
+    c->emit_zero_bytes = lb_bytes + 256;
+    TRY(dev_alloc(c, &c->d_emit_zero, c->emit_zero_bytes));
+    c->d_lookback = reinterpret_cast<uint32_t*>(c->d_emit_zero);
+    c->d_ticket = reinterpret_cast<uint32_t*>(c->d_emit_zero + lb_bytes);
+    c->d_totals = c->d_ticket + 16;
+    c->d_overflow = c->d_ticket + 32;
+    TRY(dev_alloc(c, &c->d_seg_count, V * c->max_draws));
+    TRY(cudaMemsetAsync(c->d_seg_count, 0, V * c->max_draws * sizeof(uint32_t), c->stream));
+    TRY(dev_alloc(c, &c->d_seg_key, (size_t)c->max_draws));
+    TRY(dev_alloc(c, &c->d_seg_inst, (size_t)c->max_draws));
+
+    c->slots.resize(fif);
+    for (Slot& s : c->slots) {
+        TRY(dev_alloc(c, &s.counts_dev, V * 2 + 8));
+        TRY(cudaMemsetAsync(s.counts_dev, 0, (V * 2 + 8) * sizeof(uint32_t), c->stream));
+        for (size_t v = 0; v < V; ++v) {
+            TRY(dev_alloc(c, &s.out[v].rows, (size_t)c->cap_visible * 3));
+            TRY(dev_alloc(c, &s.out[v].keys, (size_t)c->cap_visible));
+            TRY(dev_alloc(c, &s.out[v].idx, (size_t)c->cap_visible));
+            TRY(dev_alloc(c, &s.out[v].draws, (size_t)c->max_draws));
+            TRY(dev_alloc(c, &s.out[v].draw_keys, (size_t)c->max_draws));
+            s.out[v].counts = s.counts_dev + v * 2;
+        }
+        TRY(cudaEventCreate(&s.done));
+        TRY(cudaEventCreate(&s.start));
+        TRY(cudaHostAlloc(reinterpret_cast<void**>(&s.h_counts), (V * 2 + 8) * sizeof(uint32_t), cudaHostAllocDefault));
+        memset(s.h_counts, 0, (V * 2 + 8) * sizeof(uint32_t));
+    }
+    TRY(cudaStreamSynchronize(c->stream));
+#undef TRY
+    // defaults: one level of roots, no parents
+    c->level_offsets = {0, 0};
+    *out = c;
+    return SS_OK;
+}
+
+SS_API ss_status ss_set_key_layout(ss_ctx* c, uint32_t mesh_bits, uint32_t submesh_bits, uint32_t material_bits)
+{
+    if (!c) return SS_ERR_INVALID;
+    if (mesh_bits == 0 || submesh_bits == 0 || material_bits == 0 || material_bits > 31 ||
+        mesh_bits + submesh_bits + material_bits > 62)
+        return c->fail(SS_ERR_INVALID, "ss_set_key_layout: widths must be >= 1, material <= 31, sum <= 62");
+    SS_CUDA(c, cudaSetDevice(c->device));
+    c->mesh_bits = mesh_bits;
+    c->submesh_bits = submesh_bits;
+    c->material_bits = material_bits;
+    return c->n_slots ? upload_table(c) : SS_OK;
+}
+
+SS_API ss_status ss_set_submesh_table(ss_ctx* c, const ss_submesh* table, uint32_t count)
+{
+    if (!c) return SS_ERR_INVALID;
+    if (!table || count == 0 || count > c->cfg.max_submesh_slots)
+        return c->fail(SS_ERR_INVALID, "ss_set_submesh_table: %u rows, capacity %u", count, c->cfg.max_submesh_slots);
+    for (uint32_t i = 0; i < count; ++i) {
+        const float* m = table[i].local;
+        if (m[3] != 0.f || m[7] != 0.f || m[11] != 0.f || m[15] != 1.f)
+            return c->fail(SS_ERR_INVALID, "ss_set_submesh_table: row %u LocalTransform is not affine", i);
+        if (table[i].mesh_rank >> c->mesh_bits || table[i].submesh_index >> c->submesh_bits)
+            return c->fail(SS_ERR_INVALID, "ss_set_submesh_table: row %u rank/index exceeds the key layout", i);
+    }
+    SS_CUDA(c, cudaSetDevice(c->device));
+    c->host_table.assign(table, table + count);
+    c->n_slots = count;
+    return upload_table(c);
+}
+
+SS_API ss_status ss_set_nodes(ss_ctx* c, uint32_t n_nodes, const int32_t* parent, const uint32_t* level_offsets,
+                              uint32_t n_levels)
+{
+    if (!c) return SS_ERR_INVALID;
+    if (n_nodes == 0 || n_nodes > c->cfg.max_nodes)
+        return c->fail(SS_ERR_INVALID, "ss_set_nodes: %u nodes, capacity %u", n_nodes, c->cfg.max_nodes);
+    if (parent) {
+        if (!level_offsets || n_levels == 0 || n_levels > SS_MAX_LEVELS || level_offsets[0] != 0 ||
+            level_offsets[n_levels] != n_nodes)
+            return c->fail(SS_ERR_INVALID, "ss_set_nodes: level_offsets must span [0, n_nodes] in 1..%u levels",
+                           SS_MAX_LEVELS);
+        for (uint32_t l = 0; l < n_levels; ++l) {
+            if (level_offsets[l] > level_offsets[l + 1])
+                return c->fail(SS_ERR_INVALID, "ss_set_nodes: level_offsets not monotone at level %u", l);
+            for (uint32_t i = level_offsets[l]; i < level_offsets[l + 1]; ++i) {
+                const int32_t p = parent[i];
+                const bool ok = l == 0 ? p < 0 : (p >= (int32_t)level_offsets[l - 1] && p < (int32_t)level_offsets[l]);
+                if (!ok)
+                    return c->fail(SS_ERR_INVALID, "ss_set_nodes: node %u (level %u) has parent %d outside level %d", i,
+                                   l, p, (int)l - 1);
+            }
+        }
+        c->level_offsets.assign(level_offsets, level_offsets + n_levels + 1);
+        c->n_levels = n_levels;
+    } else {
+        c->level_offsets = {0, n_nodes};
+        c->n_levels = 1;
+    }
+    SS_CUDA(c, cudaSetDevice(c->device));
+    c->n_nodes = n_nodes;
+    c->has_parent = parent != nullptr;
+    if (parent) {
+        SS_CUDA(c, cudaMemcpyAsync(c->d_parent, parent, (size_t)n_nodes * 4, cudaMemcpyHostToDevice, c->stream));
+        SS_CUDA(c, cudaStreamSynchronize(c->stream));
+    }
+    return SS_OK;
+}
+
+SS_API ss_status ss_set_instances(ss_ctx* c, uint32_t n, const uint32_t* node, uint32_t node_base,
+                                  const uint32_t* submesh_slot, const uint32_t* material_word)
+{
+    if (!c) return SS_ERR_INVALID;
+    if (!submesh_slot || !material_word || n > c->cfg.max_instances)
+        return c->fail(SS_ERR_INVALID, "ss_set_instances: %u instances, capacity %u", n, c->cfg.max_instances);
+    if (c->n_nodes == 0) return c->fail(SS_ERR_STATE, "ss_set_instances: call ss_set_nodes first");
+    if (!node && (uint64_t)node_base + n > c->n_nodes)
+        return c->fail(SS_ERR_INVALID, "ss_set_instances: node_base %u + %u instances exceeds %u nodes", node_base, n,
+                       c->n_nodes);
+    for (uint32_t i = 0; i < n; ++i) {
+        if (submesh_slot[i] != SS_SLOT_NULL && submesh_slot[i] >= c->n_slots)
+            return c->fail(SS_ERR_INVALID, "ss_set_instances: instance %u names submesh slot %u of %u", i,
+                           submesh_slot[i], c->n_slots);
+        if ((material_word[i] & ~SS_MATERIAL_TESS_BIT) >> c->material_bits)
+            return c->fail(SS_ERR_INVALID, "ss_set_instances: instance %u material rank exceeds the key layout", i);
+        if (node && node[i] >= c->n_nodes)
+            return c->fail(SS_ERR_INVALID, "ss_set_instances: instance %u names node %u of %u", i, node[i], c->n_nodes);
+    }
+    SS_CUDA(c, cudaSetDevice(c->device));
+    c->n_instances = n;
+    c->has_node_map = node != nullptr;
+    c->node_base = node ? 0 : node_base;
+    c->has_inst_aabb = false;
+    c->world_uploaded = false;
+    if (n) {
+        if (node) SS_CUDA(c, cudaMemcpyAsync(c->d_node, node, (size_t)n * 4, cudaMemcpyHostToDevice, c->stream));
+        SS_CUDA(c, cudaMemcpyAsync(c->d_slot, submesh_slot, (size_t)n * 4, cudaMemcpyHostToDevice, c->stream));
+        SS_CUDA(c, cudaMemcpyAsync(c->d_matword, material_word, (size_t)n * 4, cudaMemcpyHostToDevice, c->stream));
+        SS_CUDA(c, cudaStreamSynchronize(c->stream));
+    }
+    return SS_OK;
+}
+
+SS_API ss_status ss_set_instance_aabbs(ss_ctx* c, uint32_t first, uint32_t count, const float* minmax6)
+{
+    if (!c) return SS_ERR_INVALID;
+    if (!minmax6) {
+        c->has_inst_aabb = false;
+        return SS_OK;
+    }
+    if ((uint64_t)first + count > c->n_instances)
+        return c->fail(SS_ERR_INVALID, "ss_set_instance_aabbs: range [%u, +%u) exceeds %u instances", first, count,
+                       c->n_instances);
+    SS_CUDA(c, cudaSetDevice(c->device));
+    if (count) {
+        SS_CUDA(c, cudaMemcpyAsync(c->d_inst_aabb + (size_t)first * 6, minmax6, (size_t)count * 24,
+                                   cudaMemcpyHostToDevice, c->stream));
+        SS_CUDA(c, cudaStreamSynchronize(c->stream));
+    }
+    c->has_inst_aabb = true;
+    return SS_OK;
+}
+
+SS_API ss_status ss_upload_trs(ss_ctx* c, uint32_t first, uint32_t count, const float* trs9)
+{
+    if (!c) return SS_ERR_INVALID;
+    if (!trs9 || (uint64_t)first + count > c->n_nodes)
+        return c->fail(SS_ERR_INVALID, "ss_upload_trs: range [%u, +%u) exceeds %u nodes", first, count, c->n_nodes);
+    SS_CUDA(c, cudaSetDevice(c->device));
+    if (count)
+        SS_CUDA(c, cudaMemcpyAsync(c->d_trs + (size_t)first * 9, trs9, (size_t)count * 36, cudaMemcpyHostToDevice,
+                                   c->stream));
+    return SS_OK;
+}
+
+SS_API ss_status ss_flush_uploads(ss_ctx* c)
+{
+    if (!c) return SS_ERR_INVALID;
+    SS_CUDA(c, cudaSetDevice(c->device));
+    SS_CUDA(c, cudaStreamSynchronize(c->stream));
+    return SS_OK;
+}
+
+SS_API ss_status ss_upload_world_rows(ss_ctx* c, uint32_t first, uint32_t count, const float* rows12)
+{
+    if (!c) return SS_ERR_INVALID;
+    if (!rows12 || (uint64_t)first + count > c->n_instances)
+        return c->fail(SS_ERR_INVALID, "ss_upload_world_rows: range [%u, +%u) exceeds %u instances", first, count,
+                       c->n_instances);
+    SS_CUDA(c, cudaSetDevice(c->device));
+    if (count)
+        SS_CUDA(c, cudaMemcpyAsync(reinterpret_cast<float*>(c->d_world) + (size_t)first * 12, rows12,
+                                   (size_t)count * 48, cudaMemcpyHostToDevice, c->stream));
+    c->world_uploaded = true;
+    return SS_OK;
+}
+
+SS_API ss_status ss_frame(ss_ctx* c, const ss_view* views, uint32_t n_views, uint32_t flags, uint32_t* slot_out)
+{
+    if (!c) return SS_ERR_INVALID;
+    if (!views || n_views < 1 || n_views > c->cfg.max_views)
+        return c->fail(SS_ERR_INVALID, "ss_frame: %u views, capacity %u", n_views, c->cfg.max_views);
+    if (c->n_slots == 0 || c->n_nodes == 0) return c->fail(SS_ERR_STATE, "ss_frame: submesh table / nodes not set");
+    const bool world_given = (flags & SS_FRAME_WORLD_ROWS_GIVEN) != 0;
+    if (world_given && !c->world_uploaded)
+        return c->fail(SS_ERR_STATE, "ss_frame: SS_FRAME_WORLD_ROWS_GIVEN without ss_upload_world_rows");
+    SS_CUDA(c, cudaSetDevice(c->device));
+
+    const uint32_t si = (uint32_t)(c->frame_no % c->slots.size());
+    Slot& s = c->slots[si];
+    if (s.pending) {  // the slot's previous frame must have been consumed (FramesInFlight back-pressure)
+        SS_CUDA(c, cudaEventSynchronize(s.done));
+        s.pending = false;
+    }
+    cudaStream_t st = c->stream;
+    int launches = 0;
+    const uint32_t n = c->n_instances;
+
+    CullParams cp;
+    memset(&cp, 0, sizeof cp);
+    cp.n_views = n_views;
+    for (uint32_t v = 0; v < n_views; ++v) {
+        planes_from_view_proj(views[v].view_proj, cp.v[v]);
+        cp.v[v].skip_near = (views[v].flags & SS_VIEW_SKIP_NEAR) ? 1u : 0u;
+    }
+
+    SS_CUDA(c, cudaEventRecord(s.start, st));
+    SS_CUDA(c, cudaMemsetAsync(c->d_emit_zero, 0, c->emit_zero_bytes, st));
+
+    // N1: levels above the instances (all levels when an explicit instance->node map is in use)
+    if (!world_given && (c->has_parent || c->has_node_map)) {
+        const uint32_t node_hi = c->has_node_map ? c->n_nodes : c->node_base;
+        for (uint32_t l = 0; l < c->n_levels; ++l) {
+            NodeLevelArgs na;
+            na.trs = c->d_trs;
+            na.parent = c->has_parent ? c->d_parent : nullptr;
+            na.node_world = c->d_node_world;
+            na.lo = std::min(c->level_offsets[l], node_hi);
+            na.hi = std::min(c->level_offsets[l + 1], node_hi);
+            na.trig_mode = (int)c->cfg.trig_mode;
+            if (na.hi > na.lo) {
+                launch_node_level(na, st);
+                ++launches;
+            }
+        }
+    }
+
+    InstanceArgs ia;
+    ia.trs = c->d_trs;
+    ia.parent = c->has_parent ? c->d_parent : nullptr;
+    ia.node_world = c->d_node_world;
+    ia.node = c->has_node_map ? c->d_node : nullptr;
+    ia.node_base = c->node_base;
+    ia.slot = c->d_slot;
+    ia.matword = c->d_matword;
+    ia.inst_aabb = c->has_inst_aabb ? c->d_inst_aabb : nullptr;
+    ia.slots = c->d_slots;
+    ia.world = c->d_world;
+    ia.mask = c->d_mask;
+    ia.keys = c->d_keys_a;
+    ia.vals = c->d_vals_a;
+    ia.n = n;
+    ia.tess_shift = c->mesh_bits + c->submesh_bits + c->material_bits;
+    ia.world_given = world_given ? 1 : 0;
+    ia.trig_mode = (int)c->cfg.trig_mode;
+    if (n) {
+        launch_instances(ia, cp, st);
+        ++launches;
+    }
+
+    // bits the layout can set: material | submesh | mesh | tess | dropped
+    const int end_bit = (int)ia.tess_shift + 2;
+    SS_CUDA(c, sort_pairs_async(c->d_keys_a, c->d_vals_a, c->d_keys_b, c->d_vals_b, n, 0, end_bit, c->d_sort_scratch,
+                                st, &launches));
+
+    EmitArgs ea;
+    memset(&ea, 0, sizeof ea);
+    ea.keys_a = c->d_keys_a;
+    ea.vals_a = c->d_vals_a;
+    ea.keys_b = c->d_keys_b;
+    ea.vals_b = c->d_vals_b;
+    ea.sort_ctl = reinterpret_cast<const SortControl*>(c->d_sort_scratch);
+    ea.sort_passes = (uint32_t)sort_num_passes(0, end_bit);
+    ea.mask = c->d_mask;
+    ea.world = c->d_world;
+    ea.n = n;
+    ea.n_views = n_views;
+    for (uint32_t v = 0; v < n_views; ++v) ea.out[v] = s.out[v];
+    ea.cap_visible = c->cap_visible;
+    ea.max_draws = c->max_draws;
+    ea.lookback = c->d_lookback;
+    ea.ticket = c->d_ticket;
+    ea.seg_count = c->d_seg_count;
+    ea.seg_key = c->d_seg_key;
+    ea.seg_inst = c->d_seg_inst;
+    ea.totals = c->d_totals;
+    ea.overflow = c->d_overflow;
+    if (n) {
+        launch_emit(ea, st);
+        ++launches;
+    }
+
+    DrawArgs da;
+    memset(&da, 0, sizeof da);
+    da.n_views = n_views;
+    da.max_draws = c->max_draws;
+    da.totals = c->d_totals;
+    da.seg_count = c->d_seg_count;
+    da.seg_key = c->d_seg_key;
+    da.seg_inst = c->d_seg_inst;
+    da.slot = c->d_slot;
+    da.slots = c->d_slots;
+    for (uint32_t v = 0; v < n_views; ++v) da.out[v] = s.out[v];
+    da.overflow = c->d_overflow;
+    launch_draws(da, st);
+    ++launches;
+    SS_CUDA(c, cudaGetLastError());
+
+    const size_t V = c->cfg.max_views;
+    SS_CUDA(c, cudaMemcpyAsync(s.h_counts, s.counts_dev, V * 2 * sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
+    SS_CUDA(c, cudaMemcpyAsync(s.h_counts + V * 2, c->d_overflow, sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
+    SS_CUDA(c, cudaMemcpyAsync(s.h_counts + V * 2 + 1,
+                               &reinterpret_cast<SortControl*>(c->d_sort_scratch)->passes_run, sizeof(uint32_t),
+                               cudaMemcpyDeviceToHost, st));
+    SS_CUDA(c, cudaEventRecord(s.done, st));
+    s.pending = true;
+    s.n_views = n_views;
+    s.n_instances = n;
+    s.launches = launches;
+    ++c->frame_no;
+    if (slot_out) *slot_out = si;
+    return SS_OK;
+}
+
+SS_API ss_status ss_frame_sync(ss_ctx* c, uint32_t slot, ss_frame_stats* stats)
+{
+    if (!c) return SS_ERR_INVALID;
+    if (slot >= c->slots.size()) return c->fail(SS_ERR_INVALID, "ss_frame_sync: slot %u of %zu", slot, c->slots.size());
+    Slot& s = c->slots[slot];
+    if (s.n_views == 0) return c->fail(SS_ERR_STATE, "ss_frame_sync: slot %u has no frame", slot);
+    SS_CUDA(c, cudaSetDevice(c->device));
+    SS_CUDA(c, cudaEventSynchronize(s.done));
+    s.pending = false;
+    const size_t V = c->cfg.max_views;
+    if (stats) {
+        memset(stats, 0, sizeof *stats);
+        stats->n_instances = s.n_instances;
+        stats->n_views = s.n_views;
+        for (uint32_t v = 0; v < s.n_views; ++v) {
+            stats->visible[v] = std::min(s.h_counts[v * 2 + 0], c->cap_visible);
+            stats->draws[v] = s.h_counts[v * 2 + 1];
+        }
+        stats->overflow = s.h_counts[V * 2];
+        stats->sort_passes_run = s.h_counts[V * 2 + 1];
+        stats->kernel_launches = (uint32_t)s.launches;
+        float ms = 0.f;
+        SS_CUDA(c, cudaEventElapsedTime(&ms, s.start, s.done));
+        stats->gpu_ms = ms;
+    }
+    if (s.h_counts[V * 2]) return c->fail(SS_ERR_CAPACITY, "frame overflowed max_visible_per_view / max_draws_per_view");
+    return SS_OK;
+}
+
+SS_API ss_status ss_map_outputs(ss_ctx* c, uint32_t slot, uint32_t view, ss_outputs* out)
+{
+    if (!c || !out) return SS_ERR_INVALID;
+    if (slot >= c->slots.size() || view >= c->cfg.max_views)
+        return c->fail(SS_ERR_INVALID, "ss_map_outputs: slot %u view %u out of range", slot, view);
+    Slot& s = c->slots[slot];
+    if (view >= s.n_views) return c->fail(SS_ERR_STATE, "ss_map_outputs: slot %u ran %u views", slot, s.n_views);
+    SS_CUDA(c, cudaSetDevice(c->device));
+    SS_CUDA(c, cudaEventSynchronize(s.done));
+    s.pending = false;
+    out->instance_rows = reinterpret_cast<const float*>(s.out[view].rows);
+    out->keys = s.out[view].keys;
+    out->instance_idx = s.out[view].idx;
+    out->draws = s.out[view].draws;
+    out->draw_keys = s.out[view].draw_keys;
+    out->counts = s.out[view].counts;
+    out->world_rows = reinterpret_cast<const float*>(c->d_world);
+    out->masks = c->d_mask;
+    out->visible = std::min(s.h_counts[view * 2 + 0], c->cap_visible);
+    out->n_draws = s.h_counts[view * 2 + 1];
+    return SS_OK;
+}
+
+SS_API ss_status ss_download_view(ss_ctx* c, uint32_t slot, uint32_t view, float* rows12, uint64_t* keys,
+                                  uint32_t* instance_idx, ss_draw_cmd* draws, uint64_t* draw_keys)
+{
+    ss_outputs o;
+    ss_status st = ss_map_outputs(c, slot, view, &o);
+    if (st != SS_OK) return st;
+    cudaStream_t s = c->stream;
+    if (rows12 && o.visible)
+        SS_CUDA(c, cudaMemcpyAsync(rows12, o.instance_rows, (size_t)o.visible * 48, cudaMemcpyDeviceToHost, s));
+    if (keys && o.visible) SS_CUDA(c, cudaMemcpyAsync(keys, o.keys, (size_t)o.visible * 8, cudaMemcpyDeviceToHost, s));
+    if (instance_idx && o.visible)
+        SS_CUDA(c, cudaMemcpyAsync(instance_idx, o.instance_idx, (size_t)o.visible * 4, cudaMemcpyDeviceToHost, s));
+    if (draws && o.n_draws)
+        SS_CUDA(c, cudaMemcpyAsync(draws, o.draws, (size_t)o.n_draws * sizeof(ss_draw_cmd), cudaMemcpyDeviceToHost, s));
+    if (draw_keys && o.n_draws)
+        SS_CUDA(c, cudaMemcpyAsync(draw_keys, o.draw_keys, (size_t)o.n_draws * 8, cudaMemcpyDeviceToHost, s));
+    SS_CUDA(c, cudaStreamSynchronize(s));
+    return SS_OK;
+}
+
+static ss_status download_range(ss_ctx* c, const void* src, size_t elem, uint32_t first, uint32_t count, void* dst,
+                                const char* what)
+{
+    if (!c) return SS_ERR_INVALID;
+    if (!dst || (uint64_t)first + count > c->n_instances)
+        return c->fail(SS_ERR_INVALID, "%s: range [%u, +%u) exceeds %u instances", what, first, count, c->n_instances);
+    SS_CUDA(c, cudaSetDevice(c->device));
+    if (count)
+        SS_CUDA(c, cudaMemcpyAsync(dst, static_cast<const unsigned char*>(src) + (size_t)first * elem,
+                                   (size_t)count * elem, cudaMemcpyDeviceToHost, c->stream));
+    SS_CUDA(c, cudaStreamSynchronize(c->stream));
+    return SS_OK;
+}
+
+SS_API ss_status ss_download_world(ss_ctx* c, uint32_t first, uint32_t count, float* rows12)
+{
+    return download_range(c, c ? c->d_world : nullptr, 48, first, count, rows12, "ss_download_world");
+}
+SS_API ss_status ss_download_masks(ss_ctx* c, uint32_t first, uint32_t count, uint8_t* masks)
+{
+    return download_range(c, c ? c->d_mask : nullptr, 1, first, count, masks, "ss_download_masks");
+}
+
+SS_API void* ss_stream(ss_ctx* c) { return c ? c->stream : nullptr; }
+
+// ---- standalone sort -------------------------------------------------------------------------
+
+SS_API size_t ss_sort_scratch_bytes(uint64_t n) { return sort_scratch_bytes(n); }
+
+SS_API ss_status ss_sort_pairs(void* cuda_stream, uint64_t* keys_a, uint32_t* vals_a, uint64_t* keys_b,
+                               uint32_t* vals_b, uint64_t n, int begin_bit, int end_bit, void* scratch,
+                               size_t scratch_bytes, int* sorted_in_b)
+{
+    if (!keys_a || !vals_a || !keys_b || !vals_b || !scratch || begin_bit < 0 || end_bit > 64 || begin_bit > end_bit ||
+        n >= (1ull << 30) || scratch_bytes < sort_scratch_bytes(n)) {
+        g_create_error = "ss_sort_pairs: invalid argument (pointers, bit range, n < 2^30, scratch size)";
+        return SS_ERR_INVALID;
+    }
+    cudaStream_t st = static_cast<cudaStream_t>(cuda_stream);
+    cudaError_t e = sort_pairs_async(keys_a, vals_a, keys_b, vals_b, n, begin_bit, end_bit, scratch, st, nullptr);
+    uint32_t sel = 0;
+    if (e == cudaSuccess)
+        e = cudaMemcpyAsync(&sel, &static_cast<SortControl*>(scratch)->src_sel[sort_num_passes(begin_bit, end_bit)],
+                            sizeof sel, cudaMemcpyDeviceToHost, st);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+    if (e != cudaSuccess) {
+        g_create_error = std::string("ss_sort_pairs: ") + cudaGetErrorString(e);
+        return SS_ERR_CUDA;
+    }
+    if (sorted_in_b) *sorted_in_b = (int)sel;
+    return SS_OK;
+}
+
+SS_API ss_status ss_sort_pairs_host(int device, const uint64_t* keys_in, const uint32_t* vals_in, uint64_t* keys_out,
+                                    uint32_t* vals_out, uint64_t n, int begin_bit, int end_bit)
+{
+    if ((n && (!keys_in || !vals_in || !keys_out || !vals_out)) || n >= (1ull << 30)) {
+        g_create_error = "ss_sort_pairs_host: invalid argument";
+        return SS_ERR_INVALID;
+    }
+    cudaError_t e = cudaSetDevice(device);
+    uint64_t *ka = nullptr, *kb = nullptr;
+    uint32_t *va = nullptr, *vb = nullptr;
+    void* scratch = nullptr;
+    const size_t nn = n ? n : 1, sb = sort_scratch_bytes(n);
+    if (e == cudaSuccess) e = cudaMalloc(&ka, nn * 8);
+    if (e == cudaSuccess) e = cudaMalloc(&kb, nn * 8);
+    if (e == cudaSuccess) e = cudaMalloc(&va, nn * 4);
+    if (e == cudaSuccess) e = cudaMalloc(&vb, nn * 4);
+    if (e == cudaSuccess) e = cudaMalloc(&scratch, sb);
+    if (e == cudaSuccess && n) e = cudaMemcpy(ka, keys_in, n * 8, cudaMemcpyHostToDevice);
+    if (e == cudaSuccess && n) e = cudaMemcpy(va, vals_in, n * 4, cudaMemcpyHostToDevice);
+    ss_status st = SS_OK;
+    int in_b = 0;
+    if (e == cudaSuccess) st = ss_sort_pairs(nullptr, ka, va, kb, vb, n, begin_bit, end_bit, scratch, sb, &in_b);
+    if (e == cudaSuccess && st == SS_OK && n) e = cudaMemcpy(keys_out, in_b ? kb : ka, n * 8, cudaMemcpyDeviceToHost);
+    if (e == cudaSuccess && st == SS_OK && n) e = cudaMemcpy(vals_out, in_b ? vb : va, n * 4, cudaMemcpyDeviceToHost);
+    cudaFree(ka);
+    cudaFree(kb);
+    cudaFree(va);
+    cudaFree(vb);
+    cudaFree(scratch);
+    if (e != cudaSuccess) {
+        g_create_error = std::string("ss_sort_pairs_host: ") + cudaGetErrorString(e);
+        return SS_ERR_CUDA;
+    }
+    return st;
+}
+
+}  // extern "C"

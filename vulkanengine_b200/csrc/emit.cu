@@ -1,0 +1,374 @@
+// Per-view stream compaction + instance-row gather + indirect-draw emission, sm_100a.
+//
+// Input: the (key, instance) list sorted by key (stable), the visibility byte of every instance and
+// the world rows.  One pass over the sorted list serves every view at once:
+//   - __ballot/__popc-free packed counting: the per-view visibility bits of an item are spread into
+//     16-bit lanes of two 64-bit words, so ONE block-wide add-scan ranks the item in all views;
+//   - decoupled look-back carries the running per-view counts (and the running number of key runs)
+//     from tile to tile, so the output position of every visible item is known inside its tile;
+//   - the 48 B TransformData rows (VC/Core/Components.h:95-98) are gathered through a shared-memory
+//     index list so that the global stores are coalesced 128-bit writes in draw order;
+//   - runs of equal keys become draws: per (view, run) visible counts are accumulated with one
+//     atomic per run per tile, and k_draws turns them into VkDrawIndexedIndirectCommand records
+//     (field meanings: Platform/Vulkan/VulkanRenderer.cpp:628) in MeshKey order.
+#include "ss_kernels.h"
+
+namespace ss {
+
+namespace {
+
+constexpr uint32_t kFlagAgg = 1u << 30;
+constexpr uint32_t kFlagPrefix = 1u << 31;
+constexpr uint32_t kValueMask = kFlagAgg - 1;
+constexpr int kEmitWarps = kEmitThreads / 32;
+
+struct EmitSmem {
+    uint64_t key[kEmitTile];
+    uint32_t idx[kEmitTile];
+    uint16_t list[SS_MAX_VIEWS][kEmitTile];          // local item ids of the visible items, per view
+    uint16_t seg_start[kEmitTile + 2][SS_MAX_VIEWS]; // visible-before count at the start of each local run
+    uint64_t last_key[kEmitThreads];
+    uint64_t warp_a[kEmitWarps], warp_b[kEmitWarps];
+    uint32_t warp_h[kEmitWarps];
+    uint32_t base[kEmitWords];   // exclusive prefix over earlier tiles
+    uint32_t total[kEmitWords];  // this tile
+    uint32_t tile;
+};
+
+__device__ __forceinline__ uint64_t shfl_up_u64(uint64_t v, int o)
+{
+    uint32_t lo = __shfl_up_sync(0xffffffffu, (uint32_t)v, o);
+    uint32_t hi = __shfl_up_sync(0xffffffffu, (uint32_t)(v >> 32), o);
+    return ((uint64_t)hi << 32) | lo;
+}
+
+// bit v of m -> 1 << 16v for v in 0..3
+__device__ __forceinline__ uint64_t spread4(uint32_t m)
+{
+    return (uint64_t)(m & 1u) | ((uint64_t)(m & 2u) << 15) | ((uint64_t)(m & 4u) << 30) | ((uint64_t)(m & 8u) << 45);
+}
+
+__global__ void __launch_bounds__(kEmitThreads) k_emit(const __grid_constant__ EmitArgs a)
+{
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    EmitSmem& s = *reinterpret_cast<EmitSmem*>(smem_raw);
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+
+    if (tid == 0) s.tile = atomicAdd(a.ticket, 1u);
+    __syncthreads();
+    const uint32_t tile = s.tile;
+    const uint32_t tile_base = tile * kEmitTile;
+    const uint32_t n_valid = min((uint32_t)kEmitTile, a.n - tile_base);
+    const uint32_t n_tiles = (a.n + kEmitTile - 1) / kEmitTile;
+
+    const bool in_b = a.sort_ctl->src_sel[a.sort_passes] != 0;
+    const uint64_t* __restrict__ keys = in_b ? a.keys_b : a.keys_a;
+    const uint32_t* __restrict__ vals = in_b ? a.vals_b : a.vals_a;
+
+    // blocked arrangement: thread t owns local items 4t .. 4t+3
+    uint64_t key[kEmitItems];
+    uint32_t idx[kEmitItems], m[kEmitItems];
+    const uint32_t l0 = tid * kEmitItems;
+    if (l0 + kEmitItems <= n_valid) {
+        const ulonglong2* kp = reinterpret_cast<const ulonglong2*>(keys + tile_base + l0);
+        ulonglong2 k01 = __ldg(kp), k23 = __ldg(kp + 1);
+        key[0] = k01.x; key[1] = k01.y; key[2] = k23.x; key[3] = k23.y;
+        uint4 iv = __ldg(reinterpret_cast<const uint4*>(vals + tile_base + l0));
+        idx[0] = iv.x; idx[1] = iv.y; idx[2] = iv.z; idx[3] = iv.w;
+    } else {
+#pragma unroll
+        for (int j = 0; j < kEmitItems; ++j) {
+            const bool ok = l0 + j < n_valid;
+            key[j] = ok ? __ldg(keys + tile_base + l0 + j) : ~0ull;
+            idx[j] = ok ? __ldg(vals + tile_base + l0 + j) : 0u;
+        }
+    }
+#pragma unroll
+    for (int j = 0; j < kEmitItems; ++j) {
+        m[j] = (l0 + j < n_valid) ? (uint32_t)__ldg(a.mask + idx[j]) : 0u;
+        s.key[l0 + j] = key[j];
+        s.idx[l0 + j] = idx[j];
+    }
+    s.last_key[tid] = key[kEmitItems - 1];
+    __syncthreads();
+
+    uint64_t prev;
+    bool first_is_head = false;
+    if (tid > 0) {
+        prev = s.last_key[tid - 1];
+    } else if (tile > 0) {
+        prev = __ldg(keys + tile_base - 1);
+    } else {
+        prev = 0;
+        first_is_head = true;
+    }
+    bool head[kEmitItems];
+    uint64_t pa = 0, pb = 0;
+    uint32_t ph = 0;
+#pragma unroll
+    for (int j = 0; j < kEmitItems; ++j) {
+        const bool ok = l0 + j < n_valid;
+        head[j] = ok && ((j == 0 && first_is_head) || key[j] != (j == 0 ? prev : key[j - 1]));
+        pa += spread4(m[j] & 15u);
+        pb += spread4(m[j] >> 4);
+        ph += head[j] ? 1u : 0u;
+    }
+
+    // block-wide inclusive scans of (pa, pb, ph)
+    uint64_t xa = pa, xb = pb;
+    uint32_t xh = ph;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        uint64_t ya = shfl_up_u64(xa, o), yb = shfl_up_u64(xb, o);
+        uint32_t yh = __shfl_up_sync(0xffffffffu, xh, o);
+        if (lane >= o) {
+            xa += ya;
+            xb += yb;
+            xh += yh;
+        }
+    }
+    if (lane == 31) {
+        s.warp_a[wid] = xa;
+        s.warp_b[wid] = xb;
+        s.warp_h[wid] = xh;
+    }
+    __syncthreads();
+    uint64_t ba = 0, bb = 0;
+    uint32_t bh = 0;
+    for (int w = 0; w < wid; ++w) {
+        ba += s.warp_a[w];
+        bb += s.warp_b[w];
+        bh += s.warp_h[w];
+    }
+    // exclusive prefixes of this thread's first item
+    uint64_t ea = ba + xa - pa, eb = bb + xb - pb;
+    uint32_t eh = bh + xh - ph;
+
+    if (tid == kEmitThreads - 1) {
+        const uint64_t ta = ba + xa, tb = bb + xb;
+#pragma unroll
+        for (int v = 0; v < 4; ++v) {
+            s.total[v] = (uint32_t)(ta >> (16 * v)) & 0xffffu;
+            s.total[4 + v] = (uint32_t)(tb >> (16 * v)) & 0xffffu;
+        }
+        s.total[SS_MAX_VIEWS] = bh + xh;
+    }
+    __syncthreads();
+
+    // decoupled look-back, one thread per word
+    if (tid < kEmitWords) {
+        const uint32_t mine = s.total[tid];
+        volatile uint32_t* lb = a.lookback + (size_t)tile * kEmitWords;
+        uint32_t excl = 0;
+        if (tile == 0) {
+            lb[tid] = kFlagPrefix | mine;
+        } else {
+            lb[tid] = kFlagAgg | mine;
+            int64_t t = (int64_t)tile - 1;
+            while (true) {
+                const uint32_t v = *(volatile uint32_t*)(a.lookback + (size_t)t * kEmitWords + tid);
+                if (v & kFlagPrefix) {
+                    excl += v & kValueMask;
+                    break;
+                }
+                if (v & kFlagAgg) {
+                    excl += v & kValueMask;
+                    --t;
+                }
+            }
+            lb[tid] = kFlagPrefix | (excl + mine);
+        }
+        s.base[tid] = excl;
+        if (tile == n_tiles - 1) a.totals[tid] = excl + mine;
+    }
+
+    // local lists: where each visible item lands, and where each key run starts
+    const uint32_t n_heads = s.total[SS_MAX_VIEWS];
+    if (tid < (int)SS_MAX_VIEWS) {
+        s.seg_start[0][tid] = 0;
+        s.seg_start[n_heads + 1][tid] = (uint16_t)s.total[tid];
+    }
+#pragma unroll
+    for (int j = 0; j < kEmitItems; ++j) {
+        if (head[j]) {
+            const uint32_t lseg = eh + 1;  // 1-based among runs starting in this tile; 0 = run carried in
+#pragma unroll
+            for (int v = 0; v < 4; ++v) {
+                s.seg_start[lseg][v] = (uint16_t)(ea >> (16 * v));
+                s.seg_start[lseg][4 + v] = (uint16_t)(eb >> (16 * v));
+            }
+        }
+#pragma unroll
+        for (int v = 0; v < (int)SS_MAX_VIEWS; ++v) {
+            if ((m[j] >> v) & 1u) {
+                const uint32_t lpos = (uint32_t)((v < 4 ? ea >> (16 * v) : eb >> (16 * (v - 4))) & 0xffffu);
+                s.list[v][lpos] = (uint16_t)(l0 + j);
+            }
+        }
+        ea += spread4(m[j] & 15u);
+        eb += spread4(m[j] >> 4);
+        eh += head[j] ? 1u : 0u;
+    }
+    __syncthreads();
+
+    // run bookkeeping: first key / first instance of each run, visible count per (view, run)
+    const uint32_t seg_base = s.base[SS_MAX_VIEWS];
+    {
+        uint32_t ehh = bh + xh - ph;
+#pragma unroll
+        for (int j = 0; j < kEmitItems; ++j) {
+            if (head[j]) {
+                const uint32_t g = seg_base + ehh;
+                if (g < a.max_draws) {
+                    a.seg_key[g] = key[j];
+                    a.seg_inst[g] = idx[j];
+                } else {
+                    *a.overflow = 1u;
+                }
+                ++ehh;
+            }
+        }
+    }
+    for (uint32_t k = tid; k <= n_heads; k += kEmitThreads) {
+        const uint32_t g = seg_base + k - 1u;  // k == 0: run that started in an earlier tile
+#pragma unroll
+        for (int v = 0; v < (int)SS_MAX_VIEWS; ++v) {
+            if (v < (int)a.n_views) {
+                const uint32_t c = (uint32_t)s.seg_start[k + 1][v] - (uint32_t)s.seg_start[k][v];
+                if (c) {
+                    if (g < a.max_draws) atomicAdd(a.seg_count + (size_t)v * a.max_draws + g, c);
+                }
+            }
+        }
+    }
+
+    // per view: keys + instance ids, then the gathered rows, all as coalesced stores
+    for (uint32_t v = 0; v < a.n_views; ++v) {
+        const uint32_t cnt = s.total[v];
+        const uint32_t base = s.base[v];
+        const ViewOut& o = a.out[v];
+        if (base + cnt > a.cap_visible && tid == 0) *a.overflow = 1u;
+        for (uint32_t e = tid; e < cnt; e += kEmitThreads) {
+            const uint32_t li = s.list[v][e];
+            const uint32_t g = base + e;
+            if (g < a.cap_visible) {
+                o.keys[g] = s.key[li];
+                o.idx[g] = s.idx[li];
+            }
+        }
+        const uint32_t total4 = cnt * 3u;
+        for (uint32_t j0 = tid; j0 < total4; j0 += kEmitThreads * 4) {
+            float4 r[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                const uint32_t j = j0 + u * kEmitThreads;
+                if (j < total4) {
+                    const uint32_t e = j / 3u, part = j - e * 3u;
+                    r[u] = __ldg(a.world + (size_t)s.idx[s.list[v][e]] * 3u + part);
+                }
+            }
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                const uint32_t j = j0 + u * kEmitThreads;
+                if (j < total4) {
+                    const uint32_t e = j / 3u;
+                    if (base + e < a.cap_visible) o.rows[(size_t)base * 3u + j] = r[u];
+                }
+            }
+        }
+    }
+}
+
+// one CTA per view: runs -> draws
+__global__ void __launch_bounds__(1024) k_draws(const __grid_constant__ DrawArgs a)
+{
+    __shared__ uint32_t warp_c[32], warp_f[32];
+    __shared__ uint32_t carry_c, carry_f;
+    const uint32_t v = blockIdx.x;
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    uint32_t n_segs = a.totals[SS_MAX_VIEWS];
+    if (n_segs > a.max_draws) {
+        n_segs = a.max_draws;
+        if (tid == 0) *a.overflow = 1u;
+    }
+    if (tid == 0) {
+        carry_c = 0;
+        carry_f = 0;
+    }
+    __syncthreads();
+    uint32_t* cnt = a.seg_count + (size_t)v * a.max_draws;
+    const ViewOut& o = a.out[v];
+    for (uint32_t s0 = 0; s0 < n_segs; s0 += blockDim.x) {
+        const uint32_t sgm = s0 + tid;
+        uint32_t c = 0;
+        if (sgm < n_segs) {
+            c = cnt[sgm];
+            cnt[sgm] = 0;  // leave the accumulator clean for the next frame
+        }
+        const uint32_t f = c ? 1u : 0u;
+        uint32_t xc = c, xf = f;
+#pragma unroll
+        for (int ofs = 1; ofs < 32; ofs <<= 1) {
+            uint32_t yc = __shfl_up_sync(0xffffffffu, xc, ofs), yf = __shfl_up_sync(0xffffffffu, xf, ofs);
+            if (lane >= ofs) {
+                xc += yc;
+                xf += yf;
+            }
+        }
+        if (lane == 31) {
+            warp_c[wid] = xc;
+            warp_f[wid] = xf;
+        }
+        __syncthreads();
+        uint32_t bc = carry_c, bf = carry_f;
+        for (int w = 0; w < wid; ++w) {
+            bc += warp_c[w];
+            bf += warp_f[w];
+        }
+        if (f) {
+            const uint32_t d = bf + xf - 1u;
+            const uint32_t inst = a.seg_inst[sgm];
+            const SlotDev* sd = a.slots + a.slot[inst];
+            ss_draw_cmd dc;
+            dc.index_count = sd->index_count;
+            dc.instance_count = c;
+            dc.first_index = sd->first_index;
+            dc.vertex_offset = sd->vertex_offset;
+            dc.first_instance = bc + xc - c;
+            o.draws[d] = dc;
+            o.draw_keys[d] = a.seg_key[sgm];
+        }
+        __syncthreads();
+        if (tid == (int)blockDim.x - 1) {
+            carry_c = bc + xc;
+            carry_f = bf + xf;
+        }
+        __syncthreads();
+    }
+    if (tid == 0) {
+        o.counts[0] = a.totals[v];
+        o.counts[1] = carry_f;
+    }
+}
+
+}  // namespace
+
+size_t emit_lookback_bytes(uint64_t n)
+{
+    const uint64_t tiles = (n + kEmitTile - 1) / kEmitTile;
+    return (size_t)(tiles ? tiles : 1) * kEmitWords * sizeof(uint32_t);
+}
+
+void launch_emit(const EmitArgs& a, cudaStream_t st)
+{
+    cudaFuncSetAttribute(k_emit, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(EmitSmem));
+    const uint32_t tiles = (a.n + kEmitTile - 1) / kEmitTile;
+    if (tiles) k_emit<<<tiles, kEmitThreads, sizeof(EmitSmem), st>>>(a);
+}
+
+void launch_draws(const DrawArgs& a, cudaStream_t st)
+{
+    if (a.n_views) k_draws<<<a.n_views, 1024, 0, st>>>(a);
+}
+
+}  // namespace ss

@@ -1,0 +1,120 @@
+// Internal launch interface between the context (context.cu) and the kernels.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "ss_device.cuh"
+
+namespace ss {
+
+// ---- transform / cull / key (transform_cull.cu) ----------------------------------------------
+struct NodeLevelArgs {
+    const float* trs;          // [n_nodes][9]
+    const int32_t* parent;     // [n_nodes] or nullptr
+    float4* node_world;        // [n_nodes][3]
+    uint32_t lo, hi;           // node range of this level
+    int trig_mode;
+};
+void launch_node_level(const NodeLevelArgs& a, cudaStream_t st);
+
+struct InstanceArgs {
+    const float* trs;
+    const int32_t* parent;
+    const float4* node_world;
+    const uint32_t* node;      // explicit instance -> node map or nullptr
+    uint32_t node_base;
+    const uint32_t* slot;
+    const uint32_t* matword;
+    const float* inst_aabb;    // [n][6] or nullptr
+    const SlotDev* slots;
+    float4* world;             // [n][3] in/out
+    uint8_t* mask;
+    uint64_t* keys;
+    uint32_t* vals;            // iota payload for the sort
+    uint32_t n;
+    uint32_t tess_shift;       // mb + sb + hb
+    int world_given;           // SS_FRAME_WORLD_ROWS_GIVEN
+    int trig_mode;
+};
+void launch_instances(const InstanceArgs& a, const CullParams& cp, cudaStream_t st);
+
+// ---- onesweep radix sort (radix_sort.cu) -------------------------------------------------------
+constexpr int kRadixBits = 8;
+constexpr int kRadix = 1 << kRadixBits;
+constexpr int kMaxPasses = 8;
+constexpr int kSortThreads = 256;
+constexpr int kSortItems = 16;
+constexpr int kSortTile = kSortThreads * kSortItems;
+
+// Device-resident control block of one sort (lives at the head of the scratch buffer).
+struct SortControl {
+    uint32_t hist[kMaxPasses][kRadix];     // global digit histograms, then exclusive bin offsets
+    uint32_t ticket[kMaxPasses];           // dynamic tile ids
+    uint32_t skip[kMaxPasses];             // 1 = digit constant over all keys: pass moves nothing
+    uint32_t src_sel[kMaxPasses + 1];      // buffer (0 = a, 1 = b) holding the input of pass p; [n_passes] = result
+    uint32_t passes_run;
+    uint32_t pad[7];
+};
+
+size_t sort_scratch_bytes(uint64_t n);
+// zeroes the control block + look-back state; call before sort_pairs each time (stream-ordered)
+cudaError_t sort_reset(void* scratch, uint64_t n, cudaStream_t st);
+// enqueues histogram + scan + passes. Result location: control->src_sel[n_passes] (device).
+cudaError_t sort_pairs_async(uint64_t* keys_a, uint32_t* vals_a, uint64_t* keys_b, uint32_t* vals_b, uint64_t n,
+                             int begin_bit, int end_bit, void* scratch, cudaStream_t st, int* launches);
+inline int sort_num_passes(int begin_bit, int end_bit) { return (end_bit - begin_bit + kRadixBits - 1) / kRadixBits; }
+
+// ---- compaction + emit (emit.cu) ---------------------------------------------------------------
+constexpr int kEmitThreads = 256;
+constexpr int kEmitItems = 4;
+constexpr int kEmitTile = kEmitThreads * kEmitItems;
+constexpr int kEmitWords = SS_MAX_VIEWS + 1;  // per-tile look-back words: V visible counts + segment heads
+
+struct ViewOut {
+    float4* rows;        // [cap][3]
+    uint64_t* keys;      // [cap]
+    uint32_t* idx;       // [cap]
+    ss_draw_cmd* draws;  // [max_draws]
+    uint64_t* draw_keys; // [max_draws]
+    uint32_t* counts;    // {visible, draws}
+};
+
+struct EmitArgs {
+    const uint64_t* keys_a; const uint32_t* vals_a;
+    const uint64_t* keys_b; const uint32_t* vals_b;
+    const SortControl* sort_ctl;   // result selector
+    uint32_t sort_passes;
+    const uint8_t* mask;
+    const float4* world;
+    uint32_t n;
+    uint32_t n_views;
+    ViewOut out[SS_MAX_VIEWS];
+    uint32_t cap_visible;
+    uint32_t max_draws;
+    // scratch
+    uint32_t* lookback;      // [tiles][kEmitWords], zeroed per frame
+    uint32_t* ticket;        // zeroed per frame
+    uint32_t* seg_count;     // [n_views][max_draws], zero at rest
+    uint64_t* seg_key;       // [max_draws]
+    uint32_t* seg_inst;      // [max_draws]
+    uint32_t* totals;        // [kEmitWords] final totals (visible per view, n_segs)
+    uint32_t* overflow;      // set non-zero on capacity overflow
+};
+size_t emit_lookback_bytes(uint64_t n);
+void launch_emit(const EmitArgs& a, cudaStream_t st);
+
+struct DrawArgs {
+    uint32_t n_views;
+    uint32_t max_draws;
+    const uint32_t* totals;
+    uint32_t* seg_count;
+    const uint64_t* seg_key;
+    const uint32_t* seg_inst;
+    const uint32_t* slot;
+    const SlotDev* slots;
+    ViewOut out[SS_MAX_VIEWS];
+    uint32_t* overflow;
+};
+void launch_draws(const DrawArgs& a, cudaStream_t st);
+
+}  // namespace ss

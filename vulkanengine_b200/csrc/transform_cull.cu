@@ -1,0 +1,214 @@
+// Transform -> cull -> key kernels, sm_100a.
+//
+// HBM-bound streaming work: every input stream is a dense array of small records
+// (TransformComponent 36 B, AABB 24 B, ids 4+4 B).  A CTA copies its tile of each stream into shared
+// memory with 128-bit coalesced loads, each thread then reads its own record at an odd word stride
+// (bank-conflict free), computes, and the 48 B output rows leave through shared memory as 128-bit
+// coalesced stores.  No tensor cores: a 4x4 affine product per instance is not a dense contraction.
+#include "ss_kernels.h"
+
+namespace ss {
+
+namespace {
+
+constexpr int kTile = 256;  // instances per CTA == threads per CTA
+
+// Cooperative copy of `count` floats from global to 16B-aligned shared memory.
+__device__ __forceinline__ void tile_load_f32(float* __restrict__ dst, const float* __restrict__ src, int count)
+{
+    const int tid = threadIdx.x;
+    if ((reinterpret_cast<uintptr_t>(src) & 15u) == 0) {
+        const int n4 = count >> 2;
+        const float4* s4 = reinterpret_cast<const float4*>(src);
+        float4* d4 = reinterpret_cast<float4*>(dst);
+        for (int i = tid; i < n4; i += kTile) d4[i] = ld_nc_f4(s4 + i);
+        for (int i = (n4 << 2) + tid; i < count; i += kTile) dst[i] = __ldg(src + i);
+    } else {
+        for (int i = tid; i < count; i += kTile) dst[i] = __ldg(src + i);
+    }
+}
+
+__device__ __forceinline__ Aff load_rows(const float4* __restrict__ p)
+{
+    Aff a;
+    a.r0 = __ldg(p + 0);
+    a.r1 = __ldg(p + 1);
+    a.r2 = __ldg(p + 2);
+    return a;
+}
+
+__device__ __forceinline__ float4 shfl_f4(float4 v, int src)
+{
+    v.x = __shfl_sync(0xffffffffu, v.x, src);
+    v.y = __shfl_sync(0xffffffffu, v.y, src);
+    v.z = __shfl_sync(0xffffffffu, v.z, src);
+    v.w = __shfl_sync(0xffffffffu, v.w, src);
+    return v;
+}
+
+// Parent rows for a whole warp.  Siblings are adjacent in a level-ordered stream, so most warps
+// share one parent: lanes 0..2 fetch one row each and the warp gets them by shuffle; mixed warps
+// fall back to per-lane loads.  Every lane of the warp must call this (p < 0 = no parent).
+__device__ __forceinline__ bool warp_parent_rows(const float4* __restrict__ node_world, int p, Aff& out)
+{
+    const int lane = threadIdx.x & 31;
+    int same;
+    __match_all_sync(0xffffffffu, p, &same);
+    if (same) {
+        if (p < 0) return false;
+        float4 mine = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (lane < 3) mine = __ldg(node_world + (size_t)p * 3 + lane);
+        out.r0 = shfl_f4(mine, 0);
+        out.r1 = shfl_f4(mine, 1);
+        out.r2 = shfl_f4(mine, 2);
+        return true;
+    }
+    if (p < 0) return false;
+    out = load_rows(node_world + (size_t)p * 3);
+    return true;
+}
+
+template <int TRIG>
+__global__ void __launch_bounds__(kTile) k_node_level(NodeLevelArgs a)
+{
+    __shared__ __align__(16) float s_trs[kTile * 9];
+    __shared__ __align__(16) float4 s_rows[kTile * 3];
+    const uint32_t base = a.lo + blockIdx.x * kTile;
+    const int n_tile = min((uint32_t)kTile, a.hi - base);
+    const int tid = threadIdx.x;
+    tile_load_f32(s_trs, a.trs + (size_t)base * 9, n_tile * 9);
+    __syncthreads();
+    const bool valid = tid < n_tile;
+    int p = -1;
+    if (valid && a.parent) p = __ldg(a.parent + base + tid);
+    Aff parent;
+    const bool has_parent = warp_parent_rows(a.node_world, p, parent);
+    if (valid) {
+        Aff m = trs_to_affine<TRIG>(s_trs + tid * 9);
+        if (has_parent) m = aff_mul(parent, m);
+        s_rows[tid * 3 + 0] = m.r0;
+        s_rows[tid * 3 + 1] = m.r1;
+        s_rows[tid * 3 + 2] = m.r2;
+    }
+    __syncthreads();
+    float4* dst = a.node_world + (size_t)base * 3;
+    for (int i = tid; i < n_tile * 3; i += kTile) dst[i] = s_rows[i];
+}
+
+template <int TRIG>
+__global__ void __launch_bounds__(kTile) k_instances(InstanceArgs a, const __grid_constant__ CullParams cp)
+{
+    __shared__ __align__(16) float s_trs[kTile * 9];
+    __shared__ __align__(16) float s_box[kTile * 6];
+    __shared__ __align__(16) float4 s_rows[kTile * 3];
+
+    const uint32_t base = blockIdx.x * kTile;
+    const int n_tile = min((uint32_t)kTile, a.n - base);
+    const int tid = threadIdx.x;
+    const bool valid = tid < n_tile;
+    const uint32_t i = base + tid;
+    const bool from_trs = !a.world_given && a.node == nullptr;
+
+    if (from_trs) tile_load_f32(s_trs, a.trs + ((size_t)a.node_base + base) * 9, n_tile * 9);
+    if (a.inst_aabb) tile_load_f32(s_box, a.inst_aabb + (size_t)base * 6, n_tile * 6);
+    if (a.world_given) {
+        const float4* src = a.world + (size_t)base * 3;
+        for (int k = tid; k < n_tile * 3; k += kTile) s_rows[k] = ld_nc_f4(src + k);
+    }
+    uint32_t slot = SS_SLOT_NULL, mw = 0;
+    if (valid) {
+        slot = __ldg(a.slot + i);
+        mw = __ldg(a.matword + i);
+    }
+    int p = -1;
+    if (from_trs && valid && a.parent) p = __ldg(a.parent + a.node_base + i);
+    __syncthreads();
+
+    Aff parent;
+    const bool has_parent = warp_parent_rows(a.node_world, p, parent);
+
+    const bool live = valid && slot != SS_SLOT_NULL;
+    Aff w;
+    w.r0 = w.r1 = w.r2 = make_float4(0.f, 0.f, 0.f, 0.f);
+    uint32_t mask = 0;
+    uint64_t key = 2ull << a.tess_shift;  // dropped: the bit above tess, behind every real key
+    if (live) {
+        const SlotDev* sd = a.slots + slot;
+        if (a.world_given) {
+            w.r0 = s_rows[tid * 3 + 0];
+            w.r1 = s_rows[tid * 3 + 1];
+            w.r2 = s_rows[tid * 3 + 2];
+        } else {
+            Aff m;
+            if (from_trs) {
+                m = trs_to_affine<TRIG>(s_trs + tid * 9);
+                if (has_parent) m = aff_mul(parent, m);  // N1: world = world[parent] * local
+            } else {
+                m = load_rows(a.node_world + (size_t)__ldg(a.node + i) * 3);
+            }
+            Aff loc;
+            loc.r0 = __ldg(&sd->r0);
+            loc.r1 = __ldg(&sd->r1);
+            loc.r2 = __ldg(&sd->r2);
+            w = aff_mul(m, loc);  // VC/Scene/SceneRenderer.cpp:1150
+        }
+        float mn[3], mx[3];
+        if (a.inst_aabb) {
+#pragma unroll
+            for (int k = 0; k < 3; ++k) {
+                mn[k] = s_box[tid * 6 + k];
+                mx[k] = s_box[tid * 6 + 3 + k];
+            }
+        } else {
+#pragma unroll
+            for (int k = 0; k < 3; ++k) {
+                mn[k] = __ldg(&sd->mn[k]);
+                mx[k] = __ldg(&sd->mx[k]);
+            }
+        }
+        mask = cull_box(w, mn, mx, cp);
+        // N5: [tess][meshRank][submeshIndex][materialRank]
+        key = __ldg(&sd->key_hi) | (uint64_t)(mw & ~SS_MATERIAL_TESS_BIT) |
+              ((uint64_t)(mw >> 31) << a.tess_shift);
+    }
+    if (!a.world_given) {
+        __syncthreads();  // s_rows is free (world_given reads finished above / never written)
+        if (valid) {
+            s_rows[tid * 3 + 0] = w.r0;
+            s_rows[tid * 3 + 1] = w.r1;
+            s_rows[tid * 3 + 2] = w.r2;
+        }
+        __syncthreads();
+        float4* dst = a.world + (size_t)base * 3;
+        for (int k = tid; k < n_tile * 3; k += kTile) dst[k] = s_rows[k];
+    }
+    if (valid) {
+        a.mask[i] = (uint8_t)mask;
+        a.keys[i] = key;
+        a.vals[i] = i;
+    }
+}
+
+}  // namespace
+
+void launch_node_level(const NodeLevelArgs& a, cudaStream_t st)
+{
+    if (a.hi <= a.lo) return;
+    const uint32_t grid = (a.hi - a.lo + kTile - 1) / kTile;
+    if (a.trig_mode == SS_TRIG_DETERMINISTIC)
+        k_node_level<SS_TRIG_DETERMINISTIC><<<grid, kTile, 0, st>>>(a);
+    else
+        k_node_level<SS_TRIG_LIBM><<<grid, kTile, 0, st>>>(a);
+}
+
+void launch_instances(const InstanceArgs& a, const CullParams& cp, cudaStream_t st)
+{
+    if (a.n == 0) return;
+    const uint32_t grid = (a.n + kTile - 1) / kTile;
+    if (a.trig_mode == SS_TRIG_DETERMINISTIC)
+        k_instances<SS_TRIG_DETERMINISTIC><<<grid, kTile, 0, st>>>(a, cp);
+    else
+        k_instances<SS_TRIG_LIBM><<<grid, kTile, 0, st>>>(a, cp);
+}
+
+}  // namespace ss

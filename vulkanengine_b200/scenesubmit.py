@@ -1,0 +1,249 @@
+"""ctypes binding of libscenesubmit.so (include/scenesubmit.h) — the same entry points the C++ host
+mirror and a reference-side maintainer would bind.  There is no CPU fallback: if the CUDA library
+cannot be loaded, importing the product path fails loudly."""
+import ctypes as C
+import os
+
+import numpy as np
+
+from .synth import DRAW_DTYPE, SUBMESH_DTYPE, VIEW_DTYPE
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libscenesubmit.so")
+
+SS_OK, SS_ERR_INVALID, SS_ERR_CUDA, SS_ERR_CAPACITY, SS_ERR_STATE, SS_ERR_NOMEM = range(6)
+TRIG_DETERMINISTIC, TRIG_LIBM = 0, 1
+FRAME_WORLD_ROWS_GIVEN = 1
+FRAME_NO_GRAPH = 2
+MAX_VIEWS = 8
+SLOT_NULL = 0xFFFFFFFF
+
+# every symbol include/scenesubmit.h declares (tests check the library exports exactly these)
+EXPORTS = ["ss_create", "ss_destroy", "ss_last_error", "ss_version", "ss_set_key_layout", "ss_set_submesh_table",
+           "ss_set_nodes", "ss_set_instances", "ss_set_instance_aabbs", "ss_upload_trs", "ss_flush_uploads",
+           "ss_upload_world_rows", "ss_frame", "ss_frame_sync", "ss_map_outputs", "ss_download_view",
+           "ss_download_world", "ss_download_masks", "ss_stream", "ss_sort_scratch_bytes", "ss_sort_pairs",
+           "ss_sort_pairs_host", "ss_camera_view_proj", "ss_cascade_matrices"]
+
+
+class SceneSubmitError(RuntimeError):
+    def __init__(self, status, msg):
+        super().__init__(f"libscenesubmit status {status}: {msg}")
+        self.status = status
+
+
+class Config(C.Structure):
+    _fields_ = [("struct_size", C.c_uint32), ("device", C.c_int32), ("max_nodes", C.c_uint32),
+                ("max_instances", C.c_uint32), ("max_submesh_slots", C.c_uint32), ("max_views", C.c_uint32),
+                ("max_draws_per_view", C.c_uint32), ("frames_in_flight", C.c_uint32),
+                ("max_visible_per_view", C.c_uint64), ("trig_mode", C.c_uint32), ("flags", C.c_uint32)]
+
+
+class FrameStats(C.Structure):
+    _fields_ = [("n_instances", C.c_uint32), ("n_views", C.c_uint32), ("visible", C.c_uint32 * MAX_VIEWS),
+                ("draws", C.c_uint32 * MAX_VIEWS), ("sort_passes_run", C.c_uint32), ("overflow", C.c_uint32),
+                ("gpu_ms", C.c_float), ("kernel_launches", C.c_uint32)]
+
+
+class Outputs(C.Structure):
+    _fields_ = [("instance_rows", C.c_void_p), ("keys", C.c_void_p), ("instance_idx", C.c_void_p),
+                ("draws", C.c_void_p), ("draw_keys", C.c_void_p), ("counts", C.c_void_p), ("world_rows", C.c_void_p),
+                ("masks", C.c_void_p), ("visible", C.c_uint32), ("n_draws", C.c_uint32)]
+
+
+_lib = None
+
+
+def load_library():
+    """Loads libscenesubmit.so or raises: the product has no other implementation to fall back to."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise ImportError(f"{LIB_PATH} is missing: run `make` (nvcc, sm_100a). libscenesubmit has no CPU fallback.")
+        lib = C.CDLL(LIB_PATH)
+        lib.ss_last_error.restype = C.c_char_p
+        lib.ss_last_error.argtypes = [C.c_void_p]
+        lib.ss_version.restype = C.c_uint32
+        lib.ss_stream.restype = C.c_void_p
+        lib.ss_stream.argtypes = [C.c_void_p]
+        lib.ss_sort_scratch_bytes.restype = C.c_size_t
+        lib.ss_sort_scratch_bytes.argtypes = [C.c_uint64]
+        lib.ss_destroy.argtypes = [C.c_void_p]
+        lib.ss_destroy.restype = None
+        _lib = lib
+    return _lib
+
+
+def _p(a):
+    return None if a is None else a.ctypes.data_as(C.c_void_p)
+
+
+def camera_view_proj(fov, aspect, zn, zf, pos, pitch, yaw):
+    lib = load_library()
+    pos = np.asarray(pos, np.float32)
+    v, p, vp = (np.empty(16, np.float32) for _ in range(3))
+    st = lib.ss_camera_view_proj(C.c_float(fov), C.c_float(aspect), C.c_float(zn), C.c_float(zf), _p(pos),
+                                 C.c_float(pitch), C.c_float(yaw), _p(v), _p(p), _p(vp))
+    if st != SS_OK:
+        raise SceneSubmitError(st, "ss_camera_view_proj")
+    return v, p, vp
+
+
+def cascade_matrices(vp, zn, zf, lam, near_off, far_off, light_dir):
+    lib = load_library()
+    vp = np.ascontiguousarray(vp, np.float32)
+    ld = np.asarray(light_dir, np.float32)
+    splits = np.empty(4, np.float32)
+    mats = np.empty((4, 16), np.float32)
+    st = lib.ss_cascade_matrices(_p(vp), C.c_float(zn), C.c_float(zf), C.c_float(lam), C.c_float(near_off),
+                                 C.c_float(far_off), _p(ld), _p(splits), _p(mats))
+    if st != SS_OK:
+        raise SceneSubmitError(st, "ss_cascade_matrices")
+    return splits, mats
+
+
+def sort_pairs_host(keys, vals, begin_bit=0, end_bit=64, device=0):
+    lib = load_library()
+    keys = np.ascontiguousarray(keys, np.uint64)
+    vals = np.ascontiguousarray(vals, np.uint32)
+    ko, vo = np.empty_like(keys), np.empty_like(vals)
+    st = lib.ss_sort_pairs_host(C.c_int(device), _p(keys), _p(vals), _p(ko), _p(vo), C.c_uint64(len(keys)),
+                                C.c_int(begin_bit), C.c_int(end_bit))
+    if st != SS_OK:
+        raise SceneSubmitError(st, lib.ss_last_error(None).decode())
+    return ko, vo
+
+
+class SceneSubmit:
+    """One libscenesubmit context (one GPU). Mirrors the C ABI one to one."""
+
+    def __init__(self, max_nodes, max_instances, max_submesh_slots, max_views=5, device=0, trig_mode=TRIG_DETERMINISTIC,
+                 frames_in_flight=3, max_draws_per_view=0, max_visible_per_view=0):
+        self.lib = load_library()
+        cfg = Config(C.sizeof(Config), device, max_nodes, max_instances, max_submesh_slots, max_views,
+                     max_draws_per_view, frames_in_flight, max_visible_per_view, trig_mode, 0)
+        h = C.c_void_p()
+        st = self.lib.ss_create(C.byref(cfg), C.byref(h))
+        if st != SS_OK:
+            raise SceneSubmitError(st, self.lib.ss_last_error(None).decode())
+        self.h = h
+        self.n_instances = 0
+        self.n_views = 0
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.lib.ss_destroy(self.h)
+            self.h = None
+
+    __del__ = close
+
+    def _ck(self, st):
+        if st != SS_OK:
+            raise SceneSubmitError(st, self.lib.ss_last_error(self.h).decode())
+
+    # ---- static streams
+    def set_key_layout(self, mesh_bits, submesh_bits, material_bits):
+        self._ck(self.lib.ss_set_key_layout(self.h, C.c_uint32(mesh_bits), C.c_uint32(submesh_bits),
+                                            C.c_uint32(material_bits)))
+
+    def set_submesh_table(self, slots):
+        slots = np.ascontiguousarray(slots, SUBMESH_DTYPE)
+        self._ck(self.lib.ss_set_submesh_table(self.h, _p(slots), C.c_uint32(len(slots))))
+
+    def set_nodes(self, n_nodes, parent=None, level_offsets=None):
+        parent = None if parent is None else np.ascontiguousarray(parent, np.int32)
+        lo = None if level_offsets is None else np.ascontiguousarray(level_offsets, np.uint32)
+        self._ck(self.lib.ss_set_nodes(self.h, C.c_uint32(n_nodes), _p(parent), _p(lo),
+                                       C.c_uint32(0 if lo is None else len(lo) - 1)))
+
+    def set_instances(self, slot, matword, node=None, node_base=0):
+        slot = np.ascontiguousarray(slot, np.uint32)
+        matword = np.ascontiguousarray(matword, np.uint32)
+        node = None if node is None else np.ascontiguousarray(node, np.uint32)
+        self._ck(self.lib.ss_set_instances(self.h, C.c_uint32(len(slot)), _p(node), C.c_uint32(node_base), _p(slot),
+                                           _p(matword)))
+        self.n_instances = len(slot)
+
+    def set_instance_aabbs(self, aabb, first=0):
+        aabb = np.ascontiguousarray(aabb, np.float32)
+        self._ck(self.lib.ss_set_instance_aabbs(self.h, C.c_uint32(first), C.c_uint32(len(aabb)), _p(aabb)))
+
+    def load_scene(self, sc):
+        """Convenience: every static stream + the TRS of a synth.SceneArrays-like object."""
+        self.set_key_layout(sc.mesh_bits, sc.submesh_bits, sc.material_bits)
+        self.set_submesh_table(sc.slots)
+        self.set_nodes(sc.n_nodes, sc.parent, sc.level_offsets if sc.parent is not None else None)
+        self.set_instances(sc.slot, sc.matword, sc.node, sc.node_base)
+        if sc.inst_aabb is not None:
+            self.set_instance_aabbs(sc.inst_aabb)
+        self.upload_trs(sc.trs)
+        self.flush_uploads()
+
+    # ---- per frame
+    def upload_trs(self, trs, first=0):
+        trs = np.ascontiguousarray(trs, np.float32)
+        self._ck(self.lib.ss_upload_trs(self.h, C.c_uint32(first), C.c_uint32(trs.shape[0]), _p(trs)))
+
+    def upload_trs_ptr(self, host_ptr, count, first=0):
+        """Raw host pointer (e.g. a pinned torch tensor's data_ptr())."""
+        self._ck(self.lib.ss_upload_trs(self.h, C.c_uint32(first), C.c_uint32(count), C.c_void_p(host_ptr)))
+
+    def flush_uploads(self):
+        self._ck(self.lib.ss_flush_uploads(self.h))
+
+    def upload_world_rows(self, rows, first=0):
+        rows = np.ascontiguousarray(rows, np.float32)
+        self._ck(self.lib.ss_upload_world_rows(self.h, C.c_uint32(first), C.c_uint32(rows.shape[0]), _p(rows)))
+
+    def frame(self, views, flags=0):
+        views = np.ascontiguousarray(views, VIEW_DTYPE)
+        slot = C.c_uint32()
+        self._ck(self.lib.ss_frame(self.h, _p(views), C.c_uint32(len(views)), C.c_uint32(flags), C.byref(slot)))
+        self.n_views = len(views)
+        return slot.value
+
+    def frame_sync(self, slot):
+        st = FrameStats()
+        self._ck(self.lib.ss_frame_sync(self.h, C.c_uint32(slot), C.byref(st)))
+        return st
+
+    # ---- outputs
+    def map_outputs(self, slot, view):
+        o = Outputs()
+        self._ck(self.lib.ss_map_outputs(self.h, C.c_uint32(slot), C.c_uint32(view), C.byref(o)))
+        return o
+
+    def download_view(self, slot, view, stats, want_rows=True):
+        m, d = int(stats.visible[view]), int(stats.draws[view])
+        rows = np.empty((m, 12), np.float32) if want_rows else None
+        keys = np.empty(m, np.uint64)
+        idx = np.empty(m, np.uint32)
+        draws = np.empty(d, DRAW_DTYPE)
+        dkeys = np.empty(d, np.uint64)
+        self._ck(self.lib.ss_download_view(self.h, C.c_uint32(slot), C.c_uint32(view), _p(rows), _p(keys), _p(idx),
+                                           _p(draws), _p(dkeys)))
+        return {"rows": rows, "keys": keys, "idx": idx, "draws": draws, "draw_keys": dkeys}
+
+    def download_draws(self, slot, view, stats):
+        d = int(stats.draws[view])
+        draws = np.empty(d, DRAW_DTYPE)
+        dkeys = np.empty(d, np.uint64)
+        self._ck(self.lib.ss_download_view(self.h, C.c_uint32(slot), C.c_uint32(view), None, None, None, _p(draws),
+                                           _p(dkeys)))
+        return draws, dkeys
+
+    def download_world(self, first=0, count=None):
+        count = self.n_instances - first if count is None else count
+        rows = np.empty((count, 12), np.float32)
+        self._ck(self.lib.ss_download_world(self.h, C.c_uint32(first), C.c_uint32(count), _p(rows)))
+        return rows
+
+    def download_masks(self, first=0, count=None):
+        count = self.n_instances - first if count is None else count
+        m = np.empty(count, np.uint8)
+        self._ck(self.lib.ss_download_masks(self.h, C.c_uint32(first), C.c_uint32(count), _p(m)))
+        return m
+
+    @property
+    def stream(self):
+        return self.lib.ss_stream(self.h)
