@@ -1,0 +1,328 @@
+#!/usr/bin/env python
+"""bench.py — the scene-submission hot path on B200 (BASELINE.json: culled+compacted instances/sec and
+ms/frame @16M instances, 5 views).
+
+A step = one frame of the hot path (transform -> cull -> key -> sort -> compact -> emit) over one
+synthetic scene of configs[2] ("synthetic 16M instances, main camera + 4 cascaded shadow-map
+frusta"), 2^24 instances per GPU.  N > 1 GPUs: entity-wise shards, 2^24 instances per rank (weak
+scaling; N = 4 is configs[3]'s 64M), no data-path collective in the sharded phase.
+
+  value      instances/s with every input stream resident in HBM (CUDA events, max over ranks)
+  e2e        the same metric through the C ABI from HOST buffers: pinned TRS upload (36 B/instance) +
+             view matrices in, per-view indirect draws + draw keys + counts out, every step
+  roofline   the dominant kernel (transform+cull+key) against the measured HBM peak
+  cpu_baseline / --impl reference
+             the reference's CPU path (entt-order walk, glm T*R*S, std::map<MeshKey> grouping, plus
+             the same cull) from oracle/_ref on the box's host cores, on a bounded sample
+"""
+import argparse
+import ctypes as C
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+N_PER_GPU = 1 << 24
+N_VIEWS = 5
+WORKLOAD = "synthetic 16M instances, main camera + 4 cascaded shadow-map frusta (configs[2])"
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="native", choices=["native", "reference"])
+    ap.add_argument("--instances", type=int, default=N_PER_GPU, help="instances per GPU (default 2^24)")
+    ap.add_argument("--views", type=int, default=N_VIEWS)
+    ap.add_argument("--trig", default="deterministic", choices=["deterministic", "libm"])
+    ap.add_argument("--cpu-sample", type=int, default=1 << 20, help="instances in the CPU baseline sample")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    return ap.parse_args()
+
+
+def peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks/throttle reasons DURING the timed region (B200_PROFILING.md recipe)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
+         "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.rows, self.proc, self.gpu = [], None, gpu_index
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", "100", "-i", str(self.gpu)], stdout=subprocess.PIPE, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm = [float(r[1]) for r in self.rows if len(r) >= 9 and r[1].replace(".", "").isdigit()]
+        mx = [float(r[2]) for r in self.rows if len(r) >= 9 and r[2].replace(".", "").isdigit()]
+        reasons = set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            if len(r) >= 9:
+                for k, nm in enumerate(names):
+                    if r[5 + k].lower().startswith("active"):
+                        reasons.add(nm)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def algorithmic_bytes(n, n_views, visible, draws, hierarchical):
+    """SURVEY.md §8d B_alg: compulsory I/O of one frame."""
+    per_inst = 36 + 8 + 24 + (4 if hierarchical else 0)
+    b = n * per_inst + n * 48 + n * ((n_views + 7) // 8)
+    b += sum(int(v) * (48 + 8 + 4) for v in visible) + sum(int(d) * 20 for d in draws)
+    return b
+
+
+def instances_kernel_bytes(n, n_views, hierarchical):
+    """Algorithmic bytes of the transform+cull+key launch: the streams it must read and the world rows and
+    masks it must write (the sort-key scratch it also writes is an intermediate and is not counted)."""
+    return n * (36 + 8 + 24 + (4 if hierarchical else 0)) + n * 48 + n * ((n_views + 7) // 8)
+
+
+def cpu_reference(sc, views, sample, threads):
+    """Times oracle/_ref (kind 'reference') or the plain-C oracle (kind 'port') on the first `sample`
+    instances of the same scene with `threads` host threads. Returns (instances/s, kind, seconds, n)."""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import oracle_lib as O
+    n = min(sample, sc.n_instances)
+    if O.ref_available():
+        class Flat(C.Structure):
+            _fields_ = [("n", C.c_uint32), ("trs", C.c_void_p), ("parent", C.c_void_p), ("n_nodes", C.c_uint32),
+                        ("node_base", C.c_uint32), ("slot", C.c_void_p), ("matword", C.c_void_p),
+                        ("inst_aabb", C.c_void_p), ("slot_local", C.c_void_p), ("slot_mesh_handle", C.c_void_p),
+                        ("slot_submesh", C.c_void_p), ("material_handle", C.c_void_p), ("trig_mode", C.c_int)]
+        trs = np.ascontiguousarray(sc.trs[:sc.node_base + n])
+        slot = np.ascontiguousarray(sc.slot[:n])
+        mw = np.ascontiguousarray(sc.matword[:n])
+        box = np.ascontiguousarray(sc.inst_aabb[:n])
+        local = np.ascontiguousarray(sc.slots["local"])
+        mh = np.ascontiguousarray(sc.mesh_handles[sc.slots["mesh_rank"]])
+        sub = np.ascontiguousarray(sc.slots["submesh_index"])
+        mat = np.ascontiguousarray(sc.material_handles)
+        parent = None if sc.parent is None else np.ascontiguousarray(sc.parent[:sc.node_base + n])
+        p = lambda a: None if a is None else a.ctypes.data_as(C.c_void_p)
+        f = Flat(n, p(trs), p(parent), len(trs), sc.node_base, p(slot), p(mw), p(box), p(local), p(mh), p(sub), p(mat), 1)
+        vps = np.ascontiguousarray(views["view_proj"])
+        vfl = np.ascontiguousarray(views["flags"])
+        vis = np.zeros(len(views), np.uint32)
+        drw = np.zeros(len(views), np.uint32)
+        fn = O.ref().ssr_flat_frame
+        best, total, reps = None, 0.0, 0
+        while total < 10.0 and reps < 50:
+            s = fn(C.byref(f), p(vps), p(vfl), C.c_uint32(len(views)), C.c_int(threads), p(vis), p(drw), None, None)
+            best = s if best is None else min(best, s)
+            total += s
+            reps += 1
+        return n / best, "reference", best, n
+    sub_sc = type(sc)(**{**sc.__dict__, "trs": sc.trs[:sc.node_base + n], "slot": sc.slot[:n], "matword": sc.matword[:n],
+                         "inst_aabb": sc.inst_aabb[:n],
+                         "parent": None if sc.parent is None else sc.parent[:sc.node_base + n]})
+    osc = O.OracleScene(sub_sc, 1)
+    best, total, reps = None, 0.0, 0
+    while total < 10.0 and reps < 50:
+        s = osc.frame(views, threads=threads, want_rows=True)["seconds"]
+        best = s if best is None else min(best, s)
+        total += s
+        reps += 1
+    return n / best, "port", best, n
+
+
+def main():
+    a = parse()
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    n = a.instances
+
+    from vulkanengine_b200 import synth
+
+    if a.impl == "reference":
+        # the reference's own CPU implementation of the path on this box's host cores; rank 0 only
+        if rank != 0:
+            return
+        from vulkanengine_b200 import scenesubmit as S  # host-side view matrices only (no GPU work)
+        cores = os.cpu_count() or 1
+        sample = min(a.cpu_sample, n)
+        sc = synth.flat_scene(sample, first=0)
+        views = synth.make_views(S.camera_view_proj, S.cascade_matrices, a.views)
+        for _ in range(max(a.warmup, 1)):
+            cpu_reference(sc, views, min(sample, 1 << 16), cores)
+        t0 = time.perf_counter()
+        vals = []
+        for _ in range(a.steps):
+            ips, kind, secs, ns = cpu_reference(sc, views, sample, cores)
+            vals.append((ips, secs))
+            if time.perf_counter() - t0 > 240:
+                break
+        ips = float(np.median([v[0] for v in vals]))
+        secs = float(np.median([v[1] for v in vals]))
+        line = {"impl": "reference", "metric": "culled+compacted instances/sec", "value": ips, "unit": "instances/s",
+                "n_gpus": a.gpus, "steps": len(vals), "warmup": a.warmup, "ms_per_step": secs * 1e3,
+                "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+                "config": {"workload": WORKLOAD, "views": a.views, "instances_per_gpu": n,
+                           "note": "each step = the reference CPU path on a bounded sample of the workload"},
+                "cpu_baseline": {"value": ips, "unit": "instances/s", "cores": cores, "kind": kind,
+                                 "sample": f"first {ns} instances x {a.views} views of the same scene, best of repeats"},
+                "e2e": {"value": ips, "unit": "instances/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+        print(json.dumps(line), flush=True)
+        return
+
+    import torch
+    import torch.distributed as dist
+    from vulkanengine_b200 import scenesubmit as S
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; libscenesubmit has no CPU path")
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+
+    sc = synth.flat_scene(n, first=rank * n)
+    views = synth.make_views(S.camera_view_proj, S.cascade_matrices, a.views)
+    trig = S.TRIG_DETERMINISTIC if a.trig == "deterministic" else S.TRIG_LIBM
+    ctx = S.SceneSubmit(sc.n_nodes, n, len(sc.slots), max_views=a.views, device=local_rank, trig_mode=trig,
+                        max_draws_per_view=1 << 16)
+    ctx.load_scene(sc)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- device-resident timing -----------------------------------------------------------------
+    for _ in range(max(a.warmup, 3)):
+        st = ctx.frame_sync(ctx.frame(views))
+    launches_per_frame = int(st.kernel_launches)
+    stream = torch.cuda.ExternalStream(ctx.stream, device=local_rank)
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    sampler = ClockSampler(local_rank)
+    barrier()
+    sampler.start()
+    slots = []
+    with torch.cuda.stream(stream):
+        ev0.record(stream)
+        for _ in range(a.steps):
+            slots.append(ctx.frame(views))
+        ev1.record(stream)
+    ev1.synchronize()
+    barrier()
+    clocks = sampler.stop()
+    ms_total = ev0.elapsed_time(ev1)
+    st = ctx.frame_sync(slots[-1])
+    stage = ctx.frame_stage_ms(slots[-1])
+    # per-stage times averaged over the last frames_in_flight frames still in their slots
+    stages = [ctx.frame_stage_ms(s) for s in sorted(set(slots[-3:]))]
+    stage = {k: float(np.mean([x[k] for x in stages])) for k in stage}
+    visible = [int(st.visible[v]) for v in range(a.views)]
+    draws = [int(st.draws[v]) for v in range(a.views)]
+
+    t = torch.tensor([ms_total], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_step = float(t.item()) / a.steps
+    value = world * n / (ms_step * 1e-3)
+
+    # ---- end to end through the C ABI from host buffers --------------------------------------------
+    e2e = None
+    if not a.no_e2e:
+        host_trs = torch.from_numpy(sc.trs).pin_memory()
+        h2d = host_trs.numel() * 4 + views.nbytes
+        d2h = 0
+        for _ in range(2):
+            ctx.upload_trs_ptr(host_trs.data_ptr(), n)
+            s_ = ctx.frame(views)
+            st_ = ctx.frame_sync(s_)
+            for v in range(a.views):
+                ctx.download_draws(s_, v, st_)
+        barrier()
+        t0 = time.perf_counter()
+        e_steps = max(3, min(a.steps, 10))
+        for _ in range(e_steps):
+            ctx.upload_trs_ptr(host_trs.data_ptr(), n)
+            s_ = ctx.frame(views)
+            st_ = ctx.frame_sync(s_)
+            d2h = C.sizeof(S.FrameStats)
+            for v in range(a.views):
+                dr, dk = ctx.download_draws(s_, v, st_)
+                d2h += dr.nbytes + dk.nbytes
+        torch.cuda.synchronize()
+        dt = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device="cuda")
+        if world > 1:
+            dist.all_reduce(dt, op=dist.ReduceOp.MAX)
+        e2e = {"value": world * n * e_steps / float(dt.item()), "unit": "instances/s", "h2d_bytes_per_step": int(h2d),
+               "d2h_bytes_per_step": int(d2h), "ms_per_step": float(dt.item()) / e_steps * 1e3,
+               "note": "pinned TRS (36 B/instance) + views in; counts, indirect draws and draw keys of every view out; "
+                       "compacted instance rows stay in HBM for the GPU consumer"}
+
+    if rank == 0:
+        peak, peak_src = peaks()
+        kb = instances_kernel_bytes(n, a.views, False)
+        k_ms = stage["instances"]
+        achieved = kb / (k_ms * 1e-3) / 1e9
+        balg = algorithmic_bytes(n, a.views, visible, draws, False)
+        line = {"metric": "culled+compacted instances/sec", "value": value, "unit": "instances/s", "n_gpus": world,
+                "steps": a.steps, "warmup": max(a.warmup, 3), "ms_per_step": ms_step, "higher_is_better": True,
+                "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+                "config": {"workload": WORKLOAD, "instances_per_gpu": n, "views": a.views, "keys": 4096,
+                           "trig": a.trig, "seed": int(sc.seed), "l2": "inputs_exceed_l2 (2 GB of streams per frame)",
+                           "sharding": "entity-wise, no collective in the sharded phase" if world > 1 else "none"},
+                "ms_per_frame": ms_step, "visible_per_view": visible, "draws_per_view": draws,
+                "stage_ms": stage, "sort_passes_run": int(st.sort_passes_run),
+                "frame_algorithmic_gb": balg / 1e9, "frame_frac_of_hbm_peak": balg / (ms_step * 1e-3) / 1e9 / peak,
+                "roofline": {"kernel": "k_instances (transform+cull+key)", "bound": "hbm", "achieved": achieved,
+                             "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+                             "peak_source": peak_src, "algorithmic_bytes_per_launch": kb, "kernel_ms": k_ms},
+                "gpu_launches": launches_per_frame * a.steps, "clocks": clocks}
+        if e2e:
+            line["e2e"] = e2e
+        if not a.no_cpu_baseline and world == 1:
+            cores = os.cpu_count() or 1
+            ips, kind, secs, ns = cpu_reference(sc, views, a.cpu_sample, cores)
+            ips1, _, secs1, _ = cpu_reference(sc, views, min(a.cpu_sample, 1 << 18), 1)
+            line["cpu_baseline"] = {"value": ips, "unit": "instances/s", "cores": cores, "kind": kind,
+                                    "sample": f"first {ns} instances x {a.views} views of the same scene "
+                                              f"({secs * 1e3:.1f} ms best of repeats)",
+                                    "single_thread_value": ips1}
+        print(json.dumps(line), flush=True)
+    ctx.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

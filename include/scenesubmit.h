@@ -222,6 +222,12 @@ SS_API ss_status ss_frame(ss_ctx* ctx, const ss_view* views, uint32_t n_views, u
    VC/Renderer/RenderThread.cpp:71-80). */
 SS_API ss_status ss_frame_sync(ss_ctx* ctx, uint32_t slot, ss_frame_stats* stats_out);
 
+/* Device time of the slot's frame by stage, CUDA events on the context stream:
+   {clear + hierarchy levels, transform+cull+key, sort, compact+emit, draws + count read-back}.
+   The counterpart of the reference's per-pass timestamp queries
+   (PV/VulkanRenderCommandBuffer.cpp:150-172). */
+SS_API ss_status ss_frame_stage_ms(ss_ctx* ctx, uint32_t slot, float ms_out[5]);
+
 /* ---- outputs --------------------------------------------------------------------------------- */
 
 /* Replaces `for (auto& [mk, dc] : m_MeshDrawList)` (VC/Scene/SceneRenderer.cpp:1336,1368,1381,1429):

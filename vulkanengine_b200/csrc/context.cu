@@ -22,6 +22,7 @@ struct Slot {
     ViewOut out[SS_MAX_VIEWS];
     uint32_t* counts_dev = nullptr;   // [max_views][2]
     cudaEvent_t done = nullptr, start = nullptr;
+    cudaEvent_t stage[4] = {nullptr, nullptr, nullptr, nullptr};  // after hierarchy, instances, sort, emit
     bool pending = false;
     uint32_t n_views = 0, n_instances = 0;
     int launches = 0;
@@ -174,6 +175,8 @@ SS_API void ss_destroy(ss_ctx* c)
     for (Slot& s : c->slots) {
         if (s.done) cudaEventDestroy(s.done);
         if (s.start) cudaEventDestroy(s.start);
+        for (cudaEvent_t e : s.stage)
+            if (e) cudaEventDestroy(e);
         if (s.h_counts) cudaFreeHost(s.h_counts);
     }
     for (void* p : c->allocs) cudaFree(p);
@@ -271,6 +274,7 @@ SS_API ss_status ss_create(const ss_config* cfg, ss_ctx** out)
         }
         TRY(cudaEventCreate(&s.done));
         TRY(cudaEventCreate(&s.start));
+        for (cudaEvent_t& e : s.stage) TRY(cudaEventCreate(&e));
         TRY(cudaHostAlloc(reinterpret_cast<void**>(&s.h_counts), (V * 2 + 8) * sizeof(uint32_t), cudaHostAllocDefault));
         memset(s.h_counts, 0, (V * 2 + 8) * sizeof(uint32_t));
     }
@@ -489,6 +493,8 @@ SS_API ss_status ss_frame(ss_ctx* c, const ss_view* views, uint32_t n_views, uin
         }
     }
 
+    SS_CUDA(c, cudaEventRecord(s.stage[0], st));
+
     InstanceArgs ia;
     ia.trs = c->d_trs;
     ia.parent = c->has_parent ? c->d_parent : nullptr;
@@ -511,11 +517,13 @@ SS_API ss_status ss_frame(ss_ctx* c, const ss_view* views, uint32_t n_views, uin
         launch_instances(ia, cp, st);
         ++launches;
     }
+    SS_CUDA(c, cudaEventRecord(s.stage[1], st));
 
     // bits the layout can set: material | submesh | mesh | tess | dropped
     const int end_bit = (int)ia.tess_shift + 2;
     SS_CUDA(c, sort_pairs_async(c->d_keys_a, c->d_vals_a, c->d_keys_b, c->d_vals_b, n, 0, end_bit, c->d_sort_scratch,
                                 st, &launches));
+    SS_CUDA(c, cudaEventRecord(s.stage[2], st));
 
     EmitArgs ea;
     memset(&ea, 0, sizeof ea);
@@ -543,6 +551,7 @@ SS_API ss_status ss_frame(ss_ctx* c, const ss_view* views, uint32_t n_views, uin
         launch_emit(ea, st);
         ++launches;
     }
+    SS_CUDA(c, cudaEventRecord(s.stage[3], st));
 
     DrawArgs da;
     memset(&da, 0, sizeof da);
@@ -669,6 +678,19 @@ SS_API ss_status ss_download_world(ss_ctx* c, uint32_t first, uint32_t count, fl
 SS_API ss_status ss_download_masks(ss_ctx* c, uint32_t first, uint32_t count, uint8_t* masks)
 {
     return download_range(c, c ? c->d_mask : nullptr, 1, first, count, masks, "ss_download_masks");
+}
+
+SS_API ss_status ss_frame_stage_ms(ss_ctx* c, uint32_t slot, float ms_out[5])
+{
+    if (!c || !ms_out) return SS_ERR_INVALID;
+    if (slot >= c->slots.size()) return c->fail(SS_ERR_INVALID, "ss_frame_stage_ms: slot %u of %zu", slot, c->slots.size());
+    Slot& s = c->slots[slot];
+    if (s.n_views == 0) return c->fail(SS_ERR_STATE, "ss_frame_stage_ms: slot %u has no frame", slot);
+    SS_CUDA(c, cudaSetDevice(c->device));
+    SS_CUDA(c, cudaEventSynchronize(s.done));
+    cudaEvent_t ev[6] = {s.start, s.stage[0], s.stage[1], s.stage[2], s.stage[3], s.done};
+    for (int i = 0; i < 5; ++i) SS_CUDA(c, cudaEventElapsedTime(&ms_out[i], ev[i], ev[i + 1]));
+    return SS_OK;
 }
 
 SS_API void* ss_stream(ss_ctx* c) { return c ? c->stream : nullptr; }

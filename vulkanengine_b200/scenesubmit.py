@@ -21,7 +21,7 @@ SLOT_NULL = 0xFFFFFFFF
 # every symbol include/scenesubmit.h declares (tests check the library exports exactly these)
 EXPORTS = ["ss_create", "ss_destroy", "ss_last_error", "ss_version", "ss_set_key_layout", "ss_set_submesh_table",
            "ss_set_nodes", "ss_set_instances", "ss_set_instance_aabbs", "ss_upload_trs", "ss_flush_uploads",
-           "ss_upload_world_rows", "ss_frame", "ss_frame_sync", "ss_map_outputs", "ss_download_view",
+           "ss_upload_world_rows", "ss_frame", "ss_frame_sync", "ss_frame_stage_ms", "ss_map_outputs", "ss_download_view",
            "ss_download_world", "ss_download_masks", "ss_stream", "ss_sort_scratch_bytes", "ss_sort_pairs",
            "ss_sort_pairs_host", "ss_camera_view_proj", "ss_cascade_matrices"]
 
@@ -206,6 +206,11 @@ class SceneSubmit:
         st = FrameStats()
         self._ck(self.lib.ss_frame_sync(self.h, C.c_uint32(slot), C.byref(st)))
         return st
+
+    def frame_stage_ms(self, slot):
+        ms = (C.c_float * 5)()
+        self._ck(self.lib.ss_frame_stage_ms(self.h, C.c_uint32(slot), ms))
+        return dict(zip(("hierarchy", "instances", "sort", "emit", "draws"), (float(x) for x in ms)))
 
     # ---- outputs
     def map_outputs(self, slot, view):
