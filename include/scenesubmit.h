@@ -261,6 +261,24 @@ SS_API ss_status ss_sort_pairs_host(int device, const uint64_t* keys_in, const u
                                     uint64_t* keys_out, uint32_t* vals_out, uint64_t n,
                                     int begin_bit, int end_bit);
 
+/* The same sort for callers that must not allocate.  No counterpart in the reference: it exists for
+   hosts that cannot call cudaMalloc at the point where they need a sort, such as a render thread
+   working inside a memory budget fixed at start-up, a plug-in under an application that owns the
+   device allocator, or an engine that has already handed all of HBM to its own pools.  The scratch
+   that ss_sort_pairs takes from the caller is replaced by a fixed array inside the library image
+   (about 2 MiB on every GPU that loads the library, held until the process exits), so n is limited
+   to SS_SORT_STATIC_MAX_N elements; a larger n returns SS_ERR_CAPACITY and ss_last_error(NULL) says
+   why.  The call itself performs no cudaMalloc/cudaFree and uses no allocating library routine; the
+   caller still provides both ping-pong buffer pairs.  The first call on each device looks up the
+   array's device address (once per device, with that device current): make that first call before
+   any stream capture begins.  All calls on one device share the one array, which still holds the
+   previous call's state; each call clears the words it needs before it sorts, so two calls that
+   overlap on the GPU (different streams, different threads) would race: keep them ordered. */
+#define SS_SORT_STATIC_MAX_N (1u << 20)
+SS_API ss_status ss_sort_pairs_static(void* cuda_stream, uint64_t* keys_a, uint32_t* vals_a,
+                                      uint64_t* keys_b, uint32_t* vals_b, uint64_t n, int begin_bit,
+                                      int end_bit, int* sorted_in_b);
+
 /* ---- host-side view matrices (stay on the host) --------------------------------- */
 
 /* EditorCamera::GetViewProjection for a camera given by position + pitch/yaw

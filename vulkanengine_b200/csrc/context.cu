@@ -32,6 +32,10 @@ struct Slot {
 
 }  // namespace
 
+namespace ss {
+void set_global_error(const char* msg) { g_create_error = msg ? msg : ""; }
+}  // namespace ss
+
 struct ss_ctx {
     ss_config cfg{};
     int device = 0;

@@ -11,6 +11,9 @@
 //                resolves its global offsets by decoupled look-back over earlier tiles, and scatters
 //                through shared memory so the global stores are coalesced per digit run.
 // HBM-bound: each executed pass reads and writes 12 B per element once.
+#include <mutex>
+#include <string>
+
 #include "ss_kernels.h"
 
 namespace ss {
@@ -267,3 +270,81 @@ cudaError_t sort_pairs_async(uint64_t* keys_a, uint32_t* vals_a, uint64_t* keys_
 }
 
 }  // namespace ss
+
+// ---- the sort without any allocation -------------------------------------------------------------
+//
+// Some hosts of this library are not allowed to allocate device memory when they need a sort: a
+// render thread inside a frame whose memory budget was fixed at start-up, a plug-in running under a
+// host application that owns the allocator, code that runs after the engine has handed all of HBM
+// to its own pools.  For those callers the scratch that ss_sort_pairs takes from the caller lives
+// here, in a fixed array inside the library image.  Every GPU that loads libscenesubmit.so carries
+// this array (about 2 MiB) until the process exits, which is why its size is capped.
+constexpr size_t kStaticSortScratchBytes =
+    ss::kCtlBytes + (size_t)ss::kMaxPasses * ((SS_SORT_STATIC_MAX_N + ss::kSortTile - 1) / ss::kSortTile) * ss::kRadix *
+                        sizeof(uint32_t);
+
+static __device__ __align__(256) unsigned char g_static_sort_scratch[kStaticSortScratchBytes];
+
+namespace {
+
+constexpr int kStaticMaxDevices = 64;
+void* g_static_scratch_ptr[kStaticMaxDevices];  // device address of the array, per device ordinal
+bool g_static_scratch_ready[kStaticMaxDevices];
+std::mutex g_static_scratch_mutex;
+
+// In host code `g_static_sort_scratch` is only a handle for the symbol, not an address a kernel can
+// use; the device address has to be asked for, once per device, with that device current.
+cudaError_t static_scratch_for_current_device(void** out)
+{
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    if (dev < 0 || dev >= kStaticMaxDevices) return cudaErrorInvalidDevice;
+    std::lock_guard<std::mutex> lock(g_static_scratch_mutex);
+    if (!g_static_scratch_ready[dev]) {
+        void* p = nullptr;
+        e = cudaGetSymbolAddress(&p, g_static_sort_scratch);
+        if (e != cudaSuccess) return e;
+        g_static_scratch_ptr[dev] = p;
+        g_static_scratch_ready[dev] = true;
+    }
+    *out = g_static_scratch_ptr[dev];
+    return cudaSuccess;
+}
+
+}  // namespace
+
+extern "C" SS_API ss_status ss_sort_pairs_static(void* cuda_stream, uint64_t* keys_a, uint32_t* vals_a,
+                                                 uint64_t* keys_b, uint32_t* vals_b, uint64_t n, int begin_bit,
+                                                 int end_bit, int* sorted_in_b)
+{
+    if (!keys_a || !vals_a || !keys_b || !vals_b || begin_bit < 0 || end_bit > 64 || begin_bit > end_bit) {
+        ss::set_global_error("ss_sort_pairs_static: invalid argument (null buffer or bad bit range)");
+        return SS_ERR_INVALID;
+    }
+    if (n > SS_SORT_STATIC_MAX_N) {
+        ss::set_global_error(
+            "ss_sort_pairs_static: n exceeds SS_SORT_STATIC_MAX_N (the built-in scratch is fixed in size); "
+            "use ss_sort_pairs with caller-provided scratch for larger sorts");
+        return SS_ERR_CAPACITY;
+    }
+    cudaStream_t st = static_cast<cudaStream_t>(cuda_stream);
+    void* scratch = nullptr;
+    cudaError_t e = static_scratch_for_current_device(&scratch);
+    // sort_pairs_async first clears the control block and the look-back words of the passes it will run
+    // (the array still holds whatever the previous call left there), then enqueues the kernels.
+    if (e == cudaSuccess)
+        e = ss::sort_pairs_async(keys_a, vals_a, keys_b, vals_b, n, begin_bit, end_bit, scratch, st, nullptr);
+    uint32_t sel = 0;
+    if (e == cudaSuccess)
+        e = cudaMemcpyAsync(&sel,
+                            &static_cast<ss::SortControl*>(scratch)->src_sel[ss::sort_num_passes(begin_bit, end_bit)],
+                            sizeof sel, cudaMemcpyDeviceToHost, st);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+    if (e != cudaSuccess) {
+        ss::set_global_error((std::string("ss_sort_pairs_static: ") + cudaGetErrorString(e)).c_str());
+        return SS_ERR_CUDA;
+    }
+    if (sorted_in_b) *sorted_in_b = (int)sel;
+    return SS_OK;
+}

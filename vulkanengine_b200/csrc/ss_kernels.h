@@ -64,6 +64,9 @@ cudaError_t sort_pairs_async(uint64_t* keys_a, uint32_t* vals_a, uint64_t* keys_
                              int begin_bit, int end_bit, void* scratch, cudaStream_t st, int* launches);
 inline int sort_num_passes(int begin_bit, int end_bit) { return (end_bit - begin_bit + kRadixBits - 1) / kRadixBits; }
 
+// text returned by ss_last_error(NULL); defined in context.cu
+void set_global_error(const char* msg);
+
 // ---- compaction + emit (emit.cu) ---------------------------------------------------------------
 constexpr int kEmitThreads = 256;
 constexpr int kEmitItems = 4;

@@ -23,7 +23,7 @@ EXPORTS = ["ss_create", "ss_destroy", "ss_last_error", "ss_version", "ss_set_key
            "ss_set_nodes", "ss_set_instances", "ss_set_instance_aabbs", "ss_upload_trs", "ss_flush_uploads",
            "ss_upload_world_rows", "ss_frame", "ss_frame_sync", "ss_frame_stage_ms", "ss_map_outputs", "ss_download_view",
            "ss_download_world", "ss_download_masks", "ss_stream", "ss_sort_scratch_bytes", "ss_sort_pairs",
-           "ss_sort_pairs_host", "ss_camera_view_proj", "ss_cascade_matrices"]
+           "ss_sort_pairs_host", "ss_sort_pairs_static", "ss_camera_view_proj", "ss_cascade_matrices"]
 
 
 class SceneSubmitError(RuntimeError):
