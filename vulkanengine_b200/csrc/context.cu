@@ -5,6 +5,7 @@
 #include <algorithm>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <new>
 #include <string>
@@ -157,9 +158,13 @@ void planes_from_view_proj(const float* vp, ViewPlanes& out)
         pl[4][col] = r2;
         pl[5][col] = r3 - r2;
     }
-    for (int p = 0; p < 6; ++p) {
-        out.pl[p] = make_float4(pl[p][0], pl[p][1], pl[p][2], pl[p][3]);
-        out.ab[p] = make_float4(fabsf(pl[p][0]), fabsf(pl[p][1]), fabsf(pl[p][2]), 0.f);
+    for (int p = 0; p < 6; ++p) out.pl[p] = make_float4(pl[p][0], pl[p][1], pl[p][2], pl[p][3]);
+    out.flags = 0;
+    for (int ax = 0; ax < 3; ++ax) {  // exactly opposite normals: the kernel shares the dot products
+        const float* a = pl[2 * ax];
+        const float* b = pl[2 * ax + 1];
+        // compare as values: -0.0f == 0.0f is fine here, the negation of either zero gives an equal product
+        if (b[0] == -a[0] && b[1] == -a[1] && b[2] == -a[2]) out.flags |= 1u << ax;
     }
 }
 
@@ -236,6 +241,10 @@ SS_API ss_status ss_create(const ss_config* cfg, ss_ctx** out)
 
     TRY(cudaSetDevice(c->device));
     TRY(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+    if (const char* g = getenv("SS_L2_FETCH_GRANULARITY")) {  // experiment knob: 32 / 64 / 128 bytes
+        const int v = atoi(g);
+        if (v == 32 || v == 64 || v == 128) cudaDeviceSetLimit(cudaLimitMaxL2FetchGranularity, (size_t)v);
+    }
     TRY(dev_alloc(c, &c->d_trs, NN * 9));
     TRY(dev_alloc(c, &c->d_parent, NN));
     TRY(dev_alloc(c, &c->d_node_world, NN * 3));
@@ -473,7 +482,7 @@ SS_API ss_status ss_frame(ss_ctx* c, const ss_view* views, uint32_t n_views, uin
     cp.n_views = n_views;
     for (uint32_t v = 0; v < n_views; ++v) {
         planes_from_view_proj(views[v].view_proj, cp.v[v]);
-        cp.v[v].skip_near = (views[v].flags & SS_VIEW_SKIP_NEAR) ? 1u : 0u;
+        if (views[v].flags & SS_VIEW_SKIP_NEAR) cp.v[v].flags |= kViewSkipNear;
     }
 
     SS_CUDA(c, cudaEventRecord(s.start, st));
@@ -517,16 +526,23 @@ SS_API ss_status ss_frame(ss_ctx* c, const ss_view* views, uint32_t n_views, uin
     ia.tess_shift = c->mesh_bits + c->submesh_bits + c->material_bits;
     ia.world_given = world_given ? 1 : 0;
     ia.trig_mode = (int)c->cfg.trig_mode;
+    // bits the layout can set: material | submesh | mesh | tess | dropped.  When they fit next to the
+    // instance index in one 64-bit word, key and index are sorted as that single word (8 B/element/pass).
+    const int key_bits = (int)ia.tess_shift + 2;
+    int idx_bits = 1;
+    while (idx_bits < 32 && (1ull << idx_bits) < (uint64_t)n) ++idx_bits;
+    const bool packed = idx_bits + key_bits <= 64;
+    ia.idx_bits = packed ? (uint32_t)idx_bits : 0u;
+    ia.mask_bits = (packed && idx_bits + key_bits + 8 <= 64) ? 8u : 0u;
     if (n) {
         launch_instances(ia, cp, st);
         ++launches;
     }
     SS_CUDA(c, cudaEventRecord(s.stage[1], st));
 
-    // bits the layout can set: material | submesh | mesh | tess | dropped
-    const int end_bit = (int)ia.tess_shift + 2;
-    SS_CUDA(c, sort_pairs_async(c->d_keys_a, c->d_vals_a, c->d_keys_b, c->d_vals_b, n, 0, end_bit, c->d_sort_scratch,
-                                st, &launches));
+    const int begin_bit = packed ? idx_bits + (int)ia.mask_bits : 0, end_bit = begin_bit + key_bits;
+    SS_CUDA(c, sort_async(c->d_keys_a, packed ? nullptr : c->d_vals_a, c->d_keys_b, packed ? nullptr : c->d_vals_b, n,
+                          begin_bit, end_bit, c->d_sort_scratch, st, &launches));
     SS_CUDA(c, cudaEventRecord(s.stage[2], st));
 
     EmitArgs ea;
@@ -536,7 +552,9 @@ SS_API ss_status ss_frame(ss_ctx* c, const ss_view* views, uint32_t n_views, uin
     ea.keys_b = c->d_keys_b;
     ea.vals_b = c->d_vals_b;
     ea.sort_ctl = reinterpret_cast<const SortControl*>(c->d_sort_scratch);
-    ea.sort_passes = (uint32_t)sort_num_passes(0, end_bit);
+    ea.sort_passes = (uint32_t)sort_num_passes(begin_bit, end_bit);
+    ea.idx_bits = ia.idx_bits;
+    ea.mask_bits = ia.mask_bits;
     ea.mask = c->d_mask;
     ea.world = c->d_world;
     ea.n = n;

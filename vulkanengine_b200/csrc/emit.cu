@@ -69,23 +69,37 @@ __global__ void __launch_bounds__(kEmitThreads) k_emit(const __grid_constant__ E
     uint64_t key[kEmitItems];
     uint32_t idx[kEmitItems], m[kEmitItems];
     const uint32_t l0 = tid * kEmitItems;
+    const bool packed = a.idx_bits != 0;
     if (l0 + kEmitItems <= n_valid) {
         const ulonglong2* kp = reinterpret_cast<const ulonglong2*>(keys + tile_base + l0);
         ulonglong2 k01 = __ldg(kp), k23 = __ldg(kp + 1);
         key[0] = k01.x; key[1] = k01.y; key[2] = k23.x; key[3] = k23.y;
-        uint4 iv = __ldg(reinterpret_cast<const uint4*>(vals + tile_base + l0));
-        idx[0] = iv.x; idx[1] = iv.y; idx[2] = iv.z; idx[3] = iv.w;
+        if (!packed) {
+            uint4 iv = __ldg(reinterpret_cast<const uint4*>(vals + tile_base + l0));
+            idx[0] = iv.x; idx[1] = iv.y; idx[2] = iv.z; idx[3] = iv.w;
+        }
     } else {
 #pragma unroll
         for (int j = 0; j < kEmitItems; ++j) {
             const bool ok = l0 + j < n_valid;
             key[j] = ok ? __ldg(keys + tile_base + l0 + j) : ~0ull;
-            idx[j] = ok ? __ldg(vals + tile_base + l0 + j) : 0u;
+            idx[j] = (ok && !packed) ? __ldg(vals + tile_base + l0 + j) : 0u;
+        }
+    }
+    const uint32_t key_shift = a.idx_bits + a.mask_bits;
+    if (packed) {  // [key | mask | instance]
+        const uint64_t imask = (1ull << a.idx_bits) - 1ull;
+#pragma unroll
+        for (int j = 0; j < kEmitItems; ++j) {
+            const bool ok = l0 + j < n_valid;
+            idx[j] = ok ? (uint32_t)(key[j] & imask) : 0u;
+            m[j] = (ok && a.mask_bits) ? (uint32_t)(key[j] >> a.idx_bits) & 0xffu : 0u;
+            key[j] = ok ? key[j] >> key_shift : ~0ull;
         }
     }
 #pragma unroll
     for (int j = 0; j < kEmitItems; ++j) {
-        m[j] = (l0 + j < n_valid) ? (uint32_t)__ldg(a.mask + idx[j]) : 0u;
+        if (!a.mask_bits) m[j] = (l0 + j < n_valid) ? (uint32_t)__ldg(a.mask + idx[j]) : 0u;
         s.key[l0 + j] = key[j];
         s.idx[l0 + j] = idx[j];
     }
@@ -98,6 +112,7 @@ __global__ void __launch_bounds__(kEmitThreads) k_emit(const __grid_constant__ E
         prev = s.last_key[tid - 1];
     } else if (tile > 0) {
         prev = __ldg(keys + tile_base - 1);
+        if (packed) prev >>= key_shift;
     } else {
         prev = 0;
         first_is_head = true;

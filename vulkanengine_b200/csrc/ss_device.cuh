@@ -29,12 +29,16 @@ struct SlotDev {
 };
 static_assert(sizeof(SlotDev) == 96, "SlotDev layout");
 
+// Planes of one view, (a,b,c,d), inside when a x + b y + c z + d >= 0; order L R B T N F, i.e. three
+// axes of two planes each.  flags bit k (k = 0..2): the two planes of axis k have exactly opposite
+// normals (always true for the affine cascade matrices), so their dot products are shared;
+// flags bit 3: skip the near plane (SS_VIEW_SKIP_NEAR).
 struct ViewPlanes {
-    float4 pl[6];   // (a,b,c,d), inside when a x + b y + c z + d >= 0; order L R B T N F
-    float4 ab[6];   // |a|,|b|,|c|, unused
-    uint32_t skip_near;
+    float4 pl[6];
+    uint32_t flags;
     uint32_t pad[3];
 };
+constexpr uint32_t kViewSkipNear = 8u;
 
 struct CullParams {
     ViewPlanes v[SS_MAX_VIEWS];
@@ -131,20 +135,33 @@ __device__ __forceinline__ uint32_t cull_box(const Aff& w, const float* __restri
     float ew1 = (fabsf(w.r1.x) * el0 + fabsf(w.r1.y) * el1) + fabsf(w.r1.z) * el2;
     float ew2 = (fabsf(w.r2.x) * el0 + fabsf(w.r2.y) * el1) + fabsf(w.r2.z) * el2;
 
+    // Spec (oracle): visible iff for every plane  s + r >= 0  with  s = ((a*cx + b*cy) + c*cz) + d  and
+    // r = (|a|*ex + |b|*ey) + |c|*ez.  For finite operands  s + r >= 0  <=>  s >= -r  (rounding is monotone
+    // and a non-zero sum never rounds to zero), which saves the add.  When the second plane of an axis
+    // has exactly the negated normal, its dot product is the exact negation of the first one's
+    // (rounding is symmetric), so  s1 = (-t) + d1  with the shared t, and r is shared as well.
     uint32_t mask = 0;
 #pragma unroll
     for (int v = 0; v < (int)SS_MAX_VIEWS; ++v) {
         if (v < (int)cp.n_views) {
+            const uint32_t fl = cp.v[v].flags;
             bool inside = true;
 #pragma unroll
-            for (int p = 0; p < 6; ++p) {
-                float4 pl = cp.v[v].pl[p];
-                float4 ab = cp.v[v].ab[p];
-                float s = ((pl.x * cw0 + pl.y * cw1) + pl.z * cw2) + pl.w;
-                float r = (ab.x * ew0 + ab.y * ew1) + ab.z * ew2;
-                bool ok = (s + r >= 0.0f);
-                if (p == 4) ok = ok || (cp.v[v].skip_near != 0);
-                inside = inside && ok;
+            for (int ax = 0; ax < 3; ++ax) {
+                const float4 p0 = cp.v[v].pl[2 * ax], p1 = cp.v[v].pl[2 * ax + 1];
+                const bool skip0 = (ax == 2) && (fl & kViewSkipNear);
+                const float t0 = (p0.x * cw0 + p0.y * cw1) + p0.z * cw2;
+                const float r0 = (fabsf(p0.x) * ew0 + fabsf(p0.y) * ew1) + fabsf(p0.z) * ew2;
+                const bool ok0 = skip0 || (t0 + p0.w >= -r0);
+                bool ok1;
+                if (fl & (1u << ax)) {
+                    ok1 = (p1.w - t0 >= -r0);
+                } else {
+                    const float t1 = (p1.x * cw0 + p1.y * cw1) + p1.z * cw2;
+                    const float r1 = (fabsf(p1.x) * ew0 + fabsf(p1.y) * ew1) + fabsf(p1.z) * ew2;
+                    ok1 = (t1 + p1.w >= -r1);
+                }
+                inside = inside && ok0 && ok1;
             }
             if (inside) mask |= (1u << v);
         }

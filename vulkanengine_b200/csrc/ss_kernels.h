@@ -33,14 +33,16 @@ struct InstanceArgs {
     uint32_t* vals;            // iota payload for the sort
     uint32_t n;
     uint32_t tess_shift;       // mb + sb + hb
+    uint32_t idx_bits;         // > 0: write [key | mask | i] into keys (packed sort), vals unused
+    uint32_t mask_bits;        // 8 when the visibility byte rides in the packed word, else 0
     int world_given;           // SS_FRAME_WORLD_ROWS_GIVEN
     int trig_mode;
 };
 void launch_instances(const InstanceArgs& a, const CullParams& cp, cudaStream_t st);
 
 // ---- onesweep radix sort (radix_sort.cu) -------------------------------------------------------
-constexpr int kRadixBits = 8;
-constexpr int kRadix = 1 << kRadixBits;
+constexpr int kMaxRadixBits = 9;
+constexpr int kMaxRadix = 1 << kMaxRadixBits;
 constexpr int kMaxPasses = 8;
 constexpr int kSortThreads = 256;
 constexpr int kSortItems = 16;
@@ -48,7 +50,7 @@ constexpr int kSortTile = kSortThreads * kSortItems;
 
 // Device-resident control block of one sort (lives at the head of the scratch buffer).
 struct SortControl {
-    uint32_t hist[kMaxPasses][kRadix];     // global digit histograms, then exclusive bin offsets
+    uint32_t hist[kMaxPasses][kMaxRadix];  // global digit histograms, then exclusive bin offsets
     uint32_t ticket[kMaxPasses];           // dynamic tile ids
     uint32_t skip[kMaxPasses];             // 1 = digit constant over all keys: pass moves nothing
     uint32_t src_sel[kMaxPasses + 1];      // buffer (0 = a, 1 = b) holding the input of pass p; [n_passes] = result
@@ -56,13 +58,22 @@ struct SortControl {
     uint32_t pad[7];
 };
 
+// digit positions of a sort over bits [begin_bit, end_bit)
+struct SortPlan {
+    int n_passes;
+    int shift[kMaxPasses];
+    int bits[kMaxPasses];
+};
+SortPlan sort_plan(int begin_bit, int end_bit);
+inline int sort_num_passes(int begin_bit, int end_bit) { return sort_plan(begin_bit, end_bit).n_passes; }
+
 size_t sort_scratch_bytes(uint64_t n);
-// zeroes the control block + look-back state; call before sort_pairs each time (stream-ordered)
-cudaError_t sort_reset(void* scratch, uint64_t n, cudaStream_t st);
-// enqueues histogram + scan + passes. Result location: control->src_sel[n_passes] (device).
+// Enqueues clear + histogram + scan + passes.  vals_a == nullptr: keys only.
+// Result location: control->src_sel[n_passes] (device).
+cudaError_t sort_async(uint64_t* keys_a, uint32_t* vals_a, uint64_t* keys_b, uint32_t* vals_b, uint64_t n,
+                       int begin_bit, int end_bit, void* scratch, cudaStream_t st, int* launches);
 cudaError_t sort_pairs_async(uint64_t* keys_a, uint32_t* vals_a, uint64_t* keys_b, uint32_t* vals_b, uint64_t n,
                              int begin_bit, int end_bit, void* scratch, cudaStream_t st, int* launches);
-inline int sort_num_passes(int begin_bit, int end_bit) { return (end_bit - begin_bit + kRadixBits - 1) / kRadixBits; }
 
 // text returned by ss_last_error(NULL); defined in context.cu
 void set_global_error(const char* msg);
@@ -87,6 +98,8 @@ struct EmitArgs {
     const uint64_t* keys_b; const uint32_t* vals_b;
     const SortControl* sort_ctl;   // result selector
     uint32_t sort_passes;
+    uint32_t idx_bits;             // > 0: sorted words are [key | mask | instance]
+    uint32_t mask_bits;            // 8: visibility byte sits above the instance index; 0: gather it from mask[]
     const uint8_t* mask;
     const float4* world;
     uint32_t n;

@@ -184,8 +184,13 @@ __global__ void __launch_bounds__(kTile) k_instances(InstanceArgs a, const __gri
     }
     if (valid) {
         a.mask[i] = (uint8_t)mask;
-        a.keys[i] = key;
-        a.vals[i] = i;
+        if (a.idx_bits) {  // key and instance index travel through the sort as one 64-bit word
+            // [key | visibility byte (when it fits) | instance]: emit then needs no gather of the mask
+            a.keys[i] = (key << (a.idx_bits + a.mask_bits)) | ((uint64_t)(a.mask_bits ? mask : 0u) << a.idx_bits) | i;
+        } else {
+            a.keys[i] = key;
+            a.vals[i] = i;
+        }
     }
 }
 
