@@ -132,7 +132,8 @@ typedef struct ss_outputs {
     const ss_draw_cmd* draws;     /* [draws]        one per run of equal keys, in MeshKey order */
     const uint64_t* draw_keys;    /* [draws]        key of each draw (to bind mesh + material) */
     const uint32_t* counts;       /* device: {visible, draws} of this view */
-    const float* world_rows;      /* [instances][12] every instance's world rows (not per view) */
+    const float* world_rows;      /* [instances][16] every instance's world matrix, row-major 4x4 (rows 0..2 =
+                                     TransformData, row 3 = 0,0,0,1), 64 B stride; not per view */
     const uint8_t* masks;         /* [instances]    bit v = visible in view v */
     uint32_t visible;             /* host copies, valid after ss_frame_sync */
     uint32_t n_draws;

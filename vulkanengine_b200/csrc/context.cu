@@ -253,7 +253,7 @@ SS_API ss_status ss_create(const ss_config* cfg, ss_ctx** out)
     TRY(dev_alloc(c, &c->d_matword, N));
     TRY(dev_alloc(c, &c->d_inst_aabb, N * 6));
     TRY(dev_alloc(c, &c->d_slots, (size_t)cfg->max_submesh_slots));
-    TRY(dev_alloc(c, &c->d_world, N * 3));
+    TRY(dev_alloc(c, &c->d_world, N * kWorldStride));
     TRY(dev_alloc(c, &c->d_mask, N));
     TRY(dev_alloc(c, &c->d_keys_a, N));
     TRY(dev_alloc(c, &c->d_keys_b, N));
@@ -450,8 +450,8 @@ SS_API ss_status ss_upload_world_rows(ss_ctx* c, uint32_t first, uint32_t count,
                        c->n_instances);
     SS_CUDA(c, cudaSetDevice(c->device));
     if (count)
-        SS_CUDA(c, cudaMemcpyAsync(reinterpret_cast<float*>(c->d_world) + (size_t)first * 12, rows12,
-                                   (size_t)count * 48, cudaMemcpyHostToDevice, c->stream));
+        SS_CUDA(c, cudaMemcpy2DAsync(c->d_world + (size_t)first * kWorldStride, kWorldStride * 16, rows12, 48, 48, count,
+                                     cudaMemcpyHostToDevice, c->stream));
     c->world_uploaded = true;
     return SS_OK;
 }
@@ -695,7 +695,16 @@ static ss_status download_range(ss_ctx* c, const void* src, size_t elem, uint32_
 
 SS_API ss_status ss_download_world(ss_ctx* c, uint32_t first, uint32_t count, float* rows12)
 {
-    return download_range(c, c ? c->d_world : nullptr, 48, first, count, rows12, "ss_download_world");
+    if (!c) return SS_ERR_INVALID;
+    if (!rows12 || (uint64_t)first + count > c->n_instances)
+        return c->fail(SS_ERR_INVALID, "ss_download_world: range [%u, +%u) exceeds %u instances", first, count,
+                       c->n_instances);
+    SS_CUDA(c, cudaSetDevice(c->device));
+    if (count)  // device rows sit at a 64 B stride; the host gets them packed as TransformData
+        SS_CUDA(c, cudaMemcpy2DAsync(rows12, 48, c->d_world + (size_t)first * kWorldStride, kWorldStride * 16, 48, count,
+                                     cudaMemcpyDeviceToHost, c->stream));
+    SS_CUDA(c, cudaStreamSynchronize(c->stream));
+    return SS_OK;
 }
 SS_API ss_status ss_download_masks(ss_ctx* c, uint32_t first, uint32_t count, uint8_t* masks)
 {

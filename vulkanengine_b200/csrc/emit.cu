@@ -279,7 +279,7 @@ __global__ void __launch_bounds__(kEmitThreads) k_emit(const __grid_constant__ E
                 const uint32_t j = j0 + u * kEmitThreads;
                 if (j < total4) {
                     const uint32_t e = j / 3u, part = j - e * 3u;
-                    r[u] = __ldg(a.world + (size_t)s.idx[s.list[v][e]] * 3u + part);
+                    r[u] = __ldg(a.world + (size_t)s.idx[s.list[v][e]] * kWorldStride + part);
                 }
             }
 #pragma unroll

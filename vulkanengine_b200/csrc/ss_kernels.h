@@ -7,6 +7,11 @@
 
 namespace ss {
 
+// World rows live at a 64-byte stride (rows 0..2 = TransformData, row 3 = 0,0,0,1): every row is one
+// aligned 64 B DRAM burst, which halves the bytes the sorted-order gather in k_emit pulls from HBM
+// (a 48 B stride makes half the rows straddle two bursts).
+constexpr int kWorldStride = 4;  // float4 per instance
+
 // ---- transform / cull / key (transform_cull.cu) ----------------------------------------------
 struct NodeLevelArgs {
     const float* trs;          // [n_nodes][9]
@@ -27,7 +32,7 @@ struct InstanceArgs {
     const uint32_t* matword;
     const float* inst_aabb;    // [n][6] or nullptr
     const SlotDev* slots;
-    float4* world;             // [n][3] in/out
+    float4* world;             // [n][kWorldStride] in/out
     uint8_t* mask;
     uint64_t* keys;
     uint32_t* vals;            // iota payload for the sort

@@ -13,15 +13,36 @@ namespace {
 
 constexpr int kTile = 256;  // instances per CTA == threads per CTA
 
+// Shared-memory slot of float4 number k of the tile's world rows (k = instance*4 + row).  A thread
+// writes its own 4 rows (stride 4 float4 = 16 words: every fourth lane would hit the same banks), so the
+// row index is XOR-ed with bits of the instance number; 8 consecutive lanes then cover all 32 banks on
+// both the per-thread writes and the linear copy-out.
+__device__ __forceinline__ int row_slot(int k) { return (k & ~3) | ((k ^ (k >> 3)) & 3); }
+
 // Cooperative copy of `count` floats from global to 16B-aligned shared memory.
-__device__ __forceinline__ void tile_load_f32(float* __restrict__ dst, const float* __restrict__ src, int count)
+// R = floats per record: the trip count of the vector loop is a compile-time constant, so the loads of a
+// tile are all in flight before the first shared-memory store.
+template <int R>
+__device__ __forceinline__ void tile_load_f32(float* __restrict__ dst, const float* __restrict__ src, int n_tile)
 {
     const int tid = threadIdx.x;
+    const int count = n_tile * R;
     if ((reinterpret_cast<uintptr_t>(src) & 15u) == 0) {
         const int n4 = count >> 2;
         const float4* s4 = reinterpret_cast<const float4*>(src);
         float4* d4 = reinterpret_cast<float4*>(dst);
-        for (int i = tid; i < n4; i += kTile) d4[i] = ld_nc_f4(s4 + i);
+        constexpr int kTrips = (R * kTile / 4 + kTile - 1) / kTile;
+        float4 v[kTrips];
+#pragma unroll
+        for (int u = 0; u < kTrips; ++u) {
+            const int i = tid + u * kTile;
+            if (i < n4) v[u] = ld_nc_f4(s4 + i);
+        }
+#pragma unroll
+        for (int u = 0; u < kTrips; ++u) {
+            const int i = tid + u * kTile;
+            if (i < n4) d4[i] = v[u];
+        }
         for (int i = (n4 << 2) + tid; i < count; i += kTile) dst[i] = __ldg(src + i);
     } else {
         for (int i = tid; i < count; i += kTile) dst[i] = __ldg(src + i);
@@ -76,7 +97,7 @@ __global__ void __launch_bounds__(kTile) k_node_level(NodeLevelArgs a)
     const uint32_t base = a.lo + blockIdx.x * kTile;
     const int n_tile = min((uint32_t)kTile, a.hi - base);
     const int tid = threadIdx.x;
-    tile_load_f32(s_trs, a.trs + (size_t)base * 9, n_tile * 9);
+    tile_load_f32<9>(s_trs, a.trs + (size_t)base * 9, n_tile);
     __syncthreads();
     const bool valid = tid < n_tile;
     int p = -1;
@@ -100,7 +121,7 @@ __global__ void __launch_bounds__(kTile) k_instances(InstanceArgs a, const __gri
 {
     __shared__ __align__(16) float s_trs[kTile * 9];
     __shared__ __align__(16) float s_box[kTile * 6];
-    __shared__ __align__(16) float4 s_rows[kTile * 3];
+    __shared__ __align__(16) float4 s_rows[kTile * kWorldStride];
 
     const uint32_t base = blockIdx.x * kTile;
     const int n_tile = min((uint32_t)kTile, a.n - base);
@@ -109,11 +130,11 @@ __global__ void __launch_bounds__(kTile) k_instances(InstanceArgs a, const __gri
     const uint32_t i = base + tid;
     const bool from_trs = !a.world_given && a.node == nullptr;
 
-    if (from_trs) tile_load_f32(s_trs, a.trs + ((size_t)a.node_base + base) * 9, n_tile * 9);
-    if (a.inst_aabb) tile_load_f32(s_box, a.inst_aabb + (size_t)base * 6, n_tile * 6);
+    if (from_trs) tile_load_f32<9>(s_trs, a.trs + ((size_t)a.node_base + base) * 9, n_tile);
+    if (a.inst_aabb) tile_load_f32<6>(s_box, a.inst_aabb + (size_t)base * 6, n_tile);
     if (a.world_given) {
-        const float4* src = a.world + (size_t)base * 3;
-        for (int k = tid; k < n_tile * 3; k += kTile) s_rows[k] = ld_nc_f4(src + k);
+        const float4* src = a.world + (size_t)base * kWorldStride;
+        for (int k = tid; k < n_tile * kWorldStride; k += kTile) s_rows[row_slot(k)] = ld_nc_f4(src + k);
     }
     uint32_t slot = SS_SLOT_NULL, mw = 0;
     if (valid) {
@@ -135,9 +156,9 @@ __global__ void __launch_bounds__(kTile) k_instances(InstanceArgs a, const __gri
     if (live) {
         const SlotDev* sd = a.slots + slot;
         if (a.world_given) {
-            w.r0 = s_rows[tid * 3 + 0];
-            w.r1 = s_rows[tid * 3 + 1];
-            w.r2 = s_rows[tid * 3 + 2];
+            w.r0 = s_rows[row_slot(tid * kWorldStride + 0)];
+            w.r1 = s_rows[row_slot(tid * kWorldStride + 1)];
+            w.r2 = s_rows[row_slot(tid * kWorldStride + 2)];
         } else {
             Aff m;
             if (from_trs) {
@@ -174,13 +195,18 @@ __global__ void __launch_bounds__(kTile) k_instances(InstanceArgs a, const __gri
     if (!a.world_given) {
         __syncthreads();  // s_rows is free (world_given reads finished above / never written)
         if (valid) {
-            s_rows[tid * 3 + 0] = w.r0;
-            s_rows[tid * 3 + 1] = w.r1;
-            s_rows[tid * 3 + 2] = w.r2;
+            s_rows[row_slot(tid * kWorldStride + 0)] = w.r0;
+            s_rows[row_slot(tid * kWorldStride + 1)] = w.r1;
+            s_rows[row_slot(tid * kWorldStride + 2)] = w.r2;
+            s_rows[row_slot(tid * kWorldStride + 3)] = make_float4(0.f, 0.f, 0.f, 1.f);
         }
         __syncthreads();
-        float4* dst = a.world + (size_t)base * 3;
-        for (int k = tid; k < n_tile * 3; k += kTile) dst[k] = s_rows[k];
+        float4* dst = a.world + (size_t)base * kWorldStride;
+#pragma unroll
+        for (int u = 0; u < kWorldStride; ++u) {
+            const int k = tid + u * kTile;
+            if (k < n_tile * kWorldStride) dst[k] = s_rows[row_slot(k)];
+        }
     }
     if (valid) {
         a.mask[i] = (uint8_t)mask;
