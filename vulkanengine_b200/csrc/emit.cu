@@ -179,18 +179,7 @@ __global__ void __launch_bounds__(kEmitThreads) k_emit(const __grid_constant__ E
             lb[tid] = kFlagPrefix | mine;
         } else {
             lb[tid] = kFlagAgg | mine;
-            int64_t t = (int64_t)tile - 1;
-            while (true) {
-                const uint32_t v = *(volatile uint32_t*)(a.lookback + (size_t)t * kEmitWords + tid);
-                if (v & kFlagPrefix) {
-                    excl += v & kValueMask;
-                    break;
-                }
-                if (v & kFlagAgg) {
-                    excl += v & kValueMask;
-                    --t;
-                }
-            }
+            excl = lookback_exclusive(a.lookback + tid, (size_t)kEmitWords, (int64_t)tile);
             lb[tid] = kFlagPrefix | (excl + mine);
         }
         s.base[tid] = excl;

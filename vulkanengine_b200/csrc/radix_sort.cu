@@ -199,19 +199,7 @@ k_onesweep(uint64_t* keys_a, uint32_t* vals_a, uint64_t* keys_b, uint32_t* vals_
         for (int k = 0; k < kMaxRadix / kSortThreads; ++k) {
             const int d = d0 + k;
             if (k < per_thread && d < bins) {
-                uint32_t e = 0;
-                int64_t t = (int64_t)tile - 1;
-                while (true) {
-                    const uint32_t v = *(volatile uint32_t*)(lookback + (size_t)t * bins + d);
-                    if (v & kFlagPrefix) {
-                        e += v & kValueMask;
-                        break;
-                    }
-                    if (v & kFlagAgg) {
-                        e += v & kValueMask;
-                        --t;
-                    }
-                }
+                const uint32_t e = lookback_exclusive(lookback + d, (size_t)bins, (int64_t)tile);
                 excl[k] = e;
                 *(volatile uint32_t*)(lookback + (size_t)tile * bins + d) = kFlagPrefix | (e + cnt[k]);
             }

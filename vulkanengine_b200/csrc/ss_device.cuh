@@ -169,4 +169,46 @@ __device__ __forceinline__ uint32_t cull_box(const Aff& w, const float* __restri
     return mask;
 }
 
+// ---- decoupled look-back (single-pass prefix over tiles) -------------------------------------------
+// One 32-bit status word per (tile, counter): value | flag.  A tile first publishes its own count
+// (kLbAgg), then walks back over earlier tiles summing their counts until it meets one whose inclusive
+// prefix is known (kLbPrefix), then publishes its own inclusive prefix.  Tile ids are handed out by an
+// atomic ticket at CTA start, so every tile waited on is already running: the walk cannot deadlock.
+constexpr uint32_t kLbAgg = 1u << 30;
+constexpr uint32_t kLbPrefix = 1u << 31;
+constexpr uint32_t kLbValue = kLbAgg - 1;
+
+// Sum of the counters `words[t * stride]` of tiles t < tile.  The first wave of CTAs starts together,
+// none has a prefix yet, and tile k must add up k aggregates: the loads are issued kLbBatch at a time so
+// the walk costs one L2 round trip per batch instead of one per tile.
+constexpr int kLbBatch = 8;
+__device__ __forceinline__ uint32_t lookback_exclusive(const uint32_t* words, size_t stride, int64_t tile)
+{
+    uint32_t sum = 0;
+    int64_t t = tile - 1;
+    while (t >= 0) {
+        uint32_t v[kLbBatch];
+#pragma unroll
+        for (int u = 0; u < kLbBatch; ++u)
+            v[u] = (t - u >= 0) ? *(const volatile uint32_t*)(words + (size_t)(t - u) * stride) : kLbPrefix;
+        int used = 0;
+        bool done = false;
+#pragma unroll
+        for (int u = 0; u < kLbBatch; ++u) {
+            if (!done && used == u) {
+                if (v[u] & kLbPrefix) {
+                    sum += v[u] & kLbValue;
+                    done = true;
+                } else if (v[u] & kLbAgg) {
+                    sum += v[u] & kLbValue;
+                    used = u + 1;
+                }
+            }
+        }
+        if (done) break;
+        t -= used;  // used < kLbBatch: the next tile back has not published yet, poll it again
+    }
+    return sum;
+}
+
 }  // namespace ss
