@@ -257,6 +257,47 @@ def main():
     ms_step = float(t.item()) / a.steps
     value = world * n / (ms_step * 1e-3)
 
+    # ---- merged draw list (only where one list is needed): all-gather over NCCL, timed separately ------
+    merge = None
+    if world > 1:
+        from vulkanengine_b200 import sharding
+
+        class _Dev:
+            def __init__(self, ptr, n, typestr):
+                self.__cuda_array_interface__ = {"shape": (n,), "typestr": typestr, "data": (ptr, False), "version": 2}
+
+        def dev_tensor(ptr, n, typestr):
+            if n == 0:
+                return torch.empty(0, dtype=torch.int64 if typestr == "<i8" else torch.int32, device="cuda")
+            return torch.as_tensor(_Dev(ptr, n, typestr), device="cuda")
+
+        def merge_all_views(slot_, st_):
+            total_bytes = 0
+            for v in range(a.views):
+                o = ctx.map_outputs(slot_, v)
+                keys = dev_tensor(o.keys, o.visible, "<i8")
+                idx = dev_tensor(o.instance_idx, o.visible, "<i4")
+                dk = dev_tensor(o.draw_keys, o.n_draws, "<i8")
+                draws = dev_tensor(o.draws, o.n_draws * 5, "<i4").view(-1, 5)
+                mk, mi, mdk, mdc, mfirst = sharding.merge_view_list(keys, idx, dk, draws[:, 1].contiguous(), rank * n)
+                total_bytes += mk.numel() * 16
+            return total_bytes
+
+        s_ = ctx.frame(views)
+        st_ = ctx.frame_sync(s_)
+        merge_all_views(s_, st_)  # warm-up (NCCL channels, allocator)
+        barrier()
+        m0, m1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        m0.record()
+        merged_bytes = merge_all_views(s_, st_)
+        m1.record()
+        m1.synchronize()
+        mt = torch.tensor([m0.elapsed_time(m1)], dtype=torch.float64, device="cuda")
+        dist.all_reduce(mt, op=dist.ReduceOp.MAX)
+        merge = {"ms": float(mt.item()), "merged_list_bytes": int(merged_bytes),
+                 "note": "all_gather of per-view draw keys/counts and (key, instance) lists + run placement; "
+                         "not part of the sharded phase timed in value"}
+
     # ---- end to end through the C ABI from host buffers --------------------------------------------
     e2e = None
     if not a.no_e2e:
@@ -310,6 +351,8 @@ def main():
                 "gpu_launches": launches_per_frame * a.steps, "clocks": clocks}
         if e2e:
             line["e2e"] = e2e
+        if merge:
+            line["merge"] = merge
         if not a.no_cpu_baseline and world == 1:
             cores = os.cpu_count() or 1
             ips, kind, secs, ns = cpu_reference(sc, views, a.cpu_sample, cores)

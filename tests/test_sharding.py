@@ -1,0 +1,78 @@
+"""Multi-GPU host logic on CPU: two gloo ranks shard a scene entity-wise, each builds its per-view lists
+(from the oracle here: there is no GPU), the merge step must reproduce the single-process lists."""
+import os
+import socket
+import sys
+
+import numpy as np
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+import oracle_lib as O
+from vulkanengine_b200 import sharding, synth
+
+N_TOTAL = 6000
+N_VIEWS = 3
+
+
+def _views():
+    return synth.make_views(lambda *a: O.camera_view_proj(*a), lambda *a: O.cascade_matrices(*a), N_VIEWS)
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def _worker(rank, world, port, out_dir):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    lo, hi = sharding.shard_range(N_TOTAL, rank, world)
+    sc = synth.flat_scene(hi - lo, first=lo, n_keys=200)
+    res = O.OracleScene(sc, 0).frame(_views())
+    for v in range(N_VIEWS):
+        r = res["views"][v]
+        keys = torch.from_numpy(r["keys"].view(np.int64).copy())
+        idx = torch.from_numpy(r["idx"].astype(np.int64))
+        dk = torch.from_numpy(r["draw_keys"].view(np.int64).copy())
+        dc = torch.from_numpy(r["draws"]["instance_count"].astype(np.int64))
+        mk, mi, mdk, mdc, mfirst = sharding.merge_view_list(keys, idx, dk, dc, lo)
+        np.savez(os.path.join(out_dir, f"r{rank}_v{v}.npz"), k=mk.numpy(), i=mi.numpy(), dk=mdk.numpy(),
+                 dc=mdc.numpy(), first=mfirst.numpy())
+    dist.destroy_process_group()
+
+
+def test_shard_ranges_cover_everything():
+    for world in (1, 2, 3, 8):
+        r = [sharding.shard_range(1000003, k, world) for k in range(world)]
+        assert r[0][0] == 0 and r[-1][1] == 1000003
+        assert all(r[k][1] == r[k + 1][0] for k in range(world - 1))
+
+
+def test_counter_rng_shards_are_slices_of_one_scene():
+    whole = synth.flat_scene(N_TOTAL, n_keys=200)
+    lo, hi = sharding.shard_range(N_TOTAL, 1, 2)
+    part = synth.flat_scene(hi - lo, first=lo, n_keys=200)
+    assert np.array_equal(part.trs, whole.trs[lo:hi]) and np.array_equal(part.slot, whole.slot[lo:hi])
+    assert np.array_equal(part.matword, whole.matword[lo:hi]) and np.array_equal(part.inst_aabb, whole.inst_aabb[lo:hi])
+
+
+def test_two_rank_merge_equals_single_process(tmp_path):
+    world = 2
+    port = _free_port()
+    mp.spawn(_worker, args=(world, port, str(tmp_path)), nprocs=world, join=True)
+    whole = O.OracleScene(synth.flat_scene(N_TOTAL, n_keys=200), 0).frame(_views())
+    for v in range(N_VIEWS):
+        ref = whole["views"][v]
+        for rank in range(world):
+            g = np.load(os.path.join(str(tmp_path), f"r{rank}_v{v}.npz"))
+            assert np.array_equal(g["k"].view(np.uint64), ref["keys"])
+            assert np.array_equal(g["i"], ref["idx"].astype(np.int64))
+            assert np.array_equal(g["dk"].view(np.uint64), ref["draw_keys"])
+            assert np.array_equal(g["dc"], ref["draws"]["instance_count"].astype(np.int64))
+            assert np.array_equal(g["first"], ref["draws"]["first_instance"].astype(np.int64))
