@@ -15,7 +15,18 @@ CPP      := $(CSRC)/host_views.cpp
 OBJS     := $(patsubst $(CSRC)/%.cu,$(OBJDIR)/%.o,$(CU)) $(patsubst $(CSRC)/%.cpp,$(OBJDIR)/%.o,$(CPP))
 HDRS     := $(wildcard $(CSRC)/*.h $(CSRC)/*.cuh include/*.h)
 
-all: $(LIB)
+HOSTBIN  := vulkanengine_b200/host/host_cli.bin
+HOSTSRC  := vulkanengine_b200/host/Scene.cpp vulkanengine_b200/host/host_cli.cpp
+HOSTHDR  := vulkanengine_b200/host/Scene.h vulkanengine_b200/host/Core.h include/scenesubmit.h
+
+all: $(LIB) $(HOSTBIN)
+
+# C++ host mirror of Scene / SceneRenderer: plain g++, links the C ABI only
+$(HOSTBIN): $(HOSTSRC) $(HOSTHDR) $(LIB)
+	g++ -std=c++17 -O2 -Wall -ffp-contract=off -o $@ $(HOSTSRC) -Lvulkanengine_b200 -lscenesubmit \
+	    -Wl,-rpath,'$$ORIGIN/..'
+
+host: $(HOSTBIN)
 
 $(OBJDIR)/%.o: $(CSRC)/%.cu $(HDRS)
 	@mkdir -p $(OBJDIR)

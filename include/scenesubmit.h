@@ -205,6 +205,15 @@ SS_API ss_status ss_set_instance_aabbs(ss_ctx* ctx, uint32_t first, uint32_t cou
    ss_frame_sync of the next frame. */
 SS_API ss_status ss_upload_trs(ss_ctx* ctx, uint32_t first, uint32_t count, const float* trs9);
 
+/* World rows (TransformData, 48 B each) of EXTERNAL nodes: nodes numbered past the last level given to
+   ss_set_nodes are never composed from TRS.  This is how the ad-hoc submitters that hand the renderer
+   a finished glm::mat4 keep working: SceneRenderer::SubmitMesh / SubmitSelectedMesh
+   (VC/Scene/SceneRenderer.h:32-33) when called outside Scene::OnUpdateGeometry, and SubmitPhysicsMesh
+   (VC/Scene/SceneRenderer.cpp:1211-1245, caller Platform/JoltPhysics/JoltDebugRenderer.cpp:63).
+   Instances name such a node through the explicit node map of ss_set_instances. */
+SS_API ss_status ss_upload_node_world_rows(ss_ctx* ctx, uint32_t first, uint32_t count,
+                                           const float* rows12);
+
 /* Wait until every ss_upload_* issued so far has left host memory. */
 SS_API ss_status ss_flush_uploads(ss_ctx* ctx);
 

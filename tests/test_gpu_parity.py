@@ -279,3 +279,40 @@ def test_full_size_16m_properties_and_mask_parity():
         sl = sc.slots[sc.slot[got["idx"][d["first_instance"]]]]
         assert np.array_equal(d["index_count"], sl["index_count"]) and np.array_equal(d["vertex_offset"], sl["vertex_offset"])
     ctx.close()
+
+
+def test_external_nodes_with_given_world_rows():
+    """Ad-hoc submitters (SubmitPhysicsMesh etc.) hand over a finished matrix: nodes past the last level take
+    their world rows from ss_upload_node_world_rows instead of TRS."""
+    base = synth.with_explicit_nodes(synth.hierarchy_scene(n_roots=4, fan1=4, fan2=8, n_keys=40))
+    n_ext = 16
+    n_nodes = base.n_nodes
+    rng = np.random.default_rng(9)
+    node = base.node.copy()
+    ext_inst = rng.choice(base.n_instances, 40, replace=False)
+    node[ext_inst] = n_nodes + rng.integers(0, n_ext, 40)
+    # oracle side: give the external nodes an ordinary TRS, so their world matrix is well defined
+    trs_ext = synth._trs(77, 90, 0, n_ext, 100.0, (0.5, 2.0))
+    full = synth.SceneArrays(**{**base.__dict__, "trs": np.concatenate([base.trs, trs_ext]),
+                                "parent": np.concatenate([base.parent, np.full(n_ext, -1, np.int32)]), "node": node})
+    views = oracle_views(5)
+    osc = O.OracleScene(full, 0)
+    ref = osc.frame(views)
+    ext_rows = np.stack([O.trs_to_mat4(t, 0).reshape(4, 4).T[:3].reshape(12) for t in trs_ext])
+
+    ctx = S.SceneSubmit(n_nodes + n_ext, base.n_instances, len(base.slots), max_views=5)
+    ctx.set_key_layout(base.mesh_bits, base.submesh_bits, base.material_bits)
+    ctx.set_submesh_table(base.slots)
+    ctx.set_nodes(n_nodes + n_ext, full.parent, base.level_offsets)  # levels end at n_nodes: the rest is external
+    ctx.set_instances(base.slot, base.matword, node, 0)
+    ctx.set_instance_aabbs(base.inst_aabb)
+    ctx.upload_trs(base.trs)
+    ctx.upload_node_world_rows(ext_rows, n_nodes)
+    slot = ctx.frame(views)
+    st = ctx.frame_sync(slot)
+    got = {"stats": st, "world": ctx.download_world(), "masks": ctx.download_masks(),
+           "views": [ctx.download_view(slot, v, st) for v in range(5)]}
+    check_against_oracle(full, views, got, ref)
+    with pytest.raises(S.SceneSubmitError):  # computed nodes cannot be overwritten this way
+        ctx.upload_node_world_rows(ext_rows[:1], 0)
+    ctx.close()

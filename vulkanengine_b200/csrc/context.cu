@@ -337,9 +337,11 @@ SS_API ss_status ss_set_nodes(ss_ctx* c, uint32_t n_nodes, const int32_t* parent
     if (n_nodes == 0 || n_nodes > c->cfg.max_nodes)
         return c->fail(SS_ERR_INVALID, "ss_set_nodes: %u nodes, capacity %u", n_nodes, c->cfg.max_nodes);
     if (parent) {
+        // nodes past the last level are "external": never composed from TRS, their world rows are given
+        // through ss_upload_node_world_rows (ad-hoc submitters such as SubmitPhysicsMesh)
         if (!level_offsets || n_levels == 0 || n_levels > SS_MAX_LEVELS || level_offsets[0] != 0 ||
-            level_offsets[n_levels] != n_nodes)
-            return c->fail(SS_ERR_INVALID, "ss_set_nodes: level_offsets must span [0, n_nodes] in 1..%u levels",
+            level_offsets[n_levels] > n_nodes)
+            return c->fail(SS_ERR_INVALID, "ss_set_nodes: level_offsets must start at 0 and end <= n_nodes in 1..%u levels",
                            SS_MAX_LEVELS);
         for (uint32_t l = 0; l < n_levels; ++l) {
             if (level_offsets[l] > level_offsets[l + 1])
@@ -430,6 +432,20 @@ SS_API ss_status ss_upload_trs(ss_ctx* c, uint32_t first, uint32_t count, const 
     SS_CUDA(c, cudaSetDevice(c->device));
     if (count)
         SS_CUDA(c, cudaMemcpyAsync(c->d_trs + (size_t)first * 9, trs9, (size_t)count * 36, cudaMemcpyHostToDevice,
+                                   c->stream));
+    return SS_OK;
+}
+
+SS_API ss_status ss_upload_node_world_rows(ss_ctx* c, uint32_t first, uint32_t count, const float* rows12)
+{
+    if (!c) return SS_ERR_INVALID;
+    const uint32_t computed = c->level_offsets.empty() ? 0 : c->level_offsets.back();
+    if (!rows12 || first < computed || (uint64_t)first + count > c->n_nodes)
+        return c->fail(SS_ERR_INVALID, "ss_upload_node_world_rows: range [%u, +%u) must lie in the external nodes [%u, %u)",
+                       first, count, computed, c->n_nodes);
+    SS_CUDA(c, cudaSetDevice(c->device));
+    if (count)
+        SS_CUDA(c, cudaMemcpyAsync(c->d_node_world + (size_t)first * 3, rows12, (size_t)count * 48, cudaMemcpyHostToDevice,
                                    c->stream));
     return SS_OK;
 }

@@ -20,7 +20,7 @@ SLOT_NULL = 0xFFFFFFFF
 
 # every symbol include/scenesubmit.h declares (tests check the library exports exactly these)
 EXPORTS = ["ss_create", "ss_destroy", "ss_last_error", "ss_version", "ss_set_key_layout", "ss_set_submesh_table",
-           "ss_set_nodes", "ss_set_instances", "ss_set_instance_aabbs", "ss_upload_trs", "ss_flush_uploads",
+           "ss_set_nodes", "ss_set_instances", "ss_set_instance_aabbs", "ss_upload_trs", "ss_upload_node_world_rows", "ss_flush_uploads",
            "ss_upload_world_rows", "ss_frame", "ss_frame_sync", "ss_frame_stage_ms", "ss_map_outputs", "ss_download_view",
            "ss_download_world", "ss_download_masks", "ss_stream", "ss_sort_scratch_bytes", "ss_sort_pairs",
            "ss_sort_pairs_host", "ss_sort_pairs_static", "ss_camera_view_proj", "ss_cascade_matrices"]
@@ -187,6 +187,10 @@ class SceneSubmit:
     def upload_trs_ptr(self, host_ptr, count, first=0):
         """Raw host pointer (e.g. a pinned torch tensor's data_ptr())."""
         self._ck(self.lib.ss_upload_trs(self.h, C.c_uint32(first), C.c_uint32(count), C.c_void_p(host_ptr)))
+
+    def upload_node_world_rows(self, rows, first):
+        rows = np.ascontiguousarray(rows, np.float32)
+        self._ck(self.lib.ss_upload_node_world_rows(self.h, C.c_uint32(first), C.c_uint32(rows.shape[0]), _p(rows)))
 
     def flush_uploads(self):
         self._ck(self.lib.ss_flush_uploads(self.h))
