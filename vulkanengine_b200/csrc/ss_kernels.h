@@ -44,6 +44,9 @@ struct InstanceArgs {
     int trig_mode;
 };
 void launch_instances(const InstanceArgs& a, const CullParams& cp, cudaStream_t st);
+// packed-FP32 fast path, two instances per thread (transform_cull_x2.cu); same results bit for bit
+bool instances_x2_eligible(const InstanceArgs& a);
+void launch_instances_x2(const InstanceArgs& a, const CullParams& cp, cudaStream_t st);
 
 // ---- onesweep radix sort (radix_sort.cu) -------------------------------------------------------
 constexpr int kMaxRadixBits = 9;

@@ -5,6 +5,8 @@
 // memory with 128-bit coalesced loads, each thread then reads its own record at an odd word stride
 // (bank-conflict free), computes, and the 48 B output rows leave through shared memory as 128-bit
 // coalesced stores.  No tensor cores: a 4x4 affine product per instance is not a dense contraction.
+#include <cstdlib>
+
 #include "ss_kernels.h"
 
 namespace ss {
@@ -235,6 +237,12 @@ void launch_node_level(const NodeLevelArgs& a, cudaStream_t st)
 void launch_instances(const InstanceArgs& a, const CullParams& cp, cudaStream_t st)
 {
     if (a.n == 0) return;
+    // SS_SCALAR_KERNEL=1 forces the one-instance-per-thread kernel (A/B measurements, parity tests of both)
+    static const bool force_scalar = getenv("SS_SCALAR_KERNEL") && atoi(getenv("SS_SCALAR_KERNEL")) != 0;
+    if (!force_scalar && instances_x2_eligible(a)) {
+        launch_instances_x2(a, cp, st);
+        return;
+    }
     const uint32_t grid = (a.n + kTile - 1) / kTile;
     if (a.trig_mode == SS_TRIG_DETERMINISTIC)
         k_instances<SS_TRIG_DETERMINISTIC><<<grid, kTile, 0, st>>>(a, cp);
