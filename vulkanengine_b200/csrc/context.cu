@@ -550,15 +550,28 @@ SS_API ss_status ss_frame(ss_ctx* c, const ss_view* views, uint32_t n_views, uin
     const bool packed = idx_bits + key_bits <= 64;
     ia.idx_bits = packed ? (uint32_t)idx_bits : 0u;
     ia.mask_bits = (packed && idx_bits + key_bits + 8 <= 64) ? 8u : 0u;
+    // The sort's digit plan is known up front, so its scratch is cleared before the instance kernel runs and
+    // the fast path accumulates the digit histograms on the way (saves the sort's own pass over the keys).
+    const int begin_bit = packed ? idx_bits + (int)ia.mask_bits : 0, end_bit = begin_bit + key_bits;
+    const SortPlan plan = sort_plan(begin_bit, end_bit);
+    ia.hist = reinterpret_cast<SortControl*>(c->d_sort_scratch)->hist[0];
+    ia.hist_passes = plan.n_passes <= 3 ? plan.n_passes : 0;
+    for (int p = 0; p < 3; ++p) {
+        ia.hist_shift[p] = p < plan.n_passes ? plan.shift[p] - begin_bit : 0;
+        ia.hist_bits[p] = p < plan.n_passes ? plan.bits[p] : 0;
+    }
+    SS_CUDA(c, sort_prepare(c->d_sort_scratch, n, begin_bit, end_bit, st));
+    bool hist_done = false;
     if (n) {
-        launch_instances(ia, cp, st);
+        hist_done = launch_instances(ia, cp, st);
         ++launches;
     }
     SS_CUDA(c, cudaEventRecord(s.stage[1], st));
 
-    const int begin_bit = packed ? idx_bits + (int)ia.mask_bits : 0, end_bit = begin_bit + key_bits;
+    if (!hist_done)  // the general kernel did not count digits: clear again is harmless, the sort counts itself
+        SS_CUDA(c, sort_prepare(c->d_sort_scratch, n, begin_bit, end_bit, st));
     SS_CUDA(c, sort_async(c->d_keys_a, packed ? nullptr : c->d_vals_a, c->d_keys_b, packed ? nullptr : c->d_vals_b, n,
-                          begin_bit, end_bit, c->d_sort_scratch, st, &launches));
+                          begin_bit, end_bit, c->d_sort_scratch, st, &launches, hist_done));
     SS_CUDA(c, cudaEventRecord(s.stage[2], st));
 
     EmitArgs ea;

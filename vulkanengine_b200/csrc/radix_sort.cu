@@ -283,21 +283,31 @@ size_t sort_scratch_bytes(uint64_t n)
     return kCtlBytes + num_tiles(n ? n : 1) * kLookbackWordsPerTile * sizeof(uint32_t);
 }
 
-cudaError_t sort_async(uint64_t* keys_a, uint32_t* vals_a, uint64_t* keys_b, uint32_t* vals_b, uint64_t n,
-                       int begin_bit, int end_bit, void* scratch, cudaStream_t st, int* launches)
+cudaError_t sort_prepare(void* scratch, uint64_t n, int begin_bit, int end_bit, cudaStream_t st)
 {
-    const bool has_vals = vals_a != nullptr;
     const SortPlan pl = sort_plan(begin_bit, end_bit);
     const uint64_t tiles = num_tiles(n ? n : 1);
     size_t words = 0;
     for (int p = 0; p < pl.n_passes; ++p) words += (size_t)1 << pl.bits[p];
     // the control block and the look-back words of the passes about to run must start at zero
-    cudaError_t e = cudaMemsetAsync(scratch, 0, kCtlBytes + tiles * words * sizeof(uint32_t), st);
-    if (e != cudaSuccess) return e;
+    return cudaMemsetAsync(scratch, 0, kCtlBytes + tiles * words * sizeof(uint32_t), st);
+}
+
+cudaError_t sort_async(uint64_t* keys_a, uint32_t* vals_a, uint64_t* keys_b, uint32_t* vals_b, uint64_t n,
+                       int begin_bit, int end_bit, void* scratch, cudaStream_t st, int* launches, bool prepared_with_hist)
+{
+    const bool has_vals = vals_a != nullptr;
+    const SortPlan pl = sort_plan(begin_bit, end_bit);
+    const uint64_t tiles = num_tiles(n ? n : 1);
+    cudaError_t e = cudaSuccess;
+    if (!prepared_with_hist) {
+        e = sort_prepare(scratch, n, begin_bit, end_bit, st);
+        if (e != cudaSuccess) return e;
+    }
     SortControl* ctl = reinterpret_cast<SortControl*>(scratch);
     uint32_t* lookback = reinterpret_cast<uint32_t*>(static_cast<unsigned char*>(scratch) + kCtlBytes);
     int nl = 0;
-    if (n > 0 && pl.n_passes > 0) {
+    if (n > 0 && pl.n_passes > 0 && !prepared_with_hist) {
         HistArgs ha{};
         ha.n_passes = pl.n_passes;
         for (int p = 0; p < pl.n_passes; ++p) {
@@ -341,7 +351,7 @@ cudaError_t sort_async(uint64_t* keys_a, uint32_t* vals_a, uint64_t* keys_b, uin
 cudaError_t sort_pairs_async(uint64_t* keys_a, uint32_t* vals_a, uint64_t* keys_b, uint32_t* vals_b, uint64_t n,
                              int begin_bit, int end_bit, void* scratch, cudaStream_t st, int* launches)
 {
-    return sort_async(keys_a, vals_a, keys_b, vals_b, n, begin_bit, end_bit, scratch, st, launches);
+    return sort_async(keys_a, vals_a, keys_b, vals_b, n, begin_bit, end_bit, scratch, st, launches, false);
 }
 
 }  // namespace ss

@@ -42,9 +42,16 @@ struct InstanceArgs {
     uint32_t mask_bits;        // 8 when the visibility byte rides in the packed word, else 0
     int world_given;           // SS_FRAME_WORLD_ROWS_GIVEN
     int trig_mode;
+    // optional fusion of the sort's digit histograms (fast path only): hist = SortControl::hist, zeroed;
+    // digit p of the KEY (before packing) is (key >> hist_shift[p]) & ((1 << hist_bits[p]) - 1)
+    uint32_t* hist;
+    int hist_passes;           // 0 = do not accumulate
+    int hist_shift[3];
+    int hist_bits[3];
 };
-void launch_instances(const InstanceArgs& a, const CullParams& cp, cudaStream_t st);
-// packed-FP32 fast path, two instances per thread (transform_cull_x2.cu); same results bit for bit
+// Returns true when the launched kernel also accumulated the sort histograms requested in `a`.
+bool launch_instances(const InstanceArgs& a, const CullParams& cp, cudaStream_t st);
+// persistent TMA + packed-FP32 fast path, two instances per thread (transform_cull_x2.cu); same results bit for bit
 bool instances_x2_eligible(const InstanceArgs& a);
 void launch_instances_x2(const InstanceArgs& a, const CullParams& cp, cudaStream_t st);
 
@@ -78,8 +85,12 @@ inline int sort_num_passes(int begin_bit, int end_bit) { return sort_plan(begin_
 size_t sort_scratch_bytes(uint64_t n);
 // Enqueues clear + histogram + scan + passes.  vals_a == nullptr: keys only.
 // Result location: control->src_sel[n_passes] (device).
+// prepared_with_hist: sort_prepare() ran earlier on the stream AND a producer kernel has already filled
+// control->hist with the digit histograms, so the clear and the histogram pass are skipped.
+cudaError_t sort_prepare(void* scratch, uint64_t n, int begin_bit, int end_bit, cudaStream_t st);
 cudaError_t sort_async(uint64_t* keys_a, uint32_t* vals_a, uint64_t* keys_b, uint32_t* vals_b, uint64_t n,
-                       int begin_bit, int end_bit, void* scratch, cudaStream_t st, int* launches);
+                       int begin_bit, int end_bit, void* scratch, cudaStream_t st, int* launches,
+                       bool prepared_with_hist);
 cudaError_t sort_pairs_async(uint64_t* keys_a, uint32_t* vals_a, uint64_t* keys_b, uint32_t* vals_b, uint64_t n,
                              int begin_bit, int end_bit, void* scratch, cudaStream_t st, int* launches);
 

@@ -234,20 +234,21 @@ void launch_node_level(const NodeLevelArgs& a, cudaStream_t st)
         k_node_level<SS_TRIG_LIBM><<<grid, kTile, 0, st>>>(a);
 }
 
-void launch_instances(const InstanceArgs& a, const CullParams& cp, cudaStream_t st)
+bool launch_instances(const InstanceArgs& a, const CullParams& cp, cudaStream_t st)
 {
-    if (a.n == 0) return;
+    if (a.n == 0) return false;
     // SS_SCALAR_KERNEL=1 forces the one-instance-per-thread kernel (A/B measurements, parity tests of both)
     static const bool force_scalar = getenv("SS_SCALAR_KERNEL") && atoi(getenv("SS_SCALAR_KERNEL")) != 0;
     if (!force_scalar && instances_x2_eligible(a)) {
         launch_instances_x2(a, cp, st);
-        return;
+        return a.hist_passes > 0;
     }
     const uint32_t grid = (a.n + kTile - 1) / kTile;
     if (a.trig_mode == SS_TRIG_DETERMINISTIC)
         k_instances<SS_TRIG_DETERMINISTIC><<<grid, kTile, 0, st>>>(a, cp);
     else
         k_instances<SS_TRIG_LIBM><<<grid, kTile, 0, st>>>(a, cp);
+    return false;  // the general kernel leaves the histograms to the sort
 }
 
 }  // namespace ss
