@@ -230,9 +230,14 @@ def main():
     launches_per_frame = int(st.kernel_launches)
     stream = torch.cuda.ExternalStream(ctx.stream, device=local_rank)
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    # clocks are sampled DURING load: the sampler runs through an untimed stretch of identical frames
+    # (a frame is ~2 ms, nvidia-smi samples every 100 ms) and through the timed region that follows directly
     sampler = ClockSampler(local_rank)
-    barrier()
     sampler.start()
+    t_load = time.perf_counter()
+    while time.perf_counter() - t_load < 1.2:
+        ctx.frame_sync(ctx.frame(views))
+    barrier()
     slots = []
     with torch.cuda.stream(stream):
         ev0.record(stream)

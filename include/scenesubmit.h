@@ -276,7 +276,7 @@ SS_API ss_status ss_sort_pairs_host(int device, const uint64_t* keys_in, const u
    working inside a memory budget fixed at start-up, a plug-in under an application that owns the
    device allocator, or an engine that has already handed all of HBM to its own pools.  The scratch
    that ss_sort_pairs takes from the caller is replaced by a fixed array inside the library image
-   (about 2 MiB on every GPU that loads the library, held until the process exits), so n is limited
+   (about 1 MiB on every GPU that loads the library, held until the process exits), so n is limited
    to SS_SORT_STATIC_MAX_N elements; a larger n returns SS_ERR_CAPACITY and ss_last_error(NULL) says
    why.  The call itself performs no cudaMalloc/cudaFree and uses no allocating library routine; the
    caller still provides both ping-pong buffer pairs.  The first call on each device looks up the

@@ -109,7 +109,7 @@ inline size_t onesweep_smem_bytes(int bins, bool has_vals)
 }
 
 template <bool HAS_VALS>
-__global__ void __launch_bounds__(kSortThreads, HAS_VALS ? 2 : 3)
+__global__ void __launch_bounds__(kSortThreads, HAS_VALS ? 1 : 2)
 k_onesweep(uint64_t* keys_a, uint32_t* vals_a, uint64_t* keys_b, uint32_t* vals_b, uint64_t n, int shift, int bits,
            int pass, SortControl* ctl, uint32_t* lookback)
 {
@@ -363,7 +363,7 @@ cudaError_t sort_pairs_async(uint64_t* keys_a, uint32_t* vals_a, uint64_t* keys_
 // host application that owns the allocator, code that runs after the engine has handed all of HBM
 // to its own pools.  For those callers the scratch that ss_sort_pairs takes from the caller lives
 // here, in a fixed array inside the library image.  Every GPU that loads libscenesubmit.so carries
-// this array (about 2 MiB) until the process exits, which is why its size is capped.
+// this array (about 1 MiB) until the process exits, which is why its size is capped.
 constexpr size_t kStaticSortScratchBytes =
     ss::kCtlBytes + (size_t)((SS_SORT_STATIC_MAX_N + ss::kSortTile - 1) / ss::kSortTile) * ss::kLookbackWordsPerTile *
                         sizeof(uint32_t);

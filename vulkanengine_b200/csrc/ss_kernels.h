@@ -59,7 +59,7 @@ void launch_instances_x2(const InstanceArgs& a, const CullParams& cp, cudaStream
 constexpr int kMaxRadixBits = 9;
 constexpr int kMaxRadix = 1 << kMaxRadixBits;
 constexpr int kMaxPasses = 8;
-constexpr int kSortThreads = 256;
+constexpr int kSortThreads = 512;
 constexpr int kSortItems = 16;
 constexpr int kSortTile = kSortThreads * kSortItems;
 
