@@ -75,8 +75,15 @@ typedef enum ss_frame_flags {
     /* stage-wise parity: do not run the transform stage, cull/sort/emit from the world rows given
        to ss_upload_world_rows */
     SS_FRAME_WORLD_ROWS_GIVEN = 1,
-    /* run without the CUDA graph even if one is cached for this shape */
-    SS_FRAME_NO_GRAPH = 2
+    /* reserved */
+    SS_FRAME_NO_GRAPH = 2,
+    /* Batched multi-view work (many cameras over one scene, BASELINE configs[4]): views are processed
+       SS_MAX_VIEWS at a time, one ss_frame per batch.  After a first, full frame the transforms have not
+       changed, so later batches may keep the world rows of the previous frame (cull + emit only) ... */
+    SS_FRAME_REUSE_WORLD = 4,
+    /* ... and, the sort keys being static too, its sorted (key, instance) order.  Both flags are ignored
+       (the stage runs) when no valid result of a previous frame exists. */
+    SS_FRAME_REUSE_SORT = 8
 } ss_frame_flags;
 
 typedef struct ss_ctx ss_ctx;

@@ -316,3 +316,50 @@ def test_external_nodes_with_given_world_rows():
     with pytest.raises(S.SceneSubmitError):  # computed nodes cannot be overwritten this way
         ctx.upload_node_world_rows(ext_rows[:1], 0)
     ctx.close()
+
+
+def test_batched_views_reuse_world_and_sort():
+    """configs[4] shape in small: many cameras over one scene, 8 views per frame; after the first full frame
+    the later batches reuse the world rows and the sorted order (SS_FRAME_REUSE_WORLD | SS_FRAME_REUSE_SORT)
+    and must still equal the oracle view by view."""
+    sc = synth.hierarchy_scene(n_roots=16, fan1=8, fan2=32, n_keys=200)
+    n_cams = 24
+    cams = synth.fibonacci_cameras(lambda *a: O.camera_view_proj(*a), n_cams, radius=800.0)
+    osc = O.OracleScene(sc, 0)
+    ctx = S.SceneSubmit(sc.n_nodes, sc.n_instances, len(sc.slots), max_views=8)
+    ctx.load_scene(sc)
+    seen_any = 0
+    for b in range(0, n_cams, 8):
+        batch = cams[b:b + 8]
+        flags = 0 if b == 0 else (S.FRAME_REUSE_WORLD | S.FRAME_REUSE_SORT)
+        slot = ctx.frame(batch, flags)
+        st = ctx.frame_sync(slot)
+        ref = osc.frame(batch)
+        assert np.array_equal(ctx.download_masks(), ref["masks"])
+        assert np.array_equal(ctx.download_world(), ref["rows"])
+        for v in range(len(batch)):
+            got = ctx.download_view(slot, v, st)
+            assert np.array_equal(got["idx"], ref["views"][v]["idx"]) and np.array_equal(got["keys"], ref["views"][v]["keys"])
+            assert np.array_equal(got["draws"], ref["views"][v]["draws"]) and np.array_equal(got["rows"], ref["views"][v]["rows"])
+            seen_any += len(got["idx"])
+        if b > 0:
+            assert int(st.kernel_launches) < 6  # no hierarchy, no sort: cull + emit + draws
+    assert seen_any > 0
+    # a TRS upload invalidates the kept world rows: the flag is then ignored and the transform runs again
+    trs = sc.trs.copy()
+    trs[:, 0] += 1.0
+    ctx.upload_trs(trs)
+    sc2 = synth.SceneArrays(**{**sc.__dict__, "trs": trs})
+    slot = ctx.frame(cams[:8], S.FRAME_REUSE_WORLD | S.FRAME_REUSE_SORT)
+    st = ctx.frame_sync(slot)
+    assert np.array_equal(ctx.download_world(), O.OracleScene(sc2, 0).frame(cams[:8])["rows"])
+    ctx.close()
+
+
+def test_config2_full_size_hierarchy_1m():
+    """configs[1]: 2^20 leaves under a 3-level hierarchy, one camera: bit-exact against the oracle."""
+    sc = synth.hierarchy_scene()
+    views = oracle_views(1)
+    ref = O.OracleScene(sc, 0).frame(views, threads=8)
+    got = run_gpu(sc, views, max_draws_per_view=1 << 16)
+    check_against_oracle(sc, views, got, ref)

@@ -77,6 +77,8 @@ struct ss_ctx {
     uint32_t n_nodes = 0, n_instances = 0, n_slots = 0, n_levels = 0;
     std::vector<uint32_t> level_offsets;
     bool has_parent = false, has_node_map = false, has_inst_aabb = false, world_uploaded = false;
+    bool world_valid = false;  // d_world holds the rows of a finished transform stage (SS_FRAME_REUSE_WORLD)
+    bool sort_valid = false;   // the sort buffers hold the order of the current static streams (SS_FRAME_REUSE_SORT)
     uint32_t node_base = 0;
     uint32_t mesh_bits = 22, submesh_bits = 16, material_bits = 24;
     std::vector<ss_submesh> host_table;
@@ -306,6 +308,7 @@ SS_API ss_status ss_set_key_layout(ss_ctx* c, uint32_t mesh_bits, uint32_t subme
         mesh_bits + submesh_bits + material_bits > 62)
         return c->fail(SS_ERR_INVALID, "ss_set_key_layout: widths must be >= 1, material <= 31, sum <= 62");
     SS_CUDA(c, cudaSetDevice(c->device));
+    c->world_valid = c->sort_valid = false;
     c->mesh_bits = mesh_bits;
     c->submesh_bits = submesh_bits;
     c->material_bits = material_bits;
@@ -325,6 +328,7 @@ SS_API ss_status ss_set_submesh_table(ss_ctx* c, const ss_submesh* table, uint32
             return c->fail(SS_ERR_INVALID, "ss_set_submesh_table: row %u rank/index exceeds the key layout", i);
     }
     SS_CUDA(c, cudaSetDevice(c->device));
+    c->world_valid = c->sort_valid = false;
     c->host_table.assign(table, table + count);
     c->n_slots = count;
     return upload_table(c);
@@ -361,6 +365,7 @@ SS_API ss_status ss_set_nodes(ss_ctx* c, uint32_t n_nodes, const int32_t* parent
         c->n_levels = 1;
     }
     SS_CUDA(c, cudaSetDevice(c->device));
+    c->world_valid = c->sort_valid = false;
     c->n_nodes = n_nodes;
     c->has_parent = parent != nullptr;
     if (parent) {
@@ -395,6 +400,7 @@ SS_API ss_status ss_set_instances(ss_ctx* c, uint32_t n, const uint32_t* node, u
     c->node_base = node ? 0 : node_base;
     c->has_inst_aabb = false;
     c->world_uploaded = false;
+    c->world_valid = c->sort_valid = false;
     if (n) {
         if (node) SS_CUDA(c, cudaMemcpyAsync(c->d_node, node, (size_t)n * 4, cudaMemcpyHostToDevice, c->stream));
         SS_CUDA(c, cudaMemcpyAsync(c->d_slot, submesh_slot, (size_t)n * 4, cudaMemcpyHostToDevice, c->stream));
@@ -431,6 +437,7 @@ SS_API ss_status ss_upload_trs(ss_ctx* c, uint32_t first, uint32_t count, const 
         return c->fail(SS_ERR_INVALID, "ss_upload_trs: range [%u, +%u) exceeds %u nodes", first, count, c->n_nodes);
     SS_CUDA(c, cudaSetDevice(c->device));
     if (count)
+        c->world_valid = false;  // transforms changed
         SS_CUDA(c, cudaMemcpyAsync(c->d_trs + (size_t)first * 9, trs9, (size_t)count * 36, cudaMemcpyHostToDevice,
                                    c->stream));
     return SS_OK;
@@ -478,9 +485,11 @@ SS_API ss_status ss_frame(ss_ctx* c, const ss_view* views, uint32_t n_views, uin
     if (!views || n_views < 1 || n_views > c->cfg.max_views)
         return c->fail(SS_ERR_INVALID, "ss_frame: %u views, capacity %u", n_views, c->cfg.max_views);
     if (c->n_slots == 0 || c->n_nodes == 0) return c->fail(SS_ERR_STATE, "ss_frame: submesh table / nodes not set");
-    const bool world_given = (flags & SS_FRAME_WORLD_ROWS_GIVEN) != 0;
-    if (world_given && !c->world_uploaded)
+    if ((flags & SS_FRAME_WORLD_ROWS_GIVEN) && !c->world_uploaded)
         return c->fail(SS_ERR_STATE, "ss_frame: SS_FRAME_WORLD_ROWS_GIVEN without ss_upload_world_rows");
+    // world rows already on the device: uploaded for stage-wise parity, or kept from the previous frame
+    const bool world_given = (flags & SS_FRAME_WORLD_ROWS_GIVEN) || ((flags & SS_FRAME_REUSE_WORLD) && c->world_valid);
+    const bool reuse_sort = (flags & SS_FRAME_REUSE_SORT) && c->sort_valid;
     SS_CUDA(c, cudaSetDevice(c->device));
 
     const uint32_t si = (uint32_t)(c->frame_no % c->slots.size());
@@ -560,18 +569,28 @@ SS_API ss_status ss_frame(ss_ctx* c, const ss_view* views, uint32_t n_views, uin
         ia.hist_shift[p] = p < plan.n_passes ? plan.shift[p] - begin_bit : 0;
         ia.hist_bits[p] = p < plan.n_passes ? plan.bits[p] : 0;
     }
-    SS_CUDA(c, sort_prepare(c->d_sort_scratch, n, begin_bit, end_bit, st));
+    if (reuse_sort) {  // keep the previous frame's sorted order: no keys, no histograms, no sort
+        ia.keys = nullptr;
+        ia.vals = nullptr;
+        ia.hist_passes = 0;
+    } else {
+        SS_CUDA(c, sort_prepare(c->d_sort_scratch, n, begin_bit, end_bit, st));
+    }
     bool hist_done = false;
     if (n) {
         hist_done = launch_instances(ia, cp, st);
         ++launches;
     }
+    c->world_valid = true;
     SS_CUDA(c, cudaEventRecord(s.stage[1], st));
 
-    if (!hist_done)  // the general kernel did not count digits: clear again is harmless, the sort counts itself
-        SS_CUDA(c, sort_prepare(c->d_sort_scratch, n, begin_bit, end_bit, st));
-    SS_CUDA(c, sort_async(c->d_keys_a, packed ? nullptr : c->d_vals_a, c->d_keys_b, packed ? nullptr : c->d_vals_b, n,
-                          begin_bit, end_bit, c->d_sort_scratch, st, &launches, hist_done));
+    if (!reuse_sort) {
+        if (!hist_done)  // the general kernel did not count digits: clear again is harmless, the sort counts itself
+            SS_CUDA(c, sort_prepare(c->d_sort_scratch, n, begin_bit, end_bit, st));
+        SS_CUDA(c, sort_async(c->d_keys_a, packed ? nullptr : c->d_vals_a, c->d_keys_b, packed ? nullptr : c->d_vals_b,
+                              n, begin_bit, end_bit, c->d_sort_scratch, st, &launches, hist_done));
+        c->sort_valid = true;
+    }
     SS_CUDA(c, cudaEventRecord(s.stage[2], st));
 
     EmitArgs ea;
@@ -584,6 +603,8 @@ SS_API ss_status ss_frame(ss_ctx* c, const ss_view* views, uint32_t n_views, uin
     ea.sort_passes = (uint32_t)sort_num_passes(begin_bit, end_bit);
     ea.idx_bits = ia.idx_bits;
     ea.mask_bits = ia.mask_bits;
+    // the visibility byte inside a sorted word is this frame's only if this frame built the words
+    ea.gather_mask = (!packed || ia.mask_bits == 0 || reuse_sort) ? 1u : 0u;
     ea.mask = c->d_mask;
     ea.world = c->d_world;
     ea.n = n;

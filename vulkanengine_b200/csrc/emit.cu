@@ -93,13 +93,13 @@ __global__ void __launch_bounds__(kEmitThreads) k_emit(const __grid_constant__ E
         for (int j = 0; j < kEmitItems; ++j) {
             const bool ok = l0 + j < n_valid;
             idx[j] = ok ? (uint32_t)(key[j] & imask) : 0u;
-            m[j] = (ok && a.mask_bits) ? (uint32_t)(key[j] >> a.idx_bits) & 0xffu : 0u;
+            m[j] = (ok && !a.gather_mask) ? (uint32_t)(key[j] >> a.idx_bits) & 0xffu : 0u;
             key[j] = ok ? key[j] >> key_shift : ~0ull;
         }
     }
 #pragma unroll
     for (int j = 0; j < kEmitItems; ++j) {
-        if (!a.mask_bits) m[j] = (l0 + j < n_valid) ? (uint32_t)__ldg(a.mask + idx[j]) : 0u;
+        if (a.gather_mask) m[j] = (l0 + j < n_valid) ? (uint32_t)__ldg(a.mask + idx[j]) : 0u;
         s.key[l0 + j] = key[j];
         s.idx[l0 + j] = idx[j];
     }

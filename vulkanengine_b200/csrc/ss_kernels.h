@@ -118,7 +118,8 @@ struct EmitArgs {
     const SortControl* sort_ctl;   // result selector
     uint32_t sort_passes;
     uint32_t idx_bits;             // > 0: sorted words are [key | mask | instance]
-    uint32_t mask_bits;            // 8: visibility byte sits above the instance index; 0: gather it from mask[]
+    uint32_t mask_bits;            // 8: a visibility byte sits above the instance index (layout of the word)
+    uint32_t gather_mask;          // 1: read visibility from mask[] (no byte in the word, or a reused, stale one)
     const uint8_t* mask;
     const float4* world;
     uint32_t n;

@@ -212,7 +212,9 @@ __global__ void __launch_bounds__(kTile) k_instances(InstanceArgs a, const __gri
     }
     if (valid) {
         a.mask[i] = (uint8_t)mask;
-        if (a.idx_bits) {  // key and instance index travel through the sort as one 64-bit word
+        if (a.keys == nullptr) {
+            // SS_FRAME_REUSE_SORT: the sorted order of an earlier frame is kept, no keys are produced
+        } else if (a.idx_bits) {  // key and instance index travel through the sort as one 64-bit word
             // [key | visibility byte (when it fits) | instance]: emit then needs no gather of the mask
             a.keys[i] = (key << (a.idx_bits + a.mask_bits)) | ((uint64_t)(a.mask_bits ? mask : 0u) << a.idx_bits) | i;
         } else {

@@ -478,6 +478,11 @@ __global__ void __launch_bounds__(kThreads2, 6) k_instances_x2(const __grid_cons
         if (live0) key0 = kh0 | (uint64_t)(mw0 & ~SS_MATERIAL_TESS_BIT) | ((uint64_t)(mw0 >> 31) << a.tess_shift);
         if (live1) key1 = kh1 | (uint64_t)(mw1 & ~SS_MATERIAL_TESS_BIT) | ((uint64_t)(mw1 >> 31) << a.tess_shift);
 
+        if (a.keys == nullptr) {  // SS_FRAME_REUSE_SORT: masks only
+            if (valid0) a.mask[i0] = (uint8_t)mask0;
+            if (valid1) a.mask[i1] = (uint8_t)mask1;
+            continue;
+        }
         const uint32_t sh = a.idx_bits + a.mask_bits;
         if (valid0) {
             a.mask[i0] = (uint8_t)mask0;

@@ -15,6 +15,8 @@ SS_OK, SS_ERR_INVALID, SS_ERR_CUDA, SS_ERR_CAPACITY, SS_ERR_STATE, SS_ERR_NOMEM 
 TRIG_DETERMINISTIC, TRIG_LIBM = 0, 1
 FRAME_WORLD_ROWS_GIVEN = 1
 FRAME_NO_GRAPH = 2
+FRAME_REUSE_WORLD = 4
+FRAME_REUSE_SORT = 8
 MAX_VIEWS = 8
 SLOT_NULL = 0xFFFFFFFF
 
