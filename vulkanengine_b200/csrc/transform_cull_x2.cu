@@ -245,21 +245,23 @@ __device__ __forceinline__ uint2 cull_box2(const P2& m, const Aff2& w, const f2*
         bool in0 = true, in1 = true;
 #pragma unroll
         for (int ax = 0; ax < 3; ++ax) {
-            const f2* c = s_planes + v * kViewWords + ax * kAxisWords;
-            const bool skip0 = (ax == 2) && (fl & kViewSkipNear);
-            const f2 t0 = m.add(m.add(m.mul(c[0], cw[0]), m.mul(c[1], cw[1])), m.mul(c[2], cw[2]));
-            const f2 r0 = m.add(m.add(m.mul(c[3], ew[0]), m.mul(c[4], ew[1])), m.mul(c[5], ew[2]));
-            const f2 s0 = m.add(t0, c[6]);
+            // 128-bit shared loads: two duplicated constants each
+            const ulonglong2* c2 = reinterpret_cast<const ulonglong2*>(s_planes + v * kViewWords + ax * kAxisWords);
+            const ulonglong2 n01 = c2[0], n2a0 = c2[1], a12 = c2[2], d01 = c2[3];
+            const f2 t0 = m.add(m.add(m.mul(n01.x, cw[0]), m.mul(n01.y, cw[1])), m.mul(n2a0.x, cw[2]));
+            const f2 r0 = m.add(m.add(m.mul(n2a0.y, ew[0]), m.mul(a12.x, ew[1])), m.mul(a12.y, ew[2]));
+            const f2 s0 = m.add(t0, d01.x);  // a skipped near plane has d0 = +inf: always inside
             f2 s1, r1 = r0;
             if (fl & (1u << ax)) {  // opposite normals: the second plane's dot product is -t0 exactly
-                s1 = m.sub(c[7], t0);
+                s1 = m.sub(d01.y, t0);
             } else {
-                const f2 t1 = m.add(m.add(m.mul(c[8], cw[0]), m.mul(c[9], cw[1])), m.mul(c[10], cw[2]));
-                r1 = m.add(m.add(m.mul(c[11], ew[0]), m.mul(c[12], ew[1])), m.mul(c[13], ew[2]));
-                s1 = m.add(t1, c[7]);
+                const ulonglong2 q01 = c2[4], q2b0 = c2[5], b12 = c2[6];
+                const f2 t1 = m.add(m.add(m.mul(q01.x, cw[0]), m.mul(q01.y, cw[1])), m.mul(q2b0.x, cw[2]));
+                r1 = m.add(m.add(m.mul(q2b0.y, ew[0]), m.mul(b12.x, ew[1])), m.mul(b12.y, ew[2]));
+                s1 = m.add(t1, d01.y);
             }
-            in0 = in0 && (skip0 || lo(s0) >= -lo(r0)) && (lo(s1) >= -lo(r1));
-            in1 = in1 && (skip0 || hi(s0) >= -hi(r0)) && (hi(s1) >= -hi(r1));
+            in0 = in0 && (lo(s0) >= -lo(r0)) && (lo(s1) >= -lo(r1));
+            in1 = in1 && (hi(s0) >= -hi(r0)) && (hi(s1) >= -hi(r1));
         }
         if (in0) mask.x |= (1u << v);
         if (in1) mask.y |= (1u << v);
@@ -324,7 +326,9 @@ __global__ void __launch_bounds__(kThreads2, 6) k_instances_x2(const __grid_cons
         f2* c = s.planes + v * kViewWords + ax * kAxisWords;
         c[0] = dup(p0.x); c[1] = dup(p0.y); c[2] = dup(p0.z);
         c[3] = dup(fabsf(p0.x)); c[4] = dup(fabsf(p0.y)); c[5] = dup(fabsf(p0.z));
-        c[6] = dup(p0.w); c[7] = dup(p1.w);
+        // near plane of a view flagged SS_VIEW_SKIP_NEAR: d = +inf makes the test pass for every finite box
+        const bool skip_near = ax == 2 && (cp.v[v].flags & kViewSkipNear);
+        c[6] = dup(skip_near ? __int_as_float(0x7f800000) : p0.w); c[7] = dup(p1.w);
         c[8] = dup(p1.x); c[9] = dup(p1.y); c[10] = dup(p1.z);
         c[11] = dup(fabsf(p1.x)); c[12] = dup(fabsf(p1.y)); c[13] = dup(fabsf(p1.z));
     }
