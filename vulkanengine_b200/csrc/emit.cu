@@ -21,6 +21,7 @@ constexpr uint32_t kFlagAgg = 1u << 30;
 constexpr uint32_t kFlagPrefix = 1u << 31;
 constexpr uint32_t kValueMask = kFlagAgg - 1;
 constexpr int kEmitWarps = kEmitThreads / 32;
+constexpr int kGatherBatch = 12;  // independent 16 B row gathers in flight per thread (a full 1024-row view = 12)
 
 struct EmitSmem {
     uint64_t key[kEmitTile];
@@ -261,10 +262,10 @@ __global__ void __launch_bounds__(kEmitThreads) k_emit(const __grid_constant__ E
             }
         }
         const uint32_t total4 = cnt * 3u;
-        for (uint32_t j0 = tid; j0 < total4; j0 += kEmitThreads * 4) {
-            float4 r[4];
+        for (uint32_t j0 = tid; j0 < total4; j0 += kEmitThreads * kGatherBatch) {
+            float4 r[kGatherBatch];
 #pragma unroll
-            for (int u = 0; u < 4; ++u) {
+            for (int u = 0; u < kGatherBatch; ++u) {
                 const uint32_t j = j0 + u * kEmitThreads;
                 if (j < total4) {
                     const uint32_t e = j / 3u, part = j - e * 3u;
@@ -272,7 +273,7 @@ __global__ void __launch_bounds__(kEmitThreads) k_emit(const __grid_constant__ E
                 }
             }
 #pragma unroll
-            for (int u = 0; u < 4; ++u) {
+            for (int u = 0; u < kGatherBatch; ++u) {
                 const uint32_t j = j0 + u * kEmitThreads;
                 if (j < total4) {
                     const uint32_t e = j / 3u;
