@@ -114,6 +114,32 @@ def instances_kernel_bytes(n, n_views, hierarchical):
     return n * (36 + 8 + 24 + (4 if hierarchical else 0)) + n * 48 + n * ((n_views + 7) // 8)
 
 
+def emit_kernel_bytes(n, visible, unique_visible):
+    """Algorithmic bytes of the emit launch: the sorted (key|instance) words it must read (8 B each), one 48 B
+    world row per instance visible in at least one view, and per view 48 B row + 8 B key + 4 B index out."""
+    return n * 8 + unique_visible * 48 + sum(int(v) * (48 + 8 + 4) for v in visible)
+
+
+def ncu_traffic(n, n_views):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed `ncu --set full` capture of
+    this workload (profiles/r01_ncu_full_summary.csv); only valid for the workload it was taken on."""
+    out = {}
+    if n != N_PER_GPU or n_views != N_VIEWS:
+        return out
+    try:
+        import csv
+        rows = list(csv.reader(open(os.path.join(ROOT, "profiles", "r01_ncu_full_summary.csv"))))
+        hdr = rows[0]
+        ir, iw = hdr.index("dram__bytes_read.sum"), hdr.index("dram__bytes_write.sum")
+        for r in rows[2:]:
+            for key in ("k_instances", "k_emit"):
+                if key in r[0] and key not in out:
+                    out[key] = int((float(r[ir]) + float(r[iw])) * 1e9)
+    except Exception:
+        pass
+    return out
+
+
 def cpu_reference(sc, views, sample, threads):
     """Times oracle/_ref (kind 'reference') or the plain-C oracle (kind 'port') on the first `sample`
     instances of the same scene with `threads` host threads. Returns (instances/s, kind, seconds, n)."""
@@ -337,9 +363,20 @@ def main():
 
     if rank == 0:
         peak, peak_src = peaks()
+        # per-kernel rooflines: algorithmic bytes of the launch / its CUDA-event time (ss_frame_stage_ms)
+        masks = ctx.download_masks()
+        unique_visible = int(np.count_nonzero(masks))
+        traffic = ncu_traffic(n, a.views)
         kb = instances_kernel_bytes(n, a.views, False)
-        k_ms = stage["instances"]
-        achieved = kb / (k_ms * 1e-3) / 1e9
+        eb = emit_kernel_bytes(n, visible, unique_visible)
+        roofs = []
+        for name, key, nbytes, ms_k in (("k_emit (5-view compaction + row gather)", "k_emit", eb, stage["emit"]),
+                                        ("k_instances_x2 (transform+cull+key)", "k_instances", kb, stage["instances"])):
+            ach = nbytes / (ms_k * 1e-3) / 1e9
+            roofs.append({"kernel": name, "bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
+                          "traffic": traffic.get(key), "peak_source": peak_src, "algorithmic_bytes_per_launch": nbytes,
+                          "kernel_ms": ms_k})
+        roofs.sort(key=lambda r: -r["kernel_ms"])  # the dominant kernel first
         balg = algorithmic_bytes(n, a.views, visible, draws, False)
         line = {"metric": "culled+compacted instances/sec", "value": value, "unit": "instances/s", "n_gpus": world,
                 "steps": a.steps, "warmup": max(a.warmup, 3), "ms_per_step": ms_step, "higher_is_better": True,
@@ -350,9 +387,7 @@ def main():
                 "ms_per_frame": ms_step, "visible_per_view": visible, "draws_per_view": draws,
                 "stage_ms": stage, "sort_passes_run": int(st.sort_passes_run),
                 "frame_algorithmic_gb": balg / 1e9, "frame_frac_of_hbm_peak": balg / (ms_step * 1e-3) / 1e9 / peak,
-                "roofline": {"kernel": "k_instances (transform+cull+key)", "bound": "hbm", "achieved": achieved,
-                             "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
-                             "peak_source": peak_src, "algorithmic_bytes_per_launch": kb, "kernel_ms": k_ms},
+                "roofline": roofs[0], "roofline_other_kernels": roofs[1:],
                 "gpu_launches": launches_per_frame * a.steps, "clocks": clocks}
         if e2e:
             line["e2e"] = e2e

@@ -1,13 +1,13 @@
 // Fast path of the transform -> cull -> key kernel for sm_100a:
-// persistent CTAs, TMA bulk copies into a two-stage shared-memory ring, packed FP32 arithmetic.
+// persistent CTAs, TMA bulk copies of the next tile into shared memory, packed FP32 arithmetic.
 //
 // Why.  The one-instance-per-thread kernel (transform_cull.cu) is issue-bound and latency-bound, not
 // HBM-bound: ~450 of its ~1000 warp instructions per 32 instances are FMUL/FADD that -fmad=false forbids
 // to fuse, and every CTA first waits a full DRAM round trip for its tile.  Here
 //   * each CTA lives for the whole launch and walks tiles of 256 instances; one thread issues
-//     cp.async.bulk (TMA, UBLKCP in SASS) copies of the NEXT tiles' records (TRS 36 B, AABB 24 B, ids)
-//     into the free stage of the ring and the arrival is tracked by an mbarrier, so HBM latency is
-//     hidden behind the arithmetic of the current tile;
+//     cp.async.bulk (TMA, UBLKCP in SASS) copies of the NEXT tile's records (TRS 36 B, AABB 24 B, ids)
+//     into the stage buffer as soon as the current tile has been unpacked into registers; the arrival
+//     is tracked by an mbarrier, so HBM latency is hidden behind the arithmetic of the current tile;
 //   * each thread carries TWO instances in the halves of 64-bit registers and computes with FFMA2
 //     (PTX fma.rn.f32x2): one issue slot does the arithmetic of both, and the uniform work (plane
 //     constants, addressing, control) is paid once per pair;
