@@ -363,3 +363,54 @@ def test_config2_full_size_hierarchy_1m():
     ref = O.OracleScene(sc, 0).frame(views, threads=8)
     got = run_gpu(sc, views, max_draws_per_view=1 << 16)
     check_against_oracle(sc, views, got, ref)
+
+
+def test_wide_key_layout_pairs_mode_and_digit_skip():
+    """Default-width layout (22/16/24 bits): key + instance index no longer fit one 64-bit word, so the sort
+    runs on (key, value) pairs with 8-bit digits and skips the constant ones."""
+    sc = synth.flat_scene(40_000, n_keys=300)
+    wide = synth.SceneArrays(**{**sc.__dict__, "mesh_bits": 22, "submesh_bits": 16, "material_bits": 24})
+    views = oracle_views(5)
+    ref = O.OracleScene(wide, 0).frame(views)
+    got = run_gpu(wide, views)
+    check_against_oracle(wide, views, got, ref)
+    assert 1 <= int(got["stats"].sort_passes_run) <= 5  # 8 digit positions, most of them constant
+
+
+def test_eight_views():
+    sc = synth.flat_scene(30_000, n_keys=200)
+    cams = synth.fibonacci_cameras(lambda *a: O.camera_view_proj(*a), 8, radius=900.0)
+    ref = O.OracleScene(sc, 0).frame(cams)
+    got = run_gpu(sc, cams)
+    check_against_oracle(sc, cams, got, ref)
+    assert any(int(got["stats"].visible[v]) > 0 for v in range(8))
+
+
+def test_zero_instances():
+    sc = synth.flat_scene(64, n_keys=8)
+    empty = synth.SceneArrays(**{**sc.__dict__, "slot": sc.slot[:0], "matword": sc.matword[:0], "inst_aabb": sc.inst_aabb[:0]})
+    views = oracle_views(5)
+    ctx = S.SceneSubmit(sc.n_nodes, 16, len(sc.slots), max_views=5)
+    ctx.set_key_layout(sc.mesh_bits, sc.submesh_bits, sc.material_bits)
+    ctx.set_submesh_table(sc.slots)
+    ctx.set_nodes(sc.n_nodes)
+    ctx.set_instances(empty.slot, empty.matword, None, 0)
+    ctx.upload_trs(sc.trs)
+    st = ctx.frame_sync(ctx.frame(views))
+    assert all(int(st.visible[v]) == 0 and int(st.draws[v]) == 0 for v in range(5))
+    ctx.close()
+
+
+def test_scalar_and_packed_instance_kernels_agree(monkeypatch):
+    """The general one-instance-per-thread kernel and the packed-FP32 fast path must give identical bits.
+    node_base % 4 != 0 makes the fast path ineligible (TMA alignment), so the same scene shifted by one
+    interior node runs on the general kernel."""
+    base = synth.hierarchy_scene(n_roots=5, fan1=4, fan2=64, n_keys=100)      # node_base = 25: general kernel
+    views = oracle_views(5)
+    ref = O.OracleScene(base, 0).frame(views)
+    got = run_gpu(base, views)
+    check_against_oracle(base, views, got, ref)
+    aligned = synth.hierarchy_scene(n_roots=4, fan1=7, fan2=64, n_keys=100)   # node_base = 32: fast path
+    ref = O.OracleScene(aligned, 0).frame(views)
+    got = run_gpu(aligned, views)
+    check_against_oracle(aligned, views, got, ref)
