@@ -311,7 +311,7 @@ def main():
                 dk = dev_tensor(o.draw_keys, o.n_draws, "<i8")
                 draws = dev_tensor(o.draws, o.n_draws * 5, "<i4").view(-1, 5)
                 mk, mi, mdk, mdc, mfirst = sharding.merge_view_list(keys, idx, dk, draws[:, 1].contiguous(), rank * n)
-                total_bytes += mk.numel() * 16
+                total_bytes += mi.numel() * 4  # instance indices all-gathered over NVLink (keys are rebuilt from the runs)
             return total_bytes
 
         s_ = ctx.frame(views)
@@ -325,7 +325,7 @@ def main():
         m1.synchronize()
         mt = torch.tensor([m0.elapsed_time(m1)], dtype=torch.float64, device="cuda")
         dist.all_reduce(mt, op=dist.ReduceOp.MAX)
-        merge = {"ms": float(mt.item()), "merged_list_bytes": int(merged_bytes),
+        merge = {"ms": float(mt.item()), "all_gathered_bytes": int(merged_bytes),
                  "note": "all_gather of per-view draw keys/counts and (key, instance) lists + run placement; "
                          "not part of the sharded phase timed in value"}
 

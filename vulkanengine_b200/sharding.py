@@ -34,6 +34,14 @@ def _all_gather_padded(t: torch.Tensor, counts: List[int]) -> List[torch.Tensor]
     return [o[:c] for o, c in zip(out, counts)]
 
 
+def _gather_scalar(value: int, dev) -> torch.Tensor:
+    world = dist.get_world_size()
+    mine = torch.tensor([value], dtype=torch.int64, device=dev)
+    out = [torch.empty_like(mine) for _ in range(world)]
+    dist.all_gather(out, mine)
+    return torch.cat(out)
+
+
 def merge_view_list(keys: torch.Tensor, idx: torch.Tensor, draw_keys: torch.Tensor, draw_counts: torch.Tensor,
                     idx_offset: int):
     """Merges this rank's compacted list of ONE view with every other rank's.
@@ -54,11 +62,11 @@ def merge_view_list(keys: torch.Tensor, idx: torch.Tensor, draw_keys: torch.Tens
     dist.all_gather(sizes, mine)
     n_list = [int(s[0]) for s in sizes]
     n_draw = [int(s[1]) for s in sizes]
-    # 2) draws of every rank (KBs), then 3) the lists themselves (the only large transfer)
+    # 2) draws of every rank (KBs), then 3) the instance lists (the only large transfer: 4 B per element;
+    #    the keys are NOT sent, an element's key is the key of the run it lies in)
     all_dk = _all_gather_padded(draw_keys, n_draw)
     all_dc = _all_gather_padded(draw_counts.to(torch.int64), n_draw)
-    all_k = _all_gather_padded(keys, n_list)
-    all_i = _all_gather_padded(idx.to(torch.int64) + idx_offset, n_list)
+    all_i = _all_gather_padded(idx.to(torch.int32), n_list)
 
     # merged draws: union of keys, counts summed over ranks, in key order
     cat_dk = torch.cat(all_dk)
@@ -69,23 +77,21 @@ def merge_view_list(keys: torch.Tensor, idx: torch.Tensor, draw_keys: torch.Tens
 
     # run placement: rank r's run of key k starts at first[k] + sum of the counts of ranks < r for k
     total = int(merged_dc.sum())
-    out_k = torch.empty(total, dtype=keys.dtype, device=dev)
     out_i = torch.empty(total, dtype=torch.int64, device=dev)
     before = torch.zeros(merged_dk.numel(), dtype=torch.int64, device=dev)
+    shard = [int(x) for x in _gather_scalar(idx_offset, dev)]
     off = 0
     for r in range(world):
         nd = n_draw[r]
         if nd:
             slot = inverse[off: off + nd]              # merged draw index of each of rank r's runs
-            run_dst = first[slot] + before[slot]       # destination of each run's first element
             run_len = all_dc[r]
             run_src = torch.cumsum(run_len, 0) - run_len
-            # destination of every element = its run's destination + its position inside the run
-            elem_run = torch.repeat_interleave(torch.arange(nd, device=dev), run_len)
-            pos = torch.arange(n_list[r], device=dev) - run_src[elem_run]
-            dst = run_dst[elem_run] + pos
-            out_k[dst] = all_k[r]
-            out_i[dst] = all_i[r]
+            # destination of every element = where its run starts in the merged list + its position in the run
+            shift = first[slot] + before[slot] - run_src
+            dst = torch.repeat_interleave(shift, run_len) + torch.arange(n_list[r], device=dev)
+            out_i[dst] = all_i[r].to(torch.int64) + shard[r]
             before.index_add_(0, slot, run_len)
         off += nd
+    out_k = torch.repeat_interleave(merged_dk, merged_dc)
     return out_k, out_i, merged_dk, merged_dc, first
