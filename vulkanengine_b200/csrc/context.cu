@@ -28,7 +28,8 @@ struct Slot {
     uint32_t n_views = 0, n_instances = 0;
     int launches = 0;
     // pinned host mirror
-    uint32_t* h_counts = nullptr;     // [max_views][2] + overflow + passes_run
+    uint32_t* h_counts = nullptr;     // [max_views][2] + overflow + passes_run: mapped pinned, written by k_draws
+    uint32_t* h_counts_dev = nullptr; // the same words as the device sees them
 };
 
 }  // namespace
@@ -66,7 +67,9 @@ struct ss_ctx {
     uint32_t* d_ticket = nullptr;
     uint32_t* d_totals = nullptr;
     uint32_t* d_overflow = nullptr;
-    uint32_t* d_seg_count = nullptr;
+    uint32_t* d_seg_count = nullptr;   // [2][max_views][max_draws]: per-view run counters, double-buffered by frame
+    uint32_t* d_seg_runs = nullptr;    // [2] runs left in each buffer
+    uint32_t seg_parity = 0;
     uint64_t* d_seg_key = nullptr;
     uint32_t* d_seg_inst = nullptr;
 
@@ -270,8 +273,10 @@ SS_API ss_status ss_create(const ss_config* cfg, ss_ctx** out)
     c->d_ticket = reinterpret_cast<uint32_t*>(c->d_emit_zero + lb_bytes);
     c->d_totals = c->d_ticket + 16;
     c->d_overflow = c->d_ticket + 32;
-    TRY(dev_alloc(c, &c->d_seg_count, V * c->max_draws));
-    TRY(cudaMemsetAsync(c->d_seg_count, 0, V * c->max_draws * sizeof(uint32_t), c->stream));
+    TRY(dev_alloc(c, &c->d_seg_count, 2 * V * c->max_draws));
+    TRY(cudaMemsetAsync(c->d_seg_count, 0, 2 * V * c->max_draws * sizeof(uint32_t), c->stream));
+    TRY(dev_alloc(c, &c->d_seg_runs, (size_t)8));
+    TRY(cudaMemsetAsync(c->d_seg_runs, 0, 8 * sizeof(uint32_t), c->stream));
     TRY(dev_alloc(c, &c->d_seg_key, (size_t)c->max_draws));
     TRY(dev_alloc(c, &c->d_seg_inst, (size_t)c->max_draws));
 
@@ -290,8 +295,9 @@ SS_API ss_status ss_create(const ss_config* cfg, ss_ctx** out)
         TRY(cudaEventCreate(&s.done));
         TRY(cudaEventCreate(&s.start));
         for (cudaEvent_t& e : s.stage) TRY(cudaEventCreate(&e));
-        TRY(cudaHostAlloc(reinterpret_cast<void**>(&s.h_counts), (V * 2 + 8) * sizeof(uint32_t), cudaHostAllocDefault));
+        TRY(cudaHostAlloc(reinterpret_cast<void**>(&s.h_counts), (V * 2 + 8) * sizeof(uint32_t), cudaHostAllocMapped));
         memset(s.h_counts, 0, (V * 2 + 8) * sizeof(uint32_t));
+        TRY(cudaHostGetDevicePointer(reinterpret_cast<void**>(&s.h_counts_dev), s.h_counts, 0));
     }
     TRY(cudaStreamSynchronize(c->stream));
 #undef TRY
@@ -614,7 +620,8 @@ SS_API ss_status ss_frame(ss_ctx* c, const ss_view* views, uint32_t n_views, uin
     ea.max_draws = c->max_draws;
     ea.lookback = c->d_lookback;
     ea.ticket = c->d_ticket;
-    ea.seg_count = c->d_seg_count;
+    const size_t seg_words = (size_t)c->cfg.max_views * c->max_draws;
+    ea.seg_count = c->d_seg_count + c->seg_parity * seg_words;
     ea.seg_key = c->d_seg_key;
     ea.seg_inst = c->d_seg_inst;
     ea.totals = c->d_totals;
@@ -630,7 +637,14 @@ SS_API ss_status ss_frame(ss_ctx* c, const ss_view* views, uint32_t n_views, uin
     da.n_views = n_views;
     da.max_draws = c->max_draws;
     da.totals = c->d_totals;
-    da.seg_count = c->d_seg_count;
+    da.seg_count = c->d_seg_count + c->seg_parity * seg_words;
+    da.seg_count_next = c->d_seg_count + (c->seg_parity ^ 1u) * seg_words;
+    da.runs_cur = c->d_seg_runs + c->seg_parity;
+    da.runs_next = c->d_seg_runs + (c->seg_parity ^ 1u);
+    da.passes_run = &reinterpret_cast<SortControl*>(c->d_sort_scratch)->passes_run;
+    da.host_stats = s.h_counts_dev;
+    da.stats_views = c->cfg.max_views;
+    c->seg_parity ^= 1u;
     da.seg_key = c->d_seg_key;
     da.seg_inst = c->d_seg_inst;
     da.slot = c->d_slot;
@@ -641,12 +655,7 @@ SS_API ss_status ss_frame(ss_ctx* c, const ss_view* views, uint32_t n_views, uin
     ++launches;
     SS_CUDA(c, cudaGetLastError());
 
-    const size_t V = c->cfg.max_views;
-    SS_CUDA(c, cudaMemcpyAsync(s.h_counts, s.counts_dev, V * 2 * sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
-    SS_CUDA(c, cudaMemcpyAsync(s.h_counts + V * 2, c->d_overflow, sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
-    SS_CUDA(c, cudaMemcpyAsync(s.h_counts + V * 2 + 1,
-                               &reinterpret_cast<SortControl*>(c->d_sort_scratch)->passes_run, sizeof(uint32_t),
-                               cudaMemcpyDeviceToHost, st));
+    // k_draws has written the counts, the overflow flag and passes_run into s.h_counts (mapped pinned memory)
     SS_CUDA(c, cudaEventRecord(s.done, st));
     s.pending = true;
     s.n_views = n_views;

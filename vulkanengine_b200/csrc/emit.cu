@@ -285,74 +285,146 @@ __global__ void __launch_bounds__(kEmitThreads) k_emit(const __grid_constant__ E
 }
 
 // one CTA per view: runs -> draws
-__global__ void __launch_bounds__(1024) k_draws(const __grid_constant__ DrawArgs a)
+constexpr int kDrawThreads = 256;
+constexpr int kDrawItems = 4;  // consecutive runs per thread
+constexpr int kDrawChunk = kDrawThreads * kDrawItems;
+constexpr int kDrawWarps = kDrawThreads / 32;
+
+// Grid (chunks of 1024 runs, views).  Run s of the sorted order becomes a draw of view v when its per-view count is
+// non-zero; draws keep the run order (= MeshKey order) and firstInstance is the exclusive sum of the counts.  A CTA
+// sums the counts of the chunks before its own itself (a few KB out of L2), so chunks need no hand-over; the
+// records are staged in shared memory and leave as whole lines.  The per-view counters are double-buffered by
+// frame: this frame's stay as they are, the other buffer is cleaned here for the next frame's k_emit.
+__global__ void __launch_bounds__(kDrawThreads) k_draws(const __grid_constant__ DrawArgs a)
 {
-    __shared__ uint32_t warp_c[32], warp_f[32];
-    __shared__ uint32_t carry_c, carry_f;
-    const uint32_t v = blockIdx.x;
+    __shared__ uint32_t sm_draw[kDrawChunk * 5];
+    __shared__ uint64_t sm_key[kDrawChunk];
+    __shared__ uint32_t warp_c[kDrawWarps], warp_f[kDrawWarps], pre_c[kDrawWarps], pre_f[kDrawWarps];
+    const uint32_t v = blockIdx.y, c0 = blockIdx.x * kDrawChunk;
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
-    uint32_t n_segs = a.totals[SS_MAX_VIEWS];
-    if (n_segs > a.max_draws) {
-        n_segs = a.max_draws;
-        if (tid == 0) *a.overflow = 1u;
+    const uint32_t n_raw = a.totals[SS_MAX_VIEWS];
+    const uint32_t n_segs = min(n_raw, a.max_draws);
+    const uint32_t n_dirty = min(*a.runs_next, a.max_draws);
+
+    uint32_t* nxt = a.seg_count_next + (size_t)v * a.max_draws;
+#pragma unroll
+    for (int j = 0; j < kDrawItems; ++j) {
+        const uint32_t i = c0 + j * kDrawThreads + tid;
+        if (i < n_dirty) nxt[i] = 0u;
     }
-    if (tid == 0) {
-        carry_c = 0;
-        carry_f = 0;
+    if (blockIdx.x == 0 && v == 0 && tid == 0) {
+        const uint32_t over = (n_raw > a.max_draws) ? 1u : 0u;
+        if (over) *a.overflow = 1u;
+        *a.runs_cur = n_segs;
+        a.host_stats[a.stats_views * 2] = *a.overflow | over;
+        a.host_stats[a.stats_views * 2 + 1] = *a.passes_run;
+    }
+    if (c0 >= n_segs && blockIdx.x != 0) return;
+
+    // counts and draws of the chunks before this one
+    const uint32_t* cnt = a.seg_count + (size_t)v * a.max_draws;
+    uint32_t pc = 0, pf = 0;
+#pragma unroll 4
+    for (uint32_t i = tid; i < c0; i += kDrawThreads) {
+        const uint32_t q = cnt[i];
+        pc += q;
+        pf += q ? 1u : 0u;
+    }
+    // this chunk: thread t owns runs c0 + 4t .. c0 + 4t + 3
+    const uint32_t first = c0 + tid * kDrawItems;
+    uint32_t c[kDrawItems], inst[kDrawItems];
+#pragma unroll
+    for (int j = 0; j < kDrawItems; ++j) {
+        const bool ok = first + j < n_segs;
+        c[j] = ok ? cnt[first + j] : 0u;
+        inst[j] = ok ? a.seg_inst[first + j] : 0u;
+    }
+    uint32_t sl[kDrawItems];
+#pragma unroll
+    for (int j = 0; j < kDrawItems; ++j) sl[j] = c[j] ? a.slot[inst[j]] : 0u;  // c != 0: a live instance, slot valid
+    uint32_t ic[kDrawItems], fi[kDrawItems];
+    int32_t vo[kDrawItems];
+    uint64_t sk[kDrawItems];
+#pragma unroll
+    for (int j = 0; j < kDrawItems; ++j) {
+        ic[j] = fi[j] = 0u;
+        vo[j] = 0;
+        sk[j] = 0ull;
+        if (c[j]) {
+            const SlotDev* sd = a.slots + sl[j];
+            ic[j] = sd->index_count;
+            fi[j] = sd->first_index;
+            vo[j] = sd->vertex_offset;
+            sk[j] = a.seg_key[first + j];
+        }
+    }
+#pragma unroll
+    for (int ofs = 16; ofs > 0; ofs >>= 1) {
+        pc += __shfl_xor_sync(0xffffffffu, pc, ofs);
+        pf += __shfl_xor_sync(0xffffffffu, pf, ofs);
+    }
+    uint32_t tc = 0, tf = 0;
+#pragma unroll
+    for (int j = 0; j < kDrawItems; ++j) {
+        tc += c[j];
+        tf += c[j] ? 1u : 0u;
+    }
+    uint32_t xc = tc, xf = tf;
+#pragma unroll
+    for (int ofs = 1; ofs < 32; ofs <<= 1) {
+        const uint32_t yc = __shfl_up_sync(0xffffffffu, xc, ofs), yf = __shfl_up_sync(0xffffffffu, xf, ofs);
+        if (lane >= ofs) {
+            xc += yc;
+            xf += yf;
+        }
+    }
+    if (lane == 31) {
+        warp_c[wid] = xc;
+        warp_f[wid] = xf;
+    }
+    if (lane == 0) {
+        pre_c[wid] = pc;
+        pre_f[wid] = pf;
     }
     __syncthreads();
-    uint32_t* cnt = a.seg_count + (size_t)v * a.max_draws;
-    const ViewOut& o = a.out[v];
-    for (uint32_t s0 = 0; s0 < n_segs; s0 += blockDim.x) {
-        const uint32_t sgm = s0 + tid;
-        uint32_t c = 0;
-        if (sgm < n_segs) {
-            c = cnt[sgm];
-            cnt[sgm] = 0;  // leave the accumulator clean for the next frame
-        }
-        const uint32_t f = c ? 1u : 0u;
-        uint32_t xc = c, xf = f;
+    uint32_t base_c = 0, base_f = 0, loc_c = 0, loc_f = 0, all_f = 0;
 #pragma unroll
-        for (int ofs = 1; ofs < 32; ofs <<= 1) {
-            uint32_t yc = __shfl_up_sync(0xffffffffu, xc, ofs), yf = __shfl_up_sync(0xffffffffu, xf, ofs);
-            if (lane >= ofs) {
-                xc += yc;
-                xf += yf;
-            }
+    for (int w = 0; w < kDrawWarps; ++w) {
+        base_c += pre_c[w];
+        base_f += pre_f[w];
+        if (w < wid) {
+            loc_c += warp_c[w];
+            loc_f += warp_f[w];
         }
-        if (lane == 31) {
-            warp_c[wid] = xc;
-            warp_f[wid] = xf;
-        }
-        __syncthreads();
-        uint32_t bc = carry_c, bf = carry_f;
-        for (int w = 0; w < wid; ++w) {
-            bc += warp_c[w];
-            bf += warp_f[w];
-        }
-        if (f) {
-            const uint32_t d = bf + xf - 1u;
-            const uint32_t inst = a.seg_inst[sgm];
-            const SlotDev* sd = a.slots + a.slot[inst];
-            ss_draw_cmd dc;
-            dc.index_count = sd->index_count;
-            dc.instance_count = c;
-            dc.first_index = sd->first_index;
-            dc.vertex_offset = sd->vertex_offset;
-            dc.first_instance = bc + xc - c;
-            o.draws[d] = dc;
-            o.draw_keys[d] = a.seg_key[sgm];
-        }
-        __syncthreads();
-        if (tid == (int)blockDim.x - 1) {
-            carry_c = bc + xc;
-            carry_f = bf + xf;
-        }
-        __syncthreads();
+        all_f += warp_f[w];
     }
-    if (tid == 0) {
-        o.counts[0] = a.totals[v];
-        o.counts[1] = carry_f;
+    uint32_t run_c = base_c + loc_c + xc - tc;  // instances of this view before this thread's first run
+    uint32_t run_f = loc_f + xf - tf;           // draws of this chunk before it
+#pragma unroll
+    for (int j = 0; j < kDrawItems; ++j) {
+        if (c[j]) {
+            uint32_t* d = sm_draw + run_f * 5;
+            d[0] = ic[j];
+            d[1] = c[j];
+            d[2] = fi[j];
+            d[3] = (uint32_t)vo[j];
+            d[4] = run_c;
+            sm_key[run_f] = sk[j];
+            run_c += c[j];
+            run_f += 1u;
+        }
+    }
+    __syncthreads();
+    const ViewOut& o = a.out[v];
+    uint32_t* dst = reinterpret_cast<uint32_t*>(o.draws + base_f);
+    for (uint32_t w = tid; w < all_f * 5; w += kDrawThreads) dst[w] = sm_draw[w];
+    for (uint32_t k = tid; k < all_f; k += kDrawThreads) o.draw_keys[base_f + k] = sm_key[k];
+    if (tid == 0 && c0 + kDrawChunk >= n_segs) {  // the chunk holding the last run (chunk 0 when there is none)
+        const uint32_t vis = a.totals[v], nd = base_f + all_f;
+        o.counts[0] = vis;
+        o.counts[1] = nd;
+        a.host_stats[v * 2 + 0] = vis;
+        a.host_stats[v * 2 + 1] = nd;
     }
 }
 
@@ -373,7 +445,7 @@ void launch_emit(const EmitArgs& a, cudaStream_t st)
 
 void launch_draws(const DrawArgs& a, cudaStream_t st)
 {
-    if (a.n_views) k_draws<<<a.n_views, 1024, 0, st>>>(a);
+    if (a.n_views) k_draws<<<dim3((a.max_draws + kDrawChunk - 1) / kDrawChunk, a.n_views), kDrawThreads, 0, st>>>(a);
 }
 
 }  // namespace ss

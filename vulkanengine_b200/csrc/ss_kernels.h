@@ -143,7 +143,13 @@ struct DrawArgs {
     uint32_t n_views;
     uint32_t max_draws;
     const uint32_t* totals;
-    uint32_t* seg_count;
+    const uint32_t* seg_count;     // [n_views][max_draws] per-view run counts of this frame (left as they are)
+    uint32_t* seg_count_next;      // the other buffer: zeroed here for the next frame's k_emit
+    uint32_t* runs_cur;            // out: number of runs this frame put into seg_count
+    const uint32_t* runs_next;     // runs the frame before last left in seg_count_next (bounds the zeroing)
+    const uint32_t* passes_run;    // SortControl::passes_run, forwarded to the host
+    uint32_t* host_stats;          // mapped pinned host words: [stats_views][2] visible/draws, overflow, passes_run
+    uint32_t stats_views;
     const uint64_t* seg_key;
     const uint32_t* seg_inst;
     const uint32_t* slot;
