@@ -386,6 +386,24 @@ def test_eight_views():
     assert any(int(got["stats"].visible[v]) > 0 for v in range(8))
 
 
+def test_item_major_output_ragged_tile_and_capacity():
+    """Eight views that all see (nearly) everything: every k_emit tile takes the item-major output order (each row
+    fetched once, stored to every view); 5000 instances leave a ragged last tile.  Then the same frame into a
+    context whose per-view capacity is too small: reported as SS_ERR_CAPACITY, not written out of bounds."""
+    sc = synth.flat_scene(5000, n_keys=37)
+    cam = synth.fibonacci_cameras(lambda *a: O.camera_view_proj(*a), 1, radius=1400.0)
+    cams = np.repeat(cam, 8)
+    ref = O.OracleScene(sc, 0).frame(cams)
+    got = run_gpu(sc, cams)
+    check_against_oracle(sc, cams, got, ref)
+    assert int(got["stats"].visible[0]) > 3 * 5000 // 4
+    ctx = S.SceneSubmit(sc.n_nodes, sc.n_instances, len(sc.slots), max_views=8, max_visible_per_view=1000)
+    ctx.load_scene(sc)
+    with pytest.raises(S.SceneSubmitError):
+        ctx.frame_sync(ctx.frame(cams))
+    ctx.close()
+
+
 def test_zero_instances():
     sc = synth.flat_scene(64, n_keys=8)
     empty = synth.SceneArrays(**{**sc.__dict__, "slot": sc.slot[:0], "matword": sc.matword[:0], "inst_aabb": sc.inst_aabb[:0]})

@@ -26,7 +26,13 @@ constexpr int kGatherBatch = 12;  // independent 16 B row gathers in flight per 
 struct EmitSmem {
     uint64_t key[kEmitTile];
     uint32_t idx[kEmitTile];
-    uint16_t list[SS_MAX_VIEWS][kEmitTile];          // local item ids of the visible items, per view
+    union {  // a tile uses one of the two output orders
+        uint16_t list[SS_MAX_VIEWS][kEmitTile];      // view-major: local item ids of the visible items, per view
+        struct {
+            uint64_t pos_a[kEmitTile], pos_b[kEmitTile];  // item-major: visible-before counts of views 0-3 / 4-7, 16 bits each
+        };
+    };
+    uint8_t msk[kEmitTile];                          // per item: visibility byte
     uint16_t seg_start[kEmitTile + 2][SS_MAX_VIEWS]; // visible-before count at the start of each local run
     uint64_t last_key[kEmitThreads];
     uint64_t warp_a[kEmitWarps], warp_b[kEmitWarps];
@@ -187,8 +193,15 @@ __global__ void __launch_bounds__(kEmitThreads) k_emit(const __grid_constant__ E
         if (tile == n_tiles - 1) a.totals[tid] = excl + mine;
     }
 
-    // local lists: where each visible item lands, and where each key run starts
+    // local lists: where each visible item lands, and where each key run starts.
+    // Two output orders, chosen per tile: view-major (a dense list per view; every store instruction is a full,
+    // contiguous line, but a row seen by k views is fetched k times) when items are seen by few views, item-major
+    // (each row fetched once and stored to every view that sees it) when they are seen by many.
     const uint32_t n_heads = s.total[SS_MAX_VIEWS];
+    uint32_t rows_out = 0;
+#pragma unroll
+    for (int v = 0; v < (int)SS_MAX_VIEWS; ++v) rows_out += s.total[v];
+    const bool item_major = rows_out > 3u * kEmitTile;
     if (tid < (int)SS_MAX_VIEWS) {
         s.seg_start[0][tid] = 0;
         s.seg_start[n_heads + 1][tid] = (uint16_t)s.total[tid];
@@ -203,11 +216,17 @@ __global__ void __launch_bounds__(kEmitThreads) k_emit(const __grid_constant__ E
                 s.seg_start[lseg][4 + v] = (uint16_t)(eb >> (16 * v));
             }
         }
+        if (item_major) {
+            s.pos_a[l0 + j] = ea;
+            s.pos_b[l0 + j] = eb;
+            s.msk[l0 + j] = (uint8_t)m[j];
+        } else {
 #pragma unroll
-        for (int v = 0; v < (int)SS_MAX_VIEWS; ++v) {
-            if ((m[j] >> v) & 1u) {
-                const uint32_t lpos = (uint32_t)((v < 4 ? ea >> (16 * v) : eb >> (16 * (v - 4))) & 0xffffu);
-                s.list[v][lpos] = (uint16_t)(l0 + j);
+            for (int v = 0; v < (int)SS_MAX_VIEWS; ++v) {
+                if ((m[j] >> v) & 1u) {
+                    const uint32_t lpos = (uint32_t)((v < 4 ? ea >> (16 * v) : eb >> (16 * (v - 4))) & 0xffffu);
+                    s.list[v][lpos] = (uint16_t)(l0 + j);
+                }
             }
         }
         ea += spread4(m[j] & 15u);
@@ -247,37 +266,90 @@ __global__ void __launch_bounds__(kEmitThreads) k_emit(const __grid_constant__ E
         }
     }
 
-    // per view: keys + instance ids, then the gathered rows, all as coalesced stores
-    for (uint32_t v = 0; v < a.n_views; ++v) {
-        const uint32_t cnt = s.total[v];
-        const uint32_t base = s.base[v];
-        const ViewOut& o = a.out[v];
-        if (base + cnt > a.cap_visible && tid == 0) *a.overflow = 1u;
-        for (uint32_t e = tid; e < cnt; e += kEmitThreads) {
-            const uint32_t li = s.list[v][e];
-            const uint32_t g = base + e;
-            if (g < a.cap_visible) {
-                o.keys[g] = s.key[li];
-                o.idx[g] = s.idx[li];
-            }
-        }
-        const uint32_t total4 = cnt * 3u;
-        for (uint32_t j0 = tid; j0 < total4; j0 += kEmitThreads * kGatherBatch) {
-            float4 r[kGatherBatch];
-#pragma unroll
-            for (int u = 0; u < kGatherBatch; ++u) {
-                const uint32_t j = j0 + u * kEmitThreads;
-                if (j < total4) {
-                    const uint32_t e = j / 3u, part = j - e * 3u;
-                    r[u] = __ldg(a.world + (size_t)s.idx[s.list[v][e]] * kWorldStride + part);
+    if (!item_major) {
+        // per view: keys + instance ids, then the gathered rows, all as coalesced stores
+        for (uint32_t v = 0; v < a.n_views; ++v) {
+            const uint32_t cnt = s.total[v];
+            const uint32_t base = s.base[v];
+            const ViewOut& o = a.out[v];
+            if (base + cnt > a.cap_visible && tid == 0) *a.overflow = 1u;
+            for (uint32_t e = tid; e < cnt; e += kEmitThreads) {
+                const uint32_t li = s.list[v][e];
+                const uint32_t g = base + e;
+                if (g < a.cap_visible) {
+                    o.keys[g] = s.key[li];
+                    o.idx[g] = s.idx[li];
                 }
             }
+            const uint32_t total4 = cnt * 3u;
+            for (uint32_t j0 = tid; j0 < total4; j0 += kEmitThreads * kGatherBatch) {
+                float4 r[kGatherBatch];
 #pragma unroll
-            for (int u = 0; u < kGatherBatch; ++u) {
-                const uint32_t j = j0 + u * kEmitThreads;
-                if (j < total4) {
-                    const uint32_t e = j / 3u;
-                    if (base + e < a.cap_visible) o.rows[(size_t)base * 3u + j] = r[u];
+                for (int u = 0; u < kGatherBatch; ++u) {
+                    const uint32_t j = j0 + u * kEmitThreads;
+                    if (j < total4) {
+                        const uint32_t e = j / 3u, part = j - e * 3u;
+                        r[u] = __ldg(a.world + (size_t)s.idx[s.list[v][e]] * kWorldStride + part);
+                    }
+                }
+#pragma unroll
+                for (int u = 0; u < kGatherBatch; ++u) {
+                    const uint32_t j = j0 + u * kEmitThreads;
+                    if (j < total4) {
+                        const uint32_t e = j / 3u;
+                        if (base + e < a.cap_visible) o.rows[(size_t)base * 3u + j] = r[u];
+                    }
+                }
+            }
+        }
+        return;
+    }
+
+    // Item-major output: every visible item's keys / id / row are read once and stored to each view that sees it,
+    // at base[v] + (visible-before count of view v).  Consecutive threads hold consecutive items (and row
+    // parts), so the stores of one view land next to each other.
+    for (uint32_t v = tid; v < a.n_views; v += kEmitThreads)
+        if (s.base[v] + s.total[v] > a.cap_visible) *a.overflow = 1u;
+#pragma unroll
+    for (int u = 0; u < kEmitItems; ++u) {
+        const uint32_t e = tid + u * kEmitThreads;
+        const uint32_t mm = s.msk[e];
+        if (mm) {
+            const uint64_t pa2 = s.pos_a[e], pb2 = s.pos_b[e], k = s.key[e];
+            const uint32_t ix = s.idx[e];
+#pragma unroll
+            for (int v = 0; v < (int)SS_MAX_VIEWS; ++v) {
+                if ((mm >> v) & 1u) {
+                    const uint32_t g = s.base[v] + ((uint32_t)((v < 4 ? pa2 >> (16 * v) : pb2 >> (16 * (v - 4)))) & 0xffffu);
+                    if (g < a.cap_visible) {
+                        a.out[v].keys[g] = k;
+                        a.out[v].idx[g] = ix;
+                    }
+                }
+            }
+        }
+    }
+    constexpr int kParts = kEmitTile * 3 / kEmitThreads;  // (item, row part) pairs per thread
+    static_assert(kParts == kGatherBatch, "one batch of gathers covers the tile");
+    float4 r[kGatherBatch];
+#pragma unroll
+    for (int u = 0; u < kGatherBatch; ++u) {
+        const uint32_t j = tid + u * kEmitThreads;
+        const uint32_t e = j / 3u, part = j - e * 3u;
+        if (s.msk[e]) r[u] = __ldg(a.world + (size_t)s.idx[e] * kWorldStride + part);
+    }
+#pragma unroll
+    for (int u = 0; u < kGatherBatch; ++u) {
+        const uint32_t j = tid + u * kEmitThreads;
+        const uint32_t e = j / 3u, part = j - e * 3u;
+        const uint32_t mm = s.msk[e];
+        if (mm) {
+            const uint64_t pa2 = s.pos_a[e], pb2 = s.pos_b[e];
+#pragma unroll
+            for (int v = 0; v < (int)SS_MAX_VIEWS; ++v) {
+                if ((mm >> v) & 1u) {
+                    const uint32_t g = s.base[v] + ((uint32_t)((v < 4 ? pa2 >> (16 * v) : pb2 >> (16 * (v - 4)))) & 0xffffu);
+                    if (g < a.cap_visible) a.out[v].rows[(size_t)g * 3u + part] = r[u];
                 }
             }
         }
