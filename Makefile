@@ -16,14 +16,14 @@ OBJS     := $(patsubst $(CSRC)/%.cu,$(OBJDIR)/%.o,$(CU)) $(patsubst $(CSRC)/%.cp
 HDRS     := $(wildcard $(CSRC)/*.h $(CSRC)/*.cuh include/*.h)
 
 HOSTBIN  := vulkanengine_b200/host/host_cli.bin
-HOSTSRC  := vulkanengine_b200/host/Scene.cpp vulkanengine_b200/host/host_cli.cpp
-HOSTHDR  := vulkanengine_b200/host/Scene.h vulkanengine_b200/host/Core.h include/scenesubmit.h
+HOSTSRC  := vulkanengine_b200/host/Scene.cpp vulkanengine_b200/host/SceneSerializer.cpp vulkanengine_b200/host/MeshImporter.cpp vulkanengine_b200/host/host_cli.cpp
+HOSTHDR  := $(wildcard vulkanengine_b200/host/*.h) include/scenesubmit.h
 
 all: $(LIB) $(HOSTBIN)
 
 # C++ host mirror of Scene / SceneRenderer: plain g++, links the C ABI only
 $(HOSTBIN): $(HOSTSRC) $(HOSTHDR) $(LIB)
-	g++ -std=c++17 -O2 -Wall -ffp-contract=off -o $@ $(HOSTSRC) -Lvulkanengine_b200 -lscenesubmit \
+	g++ -std=c++17 -O2 -Wall -ffp-contract=off -o $@ $(HOSTSRC) -Lvulkanengine_b200 -lscenesubmit -lz \
 	    -Wl,-rpath,'$$ORIGIN/..'
 
 host: $(HOSTBIN)

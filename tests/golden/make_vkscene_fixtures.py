@@ -17,7 +17,7 @@ REF = "/root/reference/VulkanCore/assets"
 HERE = os.path.dirname(os.path.abspath(__file__))
 
 
-def main():
+def main(REF=REF, out_name="vkscenes.json", source="VulkanCore/assets/scenes/*.vkscene @ reference commit fe134a6c"):
     reg = yaml.safe_load(open(os.path.join(REF, "AssetRegistry.vkr")))["Asset Registry"]
     by_handle = {int(e["Handle"]): e["Metadata"] for e in reg}
     materials = {}
@@ -27,7 +27,8 @@ def main():
             tess = False
             if os.path.exists(path):
                 m = yaml.safe_load(open(path))["Material"]
-                tess = int(m.get("DisplacementHandle", 0) or 0) != 0
+                dh = int(m.get("DisplacementHandle", 0) or 0)
+                tess = dh != 0 and dh in by_handle  # MaterialAssetImporter.cpp:144-181: the handle must be a valid asset
             materials[str(h)] = {"file": md["Filepath"], "tessellated": tess}
     scenes = {}
     for path in sorted(glob.glob(os.path.join(REF, "scenes", "*.vkscene"))):
@@ -38,6 +39,7 @@ def main():
             # serialized without one
             tc = e.get("TransformComponent", {"Translation": [0, 0, 0], "Rotation": [0, 0, 0], "Scale": [1, 1, 1]})
             ent = {"uuid": str(int(e["Entity"])), "tag": e.get("TagComponent", {}).get("Tag", ""),
+                   "has_transform": "TransformComponent" in e,
                    "translation": [float(x) for x in tc["Translation"]], "rotation": [float(x) for x in tc["Rotation"]],
                    "scale": [float(x) for x in tc["Scale"]], "mesh": None, "materials": {}}
             mc = e.get("MeshComponent")
@@ -47,10 +49,12 @@ def main():
             dl = e.get("DirectionalLightComponent")
             if dl and "Direction" in dl:
                 ent["light_direction"] = [float(x) for x in dl["Direction"]]
+            # the submission walk is view<TransformComponent, MeshComponent>: a mesh without a transform would never draw
+            assert ent["has_transform"] or ent["mesh"] is None, (path, ent["uuid"])
             ents.append(ent)
         scenes[os.path.splitext(os.path.basename(path))[0]] = ents
-    out = {"source": "VulkanCore/assets/scenes/*.vkscene @ reference commit fe134a6c", "materials": materials, "scenes": scenes}
-    json.dump(out, open(os.path.join(HERE, "vkscenes.json"), "w"), indent=1)
+    out = {"source": source, "materials": materials, "scenes": scenes}
+    json.dump(out, open(os.path.join(HERE, out_name), "w"), indent=1)
     print({k: (len(v), sum(1 for e in v if e["mesh"])) for k, v in scenes.items()})
 
 

@@ -153,6 +153,8 @@ def flatten_case(case):
             for k in range(int(case.table_begin[t]), int(case.table_begin[t + 1])):
                 if int(case.entry_index[k]) == int(case.sub_material_index[s]) and int(case.entry_handle[k]) != 0:
                     handle, tess = int(case.entry_handle[k]), int(case.entry_tess[k])
+            if handle == 0:  # no table entry and no base material: left out (host/Scene.cpp resolve_material)
+                continue
             rank = int(np.searchsorted(mat_sorted, np.uint64(handle)))
             node.append(e)
             slot.append(s)
@@ -163,9 +165,15 @@ def flatten_case(case):
     slots["local"] = case.sub_local
     slots["aabb_min"] = case.sub_aabb[:, :3]
     slots["aabb_max"] = case.sub_aabb[:, 3:]
-    slots["index_count"] = 3 * (np.arange(n_sub) + 10)
-    slots["first_index"] = 1000 * np.arange(n_sub)
-    slots["vertex_offset"] = 77 * np.arange(n_sub)
+    counts = getattr(case, "sub_counts", None)  # [s][BaseVertex, BaseIndex, VertexCount, IndexCount] when the case has real tables
+    if counts is None:
+        slots["index_count"] = 3 * (np.arange(n_sub) + 10)
+        slots["first_index"] = 1000 * np.arange(n_sub)
+        slots["vertex_offset"] = 77 * np.arange(n_sub)
+    else:
+        slots["index_count"] = counts[:, 3]
+        slots["first_index"] = counts[:, 1]
+        slots["vertex_offset"] = counts[:, 0]
     slots["mesh_rank"] = np.searchsorted(mesh_sorted, case.mesh_handle[mesh_of_sub])
     slots["submesh_index"] = np.arange(n_sub) - case.mesh_sub_begin[mesh_of_sub]
     sc = synth.SceneArrays(trs=case.trs, parent=case.parent, level_offsets=case.level_offsets,

@@ -25,6 +25,8 @@ def write_pack(case, path):
               case.sub_local.astype(np.float32), case.sub_aabb.astype(np.float32), case.table_begin.astype(np.uint32),
               case.entry_index.astype(np.uint32), case.entry_handle.astype(np.uint64), case.entry_tess.astype(np.uint8),
               CAMERA]
+    if getattr(case, "sub_counts", None) is not None:
+        blocks.append(case.sub_counts.astype(np.uint32))
     with open(path, "wb") as f:
         for b in blocks:
             b = np.ascontiguousarray(b)

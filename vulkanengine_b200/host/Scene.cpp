@@ -8,14 +8,21 @@ namespace VulkanCore {
 
 // ---- Scene ---------------------------------------------------------------------------------------
 
-Entity Scene::CreateEntity(const std::string& name) { return CreateEntityWithUUID(m_NextUUID++, name); }
+// Scene.cpp:83-89: a fresh UUID and a default TransformComponent.
+Entity Scene::CreateEntity(const std::string& name)
+{
+    Entity e = CreateEntityWithUUID(m_NextUUID++, name);
+    e.AddComponent<TransformComponent>();
+    return e;
+}
 
+// Scene.cpp:91-124: ID + Tag only (the tag bookkeeping is editor-side and not mirrored).  No TransformComponent:
+// the deserializer adds one only when the file has it (SceneSerializer.cpp:352-360), so an entity saved without
+// one stays outside view<TransformComponent, MeshComponent>.
 Entity Scene::CreateEntityWithUUID(UUID uuid, const std::string&)
 {
-    // the reference gives every entity an ID, a Transform and a Tag (Scene.cpp: CreateEntityWithUUID)
     Entity e{m_Registry.create(), this};
     m_Registry.emplace<IDComponent>((entity)(uint32_t)e, IDComponent{uuid});
-    m_Registry.emplace<TransformComponent>((entity)(uint32_t)e);
     ++m_StructureVersion;
     return e;
 }
@@ -53,6 +60,9 @@ Resolved resolve_material(const Mesh& mesh, const MaterialTable* table, const Ma
     std::shared_ptr<MaterialAsset> m = (materialIndex >= 0 && table->HasMaterial((uint32_t)materialIndex))
                                            ? table->GetMaterial((uint32_t)materialIndex)
                                            : mesh.GetMeshSource()->GetBaseMaterial();
+    // neither a table entry nor a base material: the reference would dereference null here (:1146); the mirror
+    // leaves that submesh out
+    if (!m) return {0, false};
     return {m->Handle, m->HasDisplacementTexture()};
 }
 
@@ -138,7 +148,10 @@ FlatScene SceneRenderer::Flatten(Scene& scene, const std::vector<AdHocInstance>&
     std::vector<AssetHandle> mats;
     for (const Pending& p : pend) {
         meshes[p.mesh->Handle] = p.mesh;
-        for (uint32_t s : p.mesh->GetSubmeshes()) mats.push_back(resolve_material(*p.mesh, p.table, p.forced, s).material);
+        for (uint32_t s : p.mesh->GetSubmeshes()) {
+            const AssetHandle m = resolve_material(*p.mesh, p.table, p.forced, s).material;
+            if (m) mats.push_back(m);
+        }
     }
     std::sort(mats.begin(), mats.end());
     mats.erase(std::unique(mats.begin(), mats.end()), mats.end());
@@ -173,6 +186,7 @@ FlatScene SceneRenderer::Flatten(Scene& scene, const std::vector<AdHocInstance>&
     for (const Pending& p : pend) {
         for (uint32_t s : p.mesh->GetSubmeshes()) {
             const Resolved r = resolve_material(*p.mesh, p.table, p.forced, s);
+            if (!r.material) continue;
             const uint32_t rank = (uint32_t)(std::lower_bound(mats.begin(), mats.end(), r.material) - mats.begin());
             f.node.push_back(p.node);
             f.slot.push_back(slotBase[p.mesh->Handle] + s);

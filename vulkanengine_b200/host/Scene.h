@@ -98,17 +98,60 @@ struct MeshComponent {  // Components.h:86-93
     std::shared_ptr<MaterialTable> MaterialTableHandle;
 };
 
-class AssetManager {  // the one lookup the hot loop performs (Scene.cpp:144)
+enum class AssetType { None, Scene, Texture2D, TextureCube, Mesh, MeshAsset, Material };  // Asset/Asset.cpp:10-42
+
+struct AssetMetadata {  // Asset/AssetMetadata.h
+    std::string FilePath;
+    AssetType Type = AssetType::None;
+};
+
+class AssetManager {  // the one lookup the hot loop performs (Scene.cpp:144) + the on-disk registry behind it
 public:
     static void Register(const std::shared_ptr<Mesh>& mesh) { Meshes()[mesh->Handle] = mesh; }
+    // a mesh that is registered, or named by the loaded registry (then imported on first use, Asset/MeshImporter.cpp)
     static std::shared_ptr<Mesh> GetMesh(AssetHandle h)
     {
         auto it = Meshes().find(h);
-        return it == Meshes().end() ? nullptr : it->second;
+        if (it != Meshes().end()) return it->second;
+        return RegistryMap().empty() ? nullptr : LoadMesh(h);
     }
-    static void Clear() { Meshes().clear(); }
+    static void Clear();
+
+    // AssetRegistry.vkr in `assetDirectory` (Asset/AssetManager.cpp:32-65); file paths inside are relative to it
+    static bool LoadRegistryFromFile(const std::string& assetDirectory);
+    static bool IsAssetHandleValid(AssetHandle h) { return h != 0 && RegistryMap().count(h) != 0; }
+    static const std::map<AssetHandle, AssetMetadata>& GetAssetRegistry() { return RegistryMap(); }
+    // .vkmat -> the one property the submission path reads (Asset/MaterialAssetImporter.cpp:144-181); nullptr when unknown
+    static std::shared_ptr<MaterialAsset> GetMaterialAsset(AssetHandle h);
+    static const std::string& LastImportError() { return ImportError(); }
 
 private:
+    static std::shared_ptr<Mesh> LoadMesh(AssetHandle h);
+    static std::map<AssetHandle, AssetMetadata>& RegistryMap()
+    {
+        static std::map<AssetHandle, AssetMetadata> s;
+        return s;
+    }
+    static std::map<AssetHandle, std::shared_ptr<MaterialAsset>>& Materials()
+    {
+        static std::map<AssetHandle, std::shared_ptr<MaterialAsset>> s;
+        return s;
+    }
+    static std::map<AssetHandle, std::shared_ptr<MeshSource>>& Sources()
+    {
+        static std::map<AssetHandle, std::shared_ptr<MeshSource>> s;
+        return s;
+    }
+    static std::string& Directory()
+    {
+        static std::string s;
+        return s;
+    }
+    static std::string& ImportError()
+    {
+        static std::string s;
+        return s;
+    }
     static std::map<AssetHandle, std::shared_ptr<Mesh>>& Meshes()
     {
         static std::map<AssetHandle, std::shared_ptr<Mesh>> s;

@@ -2,8 +2,12 @@
 //
 //   host_cli flatten <pack> <out>     build the scene through the mirror API, dump the flattened streams (no GPU)
 //   host_cli render  <pack> <out>     additionally RenderScene() on cuda:0 and dump per-view draw lists + rows
+//   host_cli load-flatten <assets_dir> <scene.vkscene> <out>   the same two dumps for a scene read from the reference's
+//   host_cli load-render  <assets_dir> <scene.vkscene> <out>   own files (AssetRegistry.vkr, .vkscene, .vkmesh, .vkmat, FBX),
+//                                                               preceded by what the loader read (entities, submesh tables)
 //
 // Pack / dump format: a sequence of blocks, each  uint64 byte_count  followed by the raw bytes.
+#include <algorithm>
 #include <cstdio>
 #include <cstdlib>
 #include <stdexcept>
@@ -11,6 +15,7 @@
 #include <vector>
 
 #include "Scene.h"
+#include "SceneSerializer.h"
 
 using namespace VulkanCore;
 
@@ -42,17 +47,10 @@ struct Writer {
     void block(const std::vector<T>& v) { block(v.data(), v.size()); }
 };
 
-}  // namespace
-
-int main(int argc, char** argv)
+// scene described by a pack written by the tests (tests/test_host_mirror.py)
+std::shared_ptr<Scene> scene_from_pack(const char* path, std::vector<float>& camera)
 {
-    if (argc < 4) {
-        fprintf(stderr, "usage: host_cli flatten|render <pack> <out>\n");
-        return 2;
-    }
-    const std::string mode = argv[1];
-    try {
-        FILE* in = fopen(argv[2], "rb");
+        FILE* in = fopen(path, "rb");
         if (!in) throw std::runtime_error("cannot open pack");
         Reader rd{in};
         auto trs = rd.block<float>();             // [n][9]
@@ -72,7 +70,16 @@ int main(int argc, char** argv)
         auto entryIndex = rd.block<uint32_t>();
         auto entryHandle = rd.block<uint64_t>();
         auto entryTess = rd.block<uint8_t>();
-        auto camera = rd.block<float>();          // fov aspect near far px py pz pitch yaw
+        camera = rd.block<float>();          // fov aspect near far px py pz pitch yaw
+        std::vector<uint32_t> subCounts;     // optional: [s][BaseVertex, BaseIndex, VertexCount, IndexCount]
+        {
+            const long at = ftell(in);
+            uint64_t bytes = 0;
+            if (fread(&bytes, 8, 1, in) == 1) {
+                fseek(in, at, SEEK_SET);
+                subCounts = rd.block<uint32_t>();
+            }
+        }
         fclose(in);
 
         const size_t n = trs.size() / 9, m = meshHandle.size(), t = tableBegin.size() - 1;
@@ -97,14 +104,21 @@ int main(int argc, char** argv)
                 std::memcpy(&sm.LocalTransform, &subLocal[(size_t)s * 16], 64);
                 sm.BoundsMin = {subAabb[s * 6 + 0], subAabb[s * 6 + 1], subAabb[s * 6 + 2]};
                 sm.BoundsMax = {subAabb[s * 6 + 3], subAabb[s * 6 + 4], subAabb[s * 6 + 5]};
-                sm.IndexCount = 3 * (s + 10);
-                sm.BaseIndex = 1000 * s;
-                sm.BaseVertex = 77 * s;
-                // spread the mesh's vertex count over its submeshes (0 stays 0: the zero-vertex early-out)
-                sm.VertexCount = meshVertexCount[k] / ns + (s == meshSubBegin[k] ? meshVertexCount[k] % ns : 0);
+                if (subCounts.size() >= (size_t)(s + 1) * 4) {  // the pack carries real counts
+                    sm.BaseVertex = subCounts[s * 4 + 0];
+                    sm.BaseIndex = subCounts[s * 4 + 1];
+                    sm.VertexCount = subCounts[s * 4 + 2];
+                    sm.IndexCount = subCounts[s * 4 + 3];
+                } else {
+                    sm.IndexCount = 3 * (s + 10);
+                    sm.BaseIndex = 1000 * s;
+                    sm.BaseVertex = 77 * s;
+                    // spread the mesh's vertex count over its submeshes (0 stays 0: the zero-vertex early-out)
+                    sm.VertexCount = meshVertexCount[k] / ns + (s == meshSubBegin[k] ? meshVertexCount[k] % ns : 0);
+                }
                 src->GetSubmeshes().push_back(sm);
             }
-            src->SetBaseMaterial(material(baseMatHandle[k], baseMatTess[k] != 0));
+            src->SetBaseMaterial(baseMatHandle[k] ? material(baseMatHandle[k], baseMatTess[k] != 0) : nullptr);
             meshes[k] = std::make_shared<Mesh>(src);
             meshes[k]->Handle = meshHandle[k];
             AssetManager::Register(meshes[k]);
@@ -133,10 +147,87 @@ int main(int argc, char** argv)
             }
         }
 
-        FILE* out = fopen(argv[3], "wb");
+        return scene;
+}
+
+// what the loader read, ahead of the flatten / render dump
+void dump_loaded(Writer& wr, Scene& scene)
+{
+    Registry& reg = scene.m_Registry;
+    std::vector<uint64_t> uuid, meshHandle;
+    std::vector<uint8_t> hasTransform;
+    std::vector<float> trs;
+    for (entity e = 0; e < reg.alive(); ++e) {
+        uuid.push_back(reg.get<IDComponent>(e).ID);
+        hasTransform.push_back(reg.all_of<TransformComponent>(e));
+        meshHandle.push_back(reg.all_of<MeshComponent>(e) ? reg.get<MeshComponent>(e).MeshHandle : 0);
+        if (hasTransform.back()) {
+            const TransformComponent& t = reg.get<TransformComponent>(e);
+            const float v[9] = {t.Translation.x, t.Translation.y, t.Translation.z, t.Rotation.x, t.Rotation.y, t.Rotation.z, t.Scale.x, t.Scale.y, t.Scale.z};
+            trs.insert(trs.end(), v, v + 9);
+        }
+    }
+    wr.block(uuid);
+    wr.block(hasTransform);
+    wr.block(meshHandle);
+    wr.block(trs);
+    const vec3 ld = scene.GetDirectionalLightDirection();
+    const float l[3] = {ld.x, ld.y, ld.z};
+    wr.block(l, 3);
+    // submesh tables of the meshes the scene names, in order of first use
+    std::vector<uint64_t> seen;
+    std::vector<uint32_t> counts, ints;
+    std::vector<float> floats;
+    for (uint64_t h : meshHandle) {
+        if (!h || std::find(seen.begin(), seen.end(), h) != seen.end()) continue;
+        seen.push_back(h);
+        std::shared_ptr<Mesh> mesh = AssetManager::GetMesh(h);
+        counts.push_back(mesh ? (uint32_t)mesh->GetMeshSource()->GetSubmeshes().size() : 0u);
+        if (!mesh) continue;
+        for (const Submesh& sm : mesh->GetMeshSource()->GetSubmeshes()) {
+            const uint32_t iv[5] = {sm.BaseVertex, sm.BaseIndex, sm.VertexCount, sm.IndexCount, (uint32_t)sm.MaterialIndex};
+            ints.insert(ints.end(), iv, iv + 5);
+            floats.insert(floats.end(), sm.LocalTransform.data(), sm.LocalTransform.data() + 16);
+            const float bb[6] = {sm.BoundsMin.x, sm.BoundsMin.y, sm.BoundsMin.z, sm.BoundsMax.x, sm.BoundsMax.y, sm.BoundsMax.z};
+            floats.insert(floats.end(), bb, bb + 6);
+        }
+    }
+    wr.block(seen);
+    wr.block(counts);
+    wr.block(ints);
+    wr.block(floats);
+}
+
+}  // namespace
+
+int main(int argc, char** argv)
+{
+    const std::string mode = argc > 1 ? argv[1] : "";
+    const bool from_files = mode == "load-flatten" || mode == "load-render";
+    if (argc < (from_files ? 5 : 4) || !(from_files || mode == "flatten" || mode == "render")) {
+        fprintf(stderr, "usage: host_cli flatten|render <pack> <out>\n       host_cli load-flatten|load-render <assets_dir> <scene.vkscene> <out>\n");
+        return 2;
+    }
+    try {
+        std::vector<float> camera;
+        std::shared_ptr<Scene> scene;
+        if (from_files) {
+            AssetManager::Clear();
+            if (!AssetManager::LoadRegistryFromFile(argv[2])) throw std::runtime_error("cannot read AssetRegistry.vkr");
+            scene = std::make_shared<Scene>();
+            SceneSerializer serializer(scene);
+            if (!serializer.Deserialize(argv[3])) throw std::runtime_error("cannot deserialize scene");
+            if (!AssetManager::LastImportError().empty()) fprintf(stderr, "host_cli: %s\n", AssetManager::LastImportError().c_str());
+        } else {
+            scene = scene_from_pack(argv[2], camera);
+        }
+        const bool render = mode == "render" || mode == "load-render";
+
+        FILE* out = fopen(argv[from_files ? 4 : 3], "wb");
         if (!out) throw std::runtime_error("cannot open output");
         Writer wr{out};
-        if (mode == "flatten") {
+        if (from_files) dump_loaded(wr, *scene);
+        if (!render) {
             FlatScene f = SceneRenderer::Flatten(*scene, {});
             wr.block(f.node);
             wr.block(f.slot);
@@ -152,10 +243,12 @@ int main(int argc, char** argv)
         } else {
             SceneRenderer renderer(0);
             renderer.SetActiveScene(scene);
-            EditorCameraData cam;
+            EditorCameraData cam;  // EditorLayer.cpp:75 defaults unless the pack names a camera
+            if (camera.size() >= 9) {
             cam.FOV = camera[0]; cam.AspectRatio = camera[1]; cam.NearClip = camera[2]; cam.FarClip = camera[3];
             cam.Position = {camera[4], camera[5], camera[6]};
             cam.Pitch = camera[7]; cam.Yaw = camera[8];
+            }
             renderer.SetSceneEditorData(cam);
             renderer.RenderScene();
             renderer.RenderScene();  // a second frame: slots rotate, static streams must not be rebuilt
