@@ -404,6 +404,62 @@ def test_item_major_output_ragged_tile_and_capacity():
     ctx.close()
 
 
+def test_whole_stream_trs_uploads_overlap_frames_and_stay_ordered():
+    """Whole-stream TRS uploads of >= 2^16 nodes go to a second device buffer on their own stream (so the copy of the
+    next frame's transforms overlaps this frame's kernels); ss_frame adopts the newest one.  Frames must see exactly
+    the transforms uploaded before them: several frames in flight, two whole uploads in a row, a dirty range on top of
+    a whole upload, a frame with no upload in between."""
+    n = 70_000
+    sc = synth.flat_scene(n, n_keys=64)
+    views = oracle_views(5)
+    ctx = S.SceneSubmit(sc.n_nodes, n, len(sc.slots), max_views=5)
+    ctx.load_scene(sc)
+    rng = np.random.default_rng(5)
+
+    def variant(k):
+        t = sc.trs.copy()
+        t[:, 0] += np.float32(0.25 * k)
+        t[:, 4] += np.float32(0.01 * k)
+        return t
+
+    def expect(trs):
+        return O.OracleScene(synth.SceneArrays(**{**sc.__dict__, "trs": trs}), 0).frame(views)
+
+    # three frames in flight, each preceded by its own whole upload; results read afterwards
+    pinned = [np.ascontiguousarray(variant(k)) for k in range(1, 4)]
+    slots = []
+    for t in pinned:
+        ctx.upload_trs(t)
+        slots.append(ctx.frame(views))
+    for t, slot in zip(pinned, slots):
+        st = ctx.frame_sync(slot)
+        ref = expect(t)
+        for v in range(5):
+            got = ctx.download_view(slot, v, st)
+            assert np.array_equal(got["idx"], ref["views"][v]["idx"]) and np.array_equal(got["rows"], ref["views"][v]["rows"])
+    assert np.array_equal(ctx.download_world(), expect(pinned[-1])["rows"])
+    # two whole uploads in a row: the later one wins; then a dirty range on top of it
+    a, b = variant(7), variant(8)
+    ctx.upload_trs(a)
+    ctx.upload_trs(b)
+    lo, cnt = 1234, 4321
+    b2 = b.copy()
+    b2[lo:lo + cnt, :3] = rng.uniform(-100, 100, (cnt, 3)).astype(np.float32)
+    ctx.upload_trs(np.ascontiguousarray(b2[lo:lo + cnt]), first=lo)
+    st = ctx.frame_sync(ctx.frame(views))
+    ref = expect(b2)
+    assert np.array_equal(ctx.download_world(), ref["rows"]) and np.array_equal(ctx.download_masks(), ref["masks"])
+    # a dirty range alone, then a frame with no upload at all
+    b3 = b2.copy()
+    b3[:100, 2] -= np.float32(3.0)
+    ctx.upload_trs(np.ascontiguousarray(b3[:100]), first=0)
+    ctx.frame_sync(ctx.frame(views))
+    assert np.array_equal(ctx.download_world(), expect(b3)["rows"])
+    ctx.frame_sync(ctx.frame(views))
+    assert np.array_equal(ctx.download_world(), expect(b3)["rows"])
+    ctx.close()
+
+
 def test_zero_instances():
     sc = synth.flat_scene(64, n_keys=8)
     empty = synth.SceneArrays(**{**sc.__dict__, "slot": sc.slot[:0], "matword": sc.matword[:0], "inst_aabb": sc.inst_aabb[:0]})

@@ -46,7 +46,17 @@ struct ss_ctx {
     std::vector<void*> allocs;
 
     // static streams
-    float* d_trs = nullptr;
+    float* d_trs = nullptr;            // = d_trs_buf[trs_cur]
+    // Whole-stream TRS uploads go to the other buffer on their own stream, so that the copy of frame f+1's
+    // transforms overlaps frame f's kernels; ss_frame adopts the new buffer.  Partial (dirty-range) uploads
+    // write into the current buffer on the frame stream.
+    float* d_trs_buf[2] = {nullptr, nullptr};
+    int trs_cur = 0;
+    bool trs_swap_pending = false;
+    cudaStream_t upload_stream = nullptr;
+    cudaStream_t download_stream = nullptr;  // reads of a fenced slot must not queue behind later frames
+    cudaEvent_t ev_upload_done = nullptr;
+    cudaEvent_t ev_trs_read[2] = {nullptr, nullptr};  // last frame that read each buffer has passed its transform stage
     int32_t* d_parent = nullptr;
     float4* d_node_world = nullptr;
     uint32_t* d_node = nullptr;
@@ -185,7 +195,13 @@ SS_API void ss_destroy(ss_ctx* c)
 {
     if (!c) return;
     cudaSetDevice(c->device);
+    if (c->upload_stream) cudaStreamSynchronize(c->upload_stream);
     if (c->stream) cudaStreamSynchronize(c->stream);
+    if (c->ev_upload_done) cudaEventDestroy(c->ev_upload_done);
+    for (cudaEvent_t e : c->ev_trs_read)
+        if (e) cudaEventDestroy(e);
+    if (c->upload_stream) cudaStreamDestroy(c->upload_stream);
+    if (c->download_stream) cudaStreamDestroy(c->download_stream);
     for (Slot& s : c->slots) {
         if (s.done) cudaEventDestroy(s.done);
         if (s.start) cudaEventDestroy(s.start);
@@ -246,11 +262,17 @@ SS_API ss_status ss_create(const ss_config* cfg, ss_ctx** out)
 
     TRY(cudaSetDevice(c->device));
     TRY(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+    TRY(cudaStreamCreateWithFlags(&c->upload_stream, cudaStreamNonBlocking));
+    TRY(cudaStreamCreateWithFlags(&c->download_stream, cudaStreamNonBlocking));
+    TRY(cudaEventCreateWithFlags(&c->ev_upload_done, cudaEventDisableTiming));
+    for (cudaEvent_t& e : c->ev_trs_read) TRY(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
     if (const char* g = getenv("SS_L2_FETCH_GRANULARITY")) {  // experiment knob: 32 / 64 / 128 bytes
         const int v = atoi(g);
         if (v == 32 || v == 64 || v == 128) cudaDeviceSetLimit(cudaLimitMaxL2FetchGranularity, (size_t)v);
     }
-    TRY(dev_alloc(c, &c->d_trs, NN * 9));
+    TRY(dev_alloc(c, &c->d_trs_buf[0], NN * 9));
+    TRY(dev_alloc(c, &c->d_trs_buf[1], NN * 9));
+    c->d_trs = c->d_trs_buf[0];
     TRY(dev_alloc(c, &c->d_parent, NN));
     TRY(dev_alloc(c, &c->d_node_world, NN * 3));
     TRY(dev_alloc(c, &c->d_node, N));
@@ -436,16 +458,42 @@ SS_API ss_status ss_set_instance_aabbs(ss_ctx* c, uint32_t first, uint32_t count
     return SS_OK;
 }
 
+namespace {
+
+constexpr uint32_t kAsyncUploadMinNodes = 1u << 16;  // below this a second stream buys nothing
+
+// A whole-stream upload is waiting in the other TRS buffer: the frame stream takes it over.
+cudaError_t adopt_pending_upload(ss_ctx* c)
+{
+    if (!c->trs_swap_pending) return cudaSuccess;
+    cudaError_t e = cudaStreamWaitEvent(c->stream, c->ev_upload_done, 0);
+    if (e != cudaSuccess) return e;
+    c->trs_cur ^= 1;
+    c->d_trs = c->d_trs_buf[c->trs_cur];
+    c->trs_swap_pending = false;
+    return cudaSuccess;
+}
+
+}  // namespace
+
 SS_API ss_status ss_upload_trs(ss_ctx* c, uint32_t first, uint32_t count, const float* trs9)
 {
     if (!c) return SS_ERR_INVALID;
     if (!trs9 || (uint64_t)first + count > c->n_nodes)
         return c->fail(SS_ERR_INVALID, "ss_upload_trs: range [%u, +%u) exceeds %u nodes", first, count, c->n_nodes);
     SS_CUDA(c, cudaSetDevice(c->device));
-    if (count)
-        c->world_valid = false;  // transforms changed
-        SS_CUDA(c, cudaMemcpyAsync(c->d_trs + (size_t)first * 9, trs9, (size_t)count * 36, cudaMemcpyHostToDevice,
-                                   c->stream));
+    if (!count) return SS_OK;
+    c->world_valid = false;  // transforms changed
+    if (first == 0 && count == c->n_nodes && count >= kAsyncUploadMinNodes) {
+        const int tgt = c->trs_cur ^ 1;
+        SS_CUDA(c, cudaStreamWaitEvent(c->upload_stream, c->ev_trs_read[tgt], 0));  // its last reader is past the transform stage
+        SS_CUDA(c, cudaMemcpyAsync(c->d_trs_buf[tgt], trs9, (size_t)count * 36, cudaMemcpyHostToDevice, c->upload_stream));
+        SS_CUDA(c, cudaEventRecord(c->ev_upload_done, c->upload_stream));
+        c->trs_swap_pending = true;
+        return SS_OK;
+    }
+    SS_CUDA(c, adopt_pending_upload(c));  // a range lands on top of whatever whole-stream upload came before it
+    SS_CUDA(c, cudaMemcpyAsync(c->d_trs + (size_t)first * 9, trs9, (size_t)count * 36, cudaMemcpyHostToDevice, c->stream));
     return SS_OK;
 }
 
@@ -467,6 +515,7 @@ SS_API ss_status ss_flush_uploads(ss_ctx* c)
 {
     if (!c) return SS_ERR_INVALID;
     SS_CUDA(c, cudaSetDevice(c->device));
+    SS_CUDA(c, cudaStreamSynchronize(c->upload_stream));
     SS_CUDA(c, cudaStreamSynchronize(c->stream));
     return SS_OK;
 }
@@ -516,6 +565,7 @@ SS_API ss_status ss_frame(ss_ctx* c, const ss_view* views, uint32_t n_views, uin
         if (views[v].flags & SS_VIEW_SKIP_NEAR) cp.v[v].flags |= kViewSkipNear;
     }
 
+    SS_CUDA(c, adopt_pending_upload(c));
     SS_CUDA(c, cudaEventRecord(s.start, st));
     SS_CUDA(c, cudaMemsetAsync(c->d_emit_zero, 0, c->emit_zero_bytes, st));
 
@@ -589,6 +639,7 @@ SS_API ss_status ss_frame(ss_ctx* c, const ss_view* views, uint32_t n_views, uin
     }
     c->world_valid = true;
     SS_CUDA(c, cudaEventRecord(s.stage[1], st));
+    SS_CUDA(c, cudaEventRecord(c->ev_trs_read[c->trs_cur], st));  // the TRS buffer may be overwritten from here on
 
     if (!reuse_sort) {
         if (!hist_done)  // the general kernel did not count digits: clear again is harmless, the sort counts itself
@@ -724,7 +775,9 @@ SS_API ss_status ss_download_view(ss_ctx* c, uint32_t slot, uint32_t view, float
     ss_outputs o;
     ss_status st = ss_map_outputs(c, slot, view, &o);
     if (st != SS_OK) return st;
-    cudaStream_t s = c->stream;
+    // the slot's frame is complete (ss_map_outputs fenced it) and its buffers stay untouched until the slot comes
+    // round again, so the copies run on their own stream instead of waiting for frames issued since
+    cudaStream_t s = c->download_stream;
     if (rows12 && o.visible)
         SS_CUDA(c, cudaMemcpyAsync(rows12, o.instance_rows, (size_t)o.visible * 48, cudaMemcpyDeviceToHost, s));
     if (keys && o.visible) SS_CUDA(c, cudaMemcpyAsync(keys, o.keys, (size_t)o.visible * 8, cudaMemcpyDeviceToHost, s));
