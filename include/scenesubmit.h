@@ -262,6 +262,38 @@ SS_API ss_status ss_download_masks(ss_ctx* ctx, uint32_t first, uint32_t count, 
 /* The CUDA stream (cudaStream_t) frames run on, so a consumer can order its own work after them. */
 SS_API void* ss_stream(ss_ctx* ctx);
 
+/* ---- consuming the lists: depth + id rasterisation ------------------------------ */
+
+/* What the reference does with the instance buffer and the draws next: ShadowPass renders depth per cascade
+   (assets/shaders/ShadowDepth.vert/.geom: clip = LightSpaceMatrices[c] * transform * position, DepthClamp,
+   VC/Scene/SceneRenderer.cpp:188, :1266-1310) and SelectionPass renders the entity id per pixel and reads ONE
+   pixel back (assets/shaders/CoreEditor.vert/.frag, VC/Scene/SceneRenderer.cpp:1421-1457).  Here both are one
+   CUDA pass over (compacted instance, triangle): every covered sample does a 64-bit atomic min of
+   [depth float bits : 32 | instance index : 32], so the result is independent of submission order.
+   Vulkan conventions: y down, depth z/w in [0, 1], samples at pixel centres, an edge belongs to one side.
+   The reference's own rasteriser is the Vulkan device (unavailable on this box); the checker is the CPU
+   restatement sso_raster_view in oracle/. */
+enum {
+    SS_RASTER_DEFAULT = 0,
+    SS_RASTER_DEPTH_CLAMP = 1 /* clamp z/w to [0, 1] instead of discarding (the shadow pipeline's DepthClamp) */
+};
+#define SS_RASTER_EMPTY 0xFFFFFFFFFFFFFFFFull
+
+/* Vertex positions (xyz floats) and 32-bit indices the submesh table's first_index / index_count /
+   vertex_offset refer to (MeshSource::m_Vertices / m_Indices, VC/Asset/MeshImporter.cpp:97-158). Host pointers. */
+SS_API ss_status ss_set_geometry(ss_ctx* ctx, const float* positions_xyz, uint32_t n_vertices,
+                                 const uint32_t* indices, uint32_t n_indices);
+/* Rasterises view `view` of the frame in `slot` with that view's view_proj into the library's target layer
+   `view` (width x height words, cleared to SS_RASTER_EMPTY first).  Asynchronous on the frame stream. */
+SS_API ss_status ss_raster_view(ss_ctx* ctx, uint32_t slot, uint32_t view, uint32_t width, uint32_t height,
+                                uint32_t flags);
+/* Device pointer of layer `view` of the last ss_raster_view size (fences the stream), or a copy to the host. */
+SS_API ss_status ss_map_raster(ss_ctx* ctx, uint32_t view, const uint64_t** words_out);
+SS_API ss_status ss_download_raster(ss_ctx* ctx, uint32_t view, uint64_t* words_out);
+/* One sample: the hovered-entity read-back of SelectionPass.  instance_out = 0xFFFFFFFF where nothing was drawn. */
+SS_API ss_status ss_read_pixel(ss_ctx* ctx, uint32_t view, uint32_t x, uint32_t y, uint32_t* instance_out,
+                               float* depth_out);
+
 /* ---- the sort on its own ---------------------------------------------------------------------- */
 
 /* Stable LSD radix sort (onesweep) of (uint64 key, uint32 value) pairs on bits [begin_bit, end_bit).

@@ -651,3 +651,79 @@ void sso_cascade_matrices(const float view_proj[16], float z_near, float z_far, 
         lastSplitDist = cascadeSplits[i];
     }
 }
+
+/* ---- depth + id rasterisation --------------------------------------------------------------------
+   Homogeneous (2DH) rasterisation: with the vertices' pixel-space homogeneous coordinates (X, Y, W) as the columns of
+   a 3x3 matrix, row i of its adjugate is the edge function of vertex i; inside = all three on the determinant's side;
+   z/w is affine in screen space, = sum(z_i E_i) / det.  No clipping is needed for triangles crossing w = 0.
+   The float operations are written in one fixed order (this file is built with -ffp-contract=off). */
+static void sso_clip_of(const float vp[16], const float* r, const float* p, float out[4])
+{
+    const float wx = (r[0] * p[0] + r[1] * p[1]) + (r[2] * p[2] + r[3]);
+    const float wy = (r[4] * p[0] + r[5] * p[1]) + (r[6] * p[2] + r[7]);
+    const float wz = (r[8] * p[0] + r[9] * p[1]) + (r[10] * p[2] + r[11]);
+    for (int j = 0; j < 4; ++j) out[j] = (vp[j] * wx + vp[4 + j] * wy) + (vp[8 + j] * wz + vp[12 + j]);
+}
+
+void sso_raster_view(const float* rows12, const uint32_t* instance_idx, uint32_t visible, const uint32_t* slot_of_instance,
+                     const sso_submesh* slots, const float* positions_xyz, uint32_t n_vertices, const uint32_t* indices,
+                     uint32_t n_indices, const float view_proj[16], uint32_t width, uint32_t height, uint32_t flags,
+                     uint64_t* target)
+{
+    const float half_w = 0.5f * (float)width, half_h = 0.5f * (float)height;
+    for (size_t i = 0; i < (size_t)width * height; ++i) target[i] = ~(uint64_t)0;
+    for (uint32_t k = 0; k < visible; ++k) {
+        const float* r = rows12 + (size_t)k * 12;
+        const uint32_t inst = instance_idx[k];
+        const sso_submesh* sm = &slots[slot_of_instance[inst]];
+        for (uint32_t t = 0; t < sm->index_count / 3u; ++t) {
+            float c[3][4];
+            int in_range = 1;
+            for (int v = 0; v < 3 && in_range; ++v) {
+                const uint64_t ii = (uint64_t)sm->first_index + (uint64_t)t * 3u + (uint64_t)v;
+                if (ii >= n_indices) { in_range = 0; break; }
+                const int64_t vi = (int64_t)sm->vertex_offset + (int64_t)indices[ii];
+                if (vi < 0 || vi >= (int64_t)n_vertices) { in_range = 0; break; }
+                sso_clip_of(view_proj, r, positions_xyz + (size_t)vi * 3, c[v]);
+            }
+            if (!in_range) continue;
+            float X[3], Y[3], W[3], a[3], b[3], cc[3];
+            for (int v = 0; v < 3; ++v) {
+                X[v] = (c[v][0] + c[v][3]) * half_w;
+                Y[v] = (c[v][1] + c[v][3]) * half_h;
+                W[v] = c[v][3];
+            }
+            a[0] = Y[1] * W[2] - Y[2] * W[1]; b[0] = X[2] * W[1] - X[1] * W[2]; cc[0] = X[1] * Y[2] - X[2] * Y[1];
+            a[1] = Y[2] * W[0] - Y[0] * W[2]; b[1] = X[0] * W[2] - X[2] * W[0]; cc[1] = X[2] * Y[0] - X[0] * Y[2];
+            a[2] = Y[0] * W[1] - Y[1] * W[0]; b[2] = X[1] * W[0] - X[0] * W[1]; cc[2] = X[0] * Y[1] - X[1] * Y[0];
+            const float det = (X[0] * a[0] + X[1] * a[1]) + X[2] * a[2];
+            if (!(det > 0.f || det < 0.f)) continue;
+            if (!(W[0] > 0.f || W[1] > 0.f || W[2] > 0.f)) continue;
+            const float s = det > 0.f ? 1.f : -1.f;
+            /* the checker walks every sample of the target: no bounding box to get wrong */
+            for (uint32_t j = 0; j < height; ++j) {
+                const float py = (float)j + 0.5f;
+                for (uint32_t i = 0; i < width; ++i) {
+                    const float px = (float)i + 0.5f;
+                    float e[3];
+                    int inside = 1;
+                    for (int q = 0; q < 3; ++q) {
+                        e[q] = (a[q] * px + b[q] * py) + cc[q];
+                        const float es = s * e[q], as = s * a[q], bs = s * b[q];
+                        if (!(es > 0.f || (es == 0.f && (as > 0.f || (as == 0.f && bs > 0.f))))) inside = 0;
+                    }
+                    if (!inside) continue;
+                    if (!(s * ((e[0] + e[1]) + e[2]) > 0.f)) continue;
+                    float depth = ((c[0][2] * e[0] + c[1][2] * e[1]) + c[2][2] * e[2]) / det;
+                    if (flags & 1u) depth = depth < 0.f ? 0.f : (depth > 1.f ? 1.f : depth);
+                    if (!(depth >= 0.f && depth <= 1.f)) continue;
+                    uint32_t bits;
+                    memcpy(&bits, &depth, 4);
+                    const uint64_t word = ((uint64_t)bits << 32) | inst;
+                    uint64_t* dst = &target[(size_t)j * width + i];
+                    if (word < *dst) *dst = word;
+                }
+            }
+        }
+    }
+}

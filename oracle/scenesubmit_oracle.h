@@ -114,6 +114,18 @@ void sso_cascade_matrices(const float view_proj[16], float z_near, float z_far, 
                           float splits[4], float light_matrices[64]);
 void sso_mat4_inverse(const float m[16], float out[16]);
 
+/* ---- the consumer of the lists: depth + id rasterisation -------------------------
+   CPU restatement of what the reference's ShadowPass / SelectionPass make the Vulkan device do with the instance
+   buffer (assets/shaders/ShadowDepth.vert/.geom, CoreEditor.vert/.frag: clip = view_proj * (transform * position);
+   SceneRenderer.cpp:1266-1310, :1421-1457).  Vulkan conventions: y down, depth z/w in [0, 1], samples at pixel
+   centres.  Target word = [depth float bits : 32 | instance : 32], nearest wins, 0xFFFF...F where nothing was drawn.
+   flags bit 0: clamp depth to [0, 1] instead of discarding (DepthClamp).  Parity with the reference's own rasteriser
+   is unpinned (it is the Vulkan device: unavailable on this box); this function is the checker of raster.cu. */
+void sso_raster_view(const float* rows12, const uint32_t* instance_idx, uint32_t visible, const uint32_t* slot_of_instance,
+                     const sso_submesh* slots, const float* positions_xyz, uint32_t n_vertices, const uint32_t* indices,
+                     uint32_t n_indices, const float view_proj[16], uint32_t width, uint32_t height, uint32_t flags,
+                     uint64_t* target);
+
 /* det sincos exposed for the accuracy test */
 void sso_det_sincos(float x, float* s, float* c);
 

@@ -189,3 +189,20 @@ def det_sincos(x):
     s, c = C.c_float(), C.c_float()
     lib().sso_det_sincos(C.c_float(float(x)), C.byref(s), C.byref(c))
     return s.value, c.value
+
+
+def raster_view(rows12, instance_idx, slot_of_instance, slots, positions, indices, view_proj, width, height, flags=0):
+    """sso_raster_view: the CPU restatement of the consumer pass (every sample of the target is tested against every
+    triangle, so keep targets and scenes small)."""
+    rows12 = np.ascontiguousarray(rows12, np.float32).reshape(-1, 12)
+    instance_idx = np.ascontiguousarray(instance_idx, np.uint32)
+    slot_of_instance = np.ascontiguousarray(slot_of_instance, np.uint32)
+    slots = np.ascontiguousarray(slots)
+    positions = np.ascontiguousarray(positions, np.float32).reshape(-1, 3)
+    indices = np.ascontiguousarray(indices, np.uint32)
+    vp = np.ascontiguousarray(view_proj, np.float32).reshape(16)
+    out = np.empty((height, width), np.uint64)
+    lib().sso_raster_view(_ptr(rows12), _ptr(instance_idx), C.c_uint32(len(instance_idx)), _ptr(slot_of_instance), _ptr(slots),
+                          _ptr(positions), C.c_uint32(len(positions)), _ptr(indices), C.c_uint32(len(indices)), _ptr(vp),
+                          C.c_uint32(width), C.c_uint32(height), C.c_uint32(flags), _ptr(out))
+    return out

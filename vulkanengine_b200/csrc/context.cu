@@ -27,6 +27,7 @@ struct Slot {
     bool pending = false;
     uint32_t n_views = 0, n_instances = 0;
     int launches = 0;
+    ss_view views[SS_MAX_VIEWS];      // as given to ss_frame (ss_raster_view projects with them)
     // pinned host mirror
     uint32_t* h_counts = nullptr;     // [max_views][2] + overflow + passes_run: mapped pinned, written by k_draws
     uint32_t* h_counts_dev = nullptr; // the same words as the device sees them
@@ -79,6 +80,12 @@ struct ss_ctx {
     uint32_t* d_overflow = nullptr;
     uint32_t* d_seg_count = nullptr;   // [2][max_views][max_draws]: per-view run counters, double-buffered by frame
     uint32_t* d_seg_runs = nullptr;    // [2] runs left in each buffer
+    // geometry + raster target of the consumer pass (ss_set_geometry / ss_raster_view); allocated on first use
+    float* d_positions = nullptr;
+    uint32_t* d_indices = nullptr;
+    uint32_t n_vertices = 0, n_indices = 0;
+    unsigned long long* d_raster = nullptr;  // [max_views][raster_h][raster_w]
+    uint32_t raster_w = 0, raster_h = 0;
     uint32_t seg_parity = 0;
     uint64_t* d_seg_key = nullptr;
     uint32_t* d_seg_inst = nullptr;
@@ -210,6 +217,9 @@ SS_API void ss_destroy(ss_ctx* c)
         if (s.h_counts) cudaFreeHost(s.h_counts);
     }
     for (void* p : c->allocs) cudaFree(p);
+    if (c->d_positions) cudaFree(c->d_positions);
+    if (c->d_indices) cudaFree(c->d_indices);
+    if (c->d_raster) cudaFree(c->d_raster);
     if (c->stream) cudaStreamDestroy(c->stream);
     delete c;
 }
@@ -710,6 +720,7 @@ SS_API ss_status ss_frame(ss_ctx* c, const ss_view* views, uint32_t n_views, uin
     SS_CUDA(c, cudaEventRecord(s.done, st));
     s.pending = true;
     s.n_views = n_views;
+    memcpy(s.views, views, n_views * sizeof(ss_view));
     s.n_instances = n;
     s.launches = launches;
     ++c->frame_no;
@@ -833,6 +844,112 @@ SS_API ss_status ss_frame_stage_ms(ss_ctx* c, uint32_t slot, float ms_out[5])
     SS_CUDA(c, cudaEventSynchronize(s.done));
     cudaEvent_t ev[6] = {s.start, s.stage[0], s.stage[1], s.stage[2], s.stage[3], s.done};
     for (int i = 0; i < 5; ++i) SS_CUDA(c, cudaEventElapsedTime(&ms_out[i], ev[i], ev[i + 1]));
+    return SS_OK;
+}
+
+// ---- consumer pass: depth + id rasterisation -------------------------------------------------------
+SS_API ss_status ss_set_geometry(ss_ctx* c, const float* positions_xyz, uint32_t n_vertices, const uint32_t* indices,
+                                 uint32_t n_indices)
+{
+    if (!c) return SS_ERR_INVALID;
+    if ((n_vertices && !positions_xyz) || (n_indices && !indices)) return c->fail(SS_ERR_INVALID, "ss_set_geometry: null array");
+    SS_CUDA(c, cudaSetDevice(c->device));
+    SS_CUDA(c, cudaStreamSynchronize(c->stream));  // a raster pass may still be reading the old arrays
+    if (c->d_positions) cudaFree(c->d_positions);
+    if (c->d_indices) cudaFree(c->d_indices);
+    c->d_positions = nullptr;
+    c->d_indices = nullptr;
+    c->n_vertices = c->n_indices = 0;
+    if (n_vertices) {
+        SS_CUDA(c, cudaMalloc(&c->d_positions, (size_t)n_vertices * 12));
+        SS_CUDA(c, cudaMemcpy(c->d_positions, positions_xyz, (size_t)n_vertices * 12, cudaMemcpyHostToDevice));
+    }
+    if (n_indices) {
+        SS_CUDA(c, cudaMalloc(&c->d_indices, (size_t)n_indices * 4));
+        SS_CUDA(c, cudaMemcpy(c->d_indices, indices, (size_t)n_indices * 4, cudaMemcpyHostToDevice));
+    }
+    c->n_vertices = n_vertices;
+    c->n_indices = n_indices;
+    return SS_OK;
+}
+
+SS_API ss_status ss_raster_view(ss_ctx* c, uint32_t slot, uint32_t view, uint32_t width, uint32_t height, uint32_t flags)
+{
+    if (!c) return SS_ERR_INVALID;
+    if (!width || !height || width > 16384 || height > 16384)
+        return c->fail(SS_ERR_INVALID, "ss_raster_view: target %u x %u", width, height);
+    ss_outputs o;
+    ss_status st = ss_map_outputs(c, slot, view, &o);  // fences the frame: counts are on the host
+    if (st != SS_OK) return st;
+    if (width != c->raster_w || height != c->raster_h || !c->d_raster) {
+        SS_CUDA(c, cudaStreamSynchronize(c->stream));
+        if (c->d_raster) cudaFree(c->d_raster);
+        c->d_raster = nullptr;
+        SS_CUDA(c, cudaMalloc(&c->d_raster, (size_t)c->cfg.max_views * width * height * sizeof(unsigned long long)));
+        c->raster_w = width;
+        c->raster_h = height;
+        launch_raster_clear(c->d_raster, (size_t)c->cfg.max_views * width * height, c->stream);
+    }
+    const size_t layer = (size_t)width * height;
+    RasterArgs ra;
+    memset(&ra, 0, sizeof ra);
+    ra.rows = reinterpret_cast<const float4*>(o.instance_rows);
+    ra.idx = o.instance_idx;
+    ra.slot = c->d_slot;
+    ra.slots = c->d_slots;
+    ra.positions = c->d_positions;
+    ra.indices = c->d_indices;
+    ra.n_vertices = c->n_vertices;
+    ra.n_indices = c->n_indices;
+    ra.visible = o.visible;
+    memcpy(ra.vp, c->slots[slot].views[view].view_proj, 64);
+    ra.width = width;
+    ra.height = height;
+    ra.flags = flags;
+    ra.target = c->d_raster + view * layer;
+    launch_raster_clear(ra.target, layer, c->stream);
+    launch_raster(ra, c->stream);
+    SS_CUDA(c, cudaGetLastError());
+    return SS_OK;
+}
+
+SS_API ss_status ss_map_raster(ss_ctx* c, uint32_t view, const uint64_t** words_out)
+{
+    if (!c || !words_out) return SS_ERR_INVALID;
+    if (!c->d_raster || view >= c->cfg.max_views) return c->fail(SS_ERR_STATE, "ss_map_raster: no target for view %u", view);
+    SS_CUDA(c, cudaSetDevice(c->device));
+    SS_CUDA(c, cudaStreamSynchronize(c->stream));
+    *words_out = reinterpret_cast<const uint64_t*>(c->d_raster + (size_t)view * c->raster_w * c->raster_h);
+    return SS_OK;
+}
+
+SS_API ss_status ss_download_raster(ss_ctx* c, uint32_t view, uint64_t* words_out)
+{
+    if (!c || !words_out) return SS_ERR_INVALID;
+    if (!c->d_raster || view >= c->cfg.max_views) return c->fail(SS_ERR_STATE, "ss_download_raster: no target for view %u", view);
+    SS_CUDA(c, cudaSetDevice(c->device));
+    const size_t layer = (size_t)c->raster_w * c->raster_h;
+    SS_CUDA(c, cudaMemcpyAsync(words_out, c->d_raster + view * layer, layer * 8, cudaMemcpyDeviceToHost, c->stream));
+    SS_CUDA(c, cudaStreamSynchronize(c->stream));
+    return SS_OK;
+}
+
+SS_API ss_status ss_read_pixel(ss_ctx* c, uint32_t view, uint32_t x, uint32_t y, uint32_t* instance_out, float* depth_out)
+{
+    if (!c) return SS_ERR_INVALID;
+    if (!c->d_raster || view >= c->cfg.max_views || x >= c->raster_w || y >= c->raster_h)
+        return c->fail(SS_ERR_INVALID, "ss_read_pixel: view %u pixel (%u, %u) outside the %u x %u target", view, x, y,
+                       c->raster_w, c->raster_h);
+    SS_CUDA(c, cudaSetDevice(c->device));
+    unsigned long long w = 0;
+    const size_t at = ((size_t)view * c->raster_h + y) * c->raster_w + x;
+    SS_CUDA(c, cudaMemcpyAsync(&w, c->d_raster + at, 8, cudaMemcpyDeviceToHost, c->stream));
+    SS_CUDA(c, cudaStreamSynchronize(c->stream));
+    if (instance_out) *instance_out = (uint32_t)(w & 0xFFFFFFFFull);
+    if (depth_out) {
+        const uint32_t bits = (uint32_t)(w >> 32);
+        memcpy(depth_out, &bits, 4);
+    }
     return SS_OK;
 }
 

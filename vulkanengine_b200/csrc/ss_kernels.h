@@ -159,4 +159,22 @@ struct DrawArgs {
 };
 void launch_draws(const DrawArgs& a, cudaStream_t st);
 
+// ---- depth + id rasterisation of a view's compacted list (raster.cu) -------------------------------
+struct RasterArgs {
+    const float4* rows;        // [visible][3] TransformData of the view, draw order
+    const uint32_t* idx;       // [visible] instance index of each row
+    const uint32_t* slot;      // instance -> submesh slot
+    const SlotDev* slots;
+    const float* positions;    // [n_vertices][3]
+    const uint32_t* indices;   // [n_indices]
+    uint32_t n_vertices, n_indices;
+    uint32_t visible;
+    float vp[16];              // column-major view-projection of the view
+    uint32_t width, height;
+    uint32_t flags;            // SS_RASTER_*
+    unsigned long long* target;  // [height][width] words [depth bits | instance], SS_RASTER_EMPTY where untouched
+};
+void launch_raster_clear(unsigned long long* target, size_t n, cudaStream_t st);
+void launch_raster(const RasterArgs& a, cudaStream_t st);
+
 }  // namespace ss

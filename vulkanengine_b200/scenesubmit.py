@@ -25,7 +25,10 @@ EXPORTS = ["ss_create", "ss_destroy", "ss_last_error", "ss_version", "ss_set_key
            "ss_set_nodes", "ss_set_instances", "ss_set_instance_aabbs", "ss_upload_trs", "ss_upload_node_world_rows", "ss_flush_uploads",
            "ss_upload_world_rows", "ss_frame", "ss_frame_sync", "ss_frame_stage_ms", "ss_map_outputs", "ss_download_view",
            "ss_download_world", "ss_download_masks", "ss_stream", "ss_sort_scratch_bytes", "ss_sort_pairs",
-           "ss_sort_pairs_host", "ss_sort_pairs_static", "ss_camera_view_proj", "ss_cascade_matrices"]
+           "ss_sort_pairs_host", "ss_sort_pairs_static", "ss_camera_view_proj", "ss_cascade_matrices",
+           "ss_set_geometry", "ss_raster_view", "ss_map_raster", "ss_download_raster", "ss_read_pixel"]
+RASTER_DEPTH_CLAMP = 1
+RASTER_EMPTY = 0xFFFFFFFFFFFFFFFF
 
 
 class SceneSubmitError(RuntimeError):
@@ -254,6 +257,27 @@ class SceneSubmit:
         m = np.empty(count, np.uint8)
         self._ck(self.lib.ss_download_masks(self.h, C.c_uint32(first), C.c_uint32(count), _p(m)))
         return m
+
+    # ---- consumer pass: depth + id rasterisation of a view's lists ----
+    def set_geometry(self, positions, indices):
+        positions = np.ascontiguousarray(positions, np.float32).reshape(-1, 3)
+        indices = np.ascontiguousarray(indices, np.uint32)
+        self._ck(self.lib.ss_set_geometry(self.h, _p(positions), C.c_uint32(len(positions)), _p(indices), C.c_uint32(len(indices))))
+
+    def raster_view(self, slot, view, width, height, flags=0):
+        self._ck(self.lib.ss_raster_view(self.h, C.c_uint32(slot), C.c_uint32(view), C.c_uint32(width), C.c_uint32(height),
+                                         C.c_uint32(flags)))
+        self._raster_shape = (height, width)
+
+    def download_raster(self, view):
+        out = np.empty(self._raster_shape, np.uint64)
+        self._ck(self.lib.ss_download_raster(self.h, C.c_uint32(view), _p(out)))
+        return out
+
+    def read_pixel(self, view, x, y):
+        inst, depth = C.c_uint32(), C.c_float()
+        self._ck(self.lib.ss_read_pixel(self.h, C.c_uint32(view), C.c_uint32(x), C.c_uint32(y), C.byref(inst), C.byref(depth)))
+        return inst.value, depth.value
 
     @property
     def stream(self):

@@ -267,3 +267,20 @@ def fibonacci_cameras(camera_fn, n_views, radius=800.0, seed=SEED_BASE + 5):
                              float(yaw))
         views["view_proj"][i] = vp
     return views
+
+
+def box_geometry(slots):
+    """One box per submesh slot, spanning the slot's local AABB: 8 vertices, 12 triangles.  Returns (positions [8S][3],
+    indices [36S], slots') where slots' is a copy whose first_index / index_count / vertex_offset address that geometry
+    (synthetic scenes carry made-up counts; the consumer pass needs real ones)."""
+    corners = np.array([[x, y, z] for z in (0, 1) for y in (0, 1) for x in (0, 1)], np.float32)       # bit k of the corner id = axis k
+    quads = [(0, 2, 3, 1), (4, 5, 7, 6), (0, 1, 5, 4), (2, 6, 7, 3), (0, 4, 6, 2), (1, 3, 7, 5)]      # -z +z -y +y -x +x
+    tri = np.array([[q[0], q[1], q[2], q[0], q[2], q[3]] for q in quads], np.uint32).reshape(-1)
+    s2 = slots.copy()
+    n = len(slots)
+    lo, hi = slots["aabb_min"].astype(np.float32), slots["aabb_max"].astype(np.float32)
+    pos = lo[:, None, :] + corners[None, :, :] * (hi - lo)[:, None, :]
+    s2["index_count"] = 36
+    s2["first_index"] = 36 * np.arange(n, dtype=np.uint32)
+    s2["vertex_offset"] = 8 * np.arange(n, dtype=np.int32)
+    return pos.reshape(-1, 3).astype(np.float32), np.tile(tri, n), s2
