@@ -653,10 +653,19 @@ void sso_cascade_matrices(const float view_proj[16], float z_near, float z_far, 
 }
 
 /* ---- depth + id rasterisation --------------------------------------------------------------------
-   Homogeneous (2DH) rasterisation: with the vertices' pixel-space homogeneous coordinates (X, Y, W) as the columns of
-   a 3x3 matrix, row i of its adjugate is the edge function of vertex i; inside = all three on the determinant's side;
-   z/w is affine in screen space, = sum(z_i E_i) / det.  No clipping is needed for triangles crossing w = 0.
-   The float operations are written in one fixed order (this file is built with -ffp-contract=off). */
+   Per (instance, triangle), the fixed-function steps of the pipeline the reference's two passes run on:
+     1. clip = view_proj * (transform * position)           (ShadowDepth.vert/.geom, CoreEditor.vert)
+     2. clip the triangle against the near plane z >= 0 (with DepthClamp: against w >= 1e-5 instead, depth is then
+        clamped per sample); new vertices are interpolated from the inside vertex towards the outside one
+     3. perspective divide, viewport (y down), snap to 1/256 pixel; coverage by exact integer edge functions at pixel
+        centres with a tie rule that gives a shared edge to exactly one triangle; depth = screen-linear z/w
+     3b. a triangle that cannot be snapped (a vertex at w <= 0 after clipping, or farther than 2^20 pixels out) is
+        rasterised in homogeneous float coordinates instead (edge functions = adjugate rows of the (X, Y, W) matrix)
+   Target word = [depth float bits : 32 | instance : 32], smallest wins.  The float operations are written in one fixed
+   order (this file is built with -ffp-contract=off) which raster.cu follows. */
+#define SSO_SUBPIXEL 256.0f
+#define SSO_SNAP_LIMIT 268435456.0f /* 2^28 sub-pixel units = 2^20 pixels */
+
 static void sso_clip_of(const float vp[16], const float* r, const float* p, float out[4])
 {
     const float wx = (r[0] * p[0] + r[1] * p[1]) + (r[2] * p[2] + r[3]);
@@ -665,12 +674,124 @@ static void sso_clip_of(const float vp[16], const float* r, const float* p, floa
     for (int j = 0; j < 4; ++j) out[j] = (vp[j] * wx + vp[4 + j] * wy) + (vp[8 + j] * wz + vp[12 + j]);
 }
 
+static void sso_put(uint64_t* target, uint32_t width, uint32_t i, uint32_t j, float depth, uint32_t flags, uint32_t inst)
+{
+    if (flags & 1u) depth = depth < 0.f ? 0.f : (depth > 1.f ? 1.f : depth);
+    if (!(depth >= 0.f && depth <= 1.f)) return;
+    uint32_t bits;
+    memcpy(&bits, &depth, 4);
+    const uint64_t word = ((uint64_t)bits << 32) | inst;
+    uint64_t* dst = &target[(size_t)j * width + i];
+    if (word < *dst) *dst = word;
+}
+
+/* 3b: homogeneous float rasterisation over every sample of the target */
+static void sso_raster_2dh(const float c[3][4], uint32_t width, uint32_t height, uint32_t flags, uint32_t inst, uint64_t* target)
+{
+    const float half_w = 0.5f * (float)width, half_h = 0.5f * (float)height;
+    float X[3], Y[3], W[3], a[3], b[3], cc[3];
+    for (int v = 0; v < 3; ++v) {
+        X[v] = (c[v][0] + c[v][3]) * half_w;
+        Y[v] = (c[v][1] + c[v][3]) * half_h;
+        W[v] = c[v][3];
+    }
+    a[0] = Y[1] * W[2] - Y[2] * W[1]; b[0] = X[2] * W[1] - X[1] * W[2]; cc[0] = X[1] * Y[2] - X[2] * Y[1];
+    a[1] = Y[2] * W[0] - Y[0] * W[2]; b[1] = X[0] * W[2] - X[2] * W[0]; cc[1] = X[2] * Y[0] - X[0] * Y[2];
+    a[2] = Y[0] * W[1] - Y[1] * W[0]; b[2] = X[1] * W[0] - X[0] * W[1]; cc[2] = X[0] * Y[1] - X[1] * Y[0];
+    const float det = (X[0] * a[0] + X[1] * a[1]) + X[2] * a[2];
+    if (!(det > 0.f || det < 0.f)) return;
+    if (!(W[0] > 0.f || W[1] > 0.f || W[2] > 0.f)) return;
+    const float s = det > 0.f ? 1.f : -1.f;
+    for (uint32_t j = 0; j < height; ++j) {
+        const float py = (float)j + 0.5f;
+        for (uint32_t i = 0; i < width; ++i) {
+            const float px = (float)i + 0.5f;
+            float e[3];
+            int inside = 1;
+            for (int q = 0; q < 3; ++q) {
+                e[q] = (a[q] * px + b[q] * py) + cc[q];
+                const float es = s * e[q], as = s * a[q], bs = s * b[q];
+                if (!(es > 0.f || (es == 0.f && (as > 0.f || (as == 0.f && bs > 0.f))))) inside = 0;
+            }
+            if (!inside) continue;
+            if (!(s * ((e[0] + e[1]) + e[2]) > 0.f)) continue;
+            sso_put(target, width, i, j, ((c[0][2] * e[0] + c[1][2] * e[1]) + c[2][2] * e[2]) / det, flags, inst);
+        }
+    }
+}
+
+static int64_t sso_floor_div256(int64_t v) { return v >= 0 ? v / 256 : -((-v + 255) / 256); }
+
+/* 3: snapped, exact coverage */
+static void sso_raster_tri(const float c[3][4], uint32_t width, uint32_t height, uint32_t flags, uint32_t inst, uint64_t* target)
+{
+    const float half_w = 0.5f * (float)width, half_h = 0.5f * (float)height;
+    int64_t x[3], y[3];
+    float zn[3];
+    int snap = 1;
+    for (int v = 0; v < 3; ++v) {
+        if (!(c[v][3] > 0.f)) { snap = 0; break; }
+        const float sx = ((c[v][0] / c[v][3]) * half_w + half_w) * SSO_SUBPIXEL;
+        const float sy = ((c[v][1] / c[v][3]) * half_h + half_h) * SSO_SUBPIXEL;
+        if (!(sx > -SSO_SNAP_LIMIT && sx < SSO_SNAP_LIMIT && sy > -SSO_SNAP_LIMIT && sy < SSO_SNAP_LIMIT)) { snap = 0; break; }
+        x[v] = llrintf(sx);
+        y[v] = llrintf(sy);
+        zn[v] = c[v][2] / c[v][3];
+    }
+    if (!snap) {
+        sso_raster_2dh(c, width, height, flags, inst, target);
+        return;
+    }
+    /* edge q is opposite vertex q: from vertex q+1 to vertex q+2 */
+    int64_t dx[3], dy[3];
+    for (int q = 0; q < 3; ++q) {
+        const int p0 = (q + 1) % 3, p1 = (q + 2) % 3;
+        dx[q] = x[p1] - x[p0];
+        dy[q] = y[p1] - y[p0];
+    }
+    const int64_t area = dx[2] * (y[2] - y[0]) - dy[2] * (x[2] - x[0]);  /* edge 2 (v0 -> v1) evaluated at v2 */
+    if (area == 0) return;
+    const int64_t s = area > 0 ? 1 : -1;
+    int64_t minx = x[0], maxx = x[0], miny = y[0], maxy = y[0];
+    for (int v = 1; v < 3; ++v) {
+        if (x[v] < minx) minx = x[v];
+        if (x[v] > maxx) maxx = x[v];
+        if (y[v] < miny) miny = y[v];
+        if (y[v] > maxy) maxy = y[v];
+    }
+    /* pixel i is sampled at 256 i + 128 */
+    int64_t i0 = sso_floor_div256(minx - 128 + 255), i1 = sso_floor_div256(maxx - 128);
+    int64_t j0 = sso_floor_div256(miny - 128 + 255), j1 = sso_floor_div256(maxy - 128);
+    if (i0 < 0) i0 = 0;
+    if (j0 < 0) j0 = 0;
+    if (i1 > (int64_t)width - 1) i1 = (int64_t)width - 1;
+    if (j1 > (int64_t)height - 1) j1 = (int64_t)height - 1;
+    const float fa = (float)(s * area);
+    for (int64_t j = j0; j <= j1; ++j) {
+        const int64_t py = 256 * j + 128;
+        for (int64_t i = i0; i <= i1; ++i) {
+            const int64_t px = 256 * i + 128;
+            int64_t e[3];
+            int inside = 1;
+            for (int q = 0; q < 3; ++q) {
+                const int p0 = (q + 1) % 3;
+                e[q] = s * (dx[q] * (py - y[p0]) - dy[q] * (px - x[p0]));
+                /* a sample exactly on an edge belongs to the triangle for which that edge runs down, or level to the right */
+                const int64_t sdx = s * dx[q], sdy = s * dy[q];
+                if (!(e[q] > 0 || (e[q] == 0 && (sdy > 0 || (sdy == 0 && sdx > 0))))) inside = 0;
+            }
+            if (!inside) continue;
+            const float l0 = (float)e[0] / fa, l1 = (float)e[1] / fa, l2 = (float)e[2] / fa;
+            sso_put(target, width, (uint32_t)i, (uint32_t)j, (zn[0] * l0 + zn[1] * l1) + zn[2] * l2, flags, inst);
+        }
+    }
+}
+
 void sso_raster_view(const float* rows12, const uint32_t* instance_idx, uint32_t visible, const uint32_t* slot_of_instance,
                      const sso_submesh* slots, const float* positions_xyz, uint32_t n_vertices, const uint32_t* indices,
                      uint32_t n_indices, const float view_proj[16], uint32_t width, uint32_t height, uint32_t flags,
                      uint64_t* target)
 {
-    const float half_w = 0.5f * (float)width, half_h = 0.5f * (float)height;
     for (size_t i = 0; i < (size_t)width * height; ++i) target[i] = ~(uint64_t)0;
     for (uint32_t k = 0; k < visible; ++k) {
         const float* r = rows12 + (size_t)k * 12;
@@ -687,42 +808,31 @@ void sso_raster_view(const float* rows12, const uint32_t* instance_idx, uint32_t
                 sso_clip_of(view_proj, r, positions_xyz + (size_t)vi * 3, c[v]);
             }
             if (!in_range) continue;
-            float X[3], Y[3], W[3], a[3], b[3], cc[3];
+            /* 2: near plane.  d >= 0 is inside */
+            float d[3], poly[4][4];
+            int n_out = 0;
+            for (int v = 0; v < 3; ++v) d[v] = (flags & 1u) ? c[v][3] - 1e-5f : c[v][2];
             for (int v = 0; v < 3; ++v) {
-                X[v] = (c[v][0] + c[v][3]) * half_w;
-                Y[v] = (c[v][1] + c[v][3]) * half_h;
-                W[v] = c[v][3];
-            }
-            a[0] = Y[1] * W[2] - Y[2] * W[1]; b[0] = X[2] * W[1] - X[1] * W[2]; cc[0] = X[1] * Y[2] - X[2] * Y[1];
-            a[1] = Y[2] * W[0] - Y[0] * W[2]; b[1] = X[0] * W[2] - X[2] * W[0]; cc[1] = X[2] * Y[0] - X[0] * Y[2];
-            a[2] = Y[0] * W[1] - Y[1] * W[0]; b[2] = X[1] * W[0] - X[0] * W[1]; cc[2] = X[0] * Y[1] - X[1] * Y[0];
-            const float det = (X[0] * a[0] + X[1] * a[1]) + X[2] * a[2];
-            if (!(det > 0.f || det < 0.f)) continue;
-            if (!(W[0] > 0.f || W[1] > 0.f || W[2] > 0.f)) continue;
-            const float s = det > 0.f ? 1.f : -1.f;
-            /* the checker walks every sample of the target: no bounding box to get wrong */
-            for (uint32_t j = 0; j < height; ++j) {
-                const float py = (float)j + 0.5f;
-                for (uint32_t i = 0; i < width; ++i) {
-                    const float px = (float)i + 0.5f;
-                    float e[3];
-                    int inside = 1;
-                    for (int q = 0; q < 3; ++q) {
-                        e[q] = (a[q] * px + b[q] * py) + cc[q];
-                        const float es = s * e[q], as = s * a[q], bs = s * b[q];
-                        if (!(es > 0.f || (es == 0.f && (as > 0.f || (as == 0.f && bs > 0.f))))) inside = 0;
-                    }
-                    if (!inside) continue;
-                    if (!(s * ((e[0] + e[1]) + e[2]) > 0.f)) continue;
-                    float depth = ((c[0][2] * e[0] + c[1][2] * e[1]) + c[2][2] * e[2]) / det;
-                    if (flags & 1u) depth = depth < 0.f ? 0.f : (depth > 1.f ? 1.f : depth);
-                    if (!(depth >= 0.f && depth <= 1.f)) continue;
-                    uint32_t bits;
-                    memcpy(&bits, &depth, 4);
-                    const uint64_t word = ((uint64_t)bits << 32) | inst;
-                    uint64_t* dst = &target[(size_t)j * width + i];
-                    if (word < *dst) *dst = word;
+                const int nx = (v + 1) % 3;
+                const int in_v = d[v] >= 0.f, in_n = d[nx] >= 0.f;
+                if (in_v) memcpy(poly[n_out++], c[v], 16);
+                if (in_v != in_n) {
+                    const int a = in_v ? v : nx, b = in_v ? nx : v; /* from the inside vertex a towards the outside one b */
+                    const float tt = d[a] / (d[a] - d[b]);
+                    for (int q = 0; q < 4; ++q) poly[n_out][q] = c[a][q] + tt * (c[b][q] - c[a][q]);
+                    ++n_out;
                 }
+            }
+            if (n_out < 3) continue;
+            {
+                const float t0[3][4] = {{poly[0][0], poly[0][1], poly[0][2], poly[0][3]}, {poly[1][0], poly[1][1], poly[1][2], poly[1][3]},
+                                        {poly[2][0], poly[2][1], poly[2][2], poly[2][3]}};
+                sso_raster_tri(t0, width, height, flags, inst, target);
+            }
+            if (n_out == 4) {
+                const float t1[3][4] = {{poly[0][0], poly[0][1], poly[0][2], poly[0][3]}, {poly[2][0], poly[2][1], poly[2][2], poly[2][3]},
+                                        {poly[3][0], poly[3][1], poly[3][2], poly[3][3]}};
+                sso_raster_tri(t1, width, height, flags, inst, target);
             }
         }
     }

@@ -119,6 +119,41 @@ def test_camera_inside_a_box_needs_no_clipper():
     ctx.close()
 
 
+def test_far_small_triangles_at_scene_scale():
+    """The shape of configs[2]: boxes of a few units seen from 600 away land on a handful of samples each; coverage is
+    decided by exact integer edge functions on snapped vertices, so it cannot depend on float cancellation."""
+    sc = synth.flat_scene(120_000, n_keys=300)
+    pos, ind, slots = synth.box_geometry(sc.slots)
+    sc = synth.SceneArrays(**{**sc.__dict__, "slots": slots})
+    views = views_for((0.0, 0.0, 600.0))
+    ctx, slot, out = run(sc, pos, ind, views, 512, 320, lambda v: 0 if v == 0 else S.RASTER_DEPTH_CLAMP)
+    for v, (img, want, got_view) in enumerate(out):
+        assert np.array_equal(img, want), f"view {v}: {np.count_nonzero(img != want)} samples differ"
+    assert np.count_nonzero(out[0][0] != np.uint64(S.RASTER_EMPTY)) > 10_000
+    ctx.close()
+
+
+def test_near_plane_cuts_triangles_and_clamp_keeps_them():
+    """Boxes straddling the camera's near plane: without DepthClamp the part in front of it is cut away (new vertices
+    interpolated from the inside vertex), with DepthClamp the triangle is cut at w = 1e-5 instead and what is left is
+    rasterised in homogeneous coordinates when its projection cannot be snapped."""
+    sc = synth.flat_scene(40, n_keys=6)
+    trs = sc.trs.copy()
+    rng = np.random.default_rng(3)
+    trs[:, :3] = rng.uniform(-3, 3, (40, 3)).astype(np.float32)
+    trs[:, 2] = rng.uniform(2.0, 8.0, 40).astype(np.float32)       # camera at z = 5 looking down -z: some in front, some around it
+    pos, ind, slots = synth.box_geometry(sc.slots)
+    sc = synth.SceneArrays(**{**sc.__dict__, "trs": trs, "slots": slots, "inst_aabb": None})
+    views = views_for((0.0, 0.0, 5.0), 1)
+    for flags in (0, S.RASTER_DEPTH_CLAMP):
+        ctx, slot, out = run(sc, pos, ind, views, 72, 40, lambda v: flags)
+        img, want, got_view = out[0]
+        assert len(got_view["idx"]) > 5
+        assert np.array_equal(img, want), f"flags {flags}: {np.count_nonzero(img != want)} samples differ"
+        assert np.count_nonzero(img != np.uint64(S.RASTER_EMPTY)) > 500
+        ctx.close()
+
+
 def test_geometry_out_of_range_draws_nothing_and_errors_are_reported():
     sc, pos, ind = close_up_scene(50, seed_shift=1)
     views = views_for((0.0, 0.0, 70.0), 1)

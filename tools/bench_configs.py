@@ -2,6 +2,8 @@
     cfg2  synthetic 1M instances, 3-level hierarchy, 1 camera          (configs[1])
     cfg3h configs[2] with the 3-level hierarchy variant (2^24 leaves)  (SURVEY.md 8d "the same 3-level variant")
     cfg3s configs[2], steady state: static streams unchanged, sorted order kept (SS_FRAME_REUSE_SORT)
+    raster the consumer pass over configs[2]'s lists: entity-id pass of the camera view at 1920x1080 and the depth pass of
+          each shadow cascade at 4096x4096 (CSMSettings::MapSize, SceneRenderer.h:179), one box (12 triangles) per instance
     cfg5  one GPU's share of configs[4]: 512 cameras x 1M instances in batches of 8 views, world rows and sorted
           order kept after the first batch (SS_FRAME_REUSE_WORLD | SS_FRAME_REUSE_SORT)
 One JSON line per config on stdout.  CUDA events on the library's stream, after warm-up.  Not a bench.py
@@ -77,6 +79,29 @@ def main():
         views = synth.make_views(S.camera_view_proj, S.cascade_matrices, 5)
         r = frames(S, torch, sc, views, a.reps, flags=S.FRAME_REUSE_SORT)
         print(json.dumps({"config": "cfg3 steady state: 2^24 flat, 5 views, sorted order kept (static keys)", **r}), flush=True)
+        del sc
+    if "raster" in a.which:
+        sc = synth.flat_scene(1 << 24)
+        pos, ind, slots = synth.box_geometry(sc.slots)
+        sc = synth.SceneArrays(**{**sc.__dict__, "slots": slots})
+        views = synth.make_views(S.camera_view_proj, S.cascade_matrices, 5)
+        ctx = S.SceneSubmit(sc.n_nodes, sc.n_instances, len(sc.slots), max_views=5, max_draws_per_view=1 << 16)
+        ctx.load_scene(sc)
+        ctx.set_geometry(pos, ind)
+        slot = ctx.frame(views)
+        st = ctx.frame_sync(slot)
+        stream = torch.cuda.ExternalStream(ctx.stream, device=0)
+        res = {}
+        for v, (w, h, flags) in enumerate([(1920, 1080, 0)] + [(4096, 4096, S.RASTER_DEPTH_CLAMP)] * 4):
+            ctx.raster_view(slot, v, w, h, flags)   # warm-up (allocates the target on a size change)
+            ms, _ = timed(torch, stream, lambda i: ctx.raster_view(slot, v, w, h, flags), 5)
+            img = ctx.download_raster(v)
+            n_vis = int(st.visible[v])
+            res[f"view{v}"] = {"target": [w, h], "instances": n_vis, "triangles": n_vis * 12, "ms": round(ms / 5, 4),
+                               "mtri_per_s": round(n_vis * 12 / (ms / 5 * 1e-3) / 1e6, 1),
+                               "covered_samples": int(np.count_nonzero(img != np.uint64(S.RASTER_EMPTY)))}
+        print(json.dumps({"config": "consumer pass over cfg3's lists: id pass 1920x1080 + 4 cascade depth passes 4096^2", **res}), flush=True)
+        ctx.close()
         del sc
     if "cfg5" in a.which:
         sc = synth.hierarchy_scene()

@@ -4,13 +4,20 @@
 //     clip = LightSpaceMatrices[cascade] * world; depth only, DepthClamp on — SceneRenderer.cpp:188)
 //   * SelectionPass (CoreEditor.vert / .frag: clip = Projection * View * world, the fragment stores a_EntityID;
 //     the editor reads ONE pixel back, SceneRenderer.cpp:1449-1456)
-// Both passes are the same arithmetic over (instance row, triangle); the target word is [depth bits : 32 | id : 32]
-// and the depth test is one 64-bit atomicMin, so the result does not depend on the order triangles arrive in.
+// Both passes are the same work per (instance row, triangle); the target word is [depth bits : 32 | id : 32] and the
+// depth test is one 64-bit atomicMin, so the result does not depend on the order triangles arrive in.
 //
-// Rasterisation is in homogeneous coordinates (edge functions from the adjugate of the clip-space (x, y, w)
-// matrix), so triangles that cross w = 0 need no clipper.  Every float operation is written out in a fixed order
-// (-fmad=false), the same order the tests' CPU restatement uses: the two must agree bit for bit.
-// The reference's own rasteriser is the Vulkan device: unavailable on this box.
+// Per triangle, the fixed-function steps of that pipeline:
+//   1. clip = view_proj * (transform * position)
+//   2. clip against the near plane z >= 0 (with DepthClamp: against w >= 1e-5, depth then clamped per sample); new
+//      vertices are interpolated from the inside vertex towards the outside one, so neighbours agree on them
+//   3. perspective divide, viewport (y down), snap to 1/256 pixel; coverage by exact integer edge functions at pixel
+//      centres, a shared edge belongs to exactly one of its triangles; depth = screen-linear z/w
+//   3b. a triangle that cannot be snapped (w <= 0 left after clipping, or a vertex farther than 2^20 pixels out) is
+//      rasterised in homogeneous float coordinates (edge functions = adjugate rows of the (X, Y, W) matrix) over the
+//      whole target
+// Every float operation is written out in a fixed order (-fmad=false), the order the tests' CPU restatement uses:
+// the two agree bit for bit.  The reference's own rasteriser is the Vulkan device: unavailable on this box.
 #include "ss_kernels.h"
 
 namespace ss {
@@ -18,13 +25,16 @@ namespace ss {
 namespace {
 
 constexpr int kRasterThreads = 128;
+constexpr int kBigSamples = 48;               // bounds holding more samples than this are walked by the whole warp
+constexpr float kSubpixel = 256.0f;
+constexpr float kSnapLimit = 268435456.0f;    // 2^28 sub-pixel units = 2^20 pixels
 
-struct Tri {
-    float a[3], b[3], c[3];  // edge functions E_i(px, py) = (a_i * px + b_i * py) + c_i
-    float z[3];
-    float det;
-    int x0, x1, y0, y1;      // inclusive pixel bounds, already clamped to the target
-    bool ok;
+// A triangle ready to be sampled.  mode 0 (snapped): w = x[3], y[3] as int32 in 1/256 pixel, zn[3] = z/w per vertex.
+// mode 1 (homogeneous): w = a[3], b[3], c[3] edge functions, z[3], det.
+struct Work {
+    uint32_t w[13];
+    int x0, x1, y0, y1;  // inclusive sample bounds inside the target
+    int mode;            // -1: nothing to draw
 };
 
 __device__ __forceinline__ void clip_of(const float* vp, float4 r0, float4 r1, float4 r2, const float* p, float out[4])
@@ -37,82 +47,267 @@ __device__ __forceinline__ void clip_of(const float* vp, float4 r0, float4 r1, f
     for (int j = 0; j < 4; ++j) out[j] = (vp[j] * wx + vp[4 + j] * wy) + (vp[8 + j] * wz + vp[12 + j]);
 }
 
-__device__ __forceinline__ Tri setup(const float c0[4], const float c1[4], const float c2[4], float half_w, float half_h,
-                                     int width, int height)
+__device__ __forceinline__ Work setup(const float c[3][4], int width, int height)
 {
-    Tri t;
-    // pixel-space homogeneous coordinates: X / W is the pixel abscissa, Y / W the ordinate (y down, as Vulkan)
-    const float X0 = (c0[0] + c0[3]) * half_w, X1 = (c1[0] + c1[3]) * half_w, X2 = (c2[0] + c2[3]) * half_w;
-    const float Y0 = (c0[1] + c0[3]) * half_h, Y1 = (c1[1] + c1[3]) * half_h, Y2 = (c2[1] + c2[3]) * half_h;
-    const float W0 = c0[3], W1 = c1[3], W2 = c2[3];
-    t.a[0] = Y1 * W2 - Y2 * W1; t.b[0] = X2 * W1 - X1 * W2; t.c[0] = X1 * Y2 - X2 * Y1;
-    t.a[1] = Y2 * W0 - Y0 * W2; t.b[1] = X0 * W2 - X2 * W0; t.c[1] = X2 * Y0 - X0 * Y2;
-    t.a[2] = Y0 * W1 - Y1 * W0; t.b[2] = X1 * W0 - X0 * W1; t.c[2] = X0 * Y1 - X1 * Y0;
-    t.det = (X0 * t.a[0] + X1 * t.a[1]) + X2 * t.a[2];
-    t.z[0] = c0[2]; t.z[1] = c1[2]; t.z[2] = c2[2];
-    t.ok = (t.det > 0.f || t.det < 0.f) && (W0 > 0.f || W1 > 0.f || W2 > 0.f);  // not degenerate (nor NaN), not wholly behind
-    float lx = 0.f, hx = (float)width, ly = 0.f, hy = (float)height;
-    if (W0 > 0.f && W1 > 0.f && W2 > 0.f) {  // all in front: the projected bounding box; otherwise the whole target
-        const float sx0 = X0 / W0, sx1 = X1 / W1, sx2 = X2 / W2, sy0 = Y0 / W0, sy1 = Y1 / W1, sy2 = Y2 / W2;
-        lx = fmaxf(fminf(fminf(sx0, sx1), sx2), 0.f);
-        hx = fminf(fmaxf(fmaxf(sx0, sx1), sx2), (float)width);
-        ly = fmaxf(fminf(fminf(sy0, sy1), sy2), 0.f);
-        hy = fminf(fmaxf(fmaxf(sy0, sy1), sy2), (float)height);
-        if (!(lx <= hx && ly <= hy)) t.ok = false;  // off the target (or NaN)
+    Work t;
+    t.mode = -1;
+    t.x0 = t.y0 = 0;
+    t.x1 = t.y1 = -1;
+    const float half_w = 0.5f * (float)width, half_h = 0.5f * (float)height;
+    int x[3], y[3];
+    float zn[3];
+    bool snap = true;
+#pragma unroll
+    for (int v = 0; v < 3; ++v) {
+        if (!(c[v][3] > 0.f)) { snap = false; break; }
+        const float sx = ((c[v][0] / c[v][3]) * half_w + half_w) * kSubpixel;
+        const float sy = ((c[v][1] / c[v][3]) * half_h + half_h) * kSubpixel;
+        if (!(sx > -kSnapLimit && sx < kSnapLimit && sy > -kSnapLimit && sy < kSnapLimit)) { snap = false; break; }
+        x[v] = (int)__float2ll_rn(sx);
+        y[v] = (int)__float2ll_rn(sy);
+        zn[v] = c[v][2] / c[v][3];
     }
-    // a pixel (i, j) is sampled at (i + 0.5, j + 0.5); one pixel of slack each side, the edge tests decide
-    t.x0 = max((int)floorf(lx) - 1, 0);
-    t.x1 = min((int)ceilf(hx), width - 1);
-    t.y0 = max((int)floorf(ly) - 1, 0);
-    t.y1 = min((int)ceilf(hy), height - 1);
+    if (snap) {
+        const long long area = (long long)(x[1] - x[0]) * (y[2] - y[0]) - (long long)(y[1] - y[0]) * (x[2] - x[0]);
+        if (area == 0) return t;
+        const int minx = min(min(x[0], x[1]), x[2]), maxx = max(max(x[0], x[1]), x[2]);
+        const int miny = min(min(y[0], y[1]), y[2]), maxy = max(max(y[0], y[1]), y[2]);
+        // pixel i is sampled at 256 i + 128; >> 8 is the floor division
+        t.x0 = max((minx - 128 + 255) >> 8, 0);
+        t.x1 = min((maxx - 128) >> 8, width - 1);
+        t.y0 = max((miny - 128 + 255) >> 8, 0);
+        t.y1 = min((maxy - 128) >> 8, height - 1);
+        if (t.x0 > t.x1 || t.y0 > t.y1) return t;  // covers no sample
+#pragma unroll
+        for (int v = 0; v < 3; ++v) {
+            t.w[v] = (uint32_t)x[v];
+            t.w[3 + v] = (uint32_t)y[v];
+            t.w[6 + v] = __float_as_uint(zn[v]);
+        }
+        t.mode = 0;
+        return t;
+    }
+    // homogeneous pixel-space coordinates: X / W is the pixel abscissa, Y / W the ordinate
+    const float X0 = (c[0][0] + c[0][3]) * half_w, X1 = (c[1][0] + c[1][3]) * half_w, X2 = (c[2][0] + c[2][3]) * half_w;
+    const float Y0 = (c[0][1] + c[0][3]) * half_h, Y1 = (c[1][1] + c[1][3]) * half_h, Y2 = (c[2][1] + c[2][3]) * half_h;
+    const float W0 = c[0][3], W1 = c[1][3], W2 = c[2][3];
+    float a[3], b[3], cc[3];
+    a[0] = Y1 * W2 - Y2 * W1; b[0] = X2 * W1 - X1 * W2; cc[0] = X1 * Y2 - X2 * Y1;
+    a[1] = Y2 * W0 - Y0 * W2; b[1] = X0 * W2 - X2 * W0; cc[1] = X2 * Y0 - X0 * Y2;
+    a[2] = Y0 * W1 - Y1 * W0; b[2] = X1 * W0 - X0 * W1; cc[2] = X0 * Y1 - X1 * Y0;
+    const float det = (X0 * a[0] + X1 * a[1]) + X2 * a[2];
+    if (!(det > 0.f || det < 0.f)) return t;                  // degenerate, or NaN
+    if (!(W0 > 0.f || W1 > 0.f || W2 > 0.f)) return t;        // wholly behind
+#pragma unroll
+    for (int q = 0; q < 3; ++q) {
+        t.w[q] = __float_as_uint(a[q]);
+        t.w[3 + q] = __float_as_uint(b[q]);
+        t.w[6 + q] = __float_as_uint(cc[q]);
+        t.w[9 + q] = __float_as_uint(c[q][2]);
+    }
+    t.w[12] = __float_as_uint(det);
+    t.x0 = 0; t.x1 = width - 1; t.y0 = 0; t.y1 = height - 1;
+    t.mode = 1;
     return t;
 }
 
+__device__ __forceinline__ void put(unsigned long long* target, uint32_t width, int i, int j, float depth, bool clamp_depth,
+                                    uint32_t inst)
+{
+    if (clamp_depth) depth = depth < 0.f ? 0.f : (depth > 1.f ? 1.f : depth);  // a NaN stays one and is dropped
+    if (!(depth >= 0.f && depth <= 1.f)) return;
+    atomicMin(target + (size_t)j * width + i, ((unsigned long long)__float_as_uint(depth) << 32) | inst);
+}
+
+// what the sample loop needs, derived once per triangle
+struct Prep {
+    int x[3], y[3], dx[3], dy[3];  // mode 0; edge q runs from vertex q+1 to vertex q+2 (opposite vertex q)
+    long long s;
+    float fa, zn[3];
+    float a[3], b[3], c[3], z[3], det, sf;  // mode 1
+};
+
+__device__ __forceinline__ Prep prepare(const Work& t)
+{
+    Prep p;
+    if (t.mode == 0) {
+#pragma unroll
+        for (int v = 0; v < 3; ++v) {
+            p.x[v] = (int)t.w[v];
+            p.y[v] = (int)t.w[3 + v];
+            p.zn[v] = __uint_as_float(t.w[6 + v]);
+        }
+#pragma unroll
+        for (int q = 0; q < 3; ++q) {
+            const int p0 = (q + 1) % 3, p1 = (q + 2) % 3;
+            p.dx[q] = p.x[p1] - p.x[p0];
+            p.dy[q] = p.y[p1] - p.y[p0];
+        }
+        const long long area = (long long)p.dx[2] * (p.y[2] - p.y[0]) - (long long)p.dy[2] * (p.x[2] - p.x[0]);
+        p.s = area > 0 ? 1 : -1;
+        p.fa = (float)(p.s * area);
+    } else {
+#pragma unroll
+        for (int q = 0; q < 3; ++q) {
+            p.a[q] = __uint_as_float(t.w[q]);
+            p.b[q] = __uint_as_float(t.w[3 + q]);
+            p.c[q] = __uint_as_float(t.w[6 + q]);
+            p.z[q] = __uint_as_float(t.w[9 + q]);
+        }
+        p.det = __uint_as_float(t.w[12]);
+        p.sf = p.det > 0.f ? 1.f : -1.f;
+    }
+    return p;
+}
+
+__device__ __forceinline__ void shade(const Prep& p, int mode, int i, int j, bool clamp_depth, uint32_t inst,
+                                      unsigned long long* target, uint32_t width)
+{
+    if (mode == 0) {
+        const int px = 256 * i + 128, py = 256 * j + 128;
+        long long e[3];
+        bool inside = true;
+#pragma unroll
+        for (int q = 0; q < 3; ++q) {
+            const int p0 = (q + 1) % 3;
+            e[q] = p.s * ((long long)p.dx[q] * (py - p.y[p0]) - (long long)p.dy[q] * (px - p.x[p0]));
+            // a sample exactly on an edge belongs to the triangle for which that edge runs down, or level to the right
+            const long long sdx = p.s * p.dx[q], sdy = p.s * p.dy[q];
+            inside = inside && (e[q] > 0 || (e[q] == 0 && (sdy > 0 || (sdy == 0 && sdx > 0))));
+        }
+        if (!inside) return;
+        const float l0 = (float)e[0] / p.fa, l1 = (float)e[1] / p.fa, l2 = (float)e[2] / p.fa;
+        put(target, width, i, j, (p.zn[0] * l0 + p.zn[1] * l1) + p.zn[2] * l2, clamp_depth, inst);
+    } else {
+        const float px = (float)i + 0.5f, py = (float)j + 0.5f;
+        float e[3];
+        bool inside = true;
+#pragma unroll
+        for (int q = 0; q < 3; ++q) {
+            e[q] = (p.a[q] * px + p.b[q] * py) + p.c[q];
+            const float es = p.sf * e[q], as = p.sf * p.a[q], bs = p.sf * p.b[q];
+            inside = inside && (es > 0.f || (es == 0.f && (as > 0.f || (as == 0.f && bs > 0.f))));
+        }
+        if (!inside) return;
+        if (!(p.sf * ((e[0] + e[1]) + e[2]) > 0.f)) return;  // 1 / w at the sample must be positive
+        put(target, width, i, j, ((p.z[0] * e[0] + p.z[1] * e[1]) + p.z[2] * e[2]) / p.det, clamp_depth, inst);
+    }
+}
+
+// One thread per visible instance; its triangles in order.  Small triangles (the common case at scene scale: a few
+// samples) are walked by the thread; a large one is handed to the warp, lanes striding over the samples of its
+// bounds, so that a view whose instances cover thousands of pixels each (the near shadow cascades) is not serialised.
 __global__ void __launch_bounds__(kRasterThreads) k_raster(const __grid_constant__ RasterArgs a)
 {
     const uint32_t k = blockIdx.x * kRasterThreads + threadIdx.x;
-    if (k >= a.visible) return;
-    const float4 r0 = a.rows[(size_t)k * 3 + 0], r1 = a.rows[(size_t)k * 3 + 1], r2 = a.rows[(size_t)k * 3 + 2];
-    const uint32_t inst = a.idx[k];
-    const SlotDev& sd = a.slots[a.slot[inst]];
-    const uint32_t n_tri = sd.index_count / 3u;
-    const float half_w = 0.5f * (float)a.width, half_h = 0.5f * (float)a.height;
+    const int lane = threadIdx.x & 31;
+    const bool live = k < a.visible;
+    float4 r0 = make_float4(0, 0, 0, 0), r1 = r0, r2 = r0;
+    uint32_t inst = 0, n_tri = 0, first_index = 0;
+    int32_t vertex_offset = 0;
+    if (live) {
+        r0 = a.rows[(size_t)k * 3 + 0];
+        r1 = a.rows[(size_t)k * 3 + 1];
+        r2 = a.rows[(size_t)k * 3 + 2];
+        inst = a.idx[k];
+        const SlotDev& sd = a.slots[a.slot[inst]];
+        n_tri = sd.index_count / 3u;
+        first_index = sd.first_index;
+        vertex_offset = sd.vertex_offset;
+    }
     const bool clamp_depth = (a.flags & SS_RASTER_DEPTH_CLAMP) != 0;
-    for (uint32_t tI = 0; tI < n_tri; ++tI) {
-        float c[3][4];
-        bool in_range = true;
+    const uint32_t n_iter = __reduce_max_sync(0xffffffffu, n_tri);
+    for (uint32_t tI = 0; tI < n_iter; ++tI) {
+        // 1 + 2: the triangle in clip space, cut by the near plane into 0, 1 or 2 triangles
+        float poly[4][4];
+        int n_out = 0;
+        if (tI < n_tri) {
+            float c[3][4], d[3];
+            bool in_range = true;
 #pragma unroll
-        for (int v = 0; v < 3; ++v) {
-            const uint64_t ii = (uint64_t)sd.first_index + (uint64_t)tI * 3u + (uint64_t)v;
-            if (ii >= a.n_indices) { in_range = false; break; }
-            const int64_t vi = (int64_t)sd.vertex_offset + (int64_t)a.indices[ii];
-            if (vi < 0 || vi >= (int64_t)a.n_vertices) { in_range = false; break; }
-            clip_of(a.vp, r0, r1, r2, a.positions + (size_t)vi * 3, c[v]);
-        }
-        if (!in_range) continue;  // a table that points outside the geometry draws nothing
-        const Tri t = setup(c[0], c[1], c[2], half_w, half_h, (int)a.width, (int)a.height);
-        if (!t.ok) continue;
-        const float s = t.det > 0.f ? 1.f : -1.f;
-        for (int j = t.y0; j <= t.y1; ++j) {
-            const float py = (float)j + 0.5f;
-            for (int i = t.x0; i <= t.x1; ++i) {
-                const float px = (float)i + 0.5f;
-                float e[3];
-                bool inside = true;
+            for (int v = 0; v < 3; ++v) {
+                const uint64_t ii = (uint64_t)first_index + (uint64_t)tI * 3u + (uint64_t)v;
+                if (ii >= a.n_indices) { in_range = false; break; }
+                const int64_t vi = (int64_t)vertex_offset + (int64_t)a.indices[ii];
+                if (vi < 0 || vi >= (int64_t)a.n_vertices) { in_range = false; break; }
+                clip_of(a.vp, r0, r1, r2, a.positions + (size_t)vi * 3, c[v]);
+            }
+            if (in_range) {  // a table that points outside the geometry draws nothing
 #pragma unroll
-                for (int q = 0; q < 3; ++q) {
-                    e[q] = (t.a[q] * px + t.b[q] * py) + t.c[q];
-                    const float es = s * e[q], as = s * t.a[q], bs = s * t.b[q];
-                    // on an edge: owned by the triangle whose edge normal points right, or straight down
-                    inside = inside && (es > 0.f || (es == 0.f && (as > 0.f || (as == 0.f && bs > 0.f))));
+                for (int v = 0; v < 3; ++v) d[v] = clamp_depth ? c[v][3] - 1e-5f : c[v][2];
+                if (d[0] >= 0.f && d[1] >= 0.f && d[2] >= 0.f) {
+#pragma unroll
+                    for (int v = 0; v < 3; ++v)
+#pragma unroll
+                        for (int q = 0; q < 4; ++q) poly[v][q] = c[v][q];
+                    n_out = 3;
+                } else {
+#pragma unroll
+                    for (int v = 0; v < 3; ++v) {
+                        const int nx = (v + 1) % 3;
+                        const bool in_v = d[v] >= 0.f, in_n = d[nx] >= 0.f;
+                        if (in_v) {
+#pragma unroll
+                            for (int q = 0; q < 4; ++q) poly[n_out][q] = c[v][q];
+                            ++n_out;
+                        }
+                        if (in_v != in_n) {
+                            const int ia = in_v ? v : nx, ib = in_v ? nx : v;  // inside vertex, outside vertex
+                            const float tt = d[ia] / (d[ia] - d[ib]);
+#pragma unroll
+                            for (int q = 0; q < 4; ++q) poly[n_out][q] = c[ia][q] + tt * (c[ib][q] - c[ia][q]);
+                            ++n_out;
+                        }
+                    }
                 }
-                if (!inside) continue;
-                if (!(s * ((e[0] + e[1]) + e[2]) > 0.f)) continue;  // 1 / w at the sample must be positive
-                float depth = ((t.z[0] * e[0] + t.z[1] * e[1]) + t.z[2] * e[2]) / t.det;
-                if (clamp_depth) depth = depth < 0.f ? 0.f : (depth > 1.f ? 1.f : depth);  // a NaN stays one and is dropped
-                if (!(depth >= 0.f && depth <= 1.f)) continue;
-                const unsigned long long word = ((unsigned long long)__float_as_uint(depth) << 32) | inst;
-                atomicMin(a.target + (size_t)j * a.width + i, word);
+            }
+        }
+        const int n_sub = n_out < 3 ? 0 : n_out - 2;
+        const int sub_iter = __reduce_max_sync(0xffffffffu, n_sub);
+        for (int u = 0; u < sub_iter; ++u) {
+            Work t;
+            t.mode = -1;
+            t.x0 = t.y0 = 0;
+            t.x1 = t.y1 = -1;
+            if (u < n_sub) {
+                float c3[3][4];
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    c3[0][q] = poly[0][q];
+                    c3[1][q] = poly[u + 1][q];
+                    c3[2][q] = poly[u + 2][q];
+                }
+                t = setup(c3, (int)a.width, (int)a.height);
+            }
+            const bool big = t.mode >= 0 && (long long)(t.x1 - t.x0 + 1) * (t.y1 - t.y0 + 1) > kBigSamples;
+            if (t.mode >= 0 && !big) {
+                const Prep p = prepare(t);
+                for (int j = t.y0; j <= t.y1; ++j)
+                    for (int i = t.x0; i <= t.x1; ++i) shade(p, t.mode, i, j, clamp_depth, inst, a.target, a.width);
+            }
+            uint32_t todo = __ballot_sync(0xffffffffu, big);
+            while (todo) {
+                const int src = __ffs(todo) - 1;
+                todo &= todo - 1;
+                Work w;
+#pragma unroll
+                for (int q = 0; q < 13; ++q) w.w[q] = __shfl_sync(0xffffffffu, t.w[q], src);
+                w.x0 = __shfl_sync(0xffffffffu, t.x0, src);
+                w.x1 = __shfl_sync(0xffffffffu, t.x1, src);
+                w.y0 = __shfl_sync(0xffffffffu, t.y0, src);
+                w.y1 = __shfl_sync(0xffffffffu, t.y1, src);
+                w.mode = __shfl_sync(0xffffffffu, t.mode, src);
+                const uint32_t w_inst = __shfl_sync(0xffffffffu, inst, src);
+                const Prep p = prepare(w);
+                const int bw = w.x1 - w.x0 + 1;
+                // lanes take consecutive samples of the bounds in row-major order, 32 at a time
+                int i = w.x0 + lane, j = w.y0;
+                while (i > w.x1) { i -= bw; ++j; }
+                while (j <= w.y1) {
+                    shade(p, w.mode, i, j, clamp_depth, w_inst, a.target, a.width);
+                    i += 32;
+                    while (i > w.x1) { i -= bw; ++j; }
+                }
             }
         }
     }
