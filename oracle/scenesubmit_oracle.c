@@ -731,12 +731,13 @@ static void sso_raster_tri(const float c[3][4], uint32_t width, uint32_t height,
     int snap = 1;
     for (int v = 0; v < 3; ++v) {
         if (!(c[v][3] > 0.f)) { snap = 0; break; }
-        const float sx = ((c[v][0] / c[v][3]) * half_w + half_w) * SSO_SUBPIXEL;
-        const float sy = ((c[v][1] / c[v][3]) * half_h + half_h) * SSO_SUBPIXEL;
+        const float iw = 1.0f / c[v][3];
+        const float sx = ((c[v][0] * iw) * half_w + half_w) * SSO_SUBPIXEL;
+        const float sy = ((c[v][1] * iw) * half_h + half_h) * SSO_SUBPIXEL;
         if (!(sx > -SSO_SNAP_LIMIT && sx < SSO_SNAP_LIMIT && sy > -SSO_SNAP_LIMIT && sy < SSO_SNAP_LIMIT)) { snap = 0; break; }
         x[v] = llrintf(sx);
         y[v] = llrintf(sy);
-        zn[v] = c[v][2] / c[v][3];
+        zn[v] = c[v][2] * iw;
     }
     if (!snap) {
         sso_raster_2dh(c, width, height, flags, inst, target);

@@ -85,6 +85,7 @@ struct ss_ctx {
     uint32_t* d_indices = nullptr;
     uint32_t n_vertices = 0, n_indices = 0;
     unsigned long long* d_raster = nullptr;  // [max_views][raster_h][raster_w]
+    unsigned long long* d_raster_pairs = nullptr;  // [max_draws + 1]
     uint32_t raster_w = 0, raster_h = 0;
     uint32_t seg_parity = 0;
     uint64_t* d_seg_key = nullptr;
@@ -220,6 +221,7 @@ SS_API void ss_destroy(ss_ctx* c)
     if (c->d_positions) cudaFree(c->d_positions);
     if (c->d_indices) cudaFree(c->d_indices);
     if (c->d_raster) cudaFree(c->d_raster);
+    if (c->d_raster_pairs) cudaFree(c->d_raster_pairs);
     if (c->stream) cudaStreamDestroy(c->stream);
     delete c;
 }
@@ -895,8 +897,11 @@ SS_API ss_status ss_raster_view(ss_ctx* c, uint32_t slot, uint32_t view, uint32_
     memset(&ra, 0, sizeof ra);
     ra.rows = reinterpret_cast<const float4*>(o.instance_rows);
     ra.idx = o.instance_idx;
-    ra.slot = c->d_slot;
-    ra.slots = c->d_slots;
+    ra.draws = o.draws;
+    ra.counts = o.counts;
+    ra.max_draws = c->max_draws;
+    if (!c->d_raster_pairs) SS_CUDA(c, cudaMalloc(&c->d_raster_pairs, ((size_t)c->max_draws + 1) * sizeof(unsigned long long)));
+    ra.pairs = c->d_raster_pairs;
     ra.positions = c->d_positions;
     ra.indices = c->d_indices;
     ra.n_vertices = c->n_vertices;

@@ -60,12 +60,13 @@ __device__ __forceinline__ Work setup(const float c[3][4], int width, int height
 #pragma unroll
     for (int v = 0; v < 3; ++v) {
         if (!(c[v][3] > 0.f)) { snap = false; break; }
-        const float sx = ((c[v][0] / c[v][3]) * half_w + half_w) * kSubpixel;
-        const float sy = ((c[v][1] / c[v][3]) * half_h + half_h) * kSubpixel;
+        const float iw = 1.0f / c[v][3];
+        const float sx = ((c[v][0] * iw) * half_w + half_w) * kSubpixel;
+        const float sy = ((c[v][1] * iw) * half_h + half_h) * kSubpixel;
         if (!(sx > -kSnapLimit && sx < kSnapLimit && sy > -kSnapLimit && sy < kSnapLimit)) { snap = false; break; }
         x[v] = (int)__float2ll_rn(sx);
         y[v] = (int)__float2ll_rn(sy);
-        zn[v] = c[v][2] / c[v][3];
+        zn[v] = c[v][2] * iw;
     }
     if (snap) {
         const long long area = (long long)(x[1] - x[0]) * (y[2] - y[0]) - (long long)(y[1] - y[0]) * (x[2] - x[0]);
@@ -121,8 +122,8 @@ __device__ __forceinline__ void put(unsigned long long* target, uint32_t width, 
 
 // what the sample loop needs, derived once per triangle
 struct Prep {
-    int x[3], y[3], dx[3], dy[3];  // mode 0; edge q runs from vertex q+1 to vertex q+2 (opposite vertex q)
-    long long s;
+    int x[3], y[3], dx[3], dy[3];  // mode 0; edge q runs from vertex q+1 to vertex q+2 (opposite vertex q); dx, dy carry the
+                                   // triangle's orientation sign, so that the inside is the positive side
     float fa, zn[3];
     float a[3], b[3], c[3], z[3], det, sf;  // mode 1
 };
@@ -144,8 +145,14 @@ __device__ __forceinline__ Prep prepare(const Work& t)
             p.dy[q] = p.y[p1] - p.y[p0];
         }
         const long long area = (long long)p.dx[2] * (p.y[2] - p.y[0]) - (long long)p.dy[2] * (p.x[2] - p.x[0]);
-        p.s = area > 0 ? 1 : -1;
-        p.fa = (float)(p.s * area);
+        if (area < 0) {
+#pragma unroll
+            for (int q = 0; q < 3; ++q) {
+                p.dx[q] = -p.dx[q];
+                p.dy[q] = -p.dy[q];
+            }
+        }
+        p.fa = (float)(area < 0 ? -area : area);
     } else {
 #pragma unroll
         for (int q = 0; q < 3; ++q) {
@@ -170,10 +177,9 @@ __device__ __forceinline__ void shade(const Prep& p, int mode, int i, int j, boo
 #pragma unroll
         for (int q = 0; q < 3; ++q) {
             const int p0 = (q + 1) % 3;
-            e[q] = p.s * ((long long)p.dx[q] * (py - p.y[p0]) - (long long)p.dy[q] * (px - p.x[p0]));
+            e[q] = (long long)p.dx[q] * (py - p.y[p0]) - (long long)p.dy[q] * (px - p.x[p0]);
             // a sample exactly on an edge belongs to the triangle for which that edge runs down, or level to the right
-            const long long sdx = p.s * p.dx[q], sdy = p.s * p.dy[q];
-            inside = inside && (e[q] > 0 || (e[q] == 0 && (sdy > 0 || (sdy == 0 && sdx > 0))));
+            inside = inside && (e[q] > 0 || (e[q] == 0 && (p.dy[q] > 0 || (p.dy[q] == 0 && p.dx[q] > 0))));
         }
         if (!inside) return;
         const float l0 = (float)e[0] / p.fa, l1 = (float)e[1] / p.fa, l2 = (float)e[2] / p.fa;
@@ -194,48 +200,88 @@ __device__ __forceinline__ void shade(const Prep& p, int mode, int i, int j, boo
     }
 }
 
-// One thread per visible instance; its triangles in order.  Small triangles (the common case at scene scale: a few
-// samples) are walked by the thread; a large one is handed to the warp, lanes striding over the samples of its
-// bounds, so that a view whose instances cover thousands of pixels each (the near shadow cascades) is not serialised.
+// pairs[d] = number of (instance, triangle) pairs of the draws before d; pairs[n_draws] = all of them
+__global__ void __launch_bounds__(1024) k_raster_pairs(const ss_draw_cmd* draws, const uint32_t* counts, uint32_t max_draws,
+                                                       unsigned long long* pairs)
+{
+    __shared__ unsigned long long warp_sum[32];
+    __shared__ unsigned long long carry;
+    const uint32_t n_draws = min(counts[1], max_draws);
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    if (tid == 0) carry = 0;
+    __syncthreads();
+    for (uint32_t d0 = 0; d0 < n_draws; d0 += 1024) {
+        const uint32_t d = d0 + tid;
+        const unsigned long long mine = d < n_draws ? (unsigned long long)draws[d].instance_count * (draws[d].index_count / 3u) : 0ull;
+        unsigned long long x = mine;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const unsigned long long y = __shfl_up_sync(0xffffffffu, x, o);
+            if (lane >= o) x += y;
+        }
+        if (lane == 31) warp_sum[wid] = x;
+        __syncthreads();
+        unsigned long long base = carry;
+        for (int w = 0; w < wid; ++w) base += warp_sum[w];
+        if (d < n_draws) pairs[d] = base + x - mine;
+        __syncthreads();
+        if (tid == 1023) carry = base + x;
+        __syncthreads();
+    }
+    if (tid == 0) pairs[n_draws] = carry;
+}
+
+// One thread per (instance, triangle) pair of the view, pairs numbered draw by draw, instance by instance: a warp
+// holds 32 consecutive triangles (of one instance of a large mesh, or of a few instances of a small one), whatever the
+// mix of meshes.  A warp finds the draw of its first pair by bisection over the draws' prefix, its lanes walk on from
+// there.  Small triangles (the common case at scene scale: a few samples) are sampled by their thread; a large one is
+// handed to the warp, lanes striding over the samples of its bounds, so that a view whose instances cover thousands
+// of pixels each (the near shadow cascades) is not serialised.
 __global__ void __launch_bounds__(kRasterThreads) k_raster(const __grid_constant__ RasterArgs a)
 {
-    const uint32_t k = blockIdx.x * kRasterThreads + threadIdx.x;
     const int lane = threadIdx.x & 31;
-    const bool live = k < a.visible;
-    float4 r0 = make_float4(0, 0, 0, 0), r1 = r0, r2 = r0;
-    uint32_t inst = 0, n_tri = 0, first_index = 0;
-    int32_t vertex_offset = 0;
-    if (live) {
-        r0 = a.rows[(size_t)k * 3 + 0];
-        r1 = a.rows[(size_t)k * 3 + 1];
-        r2 = a.rows[(size_t)k * 3 + 2];
-        inst = a.idx[k];
-        const SlotDev& sd = a.slots[a.slot[inst]];
-        n_tri = sd.index_count / 3u;
-        first_index = sd.first_index;
-        vertex_offset = sd.vertex_offset;
-    }
+    const uint32_t n_draws = min(a.counts[1], a.max_draws);
+    const unsigned long long total = a.pairs[n_draws];
     const bool clamp_depth = (a.flags & SS_RASTER_DEPTH_CLAMP) != 0;
-    const uint32_t n_iter = __reduce_max_sync(0xffffffffu, n_tri);
-    for (uint32_t tI = 0; tI < n_iter; ++tI) {
-        // 1 + 2: the triangle in clip space, cut by the near plane into 0, 1 or 2 triangles
+    const unsigned long long warps = ((unsigned long long)gridDim.x * kRasterThreads) >> 5;
+    const unsigned long long warp_id = ((unsigned long long)blockIdx.x * kRasterThreads + threadIdx.x) >> 5;
+    for (unsigned long long g0 = warp_id * 32ull; g0 < total; g0 += warps * 32ull) {
+        // the last draw whose first pair is <= g0
+        uint32_t lo = 0, hi = n_draws;
+        while (hi - lo > 1) {
+            const uint32_t mid = (lo + hi) >> 1;
+            if (a.pairs[mid] <= g0) lo = mid; else hi = mid;
+        }
+        const unsigned long long g = g0 + (unsigned long long)lane;
+        const bool live = g < total;
         float poly[4][4];
         int n_out = 0;
-        if (tI < n_tri) {
-            float c[3][4], d[3];
+        uint32_t inst = 0;
+        if (live) {
+            uint32_t d = lo;
+            while (a.pairs[d + 1] <= g) ++d;  // draws without pairs are stepped over
+            const ss_draw_cmd dc = a.draws[d];
+            const uint32_t tris = dc.index_count / 3u;
+            const unsigned long long local = g - a.pairs[d];
+            const uint32_t ki = (uint32_t)(local / tris), tI = (uint32_t)(local - (unsigned long long)ki * tris);
+            const uint32_t k = dc.first_instance + ki;
+            const float4 r0 = a.rows[(size_t)k * 3 + 0], r1 = a.rows[(size_t)k * 3 + 1], r2 = a.rows[(size_t)k * 3 + 2];
+            inst = a.idx[k];
+            // 1 + 2: the triangle in clip space, cut by the near plane into 0, 1 or 2 triangles
+            float c[3][4], dd[3];
             bool in_range = true;
 #pragma unroll
             for (int v = 0; v < 3; ++v) {
-                const uint64_t ii = (uint64_t)first_index + (uint64_t)tI * 3u + (uint64_t)v;
+                const uint64_t ii = (uint64_t)dc.first_index + (uint64_t)tI * 3u + (uint64_t)v;
                 if (ii >= a.n_indices) { in_range = false; break; }
-                const int64_t vi = (int64_t)vertex_offset + (int64_t)a.indices[ii];
+                const int64_t vi = (int64_t)dc.vertex_offset + (int64_t)a.indices[ii];
                 if (vi < 0 || vi >= (int64_t)a.n_vertices) { in_range = false; break; }
                 clip_of(a.vp, r0, r1, r2, a.positions + (size_t)vi * 3, c[v]);
             }
             if (in_range) {  // a table that points outside the geometry draws nothing
 #pragma unroll
-                for (int v = 0; v < 3; ++v) d[v] = clamp_depth ? c[v][3] - 1e-5f : c[v][2];
-                if (d[0] >= 0.f && d[1] >= 0.f && d[2] >= 0.f) {
+                for (int v = 0; v < 3; ++v) dd[v] = clamp_depth ? c[v][3] - 1e-5f : c[v][2];
+                if (dd[0] >= 0.f && dd[1] >= 0.f && dd[2] >= 0.f) {
 #pragma unroll
                     for (int v = 0; v < 3; ++v)
 #pragma unroll
@@ -245,7 +291,7 @@ __global__ void __launch_bounds__(kRasterThreads) k_raster(const __grid_constant
 #pragma unroll
                     for (int v = 0; v < 3; ++v) {
                         const int nx = (v + 1) % 3;
-                        const bool in_v = d[v] >= 0.f, in_n = d[nx] >= 0.f;
+                        const bool in_v = dd[v] >= 0.f, in_n = dd[nx] >= 0.f;
                         if (in_v) {
 #pragma unroll
                             for (int q = 0; q < 4; ++q) poly[n_out][q] = c[v][q];
@@ -253,7 +299,7 @@ __global__ void __launch_bounds__(kRasterThreads) k_raster(const __grid_constant
                         }
                         if (in_v != in_n) {
                             const int ia = in_v ? v : nx, ib = in_v ? nx : v;  // inside vertex, outside vertex
-                            const float tt = d[ia] / (d[ia] - d[ib]);
+                            const float tt = dd[ia] / (dd[ia] - dd[ib]);
 #pragma unroll
                             for (int q = 0; q < 4; ++q) poly[n_out][q] = c[ia][q] + tt * (c[ib][q] - c[ia][q]);
                             ++n_out;
@@ -327,7 +373,9 @@ void launch_raster_clear(unsigned long long* target, size_t n, cudaStream_t st)
 
 void launch_raster(const RasterArgs& a, cudaStream_t st)
 {
-    if (a.visible) k_raster<<<(a.visible + kRasterThreads - 1) / kRasterThreads, kRasterThreads, 0, st>>>(a);
+    if (!a.visible) return;
+    k_raster_pairs<<<1, 1024, 0, st>>>(a.draws, a.counts, a.max_draws, a.pairs);
+    k_raster<<<148 * 12, kRasterThreads, 0, st>>>(a);  // persistent warps striding over the pairs
 }
 
 }  // namespace ss

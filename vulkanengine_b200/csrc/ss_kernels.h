@@ -163,8 +163,10 @@ void launch_draws(const DrawArgs& a, cudaStream_t st);
 struct RasterArgs {
     const float4* rows;        // [visible][3] TransformData of the view, draw order
     const uint32_t* idx;       // [visible] instance index of each row
-    const uint32_t* slot;      // instance -> submesh slot
-    const SlotDev* slots;
+    const ss_draw_cmd* draws;  // the view's indirect draws (index range + instance range of each run)
+    const uint32_t* counts;    // {visible, draws} of the view, device side
+    uint32_t max_draws;
+    unsigned long long* pairs; // scratch [max_draws + 1]: (instance, triangle) pairs before each draw
     const float* positions;    // [n_vertices][3]
     const uint32_t* indices;   // [n_indices]
     uint32_t n_vertices, n_indices;
