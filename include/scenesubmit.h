@@ -283,11 +283,13 @@ enum {
    vertex_offset refer to (MeshSource::m_Vertices / m_Indices, VC/Asset/MeshImporter.cpp:97-158). Host pointers. */
 SS_API ss_status ss_set_geometry(ss_ctx* ctx, const float* positions_xyz, uint32_t n_vertices,
                                  const uint32_t* indices, uint32_t n_indices);
-/* Rasterises view `view` of the frame in `slot` with that view's view_proj into the library's target layer
-   `view` (width x height words, cleared to SS_RASTER_EMPTY first).  Asynchronous on the frame stream. */
+/* Rasterises view `view` of the frame in `slot` with that view's view_proj into the library's target of that
+   view (width x height words, cleared to SS_RASTER_EMPTY first; every view keeps its own size).  Asynchronous on
+   the frame stream. */
 SS_API ss_status ss_raster_view(ss_ctx* ctx, uint32_t slot, uint32_t view, uint32_t width, uint32_t height,
                                 uint32_t flags);
-/* Device pointer of layer `view` of the last ss_raster_view size (fences the stream), or a copy to the host. */
+/* Device pointer of view `view`'s target, at the size of its last ss_raster_view (fences the stream), or a copy
+   to the host. */
 SS_API ss_status ss_map_raster(ss_ctx* ctx, uint32_t view, const uint64_t** words_out);
 SS_API ss_status ss_download_raster(ss_ctx* ctx, uint32_t view, uint64_t* words_out);
 /* One sample: the hovered-entity read-back of SelectionPass.  instance_out = 0xFFFFFFFF where nothing was drawn. */

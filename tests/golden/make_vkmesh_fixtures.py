@@ -92,7 +92,8 @@ def rot(axis, deg):
     return m
 
 
-def submeshes_of(path):
+def submeshes_of(path, geometry=None):
+    """geometry: optional dict {"positions": [], "indices": []} that receives one array per submesh"""
     top = load_fbx(path)
     unit = 1.0
     p70 = child(top["GlobalSettings"], "Properties70") if "GlobalSettings" in top else None
@@ -156,7 +157,9 @@ def submeshes_of(path):
                 corners = k - start + 1
                 slot = all_same if per_poly is None else int(per_poly[poly]) if poly < len(per_poly) else 0
                 if corners >= 3:
-                    a = acc.setdefault(slot, {"corners": 0, "indices": 0, "ids": []})
+                    a = acc.setdefault(slot, {"corners": 0, "indices": 0, "ids": [], "fan": []})
+                    for f in range(1, corners - 1):
+                        a["fan"] += [a["corners"], a["corners"] + f, a["corners"] + f + 1]
                     a["corners"] += corners
                     a["indices"] += (corners - 2) * 3
                     a["ids"] += [int(x) if x >= 0 else int(~x) for x in pvi[start:k + 1]]
@@ -164,6 +167,9 @@ def submeshes_of(path):
             for slot in sorted(acc):
                 a = acc[slot]
                 pts = verts[a["ids"]].astype(np.float32) * np.float32(scale)
+                if geometry is not None:  # one vertex per polygon corner, fans relative to the submesh's first vertex
+                    geometry["positions"].append(pts)
+                    geometry["indices"].append(np.array(a["fan"], np.uint32))
                 mat = 0
                 if 0 <= slot < len(slots):
                     mat = mat_index.setdefault(slots[slot], len(mat_index))

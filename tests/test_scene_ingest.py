@@ -90,6 +90,24 @@ def test_mini_fbx_known_answers(tmp_path):
     assert np.allclose(a, [[0, 0, 2, 2], [0, 2, 0, 0], [-2, 0, 0, 1], [0, 0, 0, 1]], atol=1e-6)
 
 
+def test_mini_fbx_geometry_matches_second_reader(tmp_path):
+    """Vertex positions (one per polygon corner, scaled) and fan-triangulated indices of the arena the consumer passes
+    draw from == the Python restatement's, submesh by submesh."""
+    import sys
+    sys.path.insert(0, os.path.join(HERE, "golden"))
+    import make_vkmesh_fixtures as MM
+    geo = {"positions": [], "indices": []}
+    subs = MM.submeshes_of(os.path.join(MINI_ASSETS, "meshes", "Source", "mini.fbx"), geo)
+    _, blocks = run_loader("load-flatten", "mini_", "Mini", tmp_path)
+    pos = np.frombuffer(blocks[10], np.float32).reshape(-1, 3)
+    ind = np.frombuffer(blocks[11], np.uint32)
+    assert np.array_equal(pos, np.concatenate(geo["positions"]))
+    assert np.array_equal(ind, np.concatenate(geo["indices"]))
+    # indices are relative to each submesh's BaseVertex and stay inside its VertexCount
+    for sm, idx in zip(subs, geo["indices"]):
+        assert len(idx) == sm["IndexCount"] and int(idx.max()) < sm["VertexCount"]
+
+
 def flat_of(blocks):
     return dict(node=np.frombuffer(blocks[0], np.uint32), slot=np.frombuffer(blocks[1], np.uint32),
                 matword=np.frombuffer(blocks[2], np.uint32), entity=np.frombuffer(blocks[3], np.uint32),
@@ -146,3 +164,62 @@ def test_loaded_mini_scene_renders_like_the_oracle(tmp_path):
         assert np.array_equal(ents, with_t[sc.node[want["idx"]]])
         assert np.array_equal(dl[:, 5].astype(np.uint32), want["draws"]["instance_count"])
         assert np.array_equal(dl[:, 4].astype(np.uint32), want["draws"]["index_count"])
+
+
+@pytest.mark.gpu
+def test_loaded_mini_scene_selection_and_shadow_passes(tmp_path):
+    """files -> loader (FBX vertices, fan indices) -> SceneRenderer mirror -> ss_frame -> SelectionPass / ShadowPass as
+    CUDA rasterisation over the compacted lists: the five targets equal the CPU restatement on the same arena, and the
+    hovered-entity read-back (SceneRenderer.cpp:1449-1456) names the entity whose instance owns that sample."""
+    W, H, SM = 320, 192, 256
+
+    def pick(mx, my):
+        out = str(tmp_path / f"pick_{mx}_{my}.bin")
+        subprocess.check_call([CLI, "load-pick", MINI_ASSETS, os.path.join(MINI_ASSETS, "scenes", "Mini.vkscene"), out,
+                               str(W), str(H), str(SM), str(mx), str(my)], stderr=subprocess.DEVNULL)
+        return read_blocks(out)
+
+    b = pick(0, 0)
+    loaded_trs = np.frombuffer(b[3], np.float32).reshape(-1, 9)
+    has_t = np.frombuffer(b[1], np.uint8)
+    light = [float(x) for x in np.frombuffer(b[4], np.float32)]
+    rb = b[9:]                                   # visible, draws, 5 x (rows, entities, draw list), then the pick blocks
+    pk = rb[2 + 15:]
+    pos = np.frombuffer(pk[0], np.float32).reshape(-1, 3)
+    ind = np.frombuffer(pk[1], np.uint32)
+    vbase, ibase = np.frombuffer(pk[2], np.uint32), np.frombuffer(pk[3], np.uint32)
+    slot_of = np.frombuffer(pk[4], np.uint32)
+    table = np.frombuffer(pk[5], synth.SUBMESH_DTYPE).copy()
+    # meshes 101 and 103 name the same source file: its vertices sit in the arena once
+    assert len(ind) == 6 + 3 + 9 and len(pos) == 4 + 3 + 5
+    table["first_index"] += ibase
+    table["vertex_offset"] += vbase.astype(np.int32)
+    # the frame the mirror ran, restated: flattened streams -> oracle lists -> oracle rasterisation
+    got, blocks = run_loader("load-flatten", "mini_", "Mini", tmp_path)
+    f = flat_of(blocks)
+    n_nodes = int(has_t.sum())
+    sc = synth.SceneArrays(trs=loaded_trs.copy(), parent=None, level_offsets=np.array([0, n_nodes], np.uint32), node=f["node"].copy(),
+                           node_base=0, slot=f["slot"].copy(), matword=f["matword"].copy(), inst_aabb=None, slots=f["slots"].copy(),
+                           mesh_bits=int(f["bits"][0]), submesh_bits=int(f["bits"][1]), material_bits=int(f["bits"][2]),
+                           mesh_handles=f["mesh_handles"].copy(), material_handles=f["material_handles"].copy(), seed=0, name="mini")
+    assert np.array_equal(slot_of, sc.slot)
+    views = default_views(light)
+    ref = O.OracleScene(sc, 0).frame(views)
+    covered = None
+    for v in range(5):
+        w, h = (W, H) if v == 0 else (SM, SM)
+        img = np.frombuffer(pk[6 + v], np.uint64).reshape(h, w)
+        want = O.raster_view(ref["views"][v]["rows"], ref["views"][v]["idx"], sc.slot, table, pos, ind, views["view_proj"][v], w, h,
+                             0 if v == 0 else 1)
+        assert np.array_equal(img, want), f"view {v}: {np.count_nonzero(img != want)} samples differ"
+        if v == 0:
+            covered = img
+    assert int(np.frombuffer(pk[11], np.int32)[0]) == -1 or covered[0, 0] != np.uint64(0xFFFFFFFFFFFFFFFF)
+    ys, xs = np.nonzero(covered != np.uint64(0xFFFFFFFFFFFFFFFF))
+    assert len(ys) > 0, "the mini scene must land on at least one sample of the selection target"
+    # hover over a covered sample: the entity of the instance that owns it
+    y, x = int(ys[len(ys) // 2]), int(xs[len(xs) // 2])
+    b2 = pick(x, y)
+    hovered = int(np.frombuffer(b2[9 + 17 + 11], np.int32)[0])
+    inst = int(covered[y, x] & np.uint64(0xFFFFFFFF))
+    assert hovered == int(f["entity"][inst])

@@ -84,9 +84,9 @@ struct ss_ctx {
     float* d_positions = nullptr;
     uint32_t* d_indices = nullptr;
     uint32_t n_vertices = 0, n_indices = 0;
-    unsigned long long* d_raster = nullptr;  // [max_views][raster_h][raster_w]
+    unsigned long long* d_raster[SS_MAX_VIEWS] = {};  // one target per view: [raster_h[v]][raster_w[v]]
     unsigned long long* d_raster_pairs = nullptr;  // [max_draws + 1]
-    uint32_t raster_w = 0, raster_h = 0;
+    uint32_t raster_w[SS_MAX_VIEWS] = {}, raster_h[SS_MAX_VIEWS] = {};
     uint32_t seg_parity = 0;
     uint64_t* d_seg_key = nullptr;
     uint32_t* d_seg_inst = nullptr;
@@ -220,7 +220,8 @@ SS_API void ss_destroy(ss_ctx* c)
     for (void* p : c->allocs) cudaFree(p);
     if (c->d_positions) cudaFree(c->d_positions);
     if (c->d_indices) cudaFree(c->d_indices);
-    if (c->d_raster) cudaFree(c->d_raster);
+    for (unsigned long long* p : c->d_raster)
+        if (p) cudaFree(p);
     if (c->d_raster_pairs) cudaFree(c->d_raster_pairs);
     if (c->stream) cudaStreamDestroy(c->stream);
     delete c;
@@ -883,14 +884,14 @@ SS_API ss_status ss_raster_view(ss_ctx* c, uint32_t slot, uint32_t view, uint32_
     ss_outputs o;
     ss_status st = ss_map_outputs(c, slot, view, &o);  // fences the frame: counts are on the host
     if (st != SS_OK) return st;
-    if (width != c->raster_w || height != c->raster_h || !c->d_raster) {
+    if (width != c->raster_w[view] || height != c->raster_h[view] || !c->d_raster[view]) {
         SS_CUDA(c, cudaStreamSynchronize(c->stream));
-        if (c->d_raster) cudaFree(c->d_raster);
-        c->d_raster = nullptr;
-        SS_CUDA(c, cudaMalloc(&c->d_raster, (size_t)c->cfg.max_views * width * height * sizeof(unsigned long long)));
-        c->raster_w = width;
-        c->raster_h = height;
-        launch_raster_clear(c->d_raster, (size_t)c->cfg.max_views * width * height, c->stream);
+        if (c->d_raster[view]) cudaFree(c->d_raster[view]);
+        c->d_raster[view] = nullptr;
+        c->raster_w[view] = c->raster_h[view] = 0;
+        SS_CUDA(c, cudaMalloc(&c->d_raster[view], (size_t)width * height * sizeof(unsigned long long)));
+        c->raster_w[view] = width;
+        c->raster_h[view] = height;
     }
     const size_t layer = (size_t)width * height;
     RasterArgs ra;
@@ -911,7 +912,7 @@ SS_API ss_status ss_raster_view(ss_ctx* c, uint32_t slot, uint32_t view, uint32_
     ra.width = width;
     ra.height = height;
     ra.flags = flags;
-    ra.target = c->d_raster + view * layer;
+    ra.target = c->d_raster[view];
     launch_raster_clear(ra.target, layer, c->stream);
     launch_raster(ra, c->stream);
     SS_CUDA(c, cudaGetLastError());
@@ -921,20 +922,20 @@ SS_API ss_status ss_raster_view(ss_ctx* c, uint32_t slot, uint32_t view, uint32_
 SS_API ss_status ss_map_raster(ss_ctx* c, uint32_t view, const uint64_t** words_out)
 {
     if (!c || !words_out) return SS_ERR_INVALID;
-    if (!c->d_raster || view >= c->cfg.max_views) return c->fail(SS_ERR_STATE, "ss_map_raster: no target for view %u", view);
+    if (view >= c->cfg.max_views || !c->d_raster[view]) return c->fail(SS_ERR_STATE, "ss_map_raster: no target for view %u", view);
     SS_CUDA(c, cudaSetDevice(c->device));
     SS_CUDA(c, cudaStreamSynchronize(c->stream));
-    *words_out = reinterpret_cast<const uint64_t*>(c->d_raster + (size_t)view * c->raster_w * c->raster_h);
+    *words_out = reinterpret_cast<const uint64_t*>(c->d_raster[view]);
     return SS_OK;
 }
 
 SS_API ss_status ss_download_raster(ss_ctx* c, uint32_t view, uint64_t* words_out)
 {
     if (!c || !words_out) return SS_ERR_INVALID;
-    if (!c->d_raster || view >= c->cfg.max_views) return c->fail(SS_ERR_STATE, "ss_download_raster: no target for view %u", view);
+    if (view >= c->cfg.max_views || !c->d_raster[view]) return c->fail(SS_ERR_STATE, "ss_download_raster: no target for view %u", view);
     SS_CUDA(c, cudaSetDevice(c->device));
-    const size_t layer = (size_t)c->raster_w * c->raster_h;
-    SS_CUDA(c, cudaMemcpyAsync(words_out, c->d_raster + view * layer, layer * 8, cudaMemcpyDeviceToHost, c->stream));
+    const size_t layer = (size_t)c->raster_w[view] * c->raster_h[view];
+    SS_CUDA(c, cudaMemcpyAsync(words_out, c->d_raster[view], layer * 8, cudaMemcpyDeviceToHost, c->stream));
     SS_CUDA(c, cudaStreamSynchronize(c->stream));
     return SS_OK;
 }
@@ -942,13 +943,12 @@ SS_API ss_status ss_download_raster(ss_ctx* c, uint32_t view, uint64_t* words_ou
 SS_API ss_status ss_read_pixel(ss_ctx* c, uint32_t view, uint32_t x, uint32_t y, uint32_t* instance_out, float* depth_out)
 {
     if (!c) return SS_ERR_INVALID;
-    if (!c->d_raster || view >= c->cfg.max_views || x >= c->raster_w || y >= c->raster_h)
-        return c->fail(SS_ERR_INVALID, "ss_read_pixel: view %u pixel (%u, %u) outside the %u x %u target", view, x, y,
-                       c->raster_w, c->raster_h);
+    if (view >= c->cfg.max_views || !c->d_raster[view] || x >= c->raster_w[view] || y >= c->raster_h[view])
+        return c->fail(SS_ERR_INVALID, "ss_read_pixel: view %u pixel (%u, %u) outside its target", view, x, y);
     SS_CUDA(c, cudaSetDevice(c->device));
     unsigned long long w = 0;
-    const size_t at = ((size_t)view * c->raster_h + y) * c->raster_w + x;
-    SS_CUDA(c, cudaMemcpyAsync(&w, c->d_raster + at, 8, cudaMemcpyDeviceToHost, c->stream));
+    const size_t at = (size_t)y * c->raster_w[view] + x;
+    SS_CUDA(c, cudaMemcpyAsync(&w, c->d_raster[view] + at, 8, cudaMemcpyDeviceToHost, c->stream));
     SS_CUDA(c, cudaStreamSynchronize(c->stream));
     if (instance_out) *instance_out = (uint32_t)(w & 0xFFFFFFFFull);
     if (depth_out) {

@@ -318,6 +318,8 @@ std::shared_ptr<MeshSource> MeshImporter::ImportAssimpMesh(const std::string& fi
                 struct Acc {
                     uint32_t corners = 0, indices = 0;
                     float lo[3] = {3.4e38f, 3.4e38f, 3.4e38f}, hi[3] = {-3.4e38f, -3.4e38f, -3.4e38f};
+                    std::vector<vec3> positions;    // one vertex per polygon corner, polygon by polygon
+                    std::vector<uint32_t> fan;      // triangle fans over them, relative to the submesh's first vertex
                 };
                 std::map<int64_t, Acc> by_slot;
                 size_t poly = 0, start = 0;
@@ -327,16 +329,24 @@ std::shared_ptr<MeshSource> MeshImporter::ImportAssimpMesh(const std::string& fi
                     const int64_t slot = per_poly.empty() ? all_same : (poly < per_poly.size() ? per_poly[poly] : 0);
                     if (corners >= 3) {
                         Acc& a = by_slot[slot];
+                        const uint32_t v0 = a.corners;
+                        for (uint32_t f = 1; f + 1 < corners; ++f) {  // aiProcess_Triangulate on a convex polygon: a fan
+                            a.fan.push_back(v0);
+                            a.fan.push_back(v0 + f);
+                            a.fan.push_back(v0 + f + 1);
+                        }
                         a.corners += (uint32_t)corners;
                         a.indices += (uint32_t)(corners - 2) * 3u;
                         for (size_t q = start; q <= k; ++q) {
                             const int64_t vi = pvi[q] < 0 ? ~pvi[q] : pvi[q];
                             if ((size_t)vi * 3 + 2 >= verts.size()) throw std::runtime_error("fbx: vertex index out of range");
+                            float p[3];
                             for (int ax = 0; ax < 3; ++ax) {
-                                const float p = (float)verts[(size_t)vi * 3 + ax] * (float)file_scale;  // aiVector3D is float
-                                a.lo[ax] = std::min(a.lo[ax], p);
-                                a.hi[ax] = std::max(a.hi[ax], p);
+                                p[ax] = (float)verts[(size_t)vi * 3 + ax] * (float)file_scale;  // aiVector3D is float
+                                a.lo[ax] = std::min(a.lo[ax], p[ax]);
+                                a.hi[ax] = std::max(a.hi[ax], p[ax]);
                             }
+                            a.positions.push_back({p[0], p[1], p[2]});
                         }
                     }
                     start = k + 1;
@@ -360,6 +370,8 @@ std::shared_ptr<MeshSource> MeshImporter::ImportAssimpMesh(const std::string& fi
                     sm.BoundsMin = {a.lo[0], a.lo[1], a.lo[2]};
                     sm.BoundsMax = {a.hi[0], a.hi[1], a.hi[2]};
                     source->GetSubmeshes().push_back(sm);
+                    source->GetPositions().insert(source->GetPositions().end(), a.positions.begin(), a.positions.end());
+                    source->GetIndices().insert(source->GetIndices().end(), a.fan.begin(), a.fan.end());
                     base_vertex += a.corners;
                     base_index += a.indices;
                 }

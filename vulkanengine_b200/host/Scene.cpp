@@ -160,9 +160,22 @@ FlatScene SceneRenderer::Flatten(Scene& scene, const std::vector<AdHocInstance>&
     // -- submesh table: meshes in handle order, their source submeshes in source order
     std::map<AssetHandle, uint32_t> slotBase;
     uint32_t maxSub = 1;
+    bool allGeometry = !meshes.empty();
+    std::map<const MeshSource*, std::pair<uint32_t, uint32_t>> arenaBase;  // source -> (first vertex, first index)
     for (auto& [handle, mesh] : meshes) {
         slotBase[handle] = (uint32_t)f.submeshTable.size();
-        const auto& subs = mesh->GetMeshSource()->GetSubmeshes();
+        const MeshSource& source = *mesh->GetMeshSource();
+        const auto& subs = source.GetSubmeshes();
+        if (source.GetIndices().empty()) allGeometry = false;
+        if (!arenaBase.count(&source)) {  // meshes naming one source share its vertices
+            arenaBase[&source] = {(uint32_t)(f.positions.size() / 3), (uint32_t)f.indices.size()};
+            for (const vec3& p : source.GetPositions()) {
+                f.positions.push_back(p.x);
+                f.positions.push_back(p.y);
+                f.positions.push_back(p.z);
+            }
+            f.indices.insert(f.indices.end(), source.GetIndices().begin(), source.GetIndices().end());
+        }
         maxSub = std::max<uint32_t>(maxSub, (uint32_t)subs.size());
         for (uint32_t s = 0; s < subs.size(); ++s) {
             ss_submesh row{};
@@ -175,8 +188,14 @@ FlatScene SceneRenderer::Flatten(Scene& scene, const std::vector<AdHocInstance>&
             row.mesh_rank = (uint32_t)f.meshHandles.size();
             row.submesh_index = s;
             f.submeshTable.push_back(row);
+            f.vertexBaseOfSlot.push_back(arenaBase[&source].first);
+            f.indexBaseOfSlot.push_back(arenaBase[&source].second);
         }
         f.meshHandles.push_back(handle);
+    }
+    if (!allGeometry) {
+        f.positions.clear();
+        f.indices.clear();
     }
     f.meshBits = bits_for(f.meshHandles.size());
     f.submeshBits = bits_for(maxSub);
@@ -253,10 +272,24 @@ void SceneRenderer::RebuildStaticStreams()
     m_Flat = Flatten(*m_Scene, m_AdHoc);
     m_AdHocBuilt = m_AdHoc;
     m_BuiltVersion = m_Scene->m_StructureVersion;
+    m_SlotOfMeshRank.assign(m_Flat.meshHandles.size(), 0);
+    for (size_t k = m_Flat.submeshTable.size(); k-- > 0;) m_SlotOfMeshRank[m_Flat.submeshTable[k].mesh_rank] = (uint32_t)k;  // first row of each mesh
     EnsureContext();
     if (m_Flat.submeshTable.empty() || m_Flat.nodeCount == 0) return;
     SS_TRY(ss_set_key_layout(m_Submit, m_Flat.meshBits, m_Flat.submeshBits, m_Flat.materialBits));
-    SS_TRY(ss_set_submesh_table(m_Submit, m_Flat.submeshTable.data(), (uint32_t)m_Flat.submeshTable.size()));
+    if (HasGeometry()) {
+        // one geometry arena for the consumer passes: the table the library sees addresses it
+        std::vector<ss_submesh> table = m_Flat.submeshTable;
+        for (size_t k = 0; k < table.size(); ++k) {
+            table[k].first_index += m_Flat.indexBaseOfSlot[k];
+            table[k].vertex_offset += (int32_t)m_Flat.vertexBaseOfSlot[k];
+        }
+        SS_TRY(ss_set_submesh_table(m_Submit, table.data(), (uint32_t)table.size()));
+        SS_TRY(ss_set_geometry(m_Submit, m_Flat.positions.data(), (uint32_t)(m_Flat.positions.size() / 3), m_Flat.indices.data(),
+                               (uint32_t)m_Flat.indices.size()));
+    } else {
+        SS_TRY(ss_set_submesh_table(m_Submit, m_Flat.submeshTable.data(), (uint32_t)m_Flat.submeshTable.size()));
+    }
     SS_TRY(ss_set_nodes(m_Submit, m_Flat.nodeCount, m_Flat.parent.empty() ? nullptr : m_Flat.parent.data(),
                         m_Flat.parent.empty() ? nullptr : m_Flat.levelOffsets.data(),
                         m_Flat.parent.empty() ? 0u : (uint32_t)m_Flat.levelOffsets.size() - 1));
@@ -367,10 +400,42 @@ void SceneRenderer::RenderScene()
             mk.SubmeshIndex = (uint32_t)((k >> mb) & ((1ull << sb) - 1));
             mk.MeshHandle = m_Flat.meshHandles[(k >> (mb + sb)) & ((1ull << hb) - 1)];
             mk.Tessellated = ((k >> (mb + sb + hb)) & 1) != 0;
+            if (HasGeometry()) {  // back to the per-source offsets the reference's draw would carry (VulkanRenderer.cpp:628)
+                const uint32_t row = m_SlotOfMeshRank[(k >> (mb + sb)) & ((1ull << hb) - 1)] + mk.SubmeshIndex;
+                cmds[d].first_index -= m_Flat.indexBaseOfSlot[row];
+                cmds[d].vertex_offset -= (int32_t)m_Flat.vertexBaseOfSlot[row];
+            }
             m_DrawLists[v][d] = {mk, cmds[d]};
         }
     }
     m_AdHoc.clear();  // ResetDrawCommands (SceneRenderer.cpp:1102, 1559-1591): per-frame submissions do not persist
+}
+
+// ---- consumers of the lists ------------------------------------------------------------------------
+// SceneRenderer.cpp:1421-1457: render the entity id of every selected-pass instance, read the pixel under the mouse.
+void SceneRenderer::SelectionPass()
+{
+    m_HoveredEntity = -1;
+    if (!m_Submit || !HasGeometry() || m_Flat.node.empty()) return;
+    SS_TRY(ss_raster_view(m_Submit, m_Slot, 0, m_ViewportWidth, m_ViewportHeight, SS_RASTER_DEFAULT));
+    if (m_MouseX >= m_ViewportWidth || m_MouseY >= m_ViewportHeight) return;
+    uint32_t instance = 0xFFFFFFFFu;
+    SS_TRY(ss_read_pixel(m_Submit, 0, m_MouseX, m_MouseY, &instance, nullptr));
+    if (instance != 0xFFFFFFFFu && instance < m_Flat.entityOfInstance.size()) m_HoveredEntity = (int)m_Flat.entityOfInstance[instance];
+}
+
+// SceneRenderer.cpp:1266-1310: depth of the four cascades, one layer each (the geometry shader's gl_Layer)
+void SceneRenderer::ShadowPass()
+{
+    if (!m_Submit || !HasGeometry() || m_Flat.node.empty()) return;
+    for (uint32_t c = 1; c <= 4; ++c) SS_TRY(ss_raster_view(m_Submit, m_Slot, c, m_ShadowMapSize, m_ShadowMapSize, SS_RASTER_DEPTH_CLAMP));
+}
+
+std::vector<uint64_t> SceneRenderer::DownloadRasterTarget(uint32_t view)
+{
+    std::vector<uint64_t> out((size_t)GetRasterWidth(view) * GetRasterHeight(view));
+    SS_TRY(ss_download_raster(m_Submit, view, out.data()));
+    return out;
 }
 
 ss_outputs SceneRenderer::GetDeviceOutputs(uint32_t view)

@@ -72,10 +72,18 @@ public:
     }
     std::shared_ptr<MaterialAsset> GetBaseMaterial() const { return m_BaseMaterial; }
     void SetBaseMaterial(std::shared_ptr<MaterialAsset> m) { m_BaseMaterial = std::move(m); }
+    // vertex positions and indices the submeshes' BaseVertex / BaseIndex refer to (Mesh.h: m_Vertices / m_Indices;
+    // only the position attribute is kept). Empty when the source carried no geometry (packs written by the tests).
+    std::vector<vec3>& GetPositions() { return m_Positions; }
+    const std::vector<vec3>& GetPositions() const { return m_Positions; }
+    std::vector<uint32_t>& GetIndices() { return m_Indices; }
+    const std::vector<uint32_t>& GetIndices() const { return m_Indices; }
 
 private:
     std::vector<Submesh> m_Submeshes;
     std::shared_ptr<MaterialAsset> m_BaseMaterial;
+    std::vector<vec3> m_Positions;
+    std::vector<uint32_t> m_Indices;
 };
 
 class Mesh {  // Mesh.h; GetSubmeshes() lists indices into the source's submesh array (Mesh.cpp:47-54)
@@ -233,6 +241,12 @@ struct FlatScene {
     std::vector<AssetHandle> meshHandles, materialHandles;  // rank -> handle
     uint32_t meshBits = 1, submeshBits = 1, materialBits = 1;
     uint32_t nodeCount = 0, externalNodes = 0;
+    // geometry arena of the consumer passes: every mesh source's positions / indices back to back, in submesh-table
+    // order; the reference binds each MeshSource's own buffers per draw, so its BaseVertex / BaseIndex are per source
+    // and these bases are what has to be added for one arena.  Empty when any mesh came without geometry.
+    std::vector<float> positions;          // xyz
+    std::vector<uint32_t> indices;
+    std::vector<uint32_t> vertexBaseOfSlot, indexBaseOfSlot;  // per submesh-table row
 };
 
 struct MeshKey {  // SceneRenderer.h:51-86, decoded from the 64-bit key
@@ -272,6 +286,20 @@ public:
     const ss_frame_stats& GetStats() const { return m_Stats; }       // RendererStats (PV/VulkanRenderer.h:13-17)
     const FlatScene& GetFlatScene() const { return m_Flat; }
     const float* GetCascadeSplits() const { return m_CascadeSplits; }
+
+    // The consumers of the lists (only with geometry: scenes read from files).  SelectionPass (SceneRenderer.cpp:
+    // 1421-1457): entity id per pixel of the camera view, then the read-back of the pixel under the mouse.
+    // ShadowPass (:1266-1310): depth of each cascade, MapSize x MapSize (CSMSettings, SceneRenderer.h:179), DepthClamp.
+    void SetViewportSize(uint32_t width, uint32_t height) { m_ViewportWidth = width; m_ViewportHeight = height; }
+    void SetViewportMousePos(uint32_t x, uint32_t y) { m_MouseX = x; m_MouseY = y; }
+    void SetShadowMapSize(uint32_t size) { m_ShadowMapSize = size; }
+    bool HasGeometry() const { return !m_Flat.indices.empty(); }
+    void SelectionPass();
+    void ShadowPass();
+    int GetHoveredEntity() const { return m_HoveredEntity; }             // -1 where nothing was drawn
+    std::vector<uint64_t> DownloadRasterTarget(uint32_t view);            // [depth bits : 32 | instance : 32] words
+    uint32_t GetRasterWidth(uint32_t view) const { return view == 0 ? m_ViewportWidth : m_ShadowMapSize; }
+    uint32_t GetRasterHeight(uint32_t view) const { return view == 0 ? m_ViewportHeight : m_ShadowMapSize; }
     const char* LastError() const;
 
     // called by Scene::OnUpdateGeometry / OnSelectGeometry
@@ -297,6 +325,9 @@ private:
     float m_CascadeSplits[4] = {0, 0, 0, 0};
     std::vector<DrawCommand> m_DrawLists[SS_MAX_VIEWS];
     std::vector<float> m_TrsStaging;
+    uint32_t m_ViewportWidth = 1280, m_ViewportHeight = 720, m_MouseX = 0, m_MouseY = 0, m_ShadowMapSize = 4096;
+    int m_HoveredEntity = -1;
+    std::vector<uint32_t> m_SlotOfMeshRank;  // first submesh-table row of each mesh
     std::string m_Error;
 };
 

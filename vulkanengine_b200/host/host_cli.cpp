@@ -5,6 +5,9 @@
 //   host_cli load-flatten <assets_dir> <scene.vkscene> <out>   the same two dumps for a scene read from the reference's
 //   host_cli load-render  <assets_dir> <scene.vkscene> <out>   own files (AssetRegistry.vkr, .vkscene, .vkmesh, .vkmat, FBX),
 //                                                               preceded by what the loader read (entities, submesh tables)
+//   host_cli load-pick    <assets_dir> <scene.vkscene> <out> <w> <h> <shadow> <mx> <my>
+//                                     load-render + SelectionPass (w x h, mouse at mx,my) + ShadowPass (shadow x shadow):
+//                                     appends the geometry arena, the five raster targets and the hovered entity
 //
 // Pack / dump format: a sequence of blocks, each  uint64 byte_count  followed by the raw bytes.
 #include <algorithm>
@@ -203,8 +206,9 @@ void dump_loaded(Writer& wr, Scene& scene)
 int main(int argc, char** argv)
 {
     const std::string mode = argc > 1 ? argv[1] : "";
-    const bool from_files = mode == "load-flatten" || mode == "load-render";
-    if (argc < (from_files ? 5 : 4) || !(from_files || mode == "flatten" || mode == "render")) {
+    const bool pick = mode == "load-pick";
+    const bool from_files = mode == "load-flatten" || mode == "load-render" || pick;
+    if (argc < (pick ? 10 : from_files ? 5 : 4) || !(from_files || mode == "flatten" || mode == "render")) {
         fprintf(stderr, "usage: host_cli flatten|render <pack> <out>\n       host_cli load-flatten|load-render <assets_dir> <scene.vkscene> <out>\n");
         return 2;
     }
@@ -221,7 +225,7 @@ int main(int argc, char** argv)
         } else {
             scene = scene_from_pack(argv[2], camera);
         }
-        const bool render = mode == "render" || mode == "load-render";
+        const bool render = mode == "render" || mode == "load-render" || pick;
 
         FILE* out = fopen(argv[from_files ? 4 : 3], "wb");
         if (!out) throw std::runtime_error("cannot open output");
@@ -240,6 +244,10 @@ int main(int argc, char** argv)
             wr.block(f.materialHandles);
             const uint32_t bits[3] = {f.meshBits, f.submeshBits, f.materialBits};
             wr.block(bits, 3);
+            wr.block(f.positions);  // geometry arena of the consumer passes (empty for packs)
+            wr.block(f.indices);
+            wr.block(f.vertexBaseOfSlot);
+            wr.block(f.indexBaseOfSlot);
         } else {
             SceneRenderer renderer(0);
             renderer.SetActiveScene(scene);
@@ -272,6 +280,24 @@ int main(int argc, char** argv)
                     flat.push_back(d.Indirect.first_instance);
                 }
                 wr.block(flat);
+            }
+            if (pick) {
+                const uint32_t w = (uint32_t)atoi(argv[5]), h = (uint32_t)atoi(argv[6]), sm = (uint32_t)atoi(argv[7]);
+                renderer.SetViewportSize(w, h);
+                renderer.SetShadowMapSize(sm);
+                renderer.SetViewportMousePos((uint32_t)atoi(argv[8]), (uint32_t)atoi(argv[9]));
+                renderer.SelectionPass();
+                renderer.ShadowPass();
+                const FlatScene& f = renderer.GetFlatScene();
+                wr.block(f.positions);
+                wr.block(f.indices);
+                wr.block(f.vertexBaseOfSlot);
+                wr.block(f.indexBaseOfSlot);
+                wr.block(f.slot);
+                wr.block(f.submeshTable);
+                for (uint32_t v = 0; v < 5; ++v) wr.block(renderer.DownloadRasterTarget(v));
+                const int32_t hovered = renderer.GetHoveredEntity();
+                wr.block(&hovered, 1);
             }
         }
         fclose(out);

@@ -267,10 +267,12 @@ class SceneSubmit:
     def raster_view(self, slot, view, width, height, flags=0):
         self._ck(self.lib.ss_raster_view(self.h, C.c_uint32(slot), C.c_uint32(view), C.c_uint32(width), C.c_uint32(height),
                                          C.c_uint32(flags)))
-        self._raster_shape = (height, width)
+        if not hasattr(self, "_raster_shape"):
+            self._raster_shape = {}
+        self._raster_shape[view] = (height, width)
 
     def download_raster(self, view):
-        out = np.empty(self._raster_shape, np.uint64)
+        out = np.empty(self._raster_shape[view], np.uint64)
         self._ck(self.lib.ss_download_raster(self.h, C.c_uint32(view), _p(out)))
         return out
 
