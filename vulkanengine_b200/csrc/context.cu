@@ -86,6 +86,7 @@ struct ss_ctx {
     uint32_t n_vertices = 0, n_indices = 0;
     unsigned long long* d_raster[SS_MAX_VIEWS] = {};  // one target per view: [raster_h[v]][raster_w[v]]
     unsigned long long* d_raster_pairs = nullptr;  // [max_draws + 1]
+    uint32_t* d_raster_queue = nullptr;            // works | tile entries | 2 counters (kRasterQueueWorks / kRasterQueueTiles)
     uint32_t raster_w[SS_MAX_VIEWS] = {}, raster_h[SS_MAX_VIEWS] = {};
     uint32_t seg_parity = 0;
     uint64_t* d_seg_key = nullptr;
@@ -223,6 +224,7 @@ SS_API void ss_destroy(ss_ctx* c)
     for (unsigned long long* p : c->d_raster)
         if (p) cudaFree(p);
     if (c->d_raster_pairs) cudaFree(c->d_raster_pairs);
+    if (c->d_raster_queue) cudaFree(c->d_raster_queue);
     if (c->stream) cudaStreamDestroy(c->stream);
     delete c;
 }
@@ -903,6 +905,14 @@ SS_API ss_status ss_raster_view(ss_ctx* c, uint32_t slot, uint32_t view, uint32_
     ra.max_draws = c->max_draws;
     if (!c->d_raster_pairs) SS_CUDA(c, cudaMalloc(&c->d_raster_pairs, ((size_t)c->max_draws + 1) * sizeof(unsigned long long)));
     ra.pairs = c->d_raster_pairs;
+    constexpr uint32_t kRasterQueueWorks = 1u << 19, kRasterQueueTiles = 1u << 23;  // 40 MB + 32 MB, on first use
+    if (!c->d_raster_queue)
+        SS_CUDA(c, cudaMalloc(&c->d_raster_queue, ((size_t)kRasterQueueWorks * 20 + kRasterQueueTiles + 2) * sizeof(uint32_t)));
+    ra.queue_works = c->d_raster_queue;
+    ra.queue_tiles = c->d_raster_queue + (size_t)kRasterQueueWorks * 20;
+    ra.queue_counts = ra.queue_tiles + kRasterQueueTiles;
+    ra.queue_work_cap = kRasterQueueWorks;
+    ra.queue_tile_cap = kRasterQueueTiles;
     ra.positions = c->d_positions;
     ra.indices = c->d_indices;
     ra.n_vertices = c->n_vertices;

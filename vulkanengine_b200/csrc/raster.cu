@@ -26,6 +26,8 @@ namespace {
 
 constexpr int kRasterThreads = 128;
 constexpr int kBigSamples = 48;               // bounds holding more samples than this are walked by the whole warp
+constexpr long long kHugeSamples = 16384;      // beyond this a triangle is queued and spread over the grid, tile by tile
+constexpr int kWorkWords = 20;                // queue record: Work::w[13], x0, x1, y0, y1, mode, instance, first tile entry
 constexpr float kSubpixel = 256.0f;
 constexpr float kSnapLimit = 268435456.0f;    // 2^28 sub-pixel units = 2^20 pixels
 
@@ -231,13 +233,84 @@ __global__ void __launch_bounds__(1024) k_raster_pairs(const ss_draw_cmd* draws,
     if (tid == 0) pairs[n_draws] = carry;
 }
 
+// A triangle its thread does not sample itself: queued for k_raster_tiles (one entry per 64 x 64-sample tile of its
+// bounds, spread over the whole grid), or, when the queue is full, walked here sample by sample.  Kept out of line:
+// it is the rare path and must not cost the common one its registers.
+__device__ __noinline__ void queue_or_walk(const Work& t, uint32_t inst, const RasterArgs& a)
+{
+    const bool clamp_depth = (a.flags & SS_RASTER_DEPTH_CLAMP) != 0;
+    if (a.queue_works) {
+        const int tx0 = t.x0 >> 6, ty0 = t.y0 >> 6;
+        const uint32_t n_tiles = (uint32_t)(((t.x1 >> 6) - tx0 + 1) * ((t.y1 >> 6) - ty0 + 1));
+        const uint32_t slot_w = atomicAdd(a.queue_counts + 0, 1u);
+        if (slot_w < a.queue_work_cap) {
+            const uint32_t base_t = atomicAdd(a.queue_counts + 1, n_tiles);
+            if ((unsigned long long)base_t + n_tiles <= a.queue_tile_cap) {
+                uint32_t* rec = a.queue_works + (size_t)slot_w * kWorkWords;
+#pragma unroll
+                for (int q = 0; q < 13; ++q) rec[q] = t.w[q];
+                rec[13] = (uint32_t)t.x0; rec[14] = (uint32_t)t.x1; rec[15] = (uint32_t)t.y0; rec[16] = (uint32_t)t.y1;
+                rec[17] = (uint32_t)t.mode; rec[18] = inst; rec[19] = base_t;
+                for (uint32_t k = 0; k < n_tiles; ++k) a.queue_tiles[base_t + k] = slot_w;
+                return;
+            }
+            // the tile list is full: the part of the range that exists is marked as nobody's
+            for (unsigned long long k = base_t; k < a.queue_tile_cap; ++k) a.queue_tiles[k] = 0xFFFFFFFFu;
+        }
+    }
+    const Prep p = prepare(t);
+    for (int j = t.y0; j <= t.y1; ++j)
+        for (int i = t.x0; i <= t.x1; ++i) shade(p, t.mode, i, j, clamp_depth, inst, a.target, a.width);
+}
+
+// Step 2 for a triangle the near plane cuts: 0, 1 or 2 triangles, each set up and handed on.  Out of line for the
+// same reason (the polygon lives in local memory).
+__device__ __noinline__ void cut_and_queue(const float c[3][4], const float dd[3], uint32_t inst, const RasterArgs& a)
+{
+    float poly[4][4];
+    int n_out = 0;
+#pragma unroll
+    for (int v = 0; v < 3; ++v) {
+        const int nx = (v + 1) % 3;
+        const bool in_v = dd[v] >= 0.f, in_n = dd[nx] >= 0.f;
+        if (in_v) {
+#pragma unroll
+            for (int q = 0; q < 4; ++q) poly[n_out][q] = c[v][q];
+            ++n_out;
+        }
+        if (in_v != in_n) {
+            // from the inside vertex towards the outside one
+            const float da = in_v ? dd[v] : dd[nx], db = in_v ? dd[nx] : dd[v];
+            const float tt = da / (da - db);
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                const float ca = in_v ? c[v][q] : c[nx][q], cb = in_v ? c[nx][q] : c[v][q];
+                poly[n_out][q] = ca + tt * (cb - ca);
+            }
+            ++n_out;
+        }
+    }
+    for (int u = 0; u + 2 < n_out; ++u) {
+        float c3[3][4];
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            c3[0][q] = poly[0][q];
+            c3[1][q] = poly[u + 1][q];
+            c3[2][q] = poly[u + 2][q];
+        }
+        const Work t = setup(c3, (int)a.width, (int)a.height);
+        if (t.mode >= 0) queue_or_walk(t, inst, a);
+    }
+}
+
 // One thread per (instance, triangle) pair of the view, pairs numbered draw by draw, instance by instance: a warp
 // holds 32 consecutive triangles (of one instance of a large mesh, or of a few instances of a small one), whatever the
 // mix of meshes.  A warp finds the draw of its first pair by bisection over the draws' prefix, its lanes walk on from
-// there.  Small triangles (the common case at scene scale: a few samples) are sampled by their thread; a large one is
-// handed to the warp, lanes striding over the samples of its bounds, so that a view whose instances cover thousands
-// of pixels each (the near shadow cascades) is not serialised.
-__global__ void __launch_bounds__(kRasterThreads) k_raster(const __grid_constant__ RasterArgs a)
+// there.  What a triangle costs decides who samples it: a few samples (the common case at scene scale) — its thread;
+// up to 16 K samples — its warp, lanes striding over the bounds; more, or anything cut by the near plane or not
+// snappable — the queue, so that a view whose instances cover thousands of pixels each (the near shadow cascades)
+// is spread over the whole grid.
+__global__ void __launch_bounds__(kRasterThreads, 4) k_raster(const __grid_constant__ RasterArgs a)
 {
     const int lane = threadIdx.x & 31;
     const uint32_t n_draws = min(a.counts[1], a.max_draws);
@@ -253,11 +326,12 @@ __global__ void __launch_bounds__(kRasterThreads) k_raster(const __grid_constant
             if (a.pairs[mid] <= g0) lo = mid; else hi = mid;
         }
         const unsigned long long g = g0 + (unsigned long long)lane;
-        const bool live = g < total;
-        float poly[4][4];
-        int n_out = 0;
+        Work t;
+        t.mode = -1;
+        t.x0 = t.y0 = 0;
+        t.x1 = t.y1 = -1;
         uint32_t inst = 0;
-        if (live) {
+        if (g < total) {
             uint32_t d = lo;
             while (a.pairs[d + 1] <= g) ++d;  // draws without pairs are stepped over
             const ss_draw_cmd dc = a.draws[d];
@@ -267,7 +341,7 @@ __global__ void __launch_bounds__(kRasterThreads) k_raster(const __grid_constant
             const uint32_t k = dc.first_instance + ki;
             const float4 r0 = a.rows[(size_t)k * 3 + 0], r1 = a.rows[(size_t)k * 3 + 1], r2 = a.rows[(size_t)k * 3 + 2];
             inst = a.idx[k];
-            // 1 + 2: the triangle in clip space, cut by the near plane into 0, 1 or 2 triangles
+            // 1: the triangle in clip space
             float c[3][4], dd[3];
             bool in_range = true;
 #pragma unroll
@@ -282,79 +356,100 @@ __global__ void __launch_bounds__(kRasterThreads) k_raster(const __grid_constant
 #pragma unroll
                 for (int v = 0; v < 3; ++v) dd[v] = clamp_depth ? c[v][3] - 1e-5f : c[v][2];
                 if (dd[0] >= 0.f && dd[1] >= 0.f && dd[2] >= 0.f) {
-#pragma unroll
-                    for (int v = 0; v < 3; ++v)
-#pragma unroll
-                        for (int q = 0; q < 4; ++q) poly[v][q] = c[v][q];
-                    n_out = 3;
-                } else {
-#pragma unroll
-                    for (int v = 0; v < 3; ++v) {
-                        const int nx = (v + 1) % 3;
-                        const bool in_v = dd[v] >= 0.f, in_n = dd[nx] >= 0.f;
-                        if (in_v) {
-#pragma unroll
-                            for (int q = 0; q < 4; ++q) poly[n_out][q] = c[v][q];
-                            ++n_out;
-                        }
-                        if (in_v != in_n) {
-                            const int ia = in_v ? v : nx, ib = in_v ? nx : v;  // inside vertex, outside vertex
-                            const float tt = dd[ia] / (dd[ia] - dd[ib]);
-#pragma unroll
-                            for (int q = 0; q < 4; ++q) poly[n_out][q] = c[ia][q] + tt * (c[ib][q] - c[ia][q]);
-                            ++n_out;
-                        }
+                    t = setup(c, (int)a.width, (int)a.height);
+                    if (t.mode == 1) {  // not snappable: never sampled here
+                        queue_or_walk(t, inst, a);
+                        t.mode = -1;
                     }
+                } else {
+                    cut_and_queue(c, dd, inst, a);
                 }
             }
         }
-        const int n_sub = n_out < 3 ? 0 : n_out - 2;
-        const int sub_iter = __reduce_max_sync(0xffffffffu, n_sub);
-        for (int u = 0; u < sub_iter; ++u) {
-            Work t;
+        // from here on: uncut, snapped triangles only
+        const long long samples = t.mode == 0 ? (long long)(t.x1 - t.x0 + 1) * (t.y1 - t.y0 + 1) : 0;
+        if (samples > kHugeSamples) {
+            queue_or_walk(t, inst, a);
             t.mode = -1;
-            t.x0 = t.y0 = 0;
-            t.x1 = t.y1 = -1;
-            if (u < n_sub) {
-                float c3[3][4];
+        }
+        const bool big = t.mode == 0 && samples > kBigSamples;
+        if (t.mode == 0 && !big) {
+            const Prep p = prepare(t);
+            for (int j = t.y0; j <= t.y1; ++j)
+                for (int i = t.x0; i <= t.x1; ++i) shade(p, 0, i, j, clamp_depth, inst, a.target, a.width);
+        }
+        uint32_t todo = __ballot_sync(0xffffffffu, big);
+        while (todo) {
+            const int src = __ffs(todo) - 1;
+            todo &= todo - 1;
+            Work w;
 #pragma unroll
-                for (int q = 0; q < 4; ++q) {
-                    c3[0][q] = poly[0][q];
-                    c3[1][q] = poly[u + 1][q];
-                    c3[2][q] = poly[u + 2][q];
-                }
-                t = setup(c3, (int)a.width, (int)a.height);
-            }
-            const bool big = t.mode >= 0 && (long long)(t.x1 - t.x0 + 1) * (t.y1 - t.y0 + 1) > kBigSamples;
-            if (t.mode >= 0 && !big) {
-                const Prep p = prepare(t);
-                for (int j = t.y0; j <= t.y1; ++j)
-                    for (int i = t.x0; i <= t.x1; ++i) shade(p, t.mode, i, j, clamp_depth, inst, a.target, a.width);
-            }
-            uint32_t todo = __ballot_sync(0xffffffffu, big);
-            while (todo) {
-                const int src = __ffs(todo) - 1;
-                todo &= todo - 1;
-                Work w;
-#pragma unroll
-                for (int q = 0; q < 13; ++q) w.w[q] = __shfl_sync(0xffffffffu, t.w[q], src);
-                w.x0 = __shfl_sync(0xffffffffu, t.x0, src);
-                w.x1 = __shfl_sync(0xffffffffu, t.x1, src);
-                w.y0 = __shfl_sync(0xffffffffu, t.y0, src);
-                w.y1 = __shfl_sync(0xffffffffu, t.y1, src);
-                w.mode = __shfl_sync(0xffffffffu, t.mode, src);
-                const uint32_t w_inst = __shfl_sync(0xffffffffu, inst, src);
-                const Prep p = prepare(w);
-                const int bw = w.x1 - w.x0 + 1;
-                // lanes take consecutive samples of the bounds in row-major order, 32 at a time
-                int i = w.x0 + lane, j = w.y0;
+            for (int q = 0; q < 9; ++q) w.w[q] = __shfl_sync(0xffffffffu, t.w[q], src);
+            w.x0 = __shfl_sync(0xffffffffu, t.x0, src);
+            w.x1 = __shfl_sync(0xffffffffu, t.x1, src);
+            w.y0 = __shfl_sync(0xffffffffu, t.y0, src);
+            w.y1 = __shfl_sync(0xffffffffu, t.y1, src);
+            w.mode = 0;
+            const uint32_t w_inst = __shfl_sync(0xffffffffu, inst, src);
+            const Prep p = prepare(w);
+            const int bw = w.x1 - w.x0 + 1;
+            // lanes take consecutive samples of the bounds in row-major order, 32 at a time
+            int i = w.x0 + lane, j = w.y0;
+            while (i > w.x1) { i -= bw; ++j; }
+            while (j <= w.y1) {
+                shade(p, 0, i, j, clamp_depth, w_inst, a.target, a.width);
+                i += 32;
                 while (i > w.x1) { i -= bw; ++j; }
-                while (j <= w.y1) {
-                    shade(p, w.mode, i, j, clamp_depth, w_inst, a.target, a.width);
-                    i += 32;
-                    while (i > w.x1) { i -= bw; ++j; }
-                }
             }
+        }
+    }
+}
+
+// The queued huge triangles: one warp per (triangle, 64 x 64-sample tile) entry.  A tile that lies wholly outside one
+// edge is dropped after three corner evaluations (exact for the snapped mode: an edge function is linear, so it is
+// negative over the tile iff it is negative at the tile corner it favours).
+__global__ void __launch_bounds__(kRasterThreads) k_raster_tiles(const __grid_constant__ RasterArgs a)
+{
+    const int lane = threadIdx.x & 31;
+    const bool clamp_depth = (a.flags & SS_RASTER_DEPTH_CLAMP) != 0;
+    const uint32_t n_entries = min(a.queue_counts[1], a.queue_tile_cap);
+    const uint32_t warps = (gridDim.x * kRasterThreads) >> 5;
+    const uint32_t warp_id = (blockIdx.x * kRasterThreads + threadIdx.x) >> 5;
+    for (uint32_t e = warp_id; e < n_entries; e += warps) {
+        const uint32_t owner = a.queue_tiles[e];
+        if (owner == 0xFFFFFFFFu) continue;
+        const uint32_t* rec = a.queue_works + (size_t)owner * kWorkWords;
+        Work w;
+#pragma unroll
+        for (int q = 0; q < 13; ++q) w.w[q] = rec[q];
+        w.x0 = (int)rec[13]; w.x1 = (int)rec[14]; w.y0 = (int)rec[15]; w.y1 = (int)rec[16];
+        w.mode = (int)rec[17];
+        const uint32_t inst = rec[18];
+        const int tx0 = w.x0 >> 6, ty0 = w.y0 >> 6, tnx = (w.x1 >> 6) - tx0 + 1;
+        const int local = (int)(e - rec[19]);
+        const int tx = tx0 + local % tnx, ty = ty0 + local / tnx;
+        // the tile's samples that lie inside the triangle's bounds
+        const int x0 = max(w.x0, tx << 6), x1 = min(w.x1, (tx << 6) + 63), y0 = max(w.y0, ty << 6), y1 = min(w.y1, (ty << 6) + 63);
+        const Prep p = prepare(w);
+        if (w.mode == 0) {
+            bool out = false;
+#pragma unroll
+            for (int q = 0; q < 3; ++q) {
+                const int p0 = (q + 1) % 3;
+                // E = dx (py - y0) - dy (px - x0) is largest where dx favours py and -dy favours px
+                const int py = 256 * (p.dx[q] >= 0 ? y1 : y0) + 128, px = 256 * (p.dy[q] <= 0 ? x1 : x0) + 128;
+                const long long best = (long long)p.dx[q] * (py - p.y[p0]) - (long long)p.dy[q] * (px - p.x[p0]);
+                out = out || best < 0;
+            }
+            if (out) continue;
+        }
+        const int bw = x1 - x0 + 1;
+        int i = x0 + lane, j = y0;
+        while (i > x1) { i -= bw; ++j; }
+        while (j <= y1) {
+            shade(p, w.mode, i, j, clamp_depth, inst, a.target, a.width);
+            i += 32;
+            while (i > x1) { i -= bw; ++j; }
         }
     }
 }
@@ -375,7 +470,9 @@ void launch_raster(const RasterArgs& a, cudaStream_t st)
 {
     if (!a.visible) return;
     k_raster_pairs<<<1, 1024, 0, st>>>(a.draws, a.counts, a.max_draws, a.pairs);
+    if (a.queue_works) cudaMemsetAsync(a.queue_counts, 0, 2 * sizeof(uint32_t), st);
     k_raster<<<148 * 12, kRasterThreads, 0, st>>>(a);  // persistent warps striding over the pairs
+    if (a.queue_works) k_raster_tiles<<<148 * 12, kRasterThreads, 0, st>>>(a);  // ... and over the queued tiles
 }
 
 }  // namespace ss

@@ -175,6 +175,11 @@ struct RasterArgs {
     uint32_t width, height;
     uint32_t flags;            // SS_RASTER_*
     unsigned long long* target;  // [height][width] words [depth bits | instance], SS_RASTER_EMPTY where untouched
+    // queue of huge triangles (nullptr: none, they are walked where they are found)
+    uint32_t* queue_works;     // [queue_work_cap][20]
+    uint32_t* queue_tiles;     // [queue_tile_cap] owner work of each 64 x 64 tile entry
+    uint32_t* queue_counts;    // {works, tile entries}
+    uint32_t queue_work_cap, queue_tile_cap;
 };
 void launch_raster_clear(unsigned long long* target, size_t n, cudaStream_t st);
 void launch_raster(const RasterArgs& a, cudaStream_t st);
