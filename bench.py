@@ -343,7 +343,7 @@ def main():
                 ctx.download_draws(s_, v, st_)
         barrier()
         t0 = time.perf_counter()
-        e_steps = max(3, min(a.steps, 10))
+        e_steps = max(3, min(a.steps, 30))
         # Pipelined the way a host with frames in flight runs it: step k's upload and ss_frame are issued, then step
         # k-1's result is fenced and read.  A whole-stream TRS upload goes to the library's second TRS buffer on its own
         # stream, so the copy for step k+1 overlaps step k's kernels; every step still moves all of its inputs.
