@@ -303,16 +303,16 @@ def main():
             return torch.as_tensor(_Dev(ptr, n, typestr), device="cuda")
 
         def merge_all_views(slot_, st_):
-            total_bytes = 0
+            lists = []
             for v in range(a.views):
                 o = ctx.map_outputs(slot_, v)
-                keys = dev_tensor(o.keys, o.visible, "<i8")
-                idx = dev_tensor(o.instance_idx, o.visible, "<i4")
+                # the whole device buffer (capacity n): ranks gather equal-length slices, nothing is copied to pad
+                idx = dev_tensor(o.instance_idx, n, "<i4")
                 dk = dev_tensor(o.draw_keys, o.n_draws, "<i8")
                 draws = dev_tensor(o.draws, o.n_draws * 5, "<i4").view(-1, 5)
-                mk, mi, mdk, mdc, mfirst = sharding.merge_view_list(keys, idx, dk, draws[:, 1].contiguous(), rank * n)
-                total_bytes += mi.numel() * 4  # instance indices all-gathered over NVLink (keys are rebuilt from the runs)
-            return total_bytes
+                lists.append((idx, dk, draws[:, 1].contiguous()))
+            merged = sharding.merge_view_lists(lists, rank * n)
+            return sum(m[1].numel() * 4 for m in merged)  # instance indices all-gathered over NVLink (keys are rebuilt from the runs)
 
         s_ = ctx.frame(views)
         st_ = ctx.frame_sync(s_)

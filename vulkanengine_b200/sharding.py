@@ -23,75 +23,97 @@ def shard_range(n_total: int, rank: int, world: int) -> Tuple[int, int]:
     return lo, hi
 
 
-def _all_gather_padded(t: torch.Tensor, counts: List[int]) -> List[torch.Tensor]:
-    """all_gather of variable-length 1-D tensors: pad to the max, gather once, trim."""
+def _gather_rows(t: torch.Tensor) -> torch.Tensor:
+    """all_gather of equally sized 1-D tensors into one [world, n] tensor (one collective, no list of copies)."""
     world = dist.get_world_size()
-    cap = max(max(counts), 1)
-    buf = torch.zeros(cap, dtype=t.dtype, device=t.device)
-    buf[: t.numel()] = t
-    out = [torch.empty_like(buf) for _ in range(world)]
-    dist.all_gather(out, buf)
-    return [o[:c] for o, c in zip(out, counts)]
+    out = torch.empty((world, t.numel()), dtype=t.dtype, device=t.device)
+    dist.all_gather_into_tensor(out.view(-1), t.contiguous())
+    return out
 
 
-def _gather_scalar(value: int, dev) -> torch.Tensor:
+def merge_view_lists(views, idx_offset: int):
+    """Merges this rank's compacted lists of SEVERAL views with every other rank's.
+
+    views        list of (idx, draw_keys, draw_counts) per view: this rank's visible instance list (sorted by key,
+                 stable), and its draws: key and instance_count per run.  `idx` may be longer than the list (a
+                 device buffer of the library's capacity): only its first sum(draw_counts) elements are read.
+    idx_offset   first global instance number of this rank's shard
+
+    Returns, per view, (merged_keys, merged_global_idx, merged_draw_keys, merged_draw_counts, merged_first_instance);
+    identical on every rank and identical to what one GPU holding all shards would emit.  Keys are int64 tensors
+    (the uint64 bit pattern; keys use at most 62 bits so order is preserved).
+
+    Collectives: one for all the sizes and shard offsets, one for all the draws, one per view for the instance lists
+    (4 B per element; the keys are NOT sent, an element's key is the key of the run it lies in).  One host
+    synchronisation (the sizes).  The merged list is written in output order: for merged run k, rank 0's elements,
+    then rank 1's, ... - a segmented gather, not a sort.
+    """
     world = dist.get_world_size()
-    mine = torch.tensor([value], dtype=torch.int64, device=dev)
-    out = [torch.empty_like(mine) for _ in range(world)]
-    dist.all_gather(out, mine)
-    return torch.cat(out)
+    V = len(views)
+    dev = views[0][0].device
+    i64 = dict(dtype=torch.int64, device=dev)
+    # 1) sizes of every view on every rank + shard offsets (tiny): the only host sync
+    mine = torch.empty(2 * V + 1, **i64)
+    for v, (idx, dk, dc) in enumerate(views):
+        mine[2 * v] = dc.sum() if dc.numel() else 0
+        mine[2 * v + 1] = dk.numel()
+    mine[2 * V] = idx_offset
+    sizes = _gather_rows(mine).cpu()
+    n_list = sizes[:, 0:2 * V:2]          # [world, V]
+    n_draw = sizes[:, 1:2 * V:2]
+    shard = sizes[:, 2 * V].to(dev)
+    cap_draw = int(n_draw.max().clamp(min=1))
+    # 2) the draws of all views (KBs): keys and counts side by side, padded to the widest
+    packed = torch.zeros((V, 2, cap_draw), **i64)
+    for v, (idx, dk, dc) in enumerate(views):
+        packed[v, 0, : dk.numel()] = dk
+        packed[v, 1, : dc.numel()] = dc.to(torch.int64)
+    all_draws = _gather_rows(packed.view(-1)).view(world, V, 2, cap_draw)
+
+    out = []
+    for v, (idx, dk, dc) in enumerate(views):
+        nd = [int(x) for x in n_draw[:, v]]
+        nl = [int(x) for x in n_list[:, v]]
+        cap = max(max(nl), 1)
+        # 3) the instance lists: equal-length slices (the tail past a rank's own count is never read)
+        src = idx.to(torch.int32) if idx.dtype != torch.int32 else idx
+        if src.numel() < cap:
+            src = torch.cat([src, torch.zeros(cap - src.numel(), dtype=torch.int32, device=dev)])
+        lists = _gather_rows(src[:cap])                                     # [world, cap] int32
+
+        # merged draws: union of the ranks' keys in key order, counts summed
+        keys_r = [all_draws[r, v, 0, : nd[r]] for r in range(world)]
+        cnts_r = [all_draws[r, v, 1, : nd[r]] for r in range(world)]
+        merged_dk, inverse = torch.unique(torch.cat(keys_r), sorted=True, return_inverse=True)
+        K = merged_dk.numel()
+        # per (merged run, rank): how many elements and where they start in that rank's list
+        seg_len = torch.zeros((K, world), **i64)
+        seg_src = torch.zeros((K, world), **i64)
+        off = 0
+        for r in range(world):
+            if nd[r]:
+                slot = inverse[off: off + nd[r]]
+                seg_len[slot, r] = cnts_r[r]
+                seg_src[slot, r] = (torch.cumsum(cnts_r[r], 0) - cnts_r[r]) + r * cap
+            off += nd[r]
+        merged_dc = seg_len.sum(1)
+        first = torch.cumsum(merged_dc, 0) - merged_dc
+        total = int(sum(nl))
+        # segments in output order (run-major, rank-minor): element e of the output comes from
+        # lists.flat[seg_src + (e - seg_out_start)], shifted by its rank's shard offset
+        flat_len = seg_len.view(-1)
+        seg_out = torch.cumsum(flat_len, 0) - flat_len
+        gather_from = torch.repeat_interleave(seg_src.view(-1) - seg_out, flat_len, output_size=total)
+        gather_from += torch.arange(total, **i64)
+        add = torch.repeat_interleave(shard.repeat(K), flat_len, output_size=total)
+        out_i = lists.view(-1)[gather_from].to(torch.int64) + add
+        out_k = torch.repeat_interleave(merged_dk, merged_dc, output_size=total)
+        out.append((out_k, out_i, merged_dk, merged_dc, first))
+    return out
 
 
 def merge_view_list(keys: torch.Tensor, idx: torch.Tensor, draw_keys: torch.Tensor, draw_counts: torch.Tensor,
                     idx_offset: int):
-    """Merges this rank's compacted list of ONE view with every other rank's.
-
-    keys, idx            this rank's visible (key, local instance) list, sorted by key (stable)
-    draw_keys, draw_counts  this rank's draws: key and instance_count per run
-    idx_offset           first global instance number of this rank's shard
-
-    Returns (merged_keys, merged_global_idx, merged_draw_keys, merged_draw_counts, merged_first_instance);
-    identical on every rank and identical to what one GPU holding all shards would emit.
-    Keys are int64 tensors (the uint64 bit pattern; keys use at most 62 bits so order is preserved).
-    """
-    world = dist.get_world_size()
-    dev = keys.device
-    # 1) counts first (tiny): how many list entries / draws every rank holds
-    mine = torch.tensor([keys.numel(), draw_keys.numel()], dtype=torch.int64, device=dev)
-    sizes = [torch.empty_like(mine) for _ in range(world)]
-    dist.all_gather(sizes, mine)
-    n_list = [int(s[0]) for s in sizes]
-    n_draw = [int(s[1]) for s in sizes]
-    # 2) draws of every rank (KBs), then 3) the instance lists (the only large transfer: 4 B per element;
-    #    the keys are NOT sent, an element's key is the key of the run it lies in)
-    all_dk = _all_gather_padded(draw_keys, n_draw)
-    all_dc = _all_gather_padded(draw_counts.to(torch.int64), n_draw)
-    all_i = _all_gather_padded(idx.to(torch.int32), n_list)
-
-    # merged draws: union of keys, counts summed over ranks, in key order
-    cat_dk = torch.cat(all_dk)
-    merged_dk, inverse = torch.unique(cat_dk, sorted=True, return_inverse=True)
-    cat_dc = torch.cat(all_dc)
-    merged_dc = torch.zeros(merged_dk.numel(), dtype=torch.int64, device=dev).index_add_(0, inverse, cat_dc)
-    first = torch.cumsum(merged_dc, 0) - merged_dc
-
-    # run placement: rank r's run of key k starts at first[k] + sum of the counts of ranks < r for k
-    total = int(merged_dc.sum())
-    out_i = torch.empty(total, dtype=torch.int64, device=dev)
-    before = torch.zeros(merged_dk.numel(), dtype=torch.int64, device=dev)
-    shard = [int(x) for x in _gather_scalar(idx_offset, dev)]
-    off = 0
-    for r in range(world):
-        nd = n_draw[r]
-        if nd:
-            slot = inverse[off: off + nd]              # merged draw index of each of rank r's runs
-            run_len = all_dc[r]
-            run_src = torch.cumsum(run_len, 0) - run_len
-            # destination of every element = where its run starts in the merged list + its position in the run
-            shift = first[slot] + before[slot] - run_src
-            dst = torch.repeat_interleave(shift, run_len) + torch.arange(n_list[r], device=dev)
-            out_i[dst] = all_i[r].to(torch.int64) + shard[r]
-            before.index_add_(0, slot, run_len)
-        off += nd
-    out_k = torch.repeat_interleave(merged_dk, merged_dc)
-    return out_k, out_i, merged_dk, merged_dc, first
+    """One view (see merge_view_lists). `keys` is accepted for symmetry with the library's outputs and not used:
+    an element's key is the key of its run."""
+    return merge_view_lists([(idx, draw_keys, draw_counts)], idx_offset)[0]
