@@ -460,6 +460,48 @@ def test_whole_stream_trs_uploads_overlap_frames_and_stay_ordered():
     ctx.close()
 
 
+@pytest.mark.parametrize("case", range(24))
+def test_randomised_configurations(case):
+    """Seeded sweep over what a host can combine: scene shape (flat / 3-level / explicit node map), size, number of
+    views and where they look from, per-instance boxes or the submesh table's, key layout, frames queued back to back,
+    reuse flags on an unchanged scene.  Everything must equal the oracle, every time."""
+    rng = np.random.default_rng(1000 + case)
+    shape = case % 3
+    n_keys = int(rng.integers(1, 400))
+    if shape == 0:
+        sc = synth.flat_scene(int(rng.integers(1, 9000)), n_keys=n_keys, seed=synth.SEED_BASE + 100 + case)
+    else:
+        sc = synth.hierarchy_scene(n_roots=int(rng.integers(1, 9)), fan1=int(rng.integers(1, 9)), fan2=int(rng.integers(1, 70)),
+                                   n_keys=n_keys, seed=synth.SEED_BASE + 100 + case)
+        if shape == 2:
+            sc = synth.with_explicit_nodes(sc, seed=case)
+    if rng.random() < 0.4:
+        sc = synth.SceneArrays(**{**sc.__dict__, "inst_aabb": None})       # cull with the submesh table's boxes
+    n_views = int(rng.integers(1, 9))
+    if n_views == 5 and rng.random() < 0.5:
+        views = oracle_views(5, position=tuple(float(x) for x in rng.uniform(-300, 300, 3)), yaw=float(rng.uniform(-3, 3)),
+                             pitch=float(rng.uniform(-1, 1)))
+    else:
+        views = synth.fibonacci_cameras(lambda *a: O.camera_view_proj(*a), max(n_views, 1), radius=float(rng.uniform(100, 1500)),
+                                        seed=synth.SEED_BASE + case)[:n_views]
+        if rng.random() < 0.5:
+            views = views.copy()
+            views["flags"][::2] = synth.VIEW_SKIP_NEAR
+    osc = O.OracleScene(sc, 0)
+    ref = osc.frame(views)
+    ctx = S.SceneSubmit(sc.n_nodes, sc.n_instances, len(sc.slots), max_views=n_views, frames_in_flight=int(rng.integers(1, 4)))
+    ctx.load_scene(sc)
+    slots = [ctx.frame(views) for _ in range(int(rng.integers(1, 4)))]
+    if rng.random() < 0.5:
+        slots.append(ctx.frame(views, S.FRAME_REUSE_WORLD | S.FRAME_REUSE_SORT))
+    for slot in slots[-min(len(slots), 1):]:
+        st = ctx.frame_sync(slot)
+        got = {"stats": st, "world": ctx.download_world(), "masks": ctx.download_masks(),
+               "views": [ctx.download_view(slot, v, st) for v in range(n_views)]}
+        check_against_oracle(sc, views, got, ref)
+    ctx.close()
+
+
 def test_zero_instances():
     sc = synth.flat_scene(64, n_keys=8)
     empty = synth.SceneArrays(**{**sc.__dict__, "slot": sc.slot[:0], "matword": sc.matword[:0], "inst_aabb": sc.inst_aabb[:0]})
