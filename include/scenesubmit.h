@@ -345,6 +345,15 @@ SS_API ss_status ss_cascade_matrices(const float view_proj[16], float z_near, fl
                                      const float light_dir[3], float splits_out[4],
                                      float light_matrices_out[4][16]);
 
+/* The same for many cameras at once, on the GPU (batched multi-camera work needs a cascade set per
+   camera).  view_proj: [n_cameras][16], light_matrices_out: [n_cameras][4][16], host pointers; the split distances
+   depend on the clip range only and come back once.  The per-camera arithmetic is the text ss_cascade_matrices
+   compiles for the host, so the matrices are the same bits. */
+SS_API ss_status ss_cascade_matrices_batch(int device, const float* view_proj, uint32_t n_cameras, float z_near,
+                                           float z_far, float split_lambda, float near_offset, float far_offset,
+                                           const float light_dir[3], float splits_out[4],
+                                           float* light_matrices_out);
+
 #ifdef __cplusplus
 }
 #endif

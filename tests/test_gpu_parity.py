@@ -502,6 +502,23 @@ def test_randomised_configurations(case):
     ctx.close()
 
 
+def test_cascade_matrices_batch_equals_host_per_camera():
+    """4096 cameras' cascade sets fitted on the GPU == ss_cascade_matrices on the host, bit for bit
+    (and == the oracle, which is pinned against the reference's UpdateCascadeMap built with its own GLM)."""
+    cams = synth.fibonacci_cameras(S.camera_view_proj, 4096)
+    light = np.array(synth.LIGHT_DIR, np.float32)
+    splits, mats = S.cascade_matrices_batch(cams["view_proj"], synth.CAMERA_NEAR, 2000.0, synth.CSM_LAMBDA, synth.CSM_NEAR_OFFSET,
+                                            synth.CSM_FAR_OFFSET, light)
+    for i in list(range(0, 4096, 97)) + [4095]:
+        hs, hm = S.cascade_matrices(cams["view_proj"][i], synth.CAMERA_NEAR, 2000.0, synth.CSM_LAMBDA, synth.CSM_NEAR_OFFSET,
+                                    synth.CSM_FAR_OFFSET, light)
+        assert np.array_equal(np.asarray(hs, np.float32), splits)
+        assert np.array_equal(np.asarray(hm, np.float32).reshape(4, 16), mats[i]), i
+        om = O.cascade_matrices(cams["view_proj"][i], synth.CAMERA_NEAR, 2000.0, synth.CSM_LAMBDA, synth.CSM_NEAR_OFFSET,
+                                synth.CSM_FAR_OFFSET, light)
+        assert np.array_equal(np.asarray(om[1], np.float32).reshape(4, 16), mats[i])
+
+
 def test_zero_instances():
     sc = synth.flat_scene(64, n_keys=8)
     empty = synth.SceneArrays(**{**sc.__dict__, "slot": sc.slot[:0], "matword": sc.matword[:0], "inst_aabb": sc.inst_aabb[:0]})

@@ -7,6 +7,13 @@
 
 #include "../../include/scenesubmit.h"
 
+#ifdef __CUDACC__
+#include <cuda_runtime.h>
+#define SS_HD __host__ __device__
+#else
+#define SS_HD
+#endif
+
 namespace {
 
 struct V3 {
@@ -16,18 +23,18 @@ struct M4 {
     float c[4][4];  // c[col][row], glm::mat4 memory
 };
 
-inline V3 sub(V3 a, V3 b) { return {a.x - b.x, a.y - b.y, a.z - b.z}; }
-inline V3 add(V3 a, V3 b) { return {a.x + b.x, a.y + b.y, a.z + b.z}; }
-inline V3 mul(V3 a, float s) { return {a.x * s, a.y * s, a.z * s}; }
-inline float dot(V3 a, V3 b)
+SS_HD inline V3 sub(V3 a, V3 b) { return {a.x - b.x, a.y - b.y, a.z - b.z}; }
+SS_HD inline V3 add(V3 a, V3 b) { return {a.x + b.x, a.y + b.y, a.z + b.z}; }
+SS_HD inline V3 mul(V3 a, float s) { return {a.x * s, a.y * s, a.z * s}; }
+SS_HD inline float dot(V3 a, V3 b)
 {
     const float px = a.x * b.x, py = a.y * b.y, pz = a.z * b.z;
     return px + py + pz;
 }
-inline V3 cross(V3 a, V3 b) { return {a.y * b.z - b.y * a.z, a.z * b.x - b.z * a.x, a.x * b.y - b.x * a.y}; }
-inline V3 normalize(V3 v) { return mul(v, 1.0f / std::sqrt(dot(v, v))); }
+SS_HD inline V3 cross(V3 a, V3 b) { return {a.y * b.z - b.y * a.z, a.z * b.x - b.z * a.x, a.x * b.y - b.x * a.y}; }
+SS_HD inline V3 normalize(V3 v) { return mul(v, 1.0f / sqrtf(dot(v, v))); }
 
-M4 identity()
+SS_HD M4 identity()
 {
     M4 m;
     std::memset(&m, 0, sizeof m);
@@ -36,7 +43,7 @@ M4 identity()
 }
 
 // column j of a*b = ((a0*b[j][0] + a1*b[j][1]) + a2*b[j][2]) + a3*b[j][3]
-M4 matmul(const M4& a, const M4& b)
+SS_HD M4 matmul(const M4& a, const M4& b)
 {
     M4 r;
     for (int j = 0; j < 4; ++j)
@@ -49,7 +56,7 @@ M4 matmul(const M4& a, const M4& b)
     return r;
 }
 
-void mulvec(const M4& m, const float v[4], float out[4])
+SS_HD void mulvec(const M4& m, const float v[4], float out[4])
 {
     for (int i = 0; i < 4; ++i) {
         const float lo = m.c[0][i] * v[0] + m.c[1][i] * v[1];
@@ -59,7 +66,7 @@ void mulvec(const M4& m, const float v[4], float out[4])
 }
 
 // cofactor expansion in glm's arrangement (six 2x2 sub-determinant triples, alternating signs)
-M4 inverse(const M4& m)
+SS_HD M4 inverse(const M4& m)
 {
     const float (*a)[4] = m.c;
     float sub2[6][3];
@@ -141,6 +148,73 @@ M4 translation(V3 t)
     return r;
 }
 
+// The part of UpdateCascadeMap that depends on the camera (SceneRenderer.cpp:605-687), given the split fractions:
+// slice the frustum, bound it with a sphere snapped to 1/16, look along the light, orthographic projection.
+// Host and device compile this same text (-fmad=false / -ffp-contract=off, IEEE division and square root on both),
+// so the batched device version gives the host version's bits.
+SS_HD void cascades_from_splits(const M4& vp, const float split[4], float z_near, float clip_range, float near_offset,
+                                float far_offset, V3 light_in, float splits_out[4], float* light_matrices_out /* [4][16] */)
+{
+    const float ndc[8][3] = {{-1, 1, 0}, {1, 1, 0}, {1, -1, 0}, {-1, -1, 0}, {-1, 1, 1}, {1, 1, 1}, {1, -1, 1}, {-1, -1, 1}};
+    const V3 light = normalize(light_in);
+    float prev = 0.0f;
+    for (unsigned i = 0; i < 4; ++i) {
+        const M4 unproject = inverse(vp);
+        V3 corner[8];
+        for (int j = 0; j < 8; ++j) {
+            const float h[4] = {ndc[j][0], ndc[j][1], ndc[j][2], 1.0f};
+            float w[4];
+            mulvec(unproject, h, w);
+            corner[j] = {w[0] / w[3], w[1] / w[3], w[2] / w[3]};
+        }
+        for (int j = 0; j < 4; ++j) {  // cut the slice [prev, split[i]] out of each frustum edge
+            const V3 edge = sub(corner[j + 4], corner[j]);
+            corner[j + 4] = add(corner[j], mul(edge, split[i]));
+            corner[j] = add(corner[j], mul(edge, prev));
+        }
+        V3 centre = {0.f, 0.f, 0.f};
+        for (int j = 0; j < 8; ++j) centre = add(centre, corner[j]);
+        centre = {centre.x / 8.0f, centre.y / 8.0f, centre.z / 8.0f};
+
+        float radius = 0.0f;
+        for (int j = 0; j < 8; ++j) {
+            const V3 d = sub(corner[j], centre);
+            const float len = sqrtf(dot(d, d));
+            radius = radius < len ? len : radius;
+        }
+        radius = ceilf(radius * 16.0f) / 16.0f;
+        const float lo = -radius, hi = radius;
+
+        // lookAtRH(centre - light * radius, centre, +Y)
+        const V3 eye = sub(centre, mul(light, -lo));
+        const V3 f = normalize(sub(centre, eye));
+        const V3 s = normalize(cross(f, {0.f, 1.f, 0.f}));
+        const V3 u = cross(s, f);
+        M4 lv = identity();
+        lv.c[0][0] = s.x; lv.c[1][0] = s.y; lv.c[2][0] = s.z;
+        lv.c[0][1] = u.x; lv.c[1][1] = u.y; lv.c[2][1] = u.z;
+        lv.c[0][2] = -f.x; lv.c[1][2] = -f.y; lv.c[2][2] = -f.z;
+        lv.c[3][0] = -dot(s, eye);
+        lv.c[3][1] = -dot(u, eye);
+        lv.c[3][2] = dot(f, eye);
+
+        // orthoRH_ZO(lo, hi, lo, hi, near_offset, (hi - lo) + far_offset)
+        const float zn = near_offset, zf = hi - lo + far_offset;
+        M4 lo_m = identity();
+        lo_m.c[0][0] = 2.0f / (hi - lo);
+        lo_m.c[1][1] = 2.0f / (hi - lo);
+        lo_m.c[2][2] = -1.0f / (zf - zn);
+        lo_m.c[3][0] = -(hi + lo) / (hi - lo);
+        lo_m.c[3][1] = -(hi + lo) / (hi - lo);
+        lo_m.c[3][2] = -zn / (zf - zn);
+
+        splits_out[i] = (z_near + split[i] * clip_range) * -1.0f;
+        const M4 lm = matmul(lo_m, lv);
+        for (int q = 0; q < 16; ++q) light_matrices_out[i * 16 + q] = (&lm.c[0][0])[q];
+        prev = split[i];
+    }
+}
+
 }  // namespace
 
 extern "C" {
@@ -188,65 +262,69 @@ SS_API ss_status ss_cascade_matrices(const float view_proj[16], float z_near, fl
         split[i] = (d - z_near) / clip_range;
     }
 
-    static const float ndc[8][3] = {{-1, 1, 0}, {1, 1, 0}, {1, -1, 0}, {-1, -1, 0}, {-1, 1, 1}, {1, 1, 1}, {1, -1, 1}, {-1, -1, 1}};
-    const V3 light = normalize({light_dir[0], light_dir[1], light_dir[2]});
-    float prev = 0.0f;
-    for (unsigned i = 0; i < 4; ++i) {
-        const M4 unproject = inverse(vp);
-        V3 corner[8];
-        for (int j = 0; j < 8; ++j) {
-            const float h[4] = {ndc[j][0], ndc[j][1], ndc[j][2], 1.0f};
-            float w[4];
-            mulvec(unproject, h, w);
-            corner[j] = {w[0] / w[3], w[1] / w[3], w[2] / w[3]};
-        }
-        for (int j = 0; j < 4; ++j) {  // cut the slice [prev, split[i]] out of each frustum edge
-            const V3 edge = sub(corner[j + 4], corner[j]);
-            corner[j + 4] = add(corner[j], mul(edge, split[i]));
-            corner[j] = add(corner[j], mul(edge, prev));
-        }
-        V3 centre = {0.f, 0.f, 0.f};
-        for (int j = 0; j < 8; ++j) centre = add(centre, corner[j]);
-        centre = {centre.x / 8.0f, centre.y / 8.0f, centre.z / 8.0f};
-
-        float radius = 0.0f;
-        for (int j = 0; j < 8; ++j) {
-            const V3 d = sub(corner[j], centre);
-            const float len = std::sqrt(dot(d, d));
-            radius = radius < len ? len : radius;
-        }
-        radius = std::ceil(radius * 16.0f) / 16.0f;
-        const float lo = -radius, hi = radius;
-
-        // lookAtRH(centre - light * radius, centre, +Y)
-        const V3 eye = sub(centre, mul(light, -lo));
-        const V3 f = normalize(sub(centre, eye));
-        const V3 s = normalize(cross(f, {0.f, 1.f, 0.f}));
-        const V3 u = cross(s, f);
-        M4 lv = identity();
-        lv.c[0][0] = s.x; lv.c[1][0] = s.y; lv.c[2][0] = s.z;
-        lv.c[0][1] = u.x; lv.c[1][1] = u.y; lv.c[2][1] = u.z;
-        lv.c[0][2] = -f.x; lv.c[1][2] = -f.y; lv.c[2][2] = -f.z;
-        lv.c[3][0] = -dot(s, eye);
-        lv.c[3][1] = -dot(u, eye);
-        lv.c[3][2] = dot(f, eye);
-
-        // orthoRH_ZO(lo, hi, lo, hi, near_offset, (hi - lo) + far_offset)
-        const float zn = near_offset, zf = hi - lo + far_offset;
-        M4 lo_m = identity();
-        lo_m.c[0][0] = 2.0f / (hi - lo);
-        lo_m.c[1][1] = 2.0f / (hi - lo);
-        lo_m.c[2][2] = -1.0f / (zf - zn);
-        lo_m.c[3][0] = -(hi + lo) / (hi - lo);
-        lo_m.c[3][1] = -(hi + lo) / (hi - lo);
-        lo_m.c[3][2] = -zn / (zf - zn);
-
-        splits_out[i] = (z_near + split[i] * clip_range) * -1.0f;
-        const M4 lm = matmul(lo_m, lv);
-        std::memcpy(light_matrices_out[i], &lm, 64);
-        prev = split[i];
-    }
+    cascades_from_splits(vp, split, z_near, clip_range, near_offset, far_offset, {light_dir[0], light_dir[1], light_dir[2]}, splits_out,
+                         &light_matrices_out[0][0]);
     return SS_OK;
 }
 
 }  // extern "C"
+
+#ifdef __CUDACC__
+namespace {
+struct CascadeBatchArgs {
+    const float* view_proj;  // [n][16] device
+    float* out;              // [n][4][16] device
+    uint32_t n;
+    float split[4], z_near, clip_range, near_offset, far_offset;
+    V3 light;
+};
+__global__ void k_cascades(const __grid_constant__ CascadeBatchArgs a)
+{
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= a.n) return;
+    M4 vp;
+    for (int q = 0; q < 16; ++q) (&vp.c[0][0])[q] = a.view_proj[(size_t)i * 16 + q];
+    float splits[4];
+    cascades_from_splits(vp, a.split, a.z_near, a.clip_range, a.near_offset, a.far_offset, a.light, splits, a.out + (size_t)i * 64);
+}
+}  // namespace
+
+extern "C" SS_API ss_status ss_cascade_matrices_batch(int device, const float* view_proj, uint32_t n_cameras, float z_near, float z_far,
+                                                      float split_lambda, float near_offset, float far_offset,
+                                                      const float light_dir[3], float splits_out[4], float* light_matrices_out)
+{
+    if (!view_proj || !light_dir || !splits_out || !light_matrices_out) return SS_ERR_INVALID;
+    if (n_cameras == 0) return SS_OK;
+    CascadeBatchArgs a;
+    const float clip_range = z_far - z_near, z_min = z_near, z_max = z_near + clip_range;
+    const float range = z_max - z_min, ratio = z_max / z_min;
+    for (unsigned i = 0; i < 4; ++i) {  // the camera-independent part stays on the host (libm pow, like the reference)
+        const float p = (float)(i + 1) / 4.0f;
+        const float logarithmic = z_min * std::pow(ratio, p);
+        const float uniform = z_min + range * p;
+        const float d = split_lambda * (logarithmic - uniform) + uniform;
+        a.split[i] = (d - z_near) / clip_range;
+        splits_out[i] = (z_near + a.split[i] * clip_range) * -1.0f;
+    }
+    a.n = n_cameras;
+    a.z_near = z_near;
+    a.clip_range = clip_range;
+    a.near_offset = near_offset;
+    a.far_offset = far_offset;
+    a.light = {light_dir[0], light_dir[1], light_dir[2]};
+    if (cudaSetDevice(device) != cudaSuccess) return SS_ERR_CUDA;
+    float *d_in = nullptr, *d_out = nullptr;
+    ss_status st = SS_OK;
+    if (cudaMalloc(&d_in, (size_t)n_cameras * 64) != cudaSuccess || cudaMalloc(&d_out, (size_t)n_cameras * 256) != cudaSuccess) st = SS_ERR_CUDA;
+    if (st == SS_OK && cudaMemcpy(d_in, view_proj, (size_t)n_cameras * 64, cudaMemcpyHostToDevice) != cudaSuccess) st = SS_ERR_CUDA;
+    if (st == SS_OK) {
+        a.view_proj = d_in;
+        a.out = d_out;
+        k_cascades<<<(n_cameras + 127) / 128, 128>>>(a);
+        if (cudaMemcpy(light_matrices_out, d_out, (size_t)n_cameras * 256, cudaMemcpyDeviceToHost) != cudaSuccess) st = SS_ERR_CUDA;
+    }
+    if (d_in) cudaFree(d_in);
+    if (d_out) cudaFree(d_out);
+    return st;
+}
+#endif

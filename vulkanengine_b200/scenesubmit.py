@@ -26,7 +26,8 @@ EXPORTS = ["ss_create", "ss_destroy", "ss_last_error", "ss_version", "ss_set_key
            "ss_upload_world_rows", "ss_frame", "ss_frame_sync", "ss_frame_stage_ms", "ss_map_outputs", "ss_download_view",
            "ss_download_world", "ss_download_masks", "ss_stream", "ss_sort_scratch_bytes", "ss_sort_pairs",
            "ss_sort_pairs_host", "ss_sort_pairs_static", "ss_camera_view_proj", "ss_cascade_matrices",
-           "ss_set_geometry", "ss_raster_view", "ss_map_raster", "ss_download_raster", "ss_read_pixel"]
+           "ss_set_geometry", "ss_raster_view", "ss_map_raster", "ss_download_raster", "ss_read_pixel",
+           "ss_cascade_matrices_batch"]
 RASTER_DEPTH_CLAMP = 1
 RASTER_EMPTY = 0xFFFFFFFFFFFFFFFF
 
@@ -105,6 +106,20 @@ def cascade_matrices(vp, zn, zf, lam, near_off, far_off, light_dir):
     if st != SS_OK:
         raise SceneSubmitError(st, "ss_cascade_matrices")
     return splits, mats
+
+
+def cascade_matrices_batch(view_projs, zn, zf, lam, near_off, far_off, light_dir, device=0):
+    """[n][16] camera view-projections -> ([4] split distances, [n][4][16] light matrices), computed on the GPU."""
+    lib = load_library()
+    vps = np.ascontiguousarray(view_projs, np.float32).reshape(-1, 16)
+    out = np.empty((len(vps), 4, 16), np.float32)
+    splits = np.empty(4, np.float32)
+    ld = np.ascontiguousarray(light_dir, np.float32)
+    st = lib.ss_cascade_matrices_batch(C.c_int(device), _p(vps), C.c_uint32(len(vps)), C.c_float(zn), C.c_float(zf), C.c_float(lam),
+                                       C.c_float(near_off), C.c_float(far_off), _p(ld), _p(splits), _p(out))
+    if st != SS_OK:
+        raise SceneSubmitError(st, "ss_cascade_matrices_batch")
+    return splits, out
 
 
 def sort_pairs_host(keys, vals, begin_bit=0, end_bit=64, device=0):
