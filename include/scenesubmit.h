@@ -212,6 +212,13 @@ SS_API ss_status ss_set_instance_aabbs(ss_ctx* ctx, uint32_t first, uint32_t cou
    ss_frame_sync of the next frame. */
 SS_API ss_status ss_upload_trs(ss_ctx* ctx, uint32_t first, uint32_t count, const float* trs9);
 
+/* The same for a scattered set of nodes: what a transform producer that touches few entities
+   leaves behind — the physics write-back loop (Platform/JoltPhysics/JoltPhysicsWorld.cpp:112-127, translation and
+   rotation of every rigid body) or a gizmo edit (VulkanEditor/src/EditorLayer.cpp:593-603).  node_index[k] names the
+   node trs9[k] belongs to; a node named twice keeps the later record.  The records cross the bus packed
+   (40 B per node) and a kernel scatters them into the TRS stream. */
+SS_API ss_status ss_upload_trs_sparse(ss_ctx* ctx, uint32_t count, const uint32_t* node_index, const float* trs9);
+
 /* World rows (TransformData, 48 B each) of EXTERNAL nodes: nodes numbered past the last level given to
    ss_set_nodes are never composed from TRS.  This is how the ad-hoc submitters that hand the renderer
    a finished glm::mat4 keep working: SceneRenderer::SubmitMesh / SubmitSelectedMesh

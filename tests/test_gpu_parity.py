@@ -519,6 +519,38 @@ def test_cascade_matrices_batch_equals_host_per_camera():
         assert np.array_equal(np.asarray(om[1], np.float32).reshape(4, 16), mats[i])
 
 
+def test_sparse_trs_upload_scatter():
+    """a producer that moves few entities (the physics write-back loop) uploads (node, TRS) records; a
+    node named twice keeps the later record; records land on top of earlier whole-stream and range uploads."""
+    n = 70_000                                   # above the threshold of the double-buffered whole-stream path
+    sc = synth.flat_scene(n, n_keys=50)
+    views = oracle_views(5)
+    ctx = S.SceneSubmit(sc.n_nodes, n, len(sc.slots), max_views=5)
+    ctx.load_scene(sc)
+    rng = np.random.default_rng(11)
+    trs = sc.trs.copy()
+    for round_ in range(3):
+        k = [5000, 17, 30_000][round_]
+        nodes = rng.integers(0, n, k).astype(np.uint32)
+        nodes[-1] = nodes[0]                     # a duplicate: the later record must win
+        rec = trs[nodes].copy()
+        rec[:, :3] += rng.uniform(-50, 50, (k, 3)).astype(np.float32)
+        rec[:, 3:6] += rng.uniform(-1, 1, (k, 3)).astype(np.float32)
+        if round_ == 1:
+            trs[:, 1] += np.float32(2.0)
+            ctx.upload_trs(trs)                  # a whole-stream upload first, the sparse records on top of it
+        ctx.upload_trs_sparse(nodes, rec)
+        for j in range(k):
+            trs[nodes[j]] = rec[j]
+        st = ctx.frame_sync(ctx.frame(views))
+        ref = O.OracleScene(synth.SceneArrays(**{**sc.__dict__, "trs": trs}), 0).frame(views)
+        assert np.array_equal(ctx.download_world(), ref["rows"]) and np.array_equal(ctx.download_masks(), ref["masks"])
+        assert [int(st.visible[v]) for v in range(5)] == [len(ref["views"][v]["idx"]) for v in range(5)]
+    with pytest.raises(S.SceneSubmitError):
+        ctx.upload_trs_sparse(np.array([n], np.uint32), trs[:1])
+    ctx.close()
+
+
 def test_zero_instances():
     sc = synth.flat_scene(64, n_keys=8)
     empty = synth.SceneArrays(**{**sc.__dict__, "slot": sc.slot[:0], "matword": sc.matword[:0], "inst_aabb": sc.inst_aabb[:0]})

@@ -9,6 +9,7 @@
 #include <cstring>
 #include <new>
 #include <string>
+#include <unordered_map>
 #include <vector>
 
 #include "ss_kernels.h"
@@ -80,6 +81,11 @@ struct ss_ctx {
     uint32_t* d_overflow = nullptr;
     uint32_t* d_seg_count = nullptr;   // [2][max_views][max_draws]: per-view run counters, double-buffered by frame
     uint32_t* d_seg_runs = nullptr;    // [2] runs left in each buffer
+    // staging of ss_upload_trs_sparse: pinned host + device, [count] indices then [count][9] records; grows on demand
+    unsigned char* h_sparse = nullptr;
+    unsigned char* d_sparse = nullptr;
+    size_t sparse_cap = 0;
+    cudaEvent_t ev_sparse = nullptr;   // the staging buffer's last copy has left the host
     // geometry + raster target of the consumer pass (ss_set_geometry / ss_raster_view); allocated on first use
     float* d_positions = nullptr;
     uint32_t* d_indices = nullptr;
@@ -219,6 +225,9 @@ SS_API void ss_destroy(ss_ctx* c)
         if (s.h_counts) cudaFreeHost(s.h_counts);
     }
     for (void* p : c->allocs) cudaFree(p);
+    if (c->h_sparse) cudaFreeHost(c->h_sparse);
+    if (c->d_sparse) cudaFree(c->d_sparse);
+    if (c->ev_sparse) cudaEventDestroy(c->ev_sparse);
     if (c->d_positions) cudaFree(c->d_positions);
     if (c->d_indices) cudaFree(c->d_indices);
     for (unsigned long long* p : c->d_raster)
@@ -509,6 +518,54 @@ SS_API ss_status ss_upload_trs(ss_ctx* c, uint32_t first, uint32_t count, const 
     }
     SS_CUDA(c, adopt_pending_upload(c));  // a range lands on top of whatever whole-stream upload came before it
     SS_CUDA(c, cudaMemcpyAsync(c->d_trs + (size_t)first * 9, trs9, (size_t)count * 36, cudaMemcpyHostToDevice, c->stream));
+    return SS_OK;
+}
+
+SS_API ss_status ss_upload_trs_sparse(ss_ctx* c, uint32_t count, const uint32_t* node_index, const float* trs9)
+{
+    if (!c) return SS_ERR_INVALID;
+    if (count && (!node_index || !trs9)) return c->fail(SS_ERR_INVALID, "ss_upload_trs_sparse: null array");
+    if (!count) return SS_OK;
+    for (uint32_t k = 0; k < count; ++k)
+        if (node_index[k] >= c->n_nodes)
+            return c->fail(SS_ERR_INVALID, "ss_upload_trs_sparse: record %u names node %u of %u", k, node_index[k], c->n_nodes);
+    SS_CUDA(c, cudaSetDevice(c->device));
+    const size_t bytes = (size_t)count * 40;
+    if (!c->ev_sparse) SS_CUDA(c, cudaEventCreateWithFlags(&c->ev_sparse, cudaEventDisableTiming));
+    if (bytes > c->sparse_cap) {
+        SS_CUDA(c, cudaStreamSynchronize(c->stream));
+        if (c->h_sparse) cudaFreeHost(c->h_sparse);
+        if (c->d_sparse) cudaFree(c->d_sparse);
+        c->h_sparse = c->d_sparse = nullptr;
+        c->sparse_cap = 0;
+        const size_t cap = std::max<size_t>(bytes * 2, 1 << 16);
+        SS_CUDA(c, cudaHostAlloc(reinterpret_cast<void**>(&c->h_sparse), cap, cudaHostAllocDefault));
+        SS_CUDA(c, cudaMalloc(reinterpret_cast<void**>(&c->d_sparse), cap));
+        c->sparse_cap = cap;
+    } else {
+        SS_CUDA(c, cudaEventSynchronize(c->ev_sparse));  // the previous call's copy must have left the staging buffer
+    }
+    // pack: indices, then records, keeping only the LAST record of a node named more than once
+    uint32_t* hi = reinterpret_cast<uint32_t*>(c->h_sparse);
+    std::unordered_map<uint32_t, uint32_t> last;
+    last.reserve(count * 2);
+    for (uint32_t k = 0; k < count; ++k) last[node_index[k]] = k;
+    uint32_t kept = 0;
+    for (uint32_t k = 0; k < count; ++k)
+        if (last[node_index[k]] == k) hi[kept++] = k;          // source positions for now
+    float* hr = reinterpret_cast<float*>(c->h_sparse + (size_t)kept * 4);
+    for (uint32_t j = 0; j < kept; ++j) {
+        const uint32_t k = hi[j];
+        memcpy(hr + (size_t)j * 9, trs9 + (size_t)k * 9, 36);
+        hi[j] = node_index[k];
+    }
+    c->world_valid = false;  // transforms changed
+    SS_CUDA(c, adopt_pending_upload(c));  // lands on top of whatever whole-stream upload came before it
+    SS_CUDA(c, cudaMemcpyAsync(c->d_sparse, c->h_sparse, (size_t)kept * 40, cudaMemcpyHostToDevice, c->stream));
+    SS_CUDA(c, cudaEventRecord(c->ev_sparse, c->stream));
+    launch_trs_scatter(c->d_trs, reinterpret_cast<const uint32_t*>(c->d_sparse),
+                       reinterpret_cast<const float*>(c->d_sparse + (size_t)kept * 4), kept, c->stream);
+    SS_CUDA(c, cudaGetLastError());
     return SS_OK;
 }
 

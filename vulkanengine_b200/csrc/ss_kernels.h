@@ -21,6 +21,8 @@ struct NodeLevelArgs {
     int trig_mode;
 };
 void launch_node_level(const NodeLevelArgs& a, cudaStream_t st);
+// TRS records of scattered nodes: trs[node_index[k]] = records[k] for k in order (a later record wins)
+void launch_trs_scatter(float* trs, const uint32_t* node_index, const float* records, uint32_t count, cudaStream_t st);
 
 struct InstanceArgs {
     const float* trs;

@@ -226,6 +226,21 @@ __global__ void __launch_bounds__(kTile) k_instances(InstanceArgs a, const __gri
 
 }  // namespace
 
+namespace {
+// one thread per float of a record; the host has already dropped all but the last record of a node named twice
+__global__ void k_trs_scatter(float* trs, const uint32_t* node_index, const float* records, uint32_t count)
+{
+    const uint32_t g = blockIdx.x * blockDim.x + threadIdx.x;
+    const uint32_t k = g / 9u, f = g - k * 9u;
+    if (k < count) trs[(size_t)node_index[k] * 9 + f] = records[(size_t)k * 9 + f];
+}
+}  // namespace
+
+void launch_trs_scatter(float* trs, const uint32_t* node_index, const float* records, uint32_t count, cudaStream_t st)
+{
+    if (count) k_trs_scatter<<<(count * 9u + 255u) / 256u, 256, 0, st>>>(trs, node_index, records, count);
+}
+
 void launch_node_level(const NodeLevelArgs& a, cudaStream_t st)
 {
     if (a.hi <= a.lo) return;

@@ -27,7 +27,7 @@ EXPORTS = ["ss_create", "ss_destroy", "ss_last_error", "ss_version", "ss_set_key
            "ss_download_world", "ss_download_masks", "ss_stream", "ss_sort_scratch_bytes", "ss_sort_pairs",
            "ss_sort_pairs_host", "ss_sort_pairs_static", "ss_camera_view_proj", "ss_cascade_matrices",
            "ss_set_geometry", "ss_raster_view", "ss_map_raster", "ss_download_raster", "ss_read_pixel",
-           "ss_cascade_matrices_batch"]
+           "ss_cascade_matrices_batch", "ss_upload_trs_sparse"]
 RASTER_DEPTH_CLAMP = 1
 RASTER_EMPTY = 0xFFFFFFFFFFFFFFFF
 
@@ -203,6 +203,12 @@ class SceneSubmit:
     def upload_trs(self, trs, first=0):
         trs = np.ascontiguousarray(trs, np.float32)
         self._ck(self.lib.ss_upload_trs(self.h, C.c_uint32(first), C.c_uint32(trs.shape[0]), _p(trs)))
+
+    def upload_trs_sparse(self, node_index, trs):
+        node_index = np.ascontiguousarray(node_index, np.uint32)
+        trs = np.ascontiguousarray(trs, np.float32).reshape(-1, 9)
+        assert len(node_index) == len(trs)
+        self._ck(self.lib.ss_upload_trs_sparse(self.h, C.c_uint32(len(trs)), _p(node_index), _p(trs)))
 
     def upload_trs_ptr(self, host_ptr, count, first=0):
         """Raw host pointer (e.g. a pinned torch tensor's data_ptr())."""
