@@ -140,6 +140,24 @@ def ncu_traffic(n, n_views):
     return out
 
 
+def bind_near_gpu(torch, device):
+    """Run this rank on the CPUs next to its GPU (NVML's affinity for the device), so that the pinned upload buffer it
+    allocates afterwards lies in that socket's memory: on a two-socket box eight ranks uploading at once otherwise pull
+    half their bytes across the socket link.  Returns a short description for the bench line; a no-op where NVML or
+    the affinity call is not available."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        props = torch.cuda.get_device_properties(device)
+        bus = "%08x:%02x:%02x.0" % (getattr(props, "pci_domain_id", 0), props.pci_bus_id, props.pci_device_id)
+        h = pynvml.nvmlDeviceGetHandleByPciBusId(bus.encode())
+        pynvml.nvmlDeviceSetCpuAffinity(h)
+        cpus = sorted(os.sched_getaffinity(0))
+        return {"cpus": f"{cpus[0]}-{cpus[-1]}", "n": len(cpus)}
+    except Exception as e:  # noqa: BLE001
+        return {"unbound": type(e).__name__}
+
+
 def cpu_reference(sc, views, sample, threads, min_seconds=10.0):
     """Times oracle/_ref (kind 'reference') or the plain-C oracle (kind 'port') on the first `sample`
     instances of the same scene with `threads` host threads. Returns (instances/s, kind, seconds, n)."""
@@ -235,6 +253,8 @@ def main():
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device; libscenesubmit has no CPU path")
     torch.cuda.set_device(local_rank)
+    all_cpus = os.sched_getaffinity(0)
+    numa = bind_near_gpu(torch, local_rank)  # before any pinned allocation: first touch places the pages
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
 
@@ -367,7 +387,7 @@ def main():
         if world > 1:
             dist.all_reduce(dt, op=dist.ReduceOp.MAX)
         e2e = {"value": world * n * e_steps / float(dt.item()), "unit": "instances/s", "h2d_bytes_per_step": int(h2d),
-               "d2h_bytes_per_step": int(d2h), "ms_per_step": float(dt.item()) / e_steps * 1e3,
+               "d2h_bytes_per_step": int(d2h), "ms_per_step": float(dt.item()) / e_steps * 1e3, "host_binding": numa,
                "note": "pinned TRS (36 B/instance) + views in; counts, indirect draws and draw keys of every view out; "
                        "compacted instance rows stay in HBM for the GPU consumer; two frames in flight (step k's result "
                        "is read after step k+1 is issued)"}
@@ -405,6 +425,7 @@ def main():
         if merge:
             line["merge"] = merge
         if not a.no_cpu_baseline and world == 1:
+            os.sched_setaffinity(0, all_cpus)  # the CPU baseline gets every core again
             cores = os.cpu_count() or 1
             ips, kind, secs, ns = cpu_reference(sc, views, a.cpu_sample, cores)
             ips1, _, secs1, _ = cpu_reference(sc, views, min(a.cpu_sample, 1 << 18), 1)

@@ -303,6 +303,19 @@ SS_API ss_status ss_download_raster(ss_ctx* ctx, uint32_t view, uint64_t* words_
 SS_API ss_status ss_read_pixel(ss_ctx* ctx, uint32_t view, uint32_t x, uint32_t y, uint32_t* instance_out,
                                float* depth_out);
 
+/* ---- merged draw list of several shards (multi-GPU) ------------------------------------ */
+
+/* Placement step of the merge: after the ranks' compacted instance lists have been all-gathered, the merged list
+   is "run k: rank 0's elements, rank 1's, ..." (rank order = input order, so this IS the single-GPU stable order).
+   The caller describes that as segments in output order; this writes, for every output position e in segment s,
+       out_idx[e]  = lists[seg_src[s] + (e - seg_out[s])] + seg_add[s]      (global instance number)
+       out_keys[e] = seg_key[s]
+   All pointers are device pointers; seg_out has n_segs + 1 entries (exclusive prefix of the segment lengths, last =
+   total).  Asynchronous on `cuda_stream`.  No counterpart in the reference (it has one list on one CPU). */
+SS_API ss_status ss_merge_place(void* cuda_stream, const int32_t* lists, const int64_t* seg_out, const int64_t* seg_src,
+                                const int64_t* seg_add, const int64_t* seg_key, uint32_t n_segs, int32_t* out_idx,
+                                int64_t* out_keys);
+
 /* ---- the sort on its own ---------------------------------------------------------------------- */
 
 /* Stable LSD radix sort (onesweep) of (uint64 key, uint32 value) pairs on bits [begin_bit, end_bit).

@@ -76,3 +76,30 @@ def test_two_rank_merge_equals_single_process(tmp_path):
             assert np.array_equal(g["dk"].view(np.uint64), ref["draw_keys"])
             assert np.array_equal(g["dc"], ref["draws"]["instance_count"].astype(np.int64))
             assert np.array_equal(g["first"], ref["draws"]["first_instance"].astype(np.int64))
+
+
+@pytest.mark.gpu
+def test_merge_place_kernel_against_numpy():
+    """ss_merge_place (the GPU placement step of the merge): random segments, empty ones among them, against the
+    definition out[e] = lists[seg_src[s] + (e - seg_out[s])] + seg_add[s], keys[e] = seg_key[s]."""
+    rng = np.random.default_rng(4)
+    n_segs = 5000
+    lens = rng.integers(0, 400, n_segs)
+    lens[rng.random(n_segs) < 0.3] = 0
+    lens[17] = 100_000
+    seg_out = np.concatenate([[0], np.cumsum(lens)]).astype(np.int64)
+    total = int(seg_out[-1])
+    lists = rng.integers(0, 1 << 20, total + 1000).astype(np.int32)
+    seg_src = np.array([rng.integers(0, len(lists) - l + 1) for l in lens], np.int64)
+    seg_add = rng.integers(0, 1 << 24, n_segs).astype(np.int64)
+    seg_key = rng.integers(0, 1 << 60, n_segs).astype(np.int64)
+    want_i = np.concatenate([lists[s:s + l].astype(np.int64) + a for s, l, a in zip(seg_src, lens, seg_add)])
+    want_k = np.repeat(seg_key, lens)
+    dev = torch.device("cuda", 0)
+    t = lambda x: torch.from_numpy(x).to(dev)
+    out_i = torch.empty(total, dtype=torch.int32, device=dev)
+    out_k = torch.empty(total, dtype=torch.int64, device=dev)
+    sharding._merge_place(t(lists), t(seg_out), t(seg_src), t(seg_add), t(seg_key), n_segs, out_i, out_k)
+    torch.cuda.synchronize()
+    assert np.array_equal(out_i.cpu().numpy().astype(np.int64), want_i)
+    assert np.array_equal(out_k.cpu().numpy(), want_k)

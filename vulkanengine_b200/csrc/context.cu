@@ -1025,6 +1025,16 @@ SS_API ss_status ss_read_pixel(ss_ctx* c, uint32_t view, uint32_t x, uint32_t y,
     return SS_OK;
 }
 
+SS_API ss_status ss_merge_place(void* cuda_stream, const int32_t* lists, const int64_t* seg_out, const int64_t* seg_src,
+                                const int64_t* seg_add, const int64_t* seg_key, uint32_t n_segs, int32_t* out_idx,
+                                int64_t* out_keys)
+{
+    if (n_segs == 0) return SS_OK;
+    if (!lists || !seg_out || !seg_src || !seg_add || !seg_key || !out_idx || !out_keys) return SS_ERR_INVALID;
+    launch_merge_place(lists, seg_out, seg_src, seg_add, seg_key, n_segs, out_idx, out_keys, static_cast<cudaStream_t>(cuda_stream));
+    return cudaGetLastError() == cudaSuccess ? SS_OK : SS_ERR_CUDA;
+}
+
 SS_API void* ss_stream(ss_ctx* c) { return c ? c->stream : nullptr; }
 
 // ---- standalone sort -------------------------------------------------------------------------

@@ -500,7 +500,37 @@ __global__ void __launch_bounds__(kDrawThreads) k_draws(const __grid_constant__ 
     }
 }
 
+// Merged-list placement (multi-GPU): persistent warps over the output, 32 positions at a time; a warp bisects the
+// segment prefix once for its first position and its lanes walk on from there (segments are mostly far longer than
+// a warp, empty ones are stepped over).
+__global__ void __launch_bounds__(256) k_merge_place(const int32_t* __restrict__ lists, const int64_t* __restrict__ seg_out,
+                                                     const int64_t* __restrict__ seg_src, const int64_t* __restrict__ seg_add,
+                                                     const int64_t* __restrict__ seg_key, uint32_t n_segs,
+                                                     int32_t* __restrict__ out_idx, int64_t* __restrict__ out_keys)
+{
+    const int lane = threadIdx.x & 31;
+    const int64_t total = seg_out[n_segs];
+    const int64_t warps = ((int64_t)gridDim.x * blockDim.x) >> 5, warp_id = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    for (int64_t g0 = warp_id * 32; g0 < total; g0 += warps * 32) {
+        uint32_t lo = 0, hi = n_segs;
+        while (hi - lo > 1) {
+            const uint32_t mid = (lo + hi) >> 1;
+            if (seg_out[mid] <= g0) lo = mid; else hi = mid;
+        }
+        const int64_t e = g0 + lane;
+        if (e < total) {
+            uint32_t sI = lo;
+            while (seg_out[sI + 1] <= e) ++sI;
+            out_idx[e] = (int32_t)((int64_t)lists[seg_src[sI] + (e - seg_out[sI])] + seg_add[sI]);
+            out_keys[e] = seg_key[sI];
+        }
+    }
+}
+
 }  // namespace
+
+void launch_merge_place(const int32_t* lists, const int64_t* seg_out, const int64_t* seg_src, const int64_t* seg_add,
+                        const int64_t* seg_key, uint32_t n_segs, int32_t* out_idx, int64_t* out_keys, cudaStream_t st);
 
 size_t emit_lookback_bytes(uint64_t n)
 {
@@ -518,6 +548,12 @@ void launch_emit(const EmitArgs& a, cudaStream_t st)
 void launch_draws(const DrawArgs& a, cudaStream_t st)
 {
     if (a.n_views) k_draws<<<dim3((a.max_draws + kDrawChunk - 1) / kDrawChunk, a.n_views), kDrawThreads, 0, st>>>(a);
+}
+
+void launch_merge_place(const int32_t* lists, const int64_t* seg_out, const int64_t* seg_src, const int64_t* seg_add,
+                        const int64_t* seg_key, uint32_t n_segs, int32_t* out_idx, int64_t* out_keys, cudaStream_t st)
+{
+    if (n_segs) k_merge_place<<<148 * 8, 256, 0, st>>>(lists, seg_out, seg_src, seg_add, seg_key, n_segs, out_idx, out_keys);
 }
 
 }  // namespace ss

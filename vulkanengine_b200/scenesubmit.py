@@ -27,7 +27,7 @@ EXPORTS = ["ss_create", "ss_destroy", "ss_last_error", "ss_version", "ss_set_key
            "ss_download_world", "ss_download_masks", "ss_stream", "ss_sort_scratch_bytes", "ss_sort_pairs",
            "ss_sort_pairs_host", "ss_sort_pairs_static", "ss_camera_view_proj", "ss_cascade_matrices",
            "ss_set_geometry", "ss_raster_view", "ss_map_raster", "ss_download_raster", "ss_read_pixel",
-           "ss_cascade_matrices_batch", "ss_upload_trs_sparse"]
+           "ss_cascade_matrices_batch", "ss_upload_trs_sparse", "ss_merge_place"]
 RASTER_DEPTH_CLAMP = 1
 RASTER_EMPTY = 0xFFFFFFFFFFFFFFFF
 

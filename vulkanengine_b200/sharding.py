@@ -31,6 +31,20 @@ def _gather_rows(t: torch.Tensor) -> torch.Tensor:
     return out
 
 
+def _merge_place(lists, seg_out, seg_src, seg_add, seg_key, n_segs, out_i, out_k):
+    """ss_merge_place on the current CUDA stream (the library must be there: no torch fallback on a GPU)."""
+    import ctypes as C
+
+    from . import scenesubmit
+    lib = scenesubmit.load_library()
+    st = lib.ss_merge_place(C.c_void_p(torch.cuda.current_stream().cuda_stream), C.c_void_p(lists.data_ptr()),
+                            C.c_void_p(seg_out.data_ptr()), C.c_void_p(seg_src.data_ptr()), C.c_void_p(seg_add.data_ptr()),
+                            C.c_void_p(seg_key.data_ptr()), C.c_uint32(n_segs), C.c_void_p(out_i.data_ptr()),
+                            C.c_void_p(out_k.data_ptr()))
+    if st != 0:
+        raise RuntimeError(f"ss_merge_place failed with status {st}")
+
+
 def merge_view_lists(views, idx_offset: int):
     """Merges this rank's compacted lists of SEVERAL views with every other rank's.
 
@@ -102,12 +116,21 @@ def merge_view_lists(views, idx_offset: int):
         # segments in output order (run-major, rank-minor): element e of the output comes from
         # lists.flat[seg_src + (e - seg_out_start)], shifted by its rank's shard offset
         flat_len = seg_len.view(-1)
-        seg_out = torch.cumsum(flat_len, 0) - flat_len
-        gather_from = torch.repeat_interleave(seg_src.view(-1) - seg_out, flat_len, output_size=total)
-        gather_from += torch.arange(total, **i64)
-        add = torch.repeat_interleave(shard.repeat(K), flat_len, output_size=total)
-        out_i = lists.view(-1)[gather_from].to(torch.int64) + add
-        out_k = torch.repeat_interleave(merged_dk, merged_dc, output_size=total)
+        if dev.type == "cuda":
+            # on the GPU the placement is one kernel of the library (ss_merge_place); instance numbers come back as int32
+            seg_out = torch.zeros(K * world + 1, **i64)
+            torch.cumsum(flat_len, 0, out=seg_out[1:])
+            out_i = torch.empty(total, dtype=torch.int32, device=dev)
+            out_k = torch.empty(total, **i64)
+            _merge_place(lists, seg_out, seg_src.view(-1).contiguous(), shard.repeat(K).contiguous(),
+                         merged_dk.repeat_interleave(world).contiguous(), K * world, out_i, out_k)
+        else:
+            seg_out = torch.cumsum(flat_len, 0) - flat_len
+            gather_from = torch.repeat_interleave(seg_src.view(-1) - seg_out, flat_len, output_size=total)
+            gather_from += torch.arange(total, **i64)
+            add = torch.repeat_interleave(shard.repeat(K), flat_len, output_size=total)
+            out_i = lists.view(-1)[gather_from].to(torch.int64) + add
+            out_k = torch.repeat_interleave(merged_dk, merged_dc, output_size=total)
         out.append((out_k, out_i, merged_dk, merged_dc, first))
     return out
 
