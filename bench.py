@@ -331,12 +331,24 @@ def main():
                 dk = dev_tensor(o.draw_keys, o.n_draws, "<i8")
                 draws = dev_tensor(o.draws, o.n_draws * 5, "<i4").view(-1, 5)
                 lists.append((idx, dk, draws[:, 1].contiguous()))
-            merged = sharding.merge_view_lists(lists, rank * n)
-            return sum(m[1].numel() * 4 for m in merged)  # instance indices all-gathered over NVLink (keys are rebuilt from the runs)
+            merged = sharding.merge_view_lists(lists, rank * n, peers=peers, frame_slot=slot_)
+            return sum(m[1].numel() * 4 for m in merged)  # instance indices crossing NVLink (keys are rebuilt from the runs)
 
         s_ = ctx.frame(views)
         st_ = ctx.frame_sync(s_)
+        peers = None
         merge_all_views(s_, st_)  # warm-up (NCCL channels, allocator)
+        barrier()
+        g0, g1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        g0.record()
+        merge_all_views(s_, st_)
+        g1.record()
+        g1.synchronize()
+        gt = torch.tensor([g0.elapsed_time(g1)], dtype=torch.float64, device="cuda")
+        dist.all_reduce(gt, op=dist.ReduceOp.MAX)
+        # the same with every rank reading its peers' lists in place over NVLink (CUDA IPC) instead of an all-gathered copy
+        peers = sharding.PeerLists(ctx, local_rank)
+        merge_all_views(s_, st_)
         barrier()
         m0, m1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         m0.record()
@@ -345,9 +357,12 @@ def main():
         m1.synchronize()
         mt = torch.tensor([m0.elapsed_time(m1)], dtype=torch.float64, device="cuda")
         dist.all_reduce(mt, op=dist.ReduceOp.MAX)
-        merge = {"ms": float(mt.item()), "all_gathered_bytes": int(merged_bytes),
-                 "note": "all_gather of per-view draw keys/counts and (key, instance) lists + run placement; "
-                         "not part of the sharded phase timed in value"}
+        barrier()
+        peers.close()
+        merge = {"ms": float(mt.item()), "ms_with_all_gather": float(gt.item()), "list_bytes_over_nvlink": int(merged_bytes),
+                 "note": "sizes and draws all-gathered (KBs); each rank's placement kernel reads the peers' instance lists in "
+                         "place over NVLink (ms) or from an NCCL all-gathered copy (ms_with_all_gather); not part of the "
+                         "sharded phase timed in value"}
 
     # ---- end to end through the C ABI from host buffers --------------------------------------------
     e2e = None

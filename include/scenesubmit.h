@@ -316,6 +316,24 @@ SS_API ss_status ss_merge_place(void* cuda_stream, const int32_t* lists, const i
                                 const int64_t* seg_add, const int64_t* seg_key, uint32_t n_segs, int32_t* out_idx,
                                 int64_t* out_keys);
 
+/* The same placement reading the ranks' lists where they lie — in each rank's own output buffers, over NVLink peer
+   access — instead of from an all-gathered copy: the exchange and the placement are one kernel.
+   ss_export_idx_lists: CUDA IPC handles of this context's instance-index output buffers, [frames_in_flight][max_views]
+   in that order (each 64 bytes), and the buffers' addresses in this process; another process opens one with ss_ipc_open (once; the mapping stays valid until
+   ss_ipc_close or the exporter's ss_destroy) and may read it after the exporter's ss_frame_sync of that slot and
+   before the exporter reuses the slot.  rank_lists: device array of one pointer per rank (this rank's own buffer
+   as it is, the others' as opened); seg_rank[s] picks the list, seg_src[s] is the offset inside it. */
+typedef struct ss_ipc_handle {
+    unsigned char bytes[64];
+} ss_ipc_handle;
+SS_API ss_status ss_export_idx_lists(ss_ctx* ctx, ss_ipc_handle* handles_out, void** own_pointers_out, uint32_t capacity,
+                                     uint32_t* count_out);
+SS_API ss_status ss_ipc_open(int device, const ss_ipc_handle* handle, void** device_ptr_out);
+SS_API ss_status ss_ipc_close(int device, void* device_ptr);
+SS_API ss_status ss_merge_place_peers(void* cuda_stream, const int32_t* const* rank_lists, const int32_t* seg_rank,
+                                      const int64_t* seg_out, const int64_t* seg_src, const int64_t* seg_add,
+                                      const int64_t* seg_key, uint32_t n_segs, int32_t* out_idx, int64_t* out_keys);
+
 /* ---- the sort on its own ---------------------------------------------------------------------- */
 
 /* Stable LSD radix sort (onesweep) of (uint64 key, uint32 value) pairs on bits [begin_bit, end_bit).

@@ -40,15 +40,19 @@ def main():
         o = ctx.map_outputs(slot, v)
         draws = dev_tensor(o.draws, o.n_draws * 5, "<i4").view(-1, 5)
         lists.append((dev_tensor(o.instance_idx, n, "<i4"), dev_tensor(o.draw_keys, o.n_draws, "<i8"), draws[:, 1].contiguous()))
-    merged = sharding.merge_view_lists(lists, rank * n)
+    peers = sharding.PeerLists(ctx, local)
+    results = {"all-gather": sharding.merge_view_lists(lists, rank * n),
+               "peer reads": sharding.merge_view_lists(lists, rank * n, peers=peers, frame_slot=slot)}
     torch.cuda.synchronize()
+    dist.barrier()   # nobody tears its buffers down while a peer may still be reading them
     if rank == 0:
         whole = synth.flat_scene(n * world, first=0, n_keys=500)
         c2 = S.SceneSubmit(whole.n_nodes, n * world, len(whole.slots), max_views=5, device=local)
         c2.load_scene(whole)
         s2 = c2.frame(views)
         st2 = c2.frame_sync(s2)
-        for v in range(5):
+        for how, v in [(h, v) for h in results for v in range(5)]:
+            merged = results[how]
             ref = c2.download_view(s2, v, st2, want_rows=False)
             k, i, dk, dc, first = merged[v]
             assert np.array_equal(i.cpu().numpy().astype(np.int64), ref["idx"].astype(np.int64)), v
@@ -56,8 +60,9 @@ def main():
             assert np.array_equal(dk.cpu().numpy().view(np.uint64), ref["draw_keys"]), v
             assert np.array_equal(dc.cpu().numpy(), ref["draws"]["instance_count"].astype(np.int64)), v
             assert np.array_equal(first.cpu().numpy(), ref["draws"]["first_instance"].astype(np.int64)), v
-        print(f"merge over {world} GPUs == one GPU holding all {n * world} instances: 5 views identical")
+        print(f"merge over {world} GPUs == one GPU holding all {n * world} instances: 5 views identical, both exchange paths")
     dist.barrier()
+    peers.close()
     dist.destroy_process_group()
 
 

@@ -1035,6 +1035,57 @@ SS_API ss_status ss_merge_place(void* cuda_stream, const int32_t* lists, const i
     return cudaGetLastError() == cudaSuccess ? SS_OK : SS_ERR_CUDA;
 }
 
+SS_API ss_status ss_export_idx_lists(ss_ctx* c, ss_ipc_handle* handles_out, void** own_pointers_out, uint32_t capacity,
+                                     uint32_t* count_out)
+{
+    if (!c || !handles_out || !own_pointers_out || !count_out) return SS_ERR_INVALID;
+    const uint32_t V = c->cfg.max_views, need = (uint32_t)c->slots.size() * V;
+    *count_out = need;
+    if (capacity < need) return c->fail(SS_ERR_INVALID, "ss_export_idx_lists: %u handles, room for %u", need, capacity);
+    static_assert(sizeof(cudaIpcMemHandle_t) == sizeof(ss_ipc_handle), "handle size");
+    SS_CUDA(c, cudaSetDevice(c->device));
+    for (size_t si = 0; si < c->slots.size(); ++si)
+        for (uint32_t v = 0; v < V; ++v) {
+            cudaIpcMemHandle_t h;
+            SS_CUDA(c, cudaIpcGetMemHandle(&h, c->slots[si].out[v].idx));
+            memcpy(&handles_out[si * V + v], &h, sizeof h);
+            own_pointers_out[si * V + v] = c->slots[si].out[v].idx;
+        }
+    return SS_OK;
+}
+
+SS_API ss_status ss_ipc_open(int device, const ss_ipc_handle* handle, void** device_ptr_out)
+{
+    if (!handle || !device_ptr_out) return SS_ERR_INVALID;
+    if (cudaSetDevice(device) != cudaSuccess) return SS_ERR_CUDA;
+    cudaIpcMemHandle_t h;
+    memcpy(&h, handle, sizeof h);
+    const cudaError_t e = cudaIpcOpenMemHandle(device_ptr_out, h, cudaIpcMemLazyEnablePeerAccess);
+    if (e != cudaSuccess) {
+        ss::set_global_error(cudaGetErrorString(e));
+        return SS_ERR_CUDA;
+    }
+    return SS_OK;
+}
+
+SS_API ss_status ss_ipc_close(int device, void* device_ptr)
+{
+    if (!device_ptr) return SS_OK;
+    if (cudaSetDevice(device) != cudaSuccess) return SS_ERR_CUDA;
+    return cudaIpcCloseMemHandle(device_ptr) == cudaSuccess ? SS_OK : SS_ERR_CUDA;
+}
+
+SS_API ss_status ss_merge_place_peers(void* cuda_stream, const int32_t* const* rank_lists, const int32_t* seg_rank,
+                                      const int64_t* seg_out, const int64_t* seg_src, const int64_t* seg_add,
+                                      const int64_t* seg_key, uint32_t n_segs, int32_t* out_idx, int64_t* out_keys)
+{
+    if (n_segs == 0) return SS_OK;
+    if (!rank_lists || !seg_rank || !seg_out || !seg_src || !seg_add || !seg_key || !out_idx || !out_keys) return SS_ERR_INVALID;
+    launch_merge_place_peers(rank_lists, seg_rank, seg_out, seg_src, seg_add, seg_key, n_segs, out_idx, out_keys,
+                             static_cast<cudaStream_t>(cuda_stream));
+    return cudaGetLastError() == cudaSuccess ? SS_OK : SS_ERR_CUDA;
+}
+
 SS_API void* ss_stream(ss_ctx* c) { return c ? c->stream : nullptr; }
 
 // ---- standalone sort -------------------------------------------------------------------------

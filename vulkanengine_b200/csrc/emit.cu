@@ -527,6 +527,50 @@ __global__ void __launch_bounds__(256) k_merge_place(const int32_t* __restrict__
     }
 }
 
+// The same over peer memory: segment s lies in rank seg_rank[s]'s own output buffer, read across NVLink where it is.
+// Four independent 128 B requests per warp are in flight per round (remote latency is several times the local one).
+__global__ void __launch_bounds__(256) k_merge_place_peers(const int32_t* const* __restrict__ rank_lists,
+                                                           const int32_t* __restrict__ seg_rank, const int64_t* __restrict__ seg_out,
+                                                           const int64_t* __restrict__ seg_src, const int64_t* __restrict__ seg_add,
+                                                           const int64_t* __restrict__ seg_key, uint32_t n_segs,
+                                                           int32_t* __restrict__ out_idx, int64_t* __restrict__ out_keys)
+{
+    constexpr int kRounds = 4;
+    const int lane = threadIdx.x & 31;
+    const int64_t total = seg_out[n_segs];
+    const int64_t warps = ((int64_t)gridDim.x * blockDim.x) >> 5, warp_id = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    for (int64_t g0 = warp_id * (32 * kRounds); g0 < total; g0 += warps * (32 * kRounds)) {
+        uint32_t lo = 0, hi = n_segs;
+        while (hi - lo > 1) {
+            const uint32_t mid = (lo + hi) >> 1;
+            if (seg_out[mid] <= g0) lo = mid; else hi = mid;
+        }
+        int32_t val[kRounds];
+        int64_t add[kRounds], key[kRounds];
+        uint32_t sI = lo;
+#pragma unroll
+        for (int r = 0; r < kRounds; ++r) {
+            const int64_t e = g0 + r * 32 + lane;
+            val[r] = 0;
+            add[r] = key[r] = 0;
+            if (e < total) {
+                while (seg_out[sI + 1] <= e) ++sI;
+                val[r] = rank_lists[seg_rank[sI]][seg_src[sI] + (e - seg_out[sI])];
+                add[r] = seg_add[sI];
+                key[r] = seg_key[sI];
+            }
+        }
+#pragma unroll
+        for (int r = 0; r < kRounds; ++r) {
+            const int64_t e = g0 + r * 32 + lane;
+            if (e < total) {
+                out_idx[e] = (int32_t)((int64_t)val[r] + add[r]);
+                out_keys[e] = key[r];
+            }
+        }
+    }
+}
+
 }  // namespace
 
 void launch_merge_place(const int32_t* lists, const int64_t* seg_out, const int64_t* seg_src, const int64_t* seg_add,
@@ -554,6 +598,14 @@ void launch_merge_place(const int32_t* lists, const int64_t* seg_out, const int6
                         const int64_t* seg_key, uint32_t n_segs, int32_t* out_idx, int64_t* out_keys, cudaStream_t st)
 {
     if (n_segs) k_merge_place<<<148 * 8, 256, 0, st>>>(lists, seg_out, seg_src, seg_add, seg_key, n_segs, out_idx, out_keys);
+}
+
+void launch_merge_place_peers(const int32_t* const* rank_lists, const int32_t* seg_rank, const int64_t* seg_out,
+                              const int64_t* seg_src, const int64_t* seg_add, const int64_t* seg_key, uint32_t n_segs,
+                              int32_t* out_idx, int64_t* out_keys, cudaStream_t st)
+{
+    if (n_segs)
+        k_merge_place_peers<<<148 * 8, 256, 0, st>>>(rank_lists, seg_rank, seg_out, seg_src, seg_add, seg_key, n_segs, out_idx, out_keys);
 }
 
 }  // namespace ss

@@ -140,6 +140,9 @@ struct EmitArgs {
 };
 size_t emit_lookback_bytes(uint64_t n);
 void launch_emit(const EmitArgs& a, cudaStream_t st);
+void launch_merge_place_peers(const int32_t* const* rank_lists, const int32_t* seg_rank, const int64_t* seg_out,
+                              const int64_t* seg_src, const int64_t* seg_add, const int64_t* seg_key, uint32_t n_segs,
+                              int32_t* out_idx, int64_t* out_keys, cudaStream_t st);
 // multi-GPU merge: out[e] = lists[seg_src[s] + (e - seg_out[s])] + seg_add[s], keys[e] = seg_key[s]
 void launch_merge_place(const int32_t* lists, const int64_t* seg_out, const int64_t* seg_src, const int64_t* seg_add,
                         const int64_t* seg_key, uint32_t n_segs, int32_t* out_idx, int64_t* out_keys, cudaStream_t st);

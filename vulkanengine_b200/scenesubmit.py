@@ -27,7 +27,8 @@ EXPORTS = ["ss_create", "ss_destroy", "ss_last_error", "ss_version", "ss_set_key
            "ss_download_world", "ss_download_masks", "ss_stream", "ss_sort_scratch_bytes", "ss_sort_pairs",
            "ss_sort_pairs_host", "ss_sort_pairs_static", "ss_camera_view_proj", "ss_cascade_matrices",
            "ss_set_geometry", "ss_raster_view", "ss_map_raster", "ss_download_raster", "ss_read_pixel",
-           "ss_cascade_matrices_batch", "ss_upload_trs_sparse", "ss_merge_place"]
+           "ss_cascade_matrices_batch", "ss_upload_trs_sparse", "ss_merge_place",
+           "ss_export_idx_lists", "ss_ipc_open", "ss_ipc_close", "ss_merge_place_peers"]
 RASTER_DEPTH_CLAMP = 1
 RASTER_EMPTY = 0xFFFFFFFFFFFFFFFF
 
@@ -122,6 +123,20 @@ def cascade_matrices_batch(view_projs, zn, zf, lam, near_off, far_off, light_dir
     return splits, out
 
 
+def ipc_open(device, handle):
+    lib = load_library()
+    buf = (C.c_ubyte * 64).from_buffer_copy(handle)
+    ptr = C.c_void_p()
+    st = lib.ss_ipc_open(C.c_int(device), buf, C.byref(ptr))
+    if st != SS_OK:
+        raise SceneSubmitError(st, "ss_ipc_open: " + lib.ss_last_error(None).decode())
+    return int(ptr.value)
+
+
+def ipc_close(device, ptr):
+    load_library().ss_ipc_close(C.c_int(device), C.c_void_p(ptr))
+
+
 def sort_pairs_host(keys, vals, begin_bit=0, end_bit=64, device=0):
     lib = load_library()
     keys = np.ascontiguousarray(keys, np.uint64)
@@ -149,6 +164,7 @@ class SceneSubmit:
         self.h = h
         self.n_instances = 0
         self.n_views = 0
+        self.max_views = max_views
 
     def close(self):
         if getattr(self, "h", None):
@@ -278,6 +294,17 @@ class SceneSubmit:
         m = np.empty(count, np.uint8)
         self._ck(self.lib.ss_download_masks(self.h, C.c_uint32(first), C.c_uint32(count), _p(m)))
         return m
+
+    def export_idx_lists(self):
+        """([frames_in_flight * max_views] 64-byte CUDA IPC handles, the same buffers' addresses in this process) of the
+        per-view instance-index outputs: what a peer rank needs to read this rank's lists over NVLink."""
+        cap = 64
+        handles = (C.c_ubyte * (64 * cap))()
+        ptrs = (C.c_void_p * cap)()
+        count = C.c_uint32()
+        self._ck(self.lib.ss_export_idx_lists(self.h, handles, ptrs, C.c_uint32(cap), C.byref(count)))
+        raw = bytes(handles)
+        return [raw[64 * k: 64 * (k + 1)] for k in range(count.value)], [int(ptrs[k] or 0) for k in range(count.value)]
 
     # ---- consumer pass: depth + id rasterisation of a view's lists ----
     def set_geometry(self, positions, indices):

@@ -31,13 +31,25 @@ def _gather_rows(t: torch.Tensor) -> torch.Tensor:
     return out
 
 
-def _merge_place(lists, seg_out, seg_src, seg_add, seg_key, n_segs, out_i, out_k):
-    """ss_merge_place on the current CUDA stream (the library must be there: no torch fallback on a GPU)."""
+def _merge_place(lists, seg_out, seg_src, seg_add, seg_key, n_segs, out_i, out_k, peer_row=None):
+    """ss_merge_place / ss_merge_place_peers on the current CUDA stream (the library must be there: no torch fallback
+    on a GPU).  peer_row: device tensor of one buffer address per rank; segments are numbered run-major, rank-minor."""
     import ctypes as C
 
     from . import scenesubmit
     lib = scenesubmit.load_library()
-    st = lib.ss_merge_place(C.c_void_p(torch.cuda.current_stream().cuda_stream), C.c_void_p(lists.data_ptr()),
+    stream = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+    if peer_row is not None:
+        world = peer_row.numel()
+        seg_rank = torch.arange(world, dtype=torch.int32, device=out_i.device).repeat(n_segs // world).contiguous()
+        st = lib.ss_merge_place_peers(stream, C.c_void_p(peer_row.data_ptr()), C.c_void_p(seg_rank.data_ptr()),
+                                      C.c_void_p(seg_out.data_ptr()), C.c_void_p(seg_src.data_ptr()),
+                                      C.c_void_p(seg_add.data_ptr()), C.c_void_p(seg_key.data_ptr()), C.c_uint32(n_segs),
+                                      C.c_void_p(out_i.data_ptr()), C.c_void_p(out_k.data_ptr()))
+        if st != 0:
+            raise RuntimeError(f"ss_merge_place_peers failed with status {st}")
+        return
+    st = lib.ss_merge_place(stream, C.c_void_p(lists.data_ptr()),
                             C.c_void_p(seg_out.data_ptr()), C.c_void_p(seg_src.data_ptr()), C.c_void_p(seg_add.data_ptr()),
                             C.c_void_p(seg_key.data_ptr()), C.c_uint32(n_segs), C.c_void_p(out_i.data_ptr()),
                             C.c_void_p(out_k.data_ptr()))
@@ -45,7 +57,43 @@ def _merge_place(lists, seg_out, seg_src, seg_add, seg_key, n_segs, out_i, out_k
         raise RuntimeError(f"ss_merge_place failed with status {st}")
 
 
-def merge_view_lists(views, idx_offset: int):
+class PeerLists:
+    """Every rank's instance-index output buffers, mapped into this process once (CUDA IPC; reads go over NVLink).
+    With it merge_view_lists does not all-gather the lists: the placement kernel reads each segment from the buffer of
+    the rank that produced it (ss_merge_place_peers).  The caller keeps the usual contract of shared buffers: a slot is
+    read by peers between its owner's ss_frame_sync (which precedes the merge call on every rank) and the owner's next
+    ss_frame into that slot (which must come after a barrier that follows the merge)."""
+
+    def __init__(self, ctx, device: int):
+        from . import scenesubmit
+        self._scenesubmit, self.device = scenesubmit, device
+        world, rank = dist.get_world_size(), dist.get_rank()
+        handles, own = ctx.export_idx_lists()
+        everyone = [None] * world
+        dist.all_gather_object(everyone, handles)
+        self.n_views = ctx.max_views
+        self._opened = []
+        table = torch.zeros((len(handles), world), dtype=torch.int64)
+        for r in range(world):
+            for k, h in enumerate(everyone[r]):
+                if r == rank:
+                    table[k, r] = own[k]
+                else:
+                    p = scenesubmit.ipc_open(device, h)
+                    self._opened.append(p)
+                    table[k, r] = p
+        self.table = table.to(torch.device("cuda", device))  # [slot * max_views + view][rank] -> device address
+
+    def row(self, slot: int, view: int) -> torch.Tensor:
+        return self.table[slot * self.n_views + view]
+
+    def close(self):
+        for p in self._opened:
+            self._scenesubmit.ipc_close(self.device, p)
+        self._opened = []
+
+
+def merge_view_lists(views, idx_offset: int, peers: "PeerLists" = None, frame_slot: int = 0):
     """Merges this rank's compacted lists of SEVERAL views with every other rank's.
 
     views        list of (idx, draw_keys, draw_counts) per view: this rank's visible instance list (sorted by key,
@@ -89,11 +137,13 @@ def merge_view_lists(views, idx_offset: int):
         nd = [int(x) for x in n_draw[:, v]]
         nl = [int(x) for x in n_list[:, v]]
         cap = max(max(nl), 1)
-        # 3) the instance lists: equal-length slices (the tail past a rank's own count is never read)
-        src = idx.to(torch.int32) if idx.dtype != torch.int32 else idx
-        if src.numel() < cap:
-            src = torch.cat([src, torch.zeros(cap - src.numel(), dtype=torch.int32, device=dev)])
-        lists = _gather_rows(src[:cap])                                     # [world, cap] int32
+        lists = None
+        if peers is None:
+            # 3) the instance lists: equal-length slices (the tail past a rank's own count is never read)
+            src = idx.to(torch.int32) if idx.dtype != torch.int32 else idx
+            if src.numel() < cap:
+                src = torch.cat([src, torch.zeros(cap - src.numel(), dtype=torch.int32, device=dev)])
+            lists = _gather_rows(src[:cap])                                 # [world, cap] int32
 
         # merged draws: union of the ranks' keys in key order, counts summed
         keys_r = [all_draws[r, v, 0, : nd[r]] for r in range(world)]
@@ -108,7 +158,7 @@ def merge_view_lists(views, idx_offset: int):
             if nd[r]:
                 slot = inverse[off: off + nd[r]]
                 seg_len[slot, r] = cnts_r[r]
-                seg_src[slot, r] = (torch.cumsum(cnts_r[r], 0) - cnts_r[r]) + r * cap
+                seg_src[slot, r] = (torch.cumsum(cnts_r[r], 0) - cnts_r[r]) + (r * cap if peers is None else 0)
             off += nd[r]
         merged_dc = seg_len.sum(1)
         first = torch.cumsum(merged_dc, 0) - merged_dc
@@ -123,7 +173,8 @@ def merge_view_lists(views, idx_offset: int):
             out_i = torch.empty(total, dtype=torch.int32, device=dev)
             out_k = torch.empty(total, **i64)
             _merge_place(lists, seg_out, seg_src.view(-1).contiguous(), shard.repeat(K).contiguous(),
-                         merged_dk.repeat_interleave(world).contiguous(), K * world, out_i, out_k)
+                         merged_dk.repeat_interleave(world).contiguous(), K * world, out_i, out_k,
+                         None if peers is None else peers.row(frame_slot, v))
         else:
             seg_out = torch.cumsum(flat_len, 0) - flat_len
             gather_from = torch.repeat_interleave(seg_src.view(-1) - seg_out, flat_len, output_size=total)
