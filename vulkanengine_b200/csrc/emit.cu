@@ -21,7 +21,7 @@ constexpr uint32_t kFlagAgg = 1u << 30;
 constexpr uint32_t kFlagPrefix = 1u << 31;
 constexpr uint32_t kValueMask = kFlagAgg - 1;
 constexpr int kEmitWarps = kEmitThreads / 32;
-constexpr int kGatherBatch = 12;  // independent 16 B row gathers in flight per thread (a full 1024-row view = 12)
+constexpr int kGatherBatch = 6;  // independent 16 B row gathers in flight per thread; with 64 registers four CTAs share an SM
 
 struct EmitSmem {
     uint64_t key[kEmitTile];
@@ -55,7 +55,7 @@ __device__ __forceinline__ uint64_t spread4(uint32_t m)
     return (uint64_t)(m & 1u) | ((uint64_t)(m & 2u) << 15) | ((uint64_t)(m & 4u) << 30) | ((uint64_t)(m & 8u) << 45);
 }
 
-__global__ void __launch_bounds__(kEmitThreads) k_emit(const __grid_constant__ EmitArgs a)
+__global__ void __launch_bounds__(kEmitThreads, 4) k_emit(const __grid_constant__ EmitArgs a)
 {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     EmitSmem& s = *reinterpret_cast<EmitSmem*>(smem_raw);
@@ -330,26 +330,27 @@ __global__ void __launch_bounds__(kEmitThreads) k_emit(const __grid_constant__ E
         }
     }
     constexpr int kParts = kEmitTile * 3 / kEmitThreads;  // (item, row part) pairs per thread
-    static_assert(kParts == kGatherBatch, "one batch of gathers covers the tile");
-    float4 r[kGatherBatch];
+    for (int u0 = 0; u0 < kParts; u0 += kGatherBatch) {
+        float4 r[kGatherBatch];
 #pragma unroll
-    for (int u = 0; u < kGatherBatch; ++u) {
-        const uint32_t j = tid + u * kEmitThreads;
-        const uint32_t e = j / 3u, part = j - e * 3u;
-        if (s.msk[e]) r[u] = __ldg(a.world + (size_t)s.idx[e] * kWorldStride + part);
-    }
+        for (int u = 0; u < kGatherBatch; ++u) {
+            const uint32_t j = tid + (u0 + u) * kEmitThreads;
+            const uint32_t e = j / 3u, part = j - e * 3u;
+            if (u0 + u < kParts && s.msk[e]) r[u] = __ldg(a.world + (size_t)s.idx[e] * kWorldStride + part);
+        }
 #pragma unroll
-    for (int u = 0; u < kGatherBatch; ++u) {
-        const uint32_t j = tid + u * kEmitThreads;
-        const uint32_t e = j / 3u, part = j - e * 3u;
-        const uint32_t mm = s.msk[e];
-        if (mm) {
-            const uint64_t pa2 = s.pos_a[e], pb2 = s.pos_b[e];
+        for (int u = 0; u < kGatherBatch; ++u) {
+            const uint32_t j = tid + (u0 + u) * kEmitThreads;
+            const uint32_t e = j / 3u, part = j - e * 3u;
+            const uint32_t mm = u0 + u < kParts ? s.msk[e] : 0u;
+            if (mm) {
+                const uint64_t pa2 = s.pos_a[e], pb2 = s.pos_b[e];
 #pragma unroll
-            for (int v = 0; v < (int)SS_MAX_VIEWS; ++v) {
-                if ((mm >> v) & 1u) {
-                    const uint32_t g = s.base[v] + ((uint32_t)((v < 4 ? pa2 >> (16 * v) : pb2 >> (16 * (v - 4)))) & 0xffffu);
-                    if (g < a.cap_visible) a.out[v].rows[(size_t)g * 3u + part] = r[u];
+                for (int v = 0; v < (int)SS_MAX_VIEWS; ++v) {
+                    if ((mm >> v) & 1u) {
+                        const uint32_t g = s.base[v] + ((uint32_t)((v < 4 ? pa2 >> (16 * v) : pb2 >> (16 * (v - 4)))) & 0xffffu);
+                        if (g < a.cap_visible) a.out[v].rows[(size_t)g * 3u + part] = r[u];
+                    }
                 }
             }
         }
