@@ -291,7 +291,7 @@ struct Smem2 {
 };
 
 template <bool HAS_PARENT>
-__global__ void __launch_bounds__(kThreads2, 6) k_instances_x2(const __grid_constant__ InstanceArgs a,
+__global__ void __launch_bounds__(kThreads2, HAS_PARENT ? 4 : 5) k_instances_x2(const __grid_constant__ InstanceArgs a,
                                                             const __grid_constant__ CullParams cp, const Neutral neutral)
 {
     extern __shared__ __align__(128) unsigned char smem_raw[];
