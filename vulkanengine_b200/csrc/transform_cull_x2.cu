@@ -4,7 +4,7 @@
 // Why.  The one-instance-per-thread kernel (transform_cull.cu) is issue-bound and latency-bound, not
 // HBM-bound: ~450 of its ~1000 warp instructions per 32 instances are FMUL/FADD that -fmad=false forbids
 // to fuse, and every CTA first waits a full DRAM round trip for its tile.  Here
-//   * each CTA lives for the whole launch and walks tiles of 256 instances; one thread issues
+//   * each CTA lives for the whole launch and walks tiles of 128 instances; one thread issues
 //     cp.async.bulk (TMA, UBLKCP in SASS) copies of the NEXT tile's records (TRS 36 B, AABB 24 B, ids)
 //     into the stage buffer as soon as the current tile has been unpacked into registers; the arrival
 //     is tracked by an mbarrier, so HBM latency is hidden behind the arithmetic of the current tile;
@@ -32,8 +32,9 @@ namespace ss {
 
 namespace {
 
-constexpr int kThreads2 = 128;            // threads per CTA
-constexpr int kTile2 = 2 * kThreads2;     // instances per tile: thread t owns instances t and t + 128
+constexpr int kThreads2 = 64;             // threads per CTA: two warps, ten CTAs per SM at 96 registers (128 threads x 5 and
+                                          // 128 x 6 at 80 registers were measured slower, 32 x 20 too)
+constexpr int kTile2 = 2 * kThreads2;     // instances per tile: thread t owns instances t and t + kThreads2
 // One stage is enough: a tile's records are unpacked into registers first thing, the stage is refilled with
 // the CTA's next tile right after, and that copy has the whole arithmetic of the current tile to land.
 constexpr int kStages = 1;
@@ -291,7 +292,7 @@ struct Smem2 {
 };
 
 template <bool HAS_PARENT>
-__global__ void __launch_bounds__(kThreads2, HAS_PARENT ? 4 : 5) k_instances_x2(const __grid_constant__ InstanceArgs a,
+__global__ void __launch_bounds__(kThreads2, HAS_PARENT ? 8 : 10) k_instances_x2(const __grid_constant__ InstanceArgs a,
                                                             const __grid_constant__ CullParams cp, const Neutral neutral)
 {
     extern __shared__ __align__(128) unsigned char smem_raw[];
@@ -531,7 +532,7 @@ __global__ void __launch_bounds__(kThreads2, HAS_PARENT ? 4 : 5) k_instances_x2(
 bool instances_x2_eligible(const InstanceArgs& a)
 {
     // TRS-driven (no explicit node map, no given world rows), deterministic trig; every bulk copy source must
-    // be 16 B aligned: the 36 B / 4 B node streams need node_base % 4 == 0 (tiles start at multiples of 256)
+    // be 16 B aligned: the 36 B / 4 B node streams need node_base % 4 == 0 (tiles start at multiples of kTile2 = 128)
     return !a.world_given && a.node == nullptr && a.trig_mode == SS_TRIG_DETERMINISTIC && a.n > 0 &&
            (a.node_base & 3u) == 0 && (reinterpret_cast<uintptr_t>(a.trs) & 15u) == 0 &&
            (reinterpret_cast<uintptr_t>(a.slot) & 15u) == 0 && (reinterpret_cast<uintptr_t>(a.matword) & 15u) == 0 &&
