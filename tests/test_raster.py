@@ -172,3 +172,21 @@ def test_geometry_out_of_range_draws_nothing_and_errors_are_reported():
     with pytest.raises(S.SceneSubmitError):
         ctx.read_pixel(0, 32, 0)
     ctx.close()
+
+
+@pytest.mark.parametrize("case", range(int(__import__("os").environ.get("SS_SWEEP_CASES", "10"))))
+def test_randomised_raster(case):
+    """Seeded sweep: scene spread, camera distance and direction, target size, clamp flag, number of instances — the
+    image must equal the CPU restatement every time (small triangles, large ones, cut ones, queued ones)."""
+    rng = np.random.default_rng(500 + case)
+    n = int(rng.integers(1, 1500))
+    spread = float(rng.choice([3.0, 30.0, 300.0]))
+    sc, pos, ind = close_up_scene(n, spread=spread, seed_shift=case)
+    dist = float(rng.choice([2.0, 10.0, 80.0, 600.0]))
+    views = synth.fibonacci_cameras(lambda *a: O.camera_view_proj(*a), 3, radius=dist, seed=synth.SEED_BASE + case)
+    W, H = int(rng.integers(8, 200)), int(rng.integers(8, 120))
+    flags = [0, S.RASTER_DEPTH_CLAMP][int(rng.integers(0, 2))]
+    ctx, slot, out = run(sc, pos, ind, views, W, H, lambda v: flags)
+    for v, (img, want, _) in enumerate(out):
+        assert np.array_equal(img, want), f"case {case} view {v}: {np.count_nonzero(img != want)} of {W * H} samples differ"
+    ctx.close()
