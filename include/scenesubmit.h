@@ -360,7 +360,11 @@ SS_API ss_status ss_sort_pairs_host(int device, const uint64_t* keys_in, const u
    why.  The call itself performs no cudaMalloc/cudaFree and uses no allocating library routine; the
    caller still provides both ping-pong buffer pairs.  The first call on each device looks up the
    array's device address (once per device, with that device current): make that first call before
-   any stream capture begins.  All calls on one device share the one array, which still holds the
+   any stream capture begins.  Every call ends by copying one word (which buffer holds the result)
+   back to the host and waits for the stream, so it returns with the sort finished.  cuda_stream must
+   belong to the device that is current when the call is made (checked; SS_ERR_INVALID otherwise), and
+   the looked-up address is remembered per device ordinal for the life of the process: it does not
+   survive a cudaDeviceReset.  All calls on one device share the one array, which still holds the
    previous call's state; each call clears the words it needs before it sorts, so two calls that
    overlap on the GPU (different streams, different threads) would race: keep them ordered. */
 #define SS_SORT_STATIC_MAX_N (1u << 20)

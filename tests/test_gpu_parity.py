@@ -581,3 +581,46 @@ def test_scalar_and_packed_instance_kernels_agree(monkeypatch):
     ref = O.OracleScene(aligned, 0).frame(views)
     got = run_gpu(aligned, views)
     check_against_oracle(aligned, views, got, ref)
+
+
+def test_view_count_changes_between_frames():
+    """ss_frame takes any n_views up to max_views, frame by frame.  The per-view run counters are double-buffered by
+    frame and cleaned one frame ahead, so 5 views, then 1, then 5 again reuses a buffer the first frame dirtied in
+    rows 1-4: every frame must still equal the oracle."""
+    sc = synth.flat_scene(20_000, n_keys=256)
+    v5 = oracle_views(5)
+    v1 = v5[:1]
+    osc = O.OracleScene(sc, 0)
+    ref5, ref1 = osc.frame(v5), osc.frame(v1)
+    ctx = S.SceneSubmit(sc.n_nodes, sc.n_instances, len(sc.slots), max_views=5, frames_in_flight=2)
+    ctx.load_scene(sc)
+    for views, ref in ((v5, ref5), (v1, ref1), (v5, ref5), (v5, ref5), (v1, ref1), (v1, ref1), (v5, ref5)):
+        slot = ctx.frame(views)
+        st = ctx.frame_sync(slot)
+        got = {"stats": st, "world": ctx.download_world(), "masks": ctx.download_masks(),
+               "views": [ctx.download_view(slot, v, st) for v in range(len(views))]}
+        check_against_oracle(sc, views, got, ref)
+    ctx.close()
+
+
+def test_implicit_node_map_must_stay_in_last_level():
+    """With node == NULL only the levels above node_base are composed before the instance kernel: a range that
+    spans levels (or starts above the last one) is refused instead of reading rows nobody computed."""
+    sc = synth.hierarchy_scene(n_roots=4, fan1=4, fan2=8, n_keys=40)
+    ctx = S.SceneSubmit(sc.n_nodes, sc.n_nodes, len(sc.slots), max_views=1)
+    ctx.set_key_layout(sc.mesh_bits, sc.submesh_bits, sc.material_bits)
+    ctx.set_submesh_table(sc.slots)
+    ctx.set_nodes(sc.n_nodes, sc.parent, sc.level_offsets)
+    n_all = sc.n_nodes
+    slot = np.zeros(n_all, np.uint32)
+    mw = np.zeros(n_all, np.uint32)
+    with pytest.raises(S.SceneSubmitError) as e:      # every node as an instance: spans three levels
+        ctx.set_instances(slot, mw, None, 0)
+    assert e.value.status == S.SS_ERR_INVALID
+    with pytest.raises(S.SceneSubmitError):           # starts in the middle level
+        ctx.set_instances(slot[:8], mw[:8], None, int(sc.level_offsets[1]))
+    ctx.set_instances(sc.slot, sc.matword, None, sc.node_base)  # the leaves: fine
+    # narrowing the key layout below what the streams hold is refused
+    with pytest.raises(S.SceneSubmitError):
+        ctx.set_key_layout(1, 1, 1)
+    ctx.close()

@@ -108,6 +108,7 @@ struct ss_ctx {
     bool world_valid = false;  // d_world holds the rows of a finished transform stage (SS_FRAME_REUSE_WORLD)
     bool sort_valid = false;   // the sort buffers hold the order of the current static streams (SS_FRAME_REUSE_SORT)
     uint32_t node_base = 0;
+    uint32_t max_material_rank = 0;  // over the instance stream (ss_set_key_layout re-checks it)
     uint32_t mesh_bits = 22, submesh_bits = 16, material_bits = 24;
     std::vector<ss_submesh> host_table;
     uint32_t max_draws = 0;
@@ -196,6 +197,15 @@ void planes_from_view_proj(const float* vp, ViewPlanes& out)
         // compare as values: -0.0f == 0.0f is fine here, the negation of either zero gives an equal product
         if (b[0] == -a[0] && b[1] == -a[1] && b[2] == -a[2]) out.flags |= 1u << ax;
     }
+}
+
+// Implicit node map (instance i sits on node node_base + i) under a parent chain: ss_frame composes the levels ABOVE
+// node_base with k_node_level and the instance kernel composes the instances' own level from world[parent], so every
+// instance node must belong to the last level.  Without parents every node is a root and any range is fine.
+bool implicit_nodes_in_last_level(const ss_ctx* c, uint32_t node_base, uint32_t n)
+{
+    if (!c->has_parent || c->n_levels == 0) return true;
+    return node_base >= c->level_offsets[c->n_levels - 1] && (uint64_t)node_base + n <= c->level_offsets[c->n_levels];
 }
 
 }  // namespace
@@ -359,6 +369,14 @@ SS_API ss_status ss_set_key_layout(ss_ctx* c, uint32_t mesh_bits, uint32_t subme
     if (mesh_bits == 0 || submesh_bits == 0 || material_bits == 0 || material_bits > 31 ||
         mesh_bits + submesh_bits + material_bits > 62)
         return c->fail(SS_ERR_INVALID, "ss_set_key_layout: widths must be >= 1, material <= 31, sum <= 62");
+    // streams set under the old layout must still fit the new one, or key fields would overlap
+    for (uint32_t i = 0; i < c->n_slots; ++i)
+        if (c->host_table[i].mesh_rank >> mesh_bits || c->host_table[i].submesh_index >> submesh_bits)
+            return c->fail(SS_ERR_INVALID, "ss_set_key_layout: submesh table row %u does not fit %u/%u bits", i, mesh_bits,
+                           submesh_bits);
+    if (c->n_instances && (c->max_material_rank >> material_bits))
+        return c->fail(SS_ERR_INVALID, "ss_set_key_layout: material rank %u of the instance stream does not fit %u bits",
+                       c->max_material_rank, material_bits);
     SS_CUDA(c, cudaSetDevice(c->device));
     c->world_valid = c->sort_valid = false;
     c->mesh_bits = mesh_bits;
@@ -437,7 +455,14 @@ SS_API ss_status ss_set_instances(ss_ctx* c, uint32_t n, const uint32_t* node, u
     if (!node && (uint64_t)node_base + n > c->n_nodes)
         return c->fail(SS_ERR_INVALID, "ss_set_instances: node_base %u + %u instances exceeds %u nodes", node_base, n,
                        c->n_nodes);
+    if (!node && n && !implicit_nodes_in_last_level(c, node_base, n))
+        return c->fail(SS_ERR_INVALID,
+                       "ss_set_instances: with node == NULL the nodes [%u, %u) must all lie in the last level [%u, %u) "
+                       "(only the levels above it are composed before the instance kernel); pass an explicit node map",
+                       node_base, node_base + n, c->level_offsets[c->n_levels - 1], c->level_offsets[c->n_levels]);
+    uint32_t max_rank = 0;
     for (uint32_t i = 0; i < n; ++i) {
+        max_rank = std::max(max_rank, material_word[i] & ~SS_MATERIAL_TESS_BIT);
         if (submesh_slot[i] != SS_SLOT_NULL && submesh_slot[i] >= c->n_slots)
             return c->fail(SS_ERR_INVALID, "ss_set_instances: instance %u names submesh slot %u of %u", i,
                            submesh_slot[i], c->n_slots);
@@ -448,6 +473,7 @@ SS_API ss_status ss_set_instances(ss_ctx* c, uint32_t n, const uint32_t* node, u
     }
     SS_CUDA(c, cudaSetDevice(c->device));
     c->n_instances = n;
+    c->max_material_rank = max_rank;
     c->has_node_map = node != nullptr;
     c->node_base = node ? 0 : node_base;
     c->has_inst_aabb = false;
@@ -577,9 +603,11 @@ SS_API ss_status ss_upload_node_world_rows(ss_ctx* c, uint32_t first, uint32_t c
         return c->fail(SS_ERR_INVALID, "ss_upload_node_world_rows: range [%u, +%u) must lie in the external nodes [%u, %u)",
                        first, count, computed, c->n_nodes);
     SS_CUDA(c, cudaSetDevice(c->device));
-    if (count)
+    if (count) {
+        c->world_valid = false;  // instances on these nodes move: SS_FRAME_REUSE_WORLD must not keep their old rows
         SS_CUDA(c, cudaMemcpyAsync(c->d_node_world + (size_t)first * 3, rows12, (size_t)count * 48, cudaMemcpyHostToDevice,
                                    c->stream));
+    }
     return SS_OK;
 }
 
@@ -614,6 +642,8 @@ SS_API ss_status ss_frame(ss_ctx* c, const ss_view* views, uint32_t n_views, uin
     if (c->n_slots == 0 || c->n_nodes == 0) return c->fail(SS_ERR_STATE, "ss_frame: submesh table / nodes not set");
     if ((flags & SS_FRAME_WORLD_ROWS_GIVEN) && !c->world_uploaded)
         return c->fail(SS_ERR_STATE, "ss_frame: SS_FRAME_WORLD_ROWS_GIVEN without ss_upload_world_rows");
+    if (!c->has_node_map && c->n_instances && !implicit_nodes_in_last_level(c, c->node_base, c->n_instances))
+        return c->fail(SS_ERR_STATE, "ss_frame: ss_set_nodes changed the levels under an implicit node map; call ss_set_instances again");
     // world rows already on the device: uploaded for stage-wise parity, or kept from the previous frame
     const bool world_given = (flags & SS_FRAME_WORLD_ROWS_GIVEN) || ((flags & SS_FRAME_REUSE_WORLD) && c->world_valid);
     const bool reuse_sort = (flags & SS_FRAME_REUSE_SORT) && c->sort_valid;

@@ -11,6 +11,8 @@
 //   - runs of equal keys become draws: per (view, run) visible counts are accumulated with one
 //     atomic per run per tile, and k_draws turns them into VkDrawIndexedIndirectCommand records
 //     (field meanings: Platform/Vulkan/VulkanRenderer.cpp:628) in MeshKey order.
+#include <algorithm>
+
 #include "ss_kernels.h"
 
 namespace ss {
@@ -392,6 +394,9 @@ __global__ void __launch_bounds__(kDrawThreads) k_draws(const __grid_constant__ 
         a.host_stats[a.stats_views * 2] = *a.overflow | over;
         a.host_stats[a.stats_views * 2 + 1] = *a.passes_run;
     }
+    // rows of views this frame does not use are cleaned all the same: the frame that filled the other buffer may
+    // have run more views than this one (ss_frame takes any n_views up to max_views)
+    if (v >= a.n_views) return;
     if (c0 >= n_segs && blockIdx.x != 0) return;
 
     // counts and draws of the chunks before this one
@@ -592,7 +597,9 @@ void launch_emit(const EmitArgs& a, cudaStream_t st)
 
 void launch_draws(const DrawArgs& a, cudaStream_t st)
 {
-    if (a.n_views) k_draws<<<dim3((a.max_draws + kDrawChunk - 1) / kDrawChunk, a.n_views), kDrawThreads, 0, st>>>(a);
+    // grid.y covers every view row of the double-buffered run counters (stats_views = max_views), not only this frame's
+    if (a.n_views)
+        k_draws<<<dim3((a.max_draws + kDrawChunk - 1) / kDrawChunk, std::max(a.n_views, a.stats_views)), kDrawThreads, 0, st>>>(a);
 }
 
 void launch_merge_place(const int32_t* lists, const int64_t* seg_out, const int64_t* seg_src, const int64_t* seg_add,

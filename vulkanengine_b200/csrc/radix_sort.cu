@@ -414,6 +414,15 @@ extern "C" SS_API ss_status ss_sort_pairs_static(void* cuda_stream, uint64_t* ke
         return SS_ERR_CAPACITY;
     }
     cudaStream_t st = static_cast<cudaStream_t>(cuda_stream);
+    // the scratch address is looked up for the CURRENT device: a stream of another device would make the kernels
+    // run where that address means nothing
+    if (st != nullptr) {
+        int cur = -1, owner = -1;
+        if (cudaGetDevice(&cur) == cudaSuccess && cudaStreamGetDevice(st, &owner) == cudaSuccess && owner != cur) {
+            ss::set_global_error("ss_sort_pairs_static: cuda_stream belongs to another device than the current one");
+            return SS_ERR_INVALID;
+        }
+    }
     void* scratch = nullptr;
     cudaError_t e = static_scratch_for_current_device(&scratch);
     // sort_pairs_async first clears the control block and the look-back words of the passes it will run

@@ -89,6 +89,9 @@ Prop read_prop(Cursor& c)
         const uint32_t count = c.get<uint32_t>(), enc = c.get<uint32_t>(), bytes = c.get<uint32_t>();
         if (c.pos + bytes > c.b.size()) throw std::runtime_error("fbx: truncated array");
         const size_t elem = p.type == 'f' || p.type == 'i' ? 4 : p.type == 'b' ? 1 : 8;
+        // the element count is a bare uint32 from the file: bound the allocation by what zlib can expand
+        // the stored bytes to (deflate tops out near 1032:1)
+        if (enc == 1 && (uint64_t)count * elem > (uint64_t)bytes * 1032 + 64) throw std::runtime_error("fbx: array count");
         std::vector<unsigned char> tmp;
         const unsigned char* data = &c.b[c.pos];
         if (enc == 1) {
@@ -120,6 +123,7 @@ bool wanted_array_owner(const std::string& name)
 
 bool read_rec(Cursor& c, Rec& out)
 {
+    const size_t rec_start = c.pos;
     const uint64_t end = c.word(), nprops = c.word(), plen = c.word();
     const uint8_t nlen = c.get<uint8_t>();
     if (c.pos + nlen > c.b.size()) throw std::runtime_error("fbx: truncated name");
@@ -127,6 +131,9 @@ bool read_rec(Cursor& c, Rec& out)
     c.pos += nlen;
     if (end == 0) return false;  // the all-zero record closing a list
     if (end > c.b.size()) throw std::runtime_error("fbx: record past end of file");
+    // offsets come from the file: a record must end after it starts and its properties must end inside it,
+    // or the parent's loop would walk backwards / past the record
+    if (end <= rec_start || plen > end - c.pos) throw std::runtime_error("fbx: record offsets out of order");
     const size_t props_end = c.pos + plen;
     const bool bulky = out.name.rfind("LayerElement", 0) != 0 && !wanted_array_owner(out.name) &&
                        (out.name == "Normals" || out.name == "UV" || out.name == "UVIndex" || out.name == "NormalsW" ||
