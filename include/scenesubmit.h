@@ -75,8 +75,10 @@ typedef enum ss_frame_flags {
     /* stage-wise parity: do not run the transform stage, cull/sort/emit from the world rows given
        to ss_upload_world_rows */
     SS_FRAME_WORLD_ROWS_GIVEN = 1,
-    /* reserved */
-    SS_FRAME_NO_GRAPH = 2,
+    /* the frame does not write the per-instance world rows and visibility bytes (ss_outputs.world_rows / masks,
+       ss_download_world / ss_download_masks): a host that only consumes the per-view lists saves their traffic
+       (49 B per instance).  Honoured by the fused pipeline; the three-kernel pipeline needs the rows itself. */
+    SS_FRAME_NO_WORLD_ROWS = 2,
     /* Batched multi-view work (many cameras over one scene, BASELINE configs[4]): views are processed
        SS_MAX_VIEWS at a time, one ss_frame per batch.  After a first, full frame the transforms have not
        changed, so later batches may keep the world rows of the previous frame (cull + emit only) ... */
@@ -85,6 +87,27 @@ typedef enum ss_frame_flags {
        (the stage runs) when no valid result of a previous frame exists. */
     SS_FRAME_REUSE_SORT = 8
 } ss_frame_flags;
+
+/* ss_config.flags */
+typedef enum ss_config_flags {
+    SS_CONFIG_DEFAULT = 0,
+    /* always run the three-kernel pipeline (transform+cull -> sort -> compact+gather) instead of the fused kernel;
+       for A/B measurements and parity tests of both */
+    SS_CONFIG_LEGACY_PIPELINE = 1,
+    /* Draw-order-resident layout.  The sort keys are static between ss_set_* calls (in the reference the std::map nodes
+       persist across frames too, VC/Scene/SceneRenderer.cpp:1559-1591), so the library sorts ONCE when a static stream
+       changes and keeps its instance records in (key, instance) order; a frame is then one streaming pass with no
+       sort and no gather.  Transform uploads are re-ordered into the records on the device.  Results are the same
+       lists, bit for bit. */
+    SS_CONFIG_DRAW_ORDER_RESIDENT = 2
+} ss_config_flags;
+
+/* which kernels produced a frame (ss_frame_stats.pipeline) */
+typedef enum ss_pipeline {
+    SS_PIPELINE_LEGACY = 0,         /* k_instances -> sort -> k_emit: explicit node maps, libm trig, given world rows, wide keys */
+    SS_PIPELINE_FUSED = 1,          /* key words -> sort -> k_submit (records gathered in draw order) */
+    SS_PIPELINE_FUSED_RESIDENT = 2  /* k_submit streaming draw-order-resident records */
+} ss_pipeline;
 
 typedef struct ss_ctx ss_ctx;
 
@@ -99,7 +122,7 @@ typedef struct ss_config {
     uint32_t frames_in_flight;     /* output slots; 0 = 3 (VC/Renderer/Renderer.h:28) */
     uint64_t max_visible_per_view; /* compacted list capacity per view; 0 = max_instances */
     uint32_t trig_mode;            /* ss_trig_mode */
-    uint32_t flags;                /* reserved, 0 */
+    uint32_t flags;                /* ss_config_flags */
 } ss_config;
 
 /* One row of the global submesh table: the per-frame facts SubmitMesh reads from Submesh
@@ -139,11 +162,19 @@ typedef struct ss_outputs {
     const ss_draw_cmd* draws;     /* [draws]        one per run of equal keys, in MeshKey order */
     const uint64_t* draw_keys;    /* [draws]        key of each draw (to bind mesh + material) */
     const uint32_t* counts;       /* device: {visible, draws} of this view */
-    const float* world_rows;      /* [instances][16] every instance's world matrix, row-major 4x4 (rows 0..2 =
-                                     TransformData, row 3 = 0,0,0,1), 64 B stride; not per view */
-    const uint8_t* masks;         /* [instances]    bit v = visible in view v */
+    /* Every instance's world rows and visibility byte.  NOT per slot: they belong to the most recent ss_frame of the
+       context and are overwritten by the next one (the per-view lists above are what stays valid per slot).
+       Three-kernel pipeline: entry i = instance i, world_stride = 16 floats (row-major 4x4, row 3 = 0,0,0,1).
+       Fused pipeline: entry j = the instance named by world_words[j] & ((1 << world_idx_bits) - 1), i.e. the arrays
+       lie in (key, instance) order, world_stride = 12 floats (TransformData); NULL after SS_FRAME_NO_WORLD_ROWS.
+       ss_download_world / ss_download_masks return instance order either way. */
+    const float* world_rows;
+    const uint8_t* masks;         /* bit v = visible in view v */
     uint32_t visible;             /* host copies, valid after ss_frame_sync */
     uint32_t n_draws;
+    const uint64_t* world_words;  /* fused pipeline: [instances] sorted words [key | instance]; NULL otherwise */
+    uint32_t world_idx_bits;
+    uint32_t world_stride;        /* floats per entry of world_rows */
 } ss_outputs;
 
 typedef struct ss_frame_stats {
@@ -155,6 +186,7 @@ typedef struct ss_frame_stats {
     uint32_t overflow;              /* non-zero: a list hit its capacity (results truncated) */
     float gpu_ms;                   /* CUDA-event time of the frame on the context stream */
     uint32_t kernel_launches;       /* kernels of this library launched for the frame */
+    uint32_t pipeline;              /* ss_pipeline */
 } ss_frame_stats;
 
 /* ---- lifecycle ------------------------------------------------------------------------------ */
@@ -247,7 +279,8 @@ SS_API ss_status ss_frame(ss_ctx* ctx, const ss_view* views, uint32_t n_views, u
 SS_API ss_status ss_frame_sync(ss_ctx* ctx, uint32_t slot, ss_frame_stats* stats_out);
 
 /* Device time of the slot's frame by stage, CUDA events on the context stream:
-   {clear + hierarchy levels, transform+cull+key, sort, compact+emit, draws + count read-back}.
+   {clear + hierarchy levels, transform+cull+key, sort, compact+emit, draws + count read-back}; for the fused
+   pipeline {clear + hierarchy levels + record refresh, key words, sort, fused transform+cull+compact+emit, draws}.
    The counterpart of the reference's per-pass timestamp queries
    (PV/VulkanRenderCommandBuffer.cpp:150-172). */
 SS_API ss_status ss_frame_stage_ms(ss_ctx* ctx, uint32_t slot, float ms_out[5]);

@@ -17,13 +17,27 @@ def oracle_views(n_views=5, **kw):
     return synth.make_views(lambda *a: O.camera_view_proj(*a), lambda *a: O.cascade_matrices(*a), n_views, **kw)
 
 
-def run_gpu(sc, views, trig_mode=S.TRIG_DETERMINISTIC, flags=0, world=None, **cfg):
-    ctx = S.SceneSubmit(sc.n_nodes, max(sc.n_instances, 1), len(sc.slots), max_views=len(views), trig_mode=trig_mode, **cfg)
+# the three pipelines a frame can take (ss_config.flags): fused kernel over gathered records (default where the
+# scene is eligible), the three-kernel pipeline, the fused kernel over draw-order-resident records
+PIPELINES = [pytest.param(0, id="fused"), pytest.param(S.CONFIG_LEGACY_PIPELINE, id="legacy"),
+             pytest.param(S.CONFIG_DRAW_ORDER_RESIDENT, id="resident")]
+EXPECT_PIPELINE = {0: S.PIPELINE_FUSED, S.CONFIG_LEGACY_PIPELINE: S.PIPELINE_LEGACY,
+                   S.CONFIG_DRAW_ORDER_RESIDENT: S.PIPELINE_FUSED_RESIDENT}
+
+
+def run_gpu(sc, views, trig_mode=S.TRIG_DETERMINISTIC, flags=0, world=None, pipe=None, **cfg):
+    """One frame through the C ABI.  pipe: ss_config.flags choosing the pipeline (None: the library's default, or
+    SS_CONFIG_FLAGS from the environment); where given, the frame must really have taken that pipeline."""
+    expect_pipeline = None if pipe is None else EXPECT_PIPELINE[pipe]
+    ctx = S.SceneSubmit(sc.n_nodes, max(sc.n_instances, 1), len(sc.slots), max_views=len(views), trig_mode=trig_mode,
+                        flags=pipe, **cfg)
     ctx.load_scene(sc)
     if world is not None:
         ctx.upload_world_rows(world)
     slot = ctx.frame(views, flags)
     st = ctx.frame_sync(slot)
+    if expect_pipeline is not None and sc.n_instances:
+        assert int(st.pipeline) == expect_pipeline, f"frame took pipeline {int(st.pipeline)}, expected {expect_pipeline}"
     out = {"stats": st, "world": ctx.download_world(), "masks": ctx.download_masks(),
            "views": [ctx.download_view(slot, v, st) for v in range(len(views))]}
     ctx.close()
@@ -49,12 +63,13 @@ def check_against_oracle(sc, views, got, ref, exact_rows=True):
         assert np.array_equal(g["draw_keys"], r["draw_keys"]), f"view {v}: draw keys"
 
 
+@pytest.mark.parametrize("pipe", PIPELINES)
 @pytest.mark.parametrize("n", [1, 31, 256, 257, 4096, 4097, 100_003])
-def test_flat_bit_exact(n):
+def test_flat_bit_exact(n, pipe):
     sc = synth.flat_scene(n, n_keys=512)
     views = oracle_views(5)
     ref = O.OracleScene(sc, 0).frame(views)
-    got = run_gpu(sc, views)
+    got = run_gpu(sc, views, pipe=pipe)
     check_against_oracle(sc, views, got, ref)
 
 
@@ -80,19 +95,21 @@ def test_stagewise_cull_bit_exact_on_oracle_matrices():
     check_against_oracle(sc, views, got, ref)
 
 
-def test_hierarchy_three_levels():
+@pytest.mark.parametrize("pipe", PIPELINES)
+def test_hierarchy_three_levels(pipe):
     sc = synth.hierarchy_scene(n_roots=16, fan1=8, fan2=32, n_keys=200)
     views = oracle_views(1)
     ref = O.OracleScene(sc, 0).frame(views)
-    got = run_gpu(sc, views)
+    got = run_gpu(sc, views, pipe=pipe)
     check_against_oracle(sc, views, got, ref)
 
 
-def test_hierarchy_mixed_parents_in_warp():
+@pytest.mark.parametrize("pipe", PIPELINES)
+def test_hierarchy_mixed_parents_in_warp(pipe):
     sc = synth.hierarchy_scene(n_roots=7, fan1=3, fan2=5, n_keys=64)
     views = oracle_views(5)
     ref = O.OracleScene(sc, 0).frame(views)
-    got = run_gpu(sc, views)
+    got = run_gpu(sc, views, pipe=pipe)
     check_against_oracle(sc, views, got, ref)
 
 
@@ -104,29 +121,32 @@ def test_explicit_node_map():
     check_against_oracle(sc, views, got, ref)
 
 
-def test_submesh_table_boxes():
+@pytest.mark.parametrize("pipe", PIPELINES)
+def test_submesh_table_boxes(pipe):
     sc = synth.flat_scene(5000, n_keys=128)
     sc.inst_aabb = None
     views = oracle_views(5)
     ref = O.OracleScene(sc, 0).frame(views)
-    got = run_gpu(sc, views)
+    got = run_gpu(sc, views, pipe=pipe)
     check_against_oracle(sc, views, got, ref)
 
 
-def test_all_dropped_and_single_key():
+@pytest.mark.parametrize("pipe", PIPELINES)
+def test_all_dropped_and_single_key(pipe):
     sc = synth.flat_scene(3000, n_keys=1)
     views = oracle_views(2)
     ref = O.OracleScene(sc, 0).frame(views)
-    got = run_gpu(sc, views)
+    got = run_gpu(sc, views, pipe=pipe)
     check_against_oracle(sc, views, got, ref)
     sc.slot[:] = synth.SLOT_NULL
     ref = O.OracleScene(sc, 0).frame(views)
-    got = run_gpu(sc, views)
+    got = run_gpu(sc, views, pipe=pipe)
     assert got["masks"].sum() == 0 and all(int(got["stats"].visible[v]) == 0 for v in range(2))
     assert all(int(got["stats"].draws[v]) == 0 for v in range(2))
 
 
-def test_every_key_distinct():
+@pytest.mark.parametrize("pipe", PIPELINES)
+def test_every_key_distinct(pipe):
     """Worst case for run bookkeeping: as many draws as instances."""
     n = 3000
     sc = synth.flat_scene(n, n_keys=4096)
@@ -135,7 +155,7 @@ def test_every_key_distinct():
     sc.slot = (np.arange(n, dtype=np.uint32) // 4096 % len(sc.slots)).astype(np.uint32)
     views = oracle_views(5)
     ref = O.OracleScene(sc, 0).frame(views)
-    got = run_gpu(sc, views)
+    got = run_gpu(sc, views, pipe=pipe)
     check_against_oracle(sc, views, got, ref)
 
 
@@ -238,33 +258,36 @@ def test_gpu_matches_reference_submission_pass(name):
     G.check_lists_against_ref_pass(sc, ref, v["idx"], v["keys"], v["rows"], v["draws"], v["draw_keys"])
 
 
-def test_full_size_16m_properties_and_mask_parity():
+_FULL_REF = {}
+
+
+@pytest.mark.parametrize("pipe", PIPELINES)
+def test_full_size_16m_properties_and_mask_parity(pipe):
     """configs[2] at full size: masks + world rows bit-exact against the oracle (threaded), and the
     size-independent properties of the lists: sorted by (key, instance), exactly the visible set,
     rows gathered from the world rows, draws partition the list."""
     n = 1 << 24
     sc = synth.flat_scene(n)
     views = oracle_views(5)
-    ctx = S.SceneSubmit(sc.n_nodes, n, len(sc.slots), max_views=5, max_draws_per_view=1 << 16)
+    ctx = S.SceneSubmit(sc.n_nodes, n, len(sc.slots), max_views=5, max_draws_per_view=1 << 16, flags=pipe)
     ctx.load_scene(sc)
     slot = ctx.frame(views)
     st = ctx.frame_sync(slot)
+    assert int(st.pipeline) == EXPECT_PIPELINE[pipe]
     masks = ctx.download_masks()
-    osc = O.OracleScene(sc, 0)
-    import ctypes as C
-    rows = np.empty((n, 12), np.float32)
-    omask = np.empty(n, np.uint8)
-    okeys = np.empty(n, np.uint64)
-    # oracle per-instance stages only (the per-view lists at 16M x 5 would need ~7 GB of host memory)
-    nw = osc.node_worlds()
-    O.lib().sso_instance_rows(C.byref(osc.s), nw.ctypes.data_as(C.c_void_p), rows.ctypes.data_as(C.c_void_p))
-    del nw
-    omask = osc.cull(rows, views)
-    okeys = osc.keys()
+    if "rows" not in _FULL_REF:  # one oracle run serves the three pipelines
+        osc = O.OracleScene(sc, 0)
+        import ctypes as C
+        rows = np.empty((n, 12), np.float32)
+        # oracle per-instance stages only (the per-view lists at 16M x 5 would need ~7 GB of host memory)
+        nw = osc.node_worlds()
+        O.lib().sso_instance_rows(C.byref(osc.s), nw.ctypes.data_as(C.c_void_p), rows.ctypes.data_as(C.c_void_p))
+        del nw
+        _FULL_REF.update(rows=rows, omask=osc.cull(rows, views), okeys=osc.keys())
+    rows, omask, okeys = _FULL_REF["rows"], _FULL_REF["omask"], _FULL_REF["okeys"]
     assert np.array_equal(masks, omask)
     world = ctx.download_world()
     assert np.array_equal(world, rows)
-    del rows
     for v in range(5):
         got = ctx.download_view(slot, v, st)
         vis = np.flatnonzero((masks >> v) & 1).astype(np.uint32)
@@ -358,12 +381,22 @@ def test_batched_views_reuse_world_and_sort():
     ctx.close()
 
 
-def test_config2_full_size_hierarchy_1m():
+_CFG2_REF = {}
+
+
+def _cfg2_reference(sc, views):
+    if "ref" not in _CFG2_REF:  # one oracle run serves the three pipelines
+        _CFG2_REF["ref"] = O.OracleScene(sc, 0).frame(views, threads=8)
+    return _CFG2_REF["ref"]
+
+
+@pytest.mark.parametrize("pipe", PIPELINES)
+def test_config2_full_size_hierarchy_1m(pipe):
     """configs[1]: 2^20 leaves under a 3-level hierarchy, one camera: bit-exact against the oracle."""
     sc = synth.hierarchy_scene()
     views = oracle_views(1)
-    ref = O.OracleScene(sc, 0).frame(views, threads=8)
-    got = run_gpu(sc, views, max_draws_per_view=1 << 16)
+    ref = _cfg2_reference(sc, views)
+    got = run_gpu(sc, views, pipe=pipe, max_draws_per_view=1 << 16)
     check_against_oracle(sc, views, got, ref)
 
 
@@ -491,7 +524,9 @@ def test_randomised_configurations(case):
             views["flags"][::2] = synth.VIEW_SKIP_NEAR
     osc = O.OracleScene(sc, 0)
     ref = osc.frame(views)
-    ctx = S.SceneSubmit(sc.n_nodes, sc.n_instances, len(sc.slots), max_views=n_views, frames_in_flight=int(rng.integers(1, 4)))
+    pipe = [0, S.CONFIG_LEGACY_PIPELINE, S.CONFIG_DRAW_ORDER_RESIDENT][(case // 3) % 3]
+    ctx = S.SceneSubmit(sc.n_nodes, sc.n_instances, len(sc.slots), max_views=n_views, frames_in_flight=int(rng.integers(1, 4)),
+                        flags=pipe)
     ctx.load_scene(sc)
     slots = [ctx.frame(views) for _ in range(int(rng.integers(1, 4)))]
     if rng.random() < 0.5:

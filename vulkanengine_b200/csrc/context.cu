@@ -29,6 +29,10 @@ struct Slot {
     uint32_t n_views = 0, n_instances = 0;
     int launches = 0;
     ss_view views[SS_MAX_VIEWS];      // as given to ss_frame (ss_raster_view projects with them)
+    int pipeline = 0;                 // ss_pipeline that produced the slot
+    const uint64_t* words_known = nullptr;  // fused pipeline: the sorted words, when the host knows the buffer
+    uint32_t idx_bits = 0;
+    bool world_rows = true;
     // pinned host mirror
     uint32_t* h_counts = nullptr;     // [max_views][2] + overflow + passes_run: mapped pinned, written by k_draws
     uint32_t* h_counts_dev = nullptr; // the same words as the device sees them
@@ -97,6 +101,21 @@ struct ss_ctx {
     uint32_t seg_parity = 0;
     uint64_t* d_seg_key = nullptr;
     uint32_t* d_seg_inst = nullptr;
+
+    // fused pipeline (submit.cu): one 64 B record per instance, sorted words, their inverse for the resident layout
+    InstRec* d_rec = nullptr;
+    int32_t* d_parent_rec = nullptr;       // resident layout: parent of record r
+    uint32_t* d_pos = nullptr;             // resident layout: pos[instance] = record
+    uint32_t* d_sub_lookback = nullptr;
+    bool rec_static_dirty = true;          // box / slot / order of the records is stale: rebuild them whole
+    uint32_t rec_trs_lo = 0, rec_trs_hi = 0;  // instance range whose TRS changed since the records were built (lo >= hi: none)
+    bool words_valid = false;              // the sort buffers hold the sorted words of the current static streams
+    bool resident_valid = false;           // the records lie in draw order (SS_CONFIG_DRAW_ORDER_RESIDENT)
+    const uint64_t* d_words_resident = nullptr;
+    uint32_t words_idx_bits = 0;
+    int last_pipeline = 0;                 // ss_pipeline of the most recent frame
+    bool last_world_rows = true;           // ... and whether it wrote world rows / masks
+    bool nodes_valid = false;              // d_node_world holds the parent levels of the current transforms
 
     std::vector<Slot> slots;
     uint64_t frame_no = 0;
@@ -202,6 +221,29 @@ void planes_from_view_proj(const float* vp, ViewPlanes& out)
 // Implicit node map (instance i sits on node node_base + i) under a parent chain: ss_frame composes the levels ABOVE
 // node_base with k_node_level and the instance kernel composes the instances' own level from world[parent], so every
 // instance node must belong to the last level.  Without parents every node is a root and any range is fine.
+// a static stream changed: kept world rows, sorted orders and instance records are all stale
+void invalidate_static(ss_ctx* c)
+{
+    c->world_valid = c->sort_valid = c->nodes_valid = false;
+    c->words_valid = c->resident_valid = false;
+    c->rec_static_dirty = true;
+}
+
+// TRS of nodes [first, first + count) changed: the records of the instances on them must be refreshed
+void mark_trs_dirty(ss_ctx* c, uint64_t first, uint64_t count)
+{
+    const uint64_t nb = c->node_base, n = c->n_instances;
+    const uint64_t lo = first > nb ? first - nb : 0, hi = std::min<uint64_t>(first + count > nb ? first + count - nb : 0, n);
+    if (lo >= hi) return;
+    if (c->rec_trs_lo >= c->rec_trs_hi) {
+        c->rec_trs_lo = (uint32_t)lo;
+        c->rec_trs_hi = (uint32_t)hi;
+    } else {
+        c->rec_trs_lo = std::min<uint32_t>(c->rec_trs_lo, (uint32_t)lo);
+        c->rec_trs_hi = std::max<uint32_t>(c->rec_trs_hi, (uint32_t)hi);
+    }
+}
+
 bool implicit_nodes_in_last_level(const ss_ctx* c, uint32_t node_base, uint32_t n)
 {
     if (!c->has_parent || c->n_levels == 0) return true;
@@ -257,8 +299,9 @@ SS_API ss_status ss_create(const ss_config* cfg, ss_ctx** out)
     *out = nullptr;
     if (cfg->struct_size != sizeof(ss_config) || cfg->max_views < 1 || cfg->max_views > SS_MAX_VIEWS ||
         cfg->max_instances == 0 || cfg->max_nodes == 0 || cfg->max_submesh_slots == 0 ||
-        cfg->max_instances >= (1u << 30) || cfg->trig_mode > SS_TRIG_LIBM) {
-        g_create_error = "ss_create: invalid ss_config (struct_size, capacities 1..2^30-1, max_views 1..8, trig_mode)";
+        cfg->max_instances >= (1u << 30) || cfg->trig_mode > SS_TRIG_LIBM ||
+        (cfg->flags & ~(uint32_t)(SS_CONFIG_LEGACY_PIPELINE | SS_CONFIG_DRAW_ORDER_RESIDENT))) {
+        g_create_error = "ss_create: invalid ss_config (struct_size, capacities 1..2^30-1, max_views 1..8, trig_mode, flags)";
         return SS_ERR_INVALID;
     }
     int n_dev = 0;
@@ -307,7 +350,7 @@ SS_API ss_status ss_create(const ss_config* cfg, ss_ctx** out)
     TRY(dev_alloc(c, &c->d_trs_buf[0], NN * 9));
     TRY(dev_alloc(c, &c->d_trs_buf[1], NN * 9));
     c->d_trs = c->d_trs_buf[0];
-    TRY(dev_alloc(c, &c->d_parent, NN));
+    TRY(dev_alloc(c, &c->d_parent, NN + kSubPad));
     TRY(dev_alloc(c, &c->d_node_world, NN * 3));
     TRY(dev_alloc(c, &c->d_node, N));
     TRY(dev_alloc(c, &c->d_slot, N));
@@ -316,16 +359,22 @@ SS_API ss_status ss_create(const ss_config* cfg, ss_ctx** out)
     TRY(dev_alloc(c, &c->d_slots, (size_t)cfg->max_submesh_slots));
     TRY(dev_alloc(c, &c->d_world, N * kWorldStride));
     TRY(dev_alloc(c, &c->d_mask, N));
-    TRY(dev_alloc(c, &c->d_keys_a, N));
-    TRY(dev_alloc(c, &c->d_keys_b, N));
+    TRY(dev_alloc(c, &c->d_keys_a, N + kSubPad));  // padded: the fused kernel copies whole tiles
+    TRY(dev_alloc(c, &c->d_keys_b, N + kSubPad));
+    TRY(dev_alloc(c, &c->d_rec, N + kSubPad));
+    if (cfg->flags & SS_CONFIG_DRAW_ORDER_RESIDENT) {
+        TRY(dev_alloc(c, &c->d_parent_rec, N + kSubPad));
+        TRY(dev_alloc(c, &c->d_pos, N));
+    }
     TRY(dev_alloc(c, &c->d_vals_a, N));
     TRY(dev_alloc(c, &c->d_vals_b, N));
     TRY(dev_alloc(c, reinterpret_cast<unsigned char**>(&c->d_sort_scratch), sort_scratch_bytes(N)));
 
-    const size_t lb_bytes = (emit_lookback_bytes(N) + 255) & ~size_t(255);
+    const size_t lb_bytes = (std::max(emit_lookback_bytes(N), submit_lookback_bytes(N)) + 255) & ~size_t(255);
     c->emit_zero_bytes = lb_bytes + 256;
     TRY(dev_alloc(c, &c->d_emit_zero, c->emit_zero_bytes));
     c->d_lookback = reinterpret_cast<uint32_t*>(c->d_emit_zero);
+    c->d_sub_lookback = c->d_lookback;  // the two pipelines never run in the same frame
     c->d_ticket = reinterpret_cast<uint32_t*>(c->d_emit_zero + lb_bytes);
     c->d_totals = c->d_ticket + 16;
     c->d_overflow = c->d_ticket + 32;
@@ -378,7 +427,7 @@ SS_API ss_status ss_set_key_layout(ss_ctx* c, uint32_t mesh_bits, uint32_t subme
         return c->fail(SS_ERR_INVALID, "ss_set_key_layout: material rank %u of the instance stream does not fit %u bits",
                        c->max_material_rank, material_bits);
     SS_CUDA(c, cudaSetDevice(c->device));
-    c->world_valid = c->sort_valid = false;
+    invalidate_static(c);
     c->mesh_bits = mesh_bits;
     c->submesh_bits = submesh_bits;
     c->material_bits = material_bits;
@@ -398,7 +447,7 @@ SS_API ss_status ss_set_submesh_table(ss_ctx* c, const ss_submesh* table, uint32
             return c->fail(SS_ERR_INVALID, "ss_set_submesh_table: row %u rank/index exceeds the key layout", i);
     }
     SS_CUDA(c, cudaSetDevice(c->device));
-    c->world_valid = c->sort_valid = false;
+    invalidate_static(c);
     c->host_table.assign(table, table + count);
     c->n_slots = count;
     return upload_table(c);
@@ -435,7 +484,7 @@ SS_API ss_status ss_set_nodes(ss_ctx* c, uint32_t n_nodes, const int32_t* parent
         c->n_levels = 1;
     }
     SS_CUDA(c, cudaSetDevice(c->device));
-    c->world_valid = c->sort_valid = false;
+    invalidate_static(c);
     c->n_nodes = n_nodes;
     c->has_parent = parent != nullptr;
     if (parent) {
@@ -478,7 +527,7 @@ SS_API ss_status ss_set_instances(ss_ctx* c, uint32_t n, const uint32_t* node, u
     c->node_base = node ? 0 : node_base;
     c->has_inst_aabb = false;
     c->world_uploaded = false;
-    c->world_valid = c->sort_valid = false;
+    invalidate_static(c);
     if (n) {
         if (node) SS_CUDA(c, cudaMemcpyAsync(c->d_node, node, (size_t)n * 4, cudaMemcpyHostToDevice, c->stream));
         SS_CUDA(c, cudaMemcpyAsync(c->d_slot, submesh_slot, (size_t)n * 4, cudaMemcpyHostToDevice, c->stream));
@@ -491,6 +540,7 @@ SS_API ss_status ss_set_instances(ss_ctx* c, uint32_t n, const uint32_t* node, u
 SS_API ss_status ss_set_instance_aabbs(ss_ctx* c, uint32_t first, uint32_t count, const float* minmax6)
 {
     if (!c) return SS_ERR_INVALID;
+    c->rec_static_dirty = true;  // the records carry the boxes
     if (!minmax6) {
         c->has_inst_aabb = false;
         return SS_OK;
@@ -533,7 +583,8 @@ SS_API ss_status ss_upload_trs(ss_ctx* c, uint32_t first, uint32_t count, const 
         return c->fail(SS_ERR_INVALID, "ss_upload_trs: range [%u, +%u) exceeds %u nodes", first, count, c->n_nodes);
     SS_CUDA(c, cudaSetDevice(c->device));
     if (!count) return SS_OK;
-    c->world_valid = false;  // transforms changed
+    c->world_valid = c->nodes_valid = false;  // transforms changed
+    mark_trs_dirty(c, first, count);
     if (first == 0 && count == c->n_nodes && count >= kAsyncUploadMinNodes) {
         const int tgt = c->trs_cur ^ 1;
         SS_CUDA(c, cudaStreamWaitEvent(c->upload_stream, c->ev_trs_read[tgt], 0));  // its last reader is past the transform stage
@@ -585,7 +636,15 @@ SS_API ss_status ss_upload_trs_sparse(ss_ctx* c, uint32_t count, const uint32_t*
         memcpy(hr + (size_t)j * 9, trs9 + (size_t)k * 9, 36);
         hi[j] = node_index[k];
     }
-    c->world_valid = false;  // transforms changed
+    c->world_valid = c->nodes_valid = false;  // transforms changed
+    {
+        uint32_t mn = 0xffffffffu, mx = 0;
+        for (uint32_t k = 0; k < count; ++k) {
+            mn = std::min(mn, node_index[k]);
+            mx = std::max(mx, node_index[k]);
+        }
+        mark_trs_dirty(c, mn, (uint64_t)mx - mn + 1);
+    }
     SS_CUDA(c, adopt_pending_upload(c));  // lands on top of whatever whole-stream upload came before it
     SS_CUDA(c, cudaMemcpyAsync(c->d_sparse, c->h_sparse, (size_t)kept * 40, cudaMemcpyHostToDevice, c->stream));
     SS_CUDA(c, cudaEventRecord(c->ev_sparse, c->stream));
@@ -604,7 +663,7 @@ SS_API ss_status ss_upload_node_world_rows(ss_ctx* c, uint32_t first, uint32_t c
                        first, count, computed, c->n_nodes);
     SS_CUDA(c, cudaSetDevice(c->device));
     if (count) {
-        c->world_valid = false;  // instances on these nodes move: SS_FRAME_REUSE_WORLD must not keep their old rows
+        c->world_valid = c->nodes_valid = false;  // instances on these nodes move: SS_FRAME_REUSE_WORLD must not keep their old rows
         SS_CUDA(c, cudaMemcpyAsync(c->d_node_world + (size_t)first * 3, rows12, (size_t)count * 48, cudaMemcpyHostToDevice,
                                    c->stream));
     }
@@ -644,9 +703,6 @@ SS_API ss_status ss_frame(ss_ctx* c, const ss_view* views, uint32_t n_views, uin
         return c->fail(SS_ERR_STATE, "ss_frame: SS_FRAME_WORLD_ROWS_GIVEN without ss_upload_world_rows");
     if (!c->has_node_map && c->n_instances && !implicit_nodes_in_last_level(c, c->node_base, c->n_instances))
         return c->fail(SS_ERR_STATE, "ss_frame: ss_set_nodes changed the levels under an implicit node map; call ss_set_instances again");
-    // world rows already on the device: uploaded for stage-wise parity, or kept from the previous frame
-    const bool world_given = (flags & SS_FRAME_WORLD_ROWS_GIVEN) || ((flags & SS_FRAME_REUSE_WORLD) && c->world_valid);
-    const bool reuse_sort = (flags & SS_FRAME_REUSE_SORT) && c->sort_valid;
     SS_CUDA(c, cudaSetDevice(c->device));
 
     const uint32_t si = (uint32_t)(c->frame_no % c->slots.size());
@@ -667,12 +723,30 @@ SS_API ss_status ss_frame(ss_ctx* c, const ss_view* views, uint32_t n_views, uin
         if (views[v].flags & SS_VIEW_SKIP_NEAR) cp.v[v].flags |= kViewSkipNear;
     }
 
+    // bits the key layout can set: material | submesh | mesh | tess | dropped.  When they fit next to the
+    // instance index in one 64-bit word, key and index are sorted as that single word (8 B/element/pass).
+    const uint32_t tess_shift = c->mesh_bits + c->submesh_bits + c->material_bits;
+    const int key_bits = (int)tess_shift + 2;
+    int idx_bits = 1;
+    while (idx_bits < 32 && (1ull << idx_bits) < (uint64_t)n) ++idx_bits;
+    const bool packed = idx_bits + key_bits <= 64;
+
+    // Which pipeline.  The fused kernel (submit.cu) serves TRS-driven instances with an implicit node map and
+    // deterministic trig whose key and index share a word; everything else takes the three-kernel pipeline.
+    const bool fused = !(c->cfg.flags & SS_CONFIG_LEGACY_PIPELINE) && !c->has_node_map &&
+                       c->cfg.trig_mode == SS_TRIG_DETERMINISTIC && !(flags & SS_FRAME_WORLD_ROWS_GIVEN) && n > 0 && packed;
+    const bool resident = fused && (c->cfg.flags & SS_CONFIG_DRAW_ORDER_RESIDENT);
+    // world rows already on the device: uploaded for stage-wise parity, or kept from the previous frame
+    const bool world_given = !fused && ((flags & SS_FRAME_WORLD_ROWS_GIVEN) || ((flags & SS_FRAME_REUSE_WORLD) && c->world_valid));
+    const bool nodes_kept = fused && (flags & SS_FRAME_REUSE_WORLD) && c->nodes_valid;  // node rows of the parent levels
+    const bool reuse_sort = !fused && (flags & SS_FRAME_REUSE_SORT) && c->sort_valid;
+
     SS_CUDA(c, adopt_pending_upload(c));
     SS_CUDA(c, cudaEventRecord(s.start, st));
     SS_CUDA(c, cudaMemsetAsync(c->d_emit_zero, 0, c->emit_zero_bytes, st));
 
     // N1: levels above the instances (all levels when an explicit instance->node map is in use)
-    if (!world_given && (c->has_parent || c->has_node_map)) {
+    if (!world_given && !nodes_kept && (c->has_parent || c->has_node_map)) {
         const uint32_t node_hi = c->has_node_map ? c->n_nodes : c->node_base;
         for (uint32_t l = 0; l < c->n_levels; ++l) {
             NodeLevelArgs na;
@@ -689,101 +763,237 @@ SS_API ss_status ss_frame(ss_ctx* c, const ss_view* views, uint32_t n_views, uin
         }
     }
 
-    SS_CUDA(c, cudaEventRecord(s.stage[0], st));
-
-    InstanceArgs ia;
-    ia.trs = c->d_trs;
-    ia.parent = c->has_parent ? c->d_parent : nullptr;
-    ia.node_world = c->d_node_world;
-    ia.node = c->has_node_map ? c->d_node : nullptr;
-    ia.node_base = c->node_base;
-    ia.slot = c->d_slot;
-    ia.matword = c->d_matword;
-    ia.inst_aabb = c->has_inst_aabb ? c->d_inst_aabb : nullptr;
-    ia.slots = c->d_slots;
-    ia.world = c->d_world;
-    ia.mask = c->d_mask;
-    ia.keys = c->d_keys_a;
-    ia.vals = c->d_vals_a;
-    ia.n = n;
-    ia.tess_shift = c->mesh_bits + c->submesh_bits + c->material_bits;
-    ia.world_given = world_given ? 1 : 0;
-    ia.trig_mode = (int)c->cfg.trig_mode;
-    // bits the layout can set: material | submesh | mesh | tess | dropped.  When they fit next to the
-    // instance index in one 64-bit word, key and index are sorted as that single word (8 B/element/pass).
-    const int key_bits = (int)ia.tess_shift + 2;
-    int idx_bits = 1;
-    while (idx_bits < 32 && (1ull << idx_bits) < (uint64_t)n) ++idx_bits;
-    const bool packed = idx_bits + key_bits <= 64;
-    ia.idx_bits = packed ? (uint32_t)idx_bits : 0u;
-    ia.mask_bits = (packed && idx_bits + key_bits + 8 <= 64) ? 8u : 0u;
-    // The sort's digit plan is known up front, so its scratch is cleared before the instance kernel runs and
-    // the fast path accumulates the digit histograms on the way (saves the sort's own pass over the keys).
-    const int begin_bit = packed ? idx_bits + (int)ia.mask_bits : 0, end_bit = begin_bit + key_bits;
-    const SortPlan plan = sort_plan(begin_bit, end_bit);
-    ia.hist = reinterpret_cast<SortControl*>(c->d_sort_scratch)->hist[0];
-    ia.hist_passes = plan.n_passes <= 3 ? plan.n_passes : 0;
-    for (int p = 0; p < 3; ++p) {
-        ia.hist_shift[p] = p < plan.n_passes ? plan.shift[p] - begin_bit : 0;
-        ia.hist_bits[p] = p < plan.n_passes ? plan.bits[p] : 0;
-    }
-    if (reuse_sort) {  // keep the previous frame's sorted order: no keys, no histograms, no sort
-        ia.keys = nullptr;
-        ia.vals = nullptr;
-        ia.hist_passes = 0;
-    } else {
-        SS_CUDA(c, sort_prepare(c->d_sort_scratch, n, begin_bit, end_bit, st));
-    }
-    bool hist_done = false;
-    if (n) {
-        hist_done = launch_instances(ia, cp, st);
-        ++launches;
-    }
-    c->world_valid = true;
-    SS_CUDA(c, cudaEventRecord(s.stage[1], st));
-    SS_CUDA(c, cudaEventRecord(c->ev_trs_read[c->trs_cur], st));  // the TRS buffer may be overwritten from here on
-
-    if (!reuse_sort) {
-        if (!hist_done)  // the general kernel did not count digits: clear again is harmless, the sort counts itself
-            SS_CUDA(c, sort_prepare(c->d_sort_scratch, n, begin_bit, end_bit, st));
-        SS_CUDA(c, sort_async(c->d_keys_a, packed ? nullptr : c->d_vals_a, c->d_keys_b, packed ? nullptr : c->d_vals_b,
-                              n, begin_bit, end_bit, c->d_sort_scratch, st, &launches, hist_done));
-        c->sort_valid = true;
-    }
-    SS_CUDA(c, cudaEventRecord(s.stage[2], st));
-
-    EmitArgs ea;
-    memset(&ea, 0, sizeof ea);
-    ea.keys_a = c->d_keys_a;
-    ea.vals_a = c->d_vals_a;
-    ea.keys_b = c->d_keys_b;
-    ea.vals_b = c->d_vals_b;
-    ea.sort_ctl = reinterpret_cast<const SortControl*>(c->d_sort_scratch);
-    ea.sort_passes = (uint32_t)sort_num_passes(begin_bit, end_bit);
-    ea.idx_bits = ia.idx_bits;
-    ea.mask_bits = ia.mask_bits;
-    // the visibility byte inside a sorted word is this frame's only if this frame built the words
-    ea.gather_mask = (!packed || ia.mask_bits == 0 || reuse_sort) ? 1u : 0u;
-    ea.mask = c->d_mask;
-    ea.world = c->d_world;
-    ea.n = n;
-    ea.n_views = n_views;
-    for (uint32_t v = 0; v < n_views; ++v) ea.out[v] = s.out[v];
-    ea.cap_visible = c->cap_visible;
-    ea.max_draws = c->max_draws;
-    ea.lookback = c->d_lookback;
-    ea.ticket = c->d_ticket;
     const size_t seg_words = (size_t)c->cfg.max_views * c->max_draws;
-    ea.seg_count = c->d_seg_count + c->seg_parity * seg_words;
-    ea.seg_key = c->d_seg_key;
-    ea.seg_inst = c->d_seg_inst;
-    ea.totals = c->d_totals;
-    ea.overflow = c->d_overflow;
-    if (n) {
-        launch_emit(ea, st);
+    const uint32_t* words_sel = nullptr;      // device word telling which sort buffer holds the fused pipeline's words
+    const uint64_t* words_known = nullptr;    // ... or the buffer itself, when the host knows it
+
+    if (fused) {
+        const int begin_bit = idx_bits, end_bit = idx_bits + key_bits;
+        const SortPlan plan = sort_plan(begin_bit, end_bit);
+        const uint64_t imask = (1ull << idx_bits) - 1ull;
+        SortControl* ctl = reinterpret_cast<SortControl*>(c->d_sort_scratch);
+        auto sort_words = [&](bool mark_stage) -> ss_status {
+            const bool with_hist = plan.n_passes <= 3;
+            WordsArgs wa;
+            memset(&wa, 0, sizeof wa);
+            wa.slot = c->d_slot;
+            wa.matword = c->d_matword;
+            wa.slots = c->d_slots;
+            wa.words = c->d_keys_a;
+            wa.n = n;
+            wa.tess_shift = tess_shift;
+            wa.idx_bits = (uint32_t)idx_bits;
+            if (with_hist) {
+                SS_CUDA(c, sort_prepare(c->d_sort_scratch, n, begin_bit, end_bit, st));
+                wa.hist = ctl->hist[0];
+                wa.hist_passes = plan.n_passes;
+                for (int p = 0; p < plan.n_passes; ++p) {
+                    wa.hist_shift[p] = plan.shift[p];
+                    wa.hist_bits[p] = plan.bits[p];
+                }
+            }
+            launch_build_words(wa, st);
+            ++launches;
+            if (mark_stage) SS_CUDA(c, cudaEventRecord(s.stage[1], st));
+            SS_CUDA(c, sort_async(c->d_keys_a, nullptr, c->d_keys_b, nullptr, n, begin_bit, end_bit, c->d_sort_scratch, st,
+                                  &launches, with_hist));
+            return SS_OK;
+        };
+        PackArgs pa;
+        memset(&pa, 0, sizeof pa);
+        pa.rec = c->d_rec;
+        pa.trs = c->d_trs + (size_t)c->node_base * 9;
+        pa.inst_aabb = c->has_inst_aabb ? c->d_inst_aabb : nullptr;
+        pa.slot = c->d_slot;
+        pa.parent = c->has_parent ? c->d_parent + c->node_base : nullptr;
+        pa.idx_mask = imask;
+        pa.n = n;
+        pa.lo = 0;
+        pa.hi = n;
+        const bool trs_dirty = c->rec_trs_lo < c->rec_trs_hi;
+        if (resident) {
+            // Draw-order-resident layout: the sort runs when a static stream changes, not per frame; the records
+            // (and the parents) are kept in sorted order, so the kernel streams them.
+            if (!c->resident_valid) {
+                ss_status rs = sort_words(false);
+                if (rs != SS_OK) return rs;
+                uint32_t sel = 0;
+                SS_CUDA(c, cudaMemcpyAsync(&sel, &ctl->src_sel[plan.n_passes], sizeof sel, cudaMemcpyDeviceToHost, st));
+                SS_CUDA(c, cudaStreamSynchronize(st));
+                c->d_words_resident = sel ? c->d_keys_b : c->d_keys_a;
+                c->resident_valid = true;
+                c->rec_static_dirty = true;
+            }
+            pa.order = c->d_words_resident;
+            pa.pos = c->d_pos;
+            pa.parent_out = c->d_parent_rec;
+            if (c->rec_static_dirty || trs_dirty) {
+                pa.trs_only = c->rec_static_dirty ? 0 : 1;
+                launch_pack_records(pa, st);
+                ++launches;
+            }
+            words_known = c->d_words_resident;
+        } else {
+            if (c->rec_static_dirty) {
+                launch_pack_records(pa, st);
+                ++launches;
+            } else if (trs_dirty) {
+                pa.trs_only = 1;
+                pa.lo = c->rec_trs_lo;
+                pa.hi = c->rec_trs_hi;
+                launch_pack_records(pa, st);
+                ++launches;
+            }
+        }
+        c->rec_static_dirty = false;
+        c->rec_trs_lo = c->rec_trs_hi = 0;
+        SS_CUDA(c, cudaEventRecord(s.stage[0], st));
+        SS_CUDA(c, cudaEventRecord(c->ev_trs_read[c->trs_cur], st));  // the records hold the transforms now
+
+        if (resident) {
+            SS_CUDA(c, cudaEventRecord(s.stage[1], st));
+        } else if ((flags & SS_FRAME_REUSE_SORT) && c->words_valid) {
+            SS_CUDA(c, cudaEventRecord(s.stage[1], st));
+            words_sel = &ctl->src_sel[plan.n_passes];
+        } else {
+            ss_status rs = sort_words(true);
+            if (rs != SS_OK) return rs;
+            c->words_valid = true;
+            words_sel = &ctl->src_sel[plan.n_passes];
+        }
+        SS_CUDA(c, cudaEventRecord(s.stage[2], st));
+
+        SubmitArgs sa;
+        memset(&sa, 0, sizeof sa);
+        sa.rec = c->d_rec;
+        sa.words_a = resident ? c->d_words_resident : c->d_keys_a;
+        sa.words_b = c->d_keys_b;
+        sa.sort_ctl = resident ? nullptr : ctl;
+        sa.sort_passes = (uint32_t)plan.n_passes;
+        sa.parent = !c->has_parent ? nullptr : resident ? c->d_parent_rec : c->d_parent + c->node_base;
+        sa.node_world = c->d_node_world;
+        sa.slots = c->d_slots;
+        sa.n = n;
+        sa.n_views = n_views;
+        sa.idx_bits = (uint32_t)idx_bits;
+        sa.gather = resident ? 0 : 1;
+        sa.has_box = c->has_inst_aabb ? 1 : 0;
+        for (uint32_t v = 0; v < n_views; ++v) sa.out[v] = s.out[v];
+        sa.cap_visible = c->cap_visible;
+        sa.max_draws = c->max_draws;
+        sa.lookback = c->d_sub_lookback;
+        sa.lb_stride = submit_lookback_stride(n);
+        sa.seg_count = c->d_seg_count + c->seg_parity * seg_words;
+        sa.seg_key = c->d_seg_key;
+        sa.seg_inst = c->d_seg_inst;
+        sa.totals = c->d_totals;
+        sa.overflow = c->d_overflow;
+        if (!(flags & SS_FRAME_NO_WORLD_ROWS)) {
+            sa.world_out = c->d_world;   // 48 B stride, word order
+            sa.mask_out = c->d_mask;
+        }
+        SS_CUDA(c, launch_submit(sa, cp, st));
         ++launches;
+        c->nodes_valid = true;
+        c->world_valid = c->sort_valid = false;  // the instance-order rows / packed words of the other pipeline are gone
+        c->words_idx_bits = (uint32_t)idx_bits;
+        c->last_pipeline = resident ? SS_PIPELINE_FUSED_RESIDENT : SS_PIPELINE_FUSED;
+        c->last_world_rows = !(flags & SS_FRAME_NO_WORLD_ROWS);
+        SS_CUDA(c, cudaEventRecord(s.stage[3], st));
+    } else {
+        SS_CUDA(c, cudaEventRecord(s.stage[0], st));
+
+        InstanceArgs ia;
+        ia.trs = c->d_trs;
+        ia.parent = c->has_parent ? c->d_parent : nullptr;
+        ia.node_world = c->d_node_world;
+        ia.node = c->has_node_map ? c->d_node : nullptr;
+        ia.node_base = c->node_base;
+        ia.slot = c->d_slot;
+        ia.matword = c->d_matword;
+        ia.inst_aabb = c->has_inst_aabb ? c->d_inst_aabb : nullptr;
+        ia.slots = c->d_slots;
+        ia.world = c->d_world;
+        ia.mask = c->d_mask;
+        ia.keys = c->d_keys_a;
+        ia.vals = c->d_vals_a;
+        ia.n = n;
+        ia.tess_shift = tess_shift;
+        ia.world_given = world_given ? 1 : 0;
+        ia.trig_mode = (int)c->cfg.trig_mode;
+        ia.idx_bits = packed ? (uint32_t)idx_bits : 0u;
+        ia.mask_bits = (packed && idx_bits + key_bits + 8 <= 64) ? 8u : 0u;
+        // The sort's digit plan is known up front, so its scratch is cleared before the instance kernel runs and
+        // the fast path accumulates the digit histograms on the way (saves the sort's own pass over the keys).
+        const int begin_bit = packed ? idx_bits + (int)ia.mask_bits : 0, end_bit = begin_bit + key_bits;
+        const SortPlan plan = sort_plan(begin_bit, end_bit);
+        ia.hist = reinterpret_cast<SortControl*>(c->d_sort_scratch)->hist[0];
+        ia.hist_passes = plan.n_passes <= 3 ? plan.n_passes : 0;
+        for (int p = 0; p < 3; ++p) {
+            ia.hist_shift[p] = p < plan.n_passes ? plan.shift[p] - begin_bit : 0;
+            ia.hist_bits[p] = p < plan.n_passes ? plan.bits[p] : 0;
+        }
+        if (reuse_sort) {  // keep the previous frame's sorted order: no keys, no histograms, no sort
+            ia.keys = nullptr;
+            ia.vals = nullptr;
+            ia.hist_passes = 0;
+        } else {
+            SS_CUDA(c, sort_prepare(c->d_sort_scratch, n, begin_bit, end_bit, st));
+        }
+        bool hist_done = false;
+        if (n) {
+            hist_done = launch_instances(ia, cp, st);
+            ++launches;
+        }
+        c->world_valid = true;
+        c->nodes_valid = true;
+        c->words_valid = c->resident_valid = false;  // the sort buffers now belong to this pipeline
+        c->last_pipeline = SS_PIPELINE_LEGACY;
+        c->last_world_rows = true;
+        SS_CUDA(c, cudaEventRecord(s.stage[1], st));
+        SS_CUDA(c, cudaEventRecord(c->ev_trs_read[c->trs_cur], st));  // the TRS buffer may be overwritten from here on
+
+        if (!reuse_sort) {
+            if (!hist_done)  // the general kernel did not count digits: clear again is harmless, the sort counts itself
+                SS_CUDA(c, sort_prepare(c->d_sort_scratch, n, begin_bit, end_bit, st));
+            SS_CUDA(c, sort_async(c->d_keys_a, packed ? nullptr : c->d_vals_a, c->d_keys_b, packed ? nullptr : c->d_vals_b,
+                                  n, begin_bit, end_bit, c->d_sort_scratch, st, &launches, hist_done));
+            c->sort_valid = true;
+        }
+        SS_CUDA(c, cudaEventRecord(s.stage[2], st));
+
+        EmitArgs ea;
+        memset(&ea, 0, sizeof ea);
+        ea.keys_a = c->d_keys_a;
+        ea.vals_a = c->d_vals_a;
+        ea.keys_b = c->d_keys_b;
+        ea.vals_b = c->d_vals_b;
+        ea.sort_ctl = reinterpret_cast<const SortControl*>(c->d_sort_scratch);
+        ea.sort_passes = (uint32_t)sort_num_passes(begin_bit, end_bit);
+        ea.idx_bits = ia.idx_bits;
+        ea.mask_bits = ia.mask_bits;
+        // the visibility byte inside a sorted word is this frame's only if this frame built the words
+        ea.gather_mask = (!packed || ia.mask_bits == 0 || reuse_sort) ? 1u : 0u;
+        ea.mask = c->d_mask;
+        ea.world = c->d_world;
+        ea.n = n;
+        ea.n_views = n_views;
+        for (uint32_t v = 0; v < n_views; ++v) ea.out[v] = s.out[v];
+        ea.cap_visible = c->cap_visible;
+        ea.max_draws = c->max_draws;
+        ea.lookback = c->d_lookback;
+        ea.ticket = c->d_ticket;
+        ea.seg_count = c->d_seg_count + c->seg_parity * seg_words;
+        ea.seg_key = c->d_seg_key;
+        ea.seg_inst = c->d_seg_inst;
+        ea.totals = c->d_totals;
+        ea.overflow = c->d_overflow;
+        if (n) {
+            launch_emit(ea, st);
+            ++launches;
+        }
+        SS_CUDA(c, cudaEventRecord(s.stage[3], st));
     }
-    SS_CUDA(c, cudaEventRecord(s.stage[3], st));
 
     DrawArgs da;
     memset(&da, 0, sizeof da);
@@ -795,6 +1005,7 @@ SS_API ss_status ss_frame(ss_ctx* c, const ss_view* views, uint32_t n_views, uin
     da.runs_cur = c->d_seg_runs + c->seg_parity;
     da.runs_next = c->d_seg_runs + (c->seg_parity ^ 1u);
     da.passes_run = &reinterpret_cast<SortControl*>(c->d_sort_scratch)->passes_run;
+    da.words_sel = words_sel;
     da.host_stats = s.h_counts_dev;
     da.stats_views = c->cfg.max_views;
     c->seg_parity ^= 1u;
@@ -815,6 +1026,10 @@ SS_API ss_status ss_frame(ss_ctx* c, const ss_view* views, uint32_t n_views, uin
     memcpy(s.views, views, n_views * sizeof(ss_view));
     s.n_instances = n;
     s.launches = launches;
+    s.pipeline = c->last_pipeline;
+    s.words_known = words_known;
+    s.idx_bits = fused ? (uint32_t)idx_bits : 0u;
+    s.world_rows = c->last_world_rows;
     ++c->frame_no;
     if (slot_out) *slot_out = si;
     return SS_OK;
@@ -841,6 +1056,7 @@ SS_API ss_status ss_frame_sync(ss_ctx* c, uint32_t slot, ss_frame_stats* stats)
         stats->overflow = s.h_counts[V * 2];
         stats->sort_passes_run = s.h_counts[V * 2 + 1];
         stats->kernel_launches = (uint32_t)s.launches;
+        stats->pipeline = (uint32_t)s.pipeline;
         float ms = 0.f;
         SS_CUDA(c, cudaEventElapsedTime(&ms, s.start, s.done));
         stats->gpu_ms = ms;
@@ -865,10 +1081,18 @@ SS_API ss_status ss_map_outputs(ss_ctx* c, uint32_t slot, uint32_t view, ss_outp
     out->draws = s.out[view].draws;
     out->draw_keys = s.out[view].draw_keys;
     out->counts = s.out[view].counts;
-    out->world_rows = reinterpret_cast<const float*>(c->d_world);
-    out->masks = c->d_mask;
+    out->world_rows = s.world_rows ? reinterpret_cast<const float*>(c->d_world) : nullptr;
+    out->masks = s.world_rows ? c->d_mask : nullptr;
     out->visible = std::min(s.h_counts[view * 2 + 0], c->cap_visible);
     out->n_draws = s.h_counts[view * 2 + 1];
+    out->world_words = nullptr;
+    out->world_idx_bits = 0;
+    out->world_stride = kWorldStride * 4;
+    if (s.pipeline != SS_PIPELINE_LEGACY) {
+        out->world_words = s.words_known ? s.words_known : (s.h_counts[c->cfg.max_views * 2 + 2] ? c->d_keys_b : c->d_keys_a);
+        out->world_idx_bits = s.idx_bits;
+        out->world_stride = 12;
+    }
     return SS_OK;
 }
 
@@ -908,6 +1132,37 @@ static ss_status download_range(ss_ctx* c, const void* src, size_t elem, uint32_
     return SS_OK;
 }
 
+// Fused pipeline: world rows and masks lie in word order; bring the rows / bytes of instances [first, first + count)
+// back to instance order through a scratch buffer (a download is not a per-frame operation).
+static ss_status download_word_ordered(ss_ctx* c, uint32_t first, uint32_t count, float* rows12, uint8_t* masks)
+{
+    if (!c->last_world_rows)
+        return c->fail(SS_ERR_STATE, "the last frame ran with SS_FRAME_NO_WORLD_ROWS: there are no world rows / masks to read");
+    SS_CUDA(c, cudaStreamSynchronize(c->stream));
+    const uint64_t* words = c->d_words_resident;
+    if (c->last_pipeline == SS_PIPELINE_FUSED) {
+        const int key_bits = (int)(c->mesh_bits + c->submesh_bits + c->material_bits) + 2;
+        const int passes = sort_num_passes((int)c->words_idx_bits, (int)c->words_idx_bits + key_bits);
+        uint32_t sel = 0;
+        SS_CUDA(c, cudaMemcpy(&sel, &reinterpret_cast<SortControl*>(c->d_sort_scratch)->src_sel[passes], sizeof sel,
+                              cudaMemcpyDeviceToHost));
+        words = sel ? c->d_keys_b : c->d_keys_a;
+    }
+    void* tmp = nullptr;
+    SS_CUDA(c, cudaMalloc(&tmp, std::max<size_t>((size_t)count * (rows12 ? 48 : 1), 256)));
+    launch_unpermute(words, (1ull << c->words_idx_bits) - 1ull, c->n_instances, first, count,
+                     reinterpret_cast<const float4*>(c->d_world), rows12 ? static_cast<float4*>(tmp) : nullptr, c->d_mask,
+                     masks ? static_cast<uint8_t*>(tmp) : nullptr, c->stream);
+    cudaError_t e = cudaGetLastError();
+    if (e == cudaSuccess)
+        e = cudaMemcpyAsync(rows12 ? static_cast<void*>(rows12) : static_cast<void*>(masks), tmp, (size_t)count * (rows12 ? 48 : 1),
+                            cudaMemcpyDeviceToHost, c->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
+    cudaFree(tmp);
+    if (e != cudaSuccess) return c->fail(SS_ERR_CUDA, "download (word order): %s", cudaGetErrorString(e));
+    return SS_OK;
+}
+
 SS_API ss_status ss_download_world(ss_ctx* c, uint32_t first, uint32_t count, float* rows12)
 {
     if (!c) return SS_ERR_INVALID;
@@ -915,6 +1170,7 @@ SS_API ss_status ss_download_world(ss_ctx* c, uint32_t first, uint32_t count, fl
         return c->fail(SS_ERR_INVALID, "ss_download_world: range [%u, +%u) exceeds %u instances", first, count,
                        c->n_instances);
     SS_CUDA(c, cudaSetDevice(c->device));
+    if (count && c->last_pipeline != SS_PIPELINE_LEGACY) return download_word_ordered(c, first, count, rows12, nullptr);
     if (count)  // device rows sit at a 64 B stride; the host gets them packed as TransformData
         SS_CUDA(c, cudaMemcpy2DAsync(rows12, 48, c->d_world + (size_t)first * kWorldStride, kWorldStride * 16, 48, count,
                                      cudaMemcpyDeviceToHost, c->stream));
@@ -923,6 +1179,10 @@ SS_API ss_status ss_download_world(ss_ctx* c, uint32_t first, uint32_t count, fl
 }
 SS_API ss_status ss_download_masks(ss_ctx* c, uint32_t first, uint32_t count, uint8_t* masks)
 {
+    if (c && masks && count && (uint64_t)first + count <= c->n_instances && c->last_pipeline != SS_PIPELINE_LEGACY) {
+        SS_CUDA(c, cudaSetDevice(c->device));
+        return download_word_ordered(c, first, count, nullptr, masks);
+    }
     return download_range(c, c ? c->d_mask : nullptr, 1, first, count, masks, "ss_download_masks");
 }
 

@@ -393,6 +393,7 @@ __global__ void __launch_bounds__(kDrawThreads) k_draws(const __grid_constant__ 
         *a.runs_cur = n_segs;
         a.host_stats[a.stats_views * 2] = *a.overflow | over;
         a.host_stats[a.stats_views * 2 + 1] = *a.passes_run;
+        a.host_stats[a.stats_views * 2 + 2] = a.words_sel ? *a.words_sel : 0u;
     }
     // rows of views this frame does not use are cleaned all the same: the frame that filled the other buffer may
     // have run more views than this one (ss_frame takes any n_views up to max_views)

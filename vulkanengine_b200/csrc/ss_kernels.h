@@ -156,6 +156,7 @@ struct DrawArgs {
     uint32_t* runs_cur;            // out: number of runs this frame put into seg_count
     const uint32_t* runs_next;     // runs the frame before last left in seg_count_next (bounds the zeroing)
     const uint32_t* passes_run;    // SortControl::passes_run, forwarded to the host
+    const uint32_t* words_sel;     // fused pipeline: which sort buffer holds the words (forwarded too), or nullptr
     uint32_t* host_stats;          // mapped pinned host words: [stats_views][2] visible/draws, overflow, passes_run
     uint32_t stats_views;
     const uint64_t* seg_key;
@@ -166,6 +167,89 @@ struct DrawArgs {
     uint32_t* overflow;
 };
 void launch_draws(const DrawArgs& a, cudaStream_t st);
+
+// ---- fused submission kernel (submit.cu) ---------------------------------------------------------
+// One 64 B record per instance: everything the transform + cull of an instance reads, in ONE aligned block, so
+// that fetching an instance in draw order costs one DRAM line instead of three (TRS, box, ids).
+struct InstRec {
+    float trs[9];    // TransformComponent of the instance's node
+    float box[6];    // per-instance local AABB {min, max} (unused when the submesh table's box applies)
+    uint32_t slot;   // submesh table row or SS_SLOT_NULL
+};
+static_assert(sizeof(InstRec) == 64, "InstRec layout");
+
+constexpr int kSubThreads = 128;
+constexpr int kSubTile = 2 * kSubThreads;     // instances per tile
+constexpr int kSubWords = SS_MAX_VIEWS + 1;   // look-back counters: V visible counts + runs
+constexpr int kSubPad = kSubTile;             // elements every array a full-tile bulk copy reads must be padded by
+
+// sort words [key | instance] from the static id streams (+ the sort's digit histograms)
+struct WordsArgs {
+    const uint32_t* slot;
+    const uint32_t* matword;
+    const SlotDev* slots;
+    uint64_t* words;
+    uint32_t n;
+    uint32_t tess_shift;
+    uint32_t idx_bits;
+    uint32_t* hist;            // SortControl::hist, zeroed; nullptr = no histograms
+    int hist_passes;
+    int hist_shift[3];         // of the word
+    int hist_bits[3];
+};
+void launch_build_words(const WordsArgs& a, cudaStream_t st);
+
+// (Re)build instance records from the streams.  order == nullptr: record r describes instance r.  Otherwise record
+// r describes instance order[r] & idx_mask (draw-order-resident layout) and pos / parent_out are filled as well.
+struct PackArgs {
+    InstRec* rec;
+    const float* trs;          // node stream, already offset to the first instance node
+    const float* inst_aabb;    // [n][6] or nullptr
+    const uint32_t* slot;
+    const int32_t* parent;     // node stream, offset like trs, or nullptr
+    const uint64_t* order;     // sorted words or nullptr
+    uint64_t idx_mask;
+    uint32_t* pos;             // out: pos[instance] = r (with order), or nullptr
+    int32_t* parent_out;       // out: parent of record r (with order), or nullptr
+    uint32_t n;
+    uint32_t lo, hi;           // instance range to refresh (identity order only; with an order the whole stream)
+    int trs_only;
+};
+void launch_pack_records(const PackArgs& a, cudaStream_t st);
+
+struct SubmitArgs {
+    const InstRec* rec;
+    const uint64_t* words_a;
+    const uint64_t* words_b;
+    const SortControl* sort_ctl;   // nullptr: the words are words_a
+    uint32_t sort_passes;
+    const int32_t* parent;         // gather: node stream offset to the first instance node, indexed by instance;
+                                   // resident: parent of record r; nullptr: no parent chain
+    const float4* node_world;
+    const SlotDev* slots;
+    uint32_t n, n_views, idx_bits;
+    int gather;                    // 1: record of word j is rec[instance]; 0: rec[j]
+    int has_box;
+    ViewOut out[SS_MAX_VIEWS];
+    uint32_t cap_visible, max_draws;
+    uint32_t* lookback;            // [kSubWords][lb_stride], zeroed per frame
+    uint32_t lb_stride;
+    uint32_t* seg_count;
+    uint64_t* seg_key;
+    uint32_t* seg_inst;
+    uint32_t* totals;
+    uint32_t* overflow;
+    float4* world_out;             // [n][3] world rows in word order, or nullptr
+    uint8_t* mask_out;             // [n] visibility bytes in word order, or nullptr
+};
+size_t submit_lookback_bytes(uint64_t n);
+uint32_t submit_lookback_stride(uint64_t n);
+cudaError_t launch_submit(const SubmitArgs& a, const CullParams& cp, cudaStream_t st);
+
+// rows / bytes of instances [first, first + count) out of word-ordered arrays (downloads, parity tests)
+void launch_unpermute(const uint64_t* words, uint64_t idx_mask, uint32_t n, uint32_t first, uint32_t count,
+                      const float4* world_words, float4* rows_out, const uint8_t* mask_words, uint8_t* mask_out,
+                      cudaStream_t st);
 
 // ---- depth + id rasterisation of a view's compacted list (raster.cu) -------------------------------
 struct RasterArgs {

@@ -14,9 +14,13 @@ LIB_PATH = os.path.join(_HERE, "libscenesubmit.so")
 SS_OK, SS_ERR_INVALID, SS_ERR_CUDA, SS_ERR_CAPACITY, SS_ERR_STATE, SS_ERR_NOMEM = range(6)
 TRIG_DETERMINISTIC, TRIG_LIBM = 0, 1
 FRAME_WORLD_ROWS_GIVEN = 1
-FRAME_NO_GRAPH = 2
+FRAME_NO_WORLD_ROWS = 2
 FRAME_REUSE_WORLD = 4
 FRAME_REUSE_SORT = 8
+CONFIG_LEGACY_PIPELINE = 1
+CONFIG_DRAW_ORDER_RESIDENT = 2
+PIPELINE_LEGACY, PIPELINE_FUSED, PIPELINE_FUSED_RESIDENT = 0, 1, 2
+PIPELINE_NAMES = {0: "legacy", 1: "fused", 2: "fused_resident"}
 MAX_VIEWS = 8
 SLOT_NULL = 0xFFFFFFFF
 
@@ -49,13 +53,14 @@ class Config(C.Structure):
 class FrameStats(C.Structure):
     _fields_ = [("n_instances", C.c_uint32), ("n_views", C.c_uint32), ("visible", C.c_uint32 * MAX_VIEWS),
                 ("draws", C.c_uint32 * MAX_VIEWS), ("sort_passes_run", C.c_uint32), ("overflow", C.c_uint32),
-                ("gpu_ms", C.c_float), ("kernel_launches", C.c_uint32)]
+                ("gpu_ms", C.c_float), ("kernel_launches", C.c_uint32), ("pipeline", C.c_uint32)]
 
 
 class Outputs(C.Structure):
     _fields_ = [("instance_rows", C.c_void_p), ("keys", C.c_void_p), ("instance_idx", C.c_void_p),
                 ("draws", C.c_void_p), ("draw_keys", C.c_void_p), ("counts", C.c_void_p), ("world_rows", C.c_void_p),
-                ("masks", C.c_void_p), ("visible", C.c_uint32), ("n_draws", C.c_uint32)]
+                ("masks", C.c_void_p), ("visible", C.c_uint32), ("n_draws", C.c_uint32), ("world_words", C.c_void_p),
+                ("world_idx_bits", C.c_uint32), ("world_stride", C.c_uint32)]
 
 
 _lib = None
@@ -153,10 +158,12 @@ class SceneSubmit:
     """One libscenesubmit context (one GPU). Mirrors the C ABI one to one."""
 
     def __init__(self, max_nodes, max_instances, max_submesh_slots, max_views=5, device=0, trig_mode=TRIG_DETERMINISTIC,
-                 frames_in_flight=3, max_draws_per_view=0, max_visible_per_view=0):
+                 frames_in_flight=3, max_draws_per_view=0, max_visible_per_view=0, flags=None):
         self.lib = load_library()
+        if flags is None:  # SS_CONFIG_FLAGS=1 / 2 / 3 in the environment: run a whole test session on one pipeline
+            flags = int(os.environ.get("SS_CONFIG_FLAGS", "0"))
         cfg = Config(C.sizeof(Config), device, max_nodes, max_instances, max_submesh_slots, max_views,
-                     max_draws_per_view, frames_in_flight, max_visible_per_view, trig_mode, 0)
+                     max_draws_per_view, frames_in_flight, max_visible_per_view, trig_mode, flags)
         h = C.c_void_p()
         st = self.lib.ss_create(C.byref(cfg), C.byref(h))
         if st != SS_OK:
@@ -256,6 +263,7 @@ class SceneSubmit:
     def frame_stage_ms(self, slot):
         ms = (C.c_float * 5)()
         self._ck(self.lib.ss_frame_stage_ms(self.h, C.c_uint32(slot), ms))
+        # fused pipeline: "instances" = building the key words, "emit" = the fused transform+cull+compact+emit kernel
         return dict(zip(("hierarchy", "instances", "sort", "emit", "draws"), (float(x) for x in ms)))
 
     # ---- outputs
