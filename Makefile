@@ -5,7 +5,7 @@
 NVCC     ?= /usr/local/cuda/bin/nvcc
 ARCH     := -gencode arch=compute_100a,code=sm_100a
 # -fmad=false: no FMA contraction anywhere, the float op order is the reference's
-NVFLAGS  := $(ARCH) -O3 -std=c++17 -lineinfo -fmad=false \
+NVFLAGS  := $(ARCH) -O3 -std=c++17 -lineinfo -fmad=false $(EXTRA) \
             -Xcompiler -fPIC,-ffp-contract=off,-fno-fast-math,-fvisibility=hidden,-Wall
 CSRC     := vulkanengine_b200/csrc
 OBJDIR   := build

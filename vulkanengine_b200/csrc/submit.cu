@@ -76,18 +76,19 @@ struct SubSmem {
     uint32_t flags[SS_MAX_VIEWS];
     uint64_t warp_a[kSubWarps], warp_b[kSubWarps];
     uint32_t warp_h[kSubWarps];
+    uint32_t sink[kSubWarps];                          // see the unpack step
     uint32_t base[kSubWords];                          // exclusive prefix over earlier tiles
     uint32_t total[kSubWords];                         // this tile
     uint64_t rbar;
     uint64_t wbar[kWordBufs];
 };
 
-// Decoupled look-back by one warp, all kSubWords counters at once.  lb[w * stride + t] is the status word of counter w
-// of tile t: value | flag (kLbAgg: the tile's own count, kLbPrefix: inclusive prefix over tiles <= t).  Each round the
-// 32 lanes read the 32 predecessors of `start` for every unresolved counter (one 128 B line per counter), take the
-// longest run of published words that ends at the nearest prefix, and go on from there.  Returns the exclusive prefix
-// of counter `lane` (lanes >= kSubWords: 0).
-__device__ __forceinline__ uint32_t warp_lookback(const uint32_t* lb, uint32_t stride, uint32_t tile, int lane)
+// Decoupled look-back by one warp, all kSubWords counters at once, over a status array lb[w * stride + i]: value | flag
+// (kLbAgg: element i's own count, kLbPrefix: inclusive prefix over elements <= i).  Each round the 32 lanes read the
+// 32 elements below `start` for every unresolved counter (one 128 B line per counter), take the longest run of
+// published words that ends at the nearest prefix, and go on from there.  Elements below `floor_i` count as an empty
+// prefix.  Returns the sum for counter `lane` (lanes >= kSubWords: 0).
+__device__ __forceinline__ uint32_t warp_walk(const uint32_t* lb, uint32_t stride, int64_t first, int64_t floor_i, int lane)
 {
     uint32_t sum[kSubWords];
     int64_t start[kSubWords];
@@ -95,15 +96,15 @@ __device__ __forceinline__ uint32_t warp_lookback(const uint32_t* lb, uint32_t s
 #pragma unroll
     for (int w = 0; w < kSubWords; ++w) {
         sum[w] = 0;
-        start[w] = (int64_t)tile - 1;
+        start[w] = first;
     }
     while (open) {
         uint32_t v[kSubWords];
 #pragma unroll
         for (int w = 0; w < kSubWords; ++w) {
             const int64_t t = start[w] - lane;
-            v[w] = kLbPrefix;  // before tile 0: an empty prefix
-            if (((open >> w) & 1u) && t >= 0) v[w] = ld_volatile_u32(lb + (size_t)w * stride + (size_t)t);
+            v[w] = kLbPrefix;  // below the floor: an empty prefix
+            if (((open >> w) & 1u) && t >= floor_i) v[w] = ld_volatile_u32(lb + (size_t)w * stride + (size_t)t);
         }
 #pragma unroll
         for (int w = 0; w < kSubWords; ++w) {
@@ -117,7 +118,7 @@ __device__ __forceinline__ uint32_t warp_lookback(const uint32_t* lb, uint32_t s
                 if (first_prefix < first_missing)
                     open &= ~(1u << w);
                 else
-                    start[w] -= take;  // take may be 0: the nearest predecessor has not published yet, poll again
+                    start[w] -= take;  // take may be 0: the nearest element has not published yet, poll again
             }
         }
     }
@@ -126,6 +127,28 @@ __device__ __forceinline__ uint32_t warp_lookback(const uint32_t* lb, uint32_t s
     for (int w = 0; w < kSubWords; ++w)
         if (lane == w) mine = sum[w];
     return mine;
+}
+
+// Exclusive prefix of tile `tile` in two levels.  The persistent CTAs run in near lock-step, so at any moment several
+// hundred consecutive tiles have published their counts but not yet their prefixes; walking them 32 at a time costs
+// dozens of L2 round trips per tile.  Instead tiles are grouped by kLbGroup = 32:
+//   level 1  lb_tile[w][t]   = kLbAgg | count of tile t               (never upgraded)
+//   level 2  lb_group[w][g]  = kLbAgg | count of group g, then kLbPrefix | inclusive prefix over groups <= g
+// A tile sums the counts of the earlier tiles of its own group (one round), then walks the groups (32 groups = 1024
+// tiles per round).  The last tile of a group publishes the group's count as soon as its first walk is done and the
+// group's prefix when its second is.
+constexpr int kLbGroup = 32;
+__device__ __forceinline__ uint32_t two_level_lookback(uint32_t* lb_tile, uint32_t* lb_group, uint32_t stride_t, uint32_t stride_g,
+                                                       uint32_t tile, uint32_t mine, int lane, bool last_tile)
+{
+    const uint32_t g = tile / kLbGroup, q = tile % kLbGroup;
+    const bool closes_group = q == kLbGroup - 1 || last_tile;
+    if (lane < kSubWords) st_volatile_u32(lb_tile + (size_t)lane * stride_t + tile, kLbAgg | mine);
+    const uint32_t within = warp_walk(lb_tile, stride_t, (int64_t)tile - 1, (int64_t)g * kLbGroup, lane);
+    if (closes_group && lane < kSubWords) st_volatile_u32(lb_group + (size_t)lane * stride_g + g, kLbAgg | (within + mine));
+    const uint32_t before = warp_walk(lb_group, stride_g, (int64_t)g - 1, 0, lane);
+    if (closes_group && lane < kSubWords) st_volatile_u32(lb_group + (size_t)lane * stride_g + g, kLbPrefix | (before + within + mine));
+    return before + within;
 }
 
 template <bool GATHER, bool HAS_PARENT>
@@ -151,7 +174,10 @@ __global__ void __launch_bounds__(kSubThreads, 5) k_submit(const __grid_constant
     };
     auto issue_rec_seq = [&](uint32_t tile) {  // one thread; resident layout: the tile's records are contiguous
         mbar_expect_tx(&s.rbar, kSubTile * 64 + ((HAS_PARENT && !GATHER) ? kSubTile * 4 : 0));
-        bulk_g2s(s.rec, a.rec + (size_t)tile * kSubTile, kSubTile * 64, &s.rbar);
+        const uint32_t chunk = (kSubTile * 64) / a.seq_chunks;  // seq_chunks bulk copies per tile (see launch_submit)
+        for (uint32_t c = 0; c < a.seq_chunks; ++c)
+            bulk_g2s(reinterpret_cast<unsigned char*>(s.rec) + c * chunk,
+                     reinterpret_cast<const unsigned char*>(a.rec + (size_t)tile * kSubTile) + c * chunk, chunk, &s.rbar);
         if (HAS_PARENT && !GATHER) bulk_g2s(s.parent, a.parent + (size_t)tile * kSubTile, kSubTile * 4, &s.rbar);
     };
     auto issue_rec_gather = [&](uint32_t tile, int b) {  // every thread, once the tile's words are in buffer b
@@ -253,6 +279,13 @@ __global__ void __launch_bounds__(kSubThreads, 5) k_submit(const __grid_constant
         }
         // the bulk stores of the previous tile (world rows, masks) must have read their shared-memory source
         // before this tile overwrites it
+        // The stage is refilled by the async proxy (TMA) right after the barrier below, and a barrier only orders
+        // loads that have been ISSUED: when every CTA of an SM unpacks at once (first tile of the launch) the
+        // bank-conflicted 128-bit loads queue for longer than the next tile's copy takes to arrive, and a queued load
+        // then reads the next tile's bytes.  A store that depends on every loaded word cannot issue before the
+        // loads have returned, so the thread only reaches the barrier with its records really in registers.
+        s.sink[wid] = __float_as_uint(A0.x) ^ __float_as_uint(A1.x) ^ __float_as_uint(A2.x) ^ slot0 ^ __float_as_uint(B0.x) ^
+                      __float_as_uint(B1.x) ^ __float_as_uint(B2.x) ^ slot1 ^ (uint32_t)p0 ^ (uint32_t)p1;
         if (tid == 0) bulk_wait_read();
         __syncthreads();  // S1: records are in registers, the previous tile's output phase is over
 
@@ -405,15 +438,8 @@ __global__ void __launch_bounds__(kSubThreads, 5) k_submit(const __grid_constant
 #pragma unroll
             for (int wq = 0; wq < kSubWords; ++wq)
                 if (lane == wq) mine = tile_total(wq);
-            uint32_t* lbw = a.lookback + (size_t)lane * a.lb_stride + tile;
-            uint32_t excl = 0;
-            if (tile == 0) {
-                if (lane < kSubWords) st_volatile_u32(lbw, kLbPrefix | mine);
-            } else {
-                if (lane < kSubWords) st_volatile_u32(lbw, kLbAgg | mine);
-                excl = warp_lookback(a.lookback, a.lb_stride, tile, lane);
-                if (lane < kSubWords) st_volatile_u32(lbw, kLbPrefix | (excl + mine));
-            }
+            const uint32_t excl = two_level_lookback(a.lookback, a.lookback + (size_t)kSubWords * a.lb_stride, a.lb_stride,
+                                                     a.lb_stride / kLbGroup, tile, mine, lane, tile == n_tiles - 1);
             if (lane < kSubWords) {
                 s.base[lane] = excl;
                 s.total[lane] = mine;
@@ -587,7 +613,12 @@ uint32_t submit_lookback_stride(uint64_t n)
     return (uint32_t)(((tiles ? tiles : 1) + 31) & ~uint64_t(31));
 }
 
-size_t submit_lookback_bytes(uint64_t n) { return (size_t)submit_lookback_stride(n) * kSubWords * sizeof(uint32_t); }
+// level 1: [kSubWords][stride] tile words, level 2: [kSubWords][stride / kLbGroup] group words
+size_t submit_lookback_bytes(uint64_t n)
+{
+    const size_t stride = submit_lookback_stride(n);
+    return (stride + stride / kLbGroup) * kSubWords * sizeof(uint32_t);
+}
 
 void launch_build_words(const WordsArgs& a, cudaStream_t st)
 {
