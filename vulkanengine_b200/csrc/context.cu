@@ -878,11 +878,6 @@ SS_API ss_status ss_frame(ss_ctx* c, const ss_view* views, uint32_t n_views, uin
         sa.idx_bits = (uint32_t)idx_bits;
         sa.gather = resident ? 0 : 1;
         sa.has_box = c->has_inst_aabb ? 1 : 0;
-        sa.seq_chunks = 16;
-        if (const char* e = getenv("SS_SEQ_CHUNKS")) {
-            const int v = atoi(e);
-            if (v == 1 || v == 2 || v == 4 || v == 8 || v == 16 || v == 32) sa.seq_chunks = (uint32_t)v;
-        }
         for (uint32_t v = 0; v < n_views; ++v) sa.out[v] = s.out[v];
         sa.cap_visible = c->cap_visible;
         sa.max_draws = c->max_draws;

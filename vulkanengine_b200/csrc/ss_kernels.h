@@ -230,7 +230,6 @@ struct SubmitArgs {
     uint32_t n, n_views, idx_bits;
     int gather;                    // 1: record of word j is rec[instance]; 0: rec[j]
     int has_box;
-    uint32_t seq_chunks;           // resident layout: bulk copies a tile's records are fetched with (1, 2, 4, 8)
     ViewOut out[SS_MAX_VIEWS];
     uint32_t cap_visible, max_draws;
     uint32_t* lookback;            // [kSubWords][lb_stride], zeroed per frame
