@@ -43,10 +43,22 @@ def parse():
     ap.add_argument("--instances", type=int, default=N_PER_GPU, help="instances per GPU (default 2^24)")
     ap.add_argument("--views", type=int, default=N_VIEWS)
     ap.add_argument("--trig", default="deterministic", choices=["deterministic", "libm"])
-    ap.add_argument("--cpu-sample", type=int, default=1 << 20, help="instances in the CPU baseline sample")
+    ap.add_argument("--cpu-sample", type=int, default=0,
+                    help="instances in the CPU sample (0: the whole scene for --impl reference, 2^20 for the cpu_baseline leg)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     return ap.parse_args()
+
+
+TRIG_NOTE = {"native": "deterministic polynomial sin/cos (include/scenesubmit_dettrig.h), bit-identical to the oracle",
+             "reference": "libm sinf/cosf through glm (GLM/detail/type_quat.inl:208-217)"}
+
+
+def bench_config(n, n_views, seed, world):
+    """The same `config` object in both arms (the driver compares them)."""
+    return {"workload": WORKLOAD, "instances_per_gpu": n, "views": n_views, "keys": 4096, "seed": seed,
+            "l2": "inputs_exceed_l2 (>1 GB of streams per frame)",
+            "sharding": "entity-wise, no collective in the sharded phase" if world > 1 else "none"}
 
 
 def peaks():
@@ -216,14 +228,17 @@ def main():
     from vulkanengine_b200 import synth
 
     if a.impl == "reference":
-        # the reference's own CPU implementation of the path on this box's host cores; rank 0 only
+        # the reference's own CPU implementation of the path on this box's host cores; rank 0 only.  Nothing of the
+        # product is imported here: the view matrices come from oracle/_ref too (the reference's GLM).
         if rank != 0:
             return
-        from vulkanengine_b200 import scenesubmit as S  # host-side view matrices only (no GPU work)
+        sys.path.insert(0, os.path.join(ROOT, "tests"))
+        import oracle_lib as O
+        which = "ref" if O.ref_available() else "oracle"
         cores = os.cpu_count() or 1
-        sample = min(a.cpu_sample, n)
+        sample = min(a.cpu_sample if a.cpu_sample else n, n)
         sc = synth.flat_scene(sample, first=0)
-        views = synth.make_views(S.camera_view_proj, S.cascade_matrices, a.views)
+        views = synth.make_views(lambda *q: O.camera_view_proj(*q, which=which), lambda *q: O.cascade_matrices(*q, which=which), a.views)
         for _ in range(max(a.warmup, 1)):
             cpu_reference(sc, views, min(sample, 1 << 16), cores, min_seconds=0.0)
         t0 = time.perf_counter()
@@ -231,17 +246,23 @@ def main():
         for _ in range(a.steps):
             ips, kind, secs, ns = cpu_reference(sc, views, sample, cores, min_seconds=0.0)  # one step = one pass over the sample
             vals.append((ips, secs))
-            if time.perf_counter() - t0 > 240:
+            if time.perf_counter() - t0 > 200:
                 break
         ips = float(np.median([v[0] for v in vals]))
         secs = float(np.median([v[1] for v in vals]))
+        # a second, smaller sample shows how the rate moves with the size (the std::map and the vectors grow with it)
+        ips_small, _, _, ns_small = cpu_reference(sc, views, min(sample, 1 << 20), cores, min_seconds=0.0)
         line = {"impl": "reference", "metric": "culled+compacted instances/sec", "value": ips, "unit": "instances/s",
                 "n_gpus": a.gpus, "steps": len(vals), "warmup": a.warmup, "ms_per_step": secs * 1e3,
                 "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-                "config": {"workload": WORKLOAD, "views": a.views, "instances_per_gpu": n,
-                           "note": "each step = the reference CPU path on a bounded sample of the workload"},
+                "config": bench_config(n, a.views, int(sc.seed), 1),
+                "trig": TRIG_NOTE,
                 "cpu_baseline": {"value": ips, "unit": "instances/s", "cores": cores, "kind": kind,
-                                 "sample": f"first {ns} instances x {a.views} views of the same scene, one pass per step, median"},
+                                 "sample": f"first {ns} instances x {a.views} views of the same scene, one pass per step, median; "
+                                           f"the first {ns_small} instances alone run at {ips_small:.3g} instances/s",
+                                 "note": "glm T*R*S + product + cull + one std::map<MeshKey> per view, range-partitioned over the "
+                                         "cores; leaves out the per-entity AssetManager::GetAsset probe and shared_ptr copies of "
+                                         "Scene.cpp:144 (conservative for the ratio)"},
                 "e2e": {"value": ips, "unit": "instances/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
         print(json.dumps(line), flush=True)
         return
@@ -442,8 +463,9 @@ def main():
         if not a.no_cpu_baseline and world == 1:
             os.sched_setaffinity(0, all_cpus)  # the CPU baseline gets every core again
             cores = os.cpu_count() or 1
-            ips, kind, secs, ns = cpu_reference(sc, views, a.cpu_sample, cores)
-            ips1, _, secs1, _ = cpu_reference(sc, views, min(a.cpu_sample, 1 << 18), 1)
+            cs = a.cpu_sample if a.cpu_sample else 1 << 20
+            ips, kind, secs, ns = cpu_reference(sc, views, cs, cores)
+            ips1, _, secs1, _ = cpu_reference(sc, views, min(cs, 1 << 18), 1)
             line["cpu_baseline"] = {"value": ips, "unit": "instances/s", "cores": cores, "kind": kind,
                                     "sample": f"first {ns} instances x {a.views} views of the same scene "
                                               f"({secs * 1e3:.1f} ms best of repeats)",

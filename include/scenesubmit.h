@@ -280,7 +280,7 @@ SS_API ss_status ss_frame_sync(ss_ctx* ctx, uint32_t slot, ss_frame_stats* stats
 
 /* Device time of the slot's frame by stage, CUDA events on the context stream:
    {clear + hierarchy levels, transform+cull+key, sort, compact+emit, draws + count read-back}; for the fused
-   pipeline {clear + hierarchy levels + record refresh, key words, sort, fused transform+cull+compact+emit, draws}.
+   pipelines {clear + hierarchy levels + record refresh, key words + sort, transform+cull, compact+emit, draws}.
    The counterpart of the reference's per-pass timestamp queries
    (PV/VulkanRenderCommandBuffer.cpp:150-172). */
 SS_API ss_status ss_frame_stage_ms(ss_ctx* ctx, uint32_t slot, float ms_out[5]);

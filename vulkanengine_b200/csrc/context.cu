@@ -772,7 +772,7 @@ SS_API ss_status ss_frame(ss_ctx* c, const ss_view* views, uint32_t n_views, uin
         const SortPlan plan = sort_plan(begin_bit, end_bit);
         const uint64_t imask = (1ull << idx_bits) - 1ull;
         SortControl* ctl = reinterpret_cast<SortControl*>(c->d_sort_scratch);
-        auto sort_words = [&](bool mark_stage) -> ss_status {
+        auto sort_words = [&]() -> ss_status {
             const bool with_hist = plan.n_passes <= 3;
             WordsArgs wa;
             memset(&wa, 0, sizeof wa);
@@ -794,7 +794,6 @@ SS_API ss_status ss_frame(ss_ctx* c, const ss_view* views, uint32_t n_views, uin
             }
             launch_build_words(wa, st);
             ++launches;
-            if (mark_stage) SS_CUDA(c, cudaEventRecord(s.stage[1], st));
             SS_CUDA(c, sort_async(c->d_keys_a, nullptr, c->d_keys_b, nullptr, n, begin_bit, end_bit, c->d_sort_scratch, st,
                                   &launches, with_hist));
             return SS_OK;
@@ -815,7 +814,7 @@ SS_API ss_status ss_frame(ss_ctx* c, const ss_view* views, uint32_t n_views, uin
             // Draw-order-resident layout: the sort runs when a static stream changes, not per frame; the records
             // (and the parents) are kept in sorted order, so the kernel streams them.
             if (!c->resident_valid) {
-                ss_status rs = sort_words(false);
+                ss_status rs = sort_words();
                 if (rs != SS_OK) return rs;
                 uint32_t sel = 0;
                 SS_CUDA(c, cudaMemcpyAsync(&sel, &ctl->src_sel[plan.n_passes], sizeof sel, cudaMemcpyDeviceToHost, st));
@@ -851,17 +850,15 @@ SS_API ss_status ss_frame(ss_ctx* c, const ss_view* views, uint32_t n_views, uin
         SS_CUDA(c, cudaEventRecord(c->ev_trs_read[c->trs_cur], st));  // the records hold the transforms now
 
         if (resident) {
-            SS_CUDA(c, cudaEventRecord(s.stage[1], st));
         } else if ((flags & SS_FRAME_REUSE_SORT) && c->words_valid) {
-            SS_CUDA(c, cudaEventRecord(s.stage[1], st));
             words_sel = &ctl->src_sel[plan.n_passes];
         } else {
-            ss_status rs = sort_words(true);
+            ss_status rs = sort_words();
             if (rs != SS_OK) return rs;
             c->words_valid = true;
             words_sel = &ctl->src_sel[plan.n_passes];
         }
-        SS_CUDA(c, cudaEventRecord(s.stage[2], st));
+        SS_CUDA(c, cudaEventRecord(s.stage[1], st));  // fused stages: records | key words + sort | transform + cull | compact + emit | draws
 
         SubmitArgs sa;
         memset(&sa, 0, sizeof sa);
@@ -888,17 +885,51 @@ SS_API ss_status ss_frame(ss_ctx* c, const ss_view* views, uint32_t n_views, uin
         sa.seg_inst = c->d_seg_inst;
         sa.totals = c->d_totals;
         sa.overflow = c->d_overflow;
-        if (!(flags & SS_FRAME_NO_WORLD_ROWS)) {
+        // Two ways from here.  Split (default): k_submit stops after the world rows and masks (word order) and k_emit
+        // compacts them with sequential reads; no tile of either kernel waits for another CTA's arithmetic.  Single
+        // kernel (SS_SUBMIT_SINGLE=1): k_submit also compacts and emits, one tile behind its arithmetic.
+        static const bool single = getenv("SS_SUBMIT_SINGLE") && atoi(getenv("SS_SUBMIT_SINGLE")) != 0;
+        const bool want_rows = !(flags & SS_FRAME_NO_WORLD_ROWS) || !single;
+        if (want_rows) {
             sa.world_out = c->d_world;   // 48 B stride, word order
             sa.mask_out = c->d_mask;
         }
+        sa.rows_only = single ? 0 : 1;
         SS_CUDA(c, launch_submit(sa, cp, st));
         ++launches;
+        SS_CUDA(c, cudaEventRecord(s.stage[2], st));
+        if (!single) {
+            EmitArgs ea;
+            memset(&ea, 0, sizeof ea);
+            ea.keys_a = sa.words_a;
+            ea.keys_b = sa.words_b;
+            ea.sort_ctl = sa.sort_ctl;
+            ea.sort_passes = sa.sort_passes;
+            ea.idx_bits = (uint32_t)idx_bits;
+            ea.mask_bits = 0;
+            ea.seq = 1;
+            ea.mask = c->d_mask;
+            ea.world = c->d_world;
+            ea.n = n;
+            ea.n_views = n_views;
+            for (uint32_t v = 0; v < n_views; ++v) ea.out[v] = s.out[v];
+            ea.cap_visible = c->cap_visible;
+            ea.max_draws = c->max_draws;
+            ea.lookback = c->d_lookback;
+            ea.ticket = c->d_ticket;
+            ea.seg_count = sa.seg_count;
+            ea.seg_key = c->d_seg_key;
+            ea.seg_inst = c->d_seg_inst;
+            ea.totals = c->d_totals;
+            ea.overflow = c->d_overflow;
+            launch_emit(ea, st);
+            ++launches;
+        }
         c->nodes_valid = true;
         c->world_valid = c->sort_valid = false;  // the instance-order rows / packed words of the other pipeline are gone
         c->words_idx_bits = (uint32_t)idx_bits;
         c->last_pipeline = resident ? SS_PIPELINE_FUSED_RESIDENT : SS_PIPELINE_FUSED;
-        c->last_world_rows = !(flags & SS_FRAME_NO_WORLD_ROWS);
+        c->last_world_rows = want_rows;
         SS_CUDA(c, cudaEventRecord(s.stage[3], st));
     } else {
         SS_CUDA(c, cudaEventRecord(s.stage[0], st));

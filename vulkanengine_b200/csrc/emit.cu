@@ -70,7 +70,7 @@ __global__ void __launch_bounds__(kEmitThreads, 4) k_emit(const __grid_constant_
     const uint32_t n_valid = min((uint32_t)kEmitTile, a.n - tile_base);
     const uint32_t n_tiles = (a.n + kEmitTile - 1) / kEmitTile;
 
-    const bool in_b = a.sort_ctl->src_sel[a.sort_passes] != 0;
+    const bool in_b = a.sort_ctl && a.sort_ctl->src_sel[a.sort_passes] != 0;
     const uint64_t* __restrict__ keys = in_b ? a.keys_b : a.keys_a;
     const uint32_t* __restrict__ vals = in_b ? a.vals_b : a.vals_a;
 
@@ -102,13 +102,23 @@ __global__ void __launch_bounds__(kEmitThreads, 4) k_emit(const __grid_constant_
         for (int j = 0; j < kEmitItems; ++j) {
             const bool ok = l0 + j < n_valid;
             idx[j] = ok ? (uint32_t)(key[j] & imask) : 0u;
-            m[j] = (ok && !a.gather_mask) ? (uint32_t)(key[j] >> a.idx_bits) & 0xffu : 0u;
+            m[j] = (ok && !a.gather_mask && !a.seq) ? (uint32_t)(key[j] >> a.idx_bits) & 0xffu : 0u;
             key[j] = ok ? key[j] >> key_shift : ~0ull;
+        }
+    }
+    if (a.seq) {  // masks in word order: this thread's four bytes are one aligned word
+        if (l0 + kEmitItems <= n_valid) {
+            const uint32_t mw = __ldg(reinterpret_cast<const uint32_t*>(a.mask + tile_base + l0));
+#pragma unroll
+            for (int j = 0; j < kEmitItems; ++j) m[j] = (mw >> (8 * j)) & 0xffu;
+        } else {
+#pragma unroll
+            for (int j = 0; j < kEmitItems; ++j) m[j] = (l0 + j < n_valid) ? (uint32_t)__ldg(a.mask + tile_base + l0 + j) : 0u;
         }
     }
 #pragma unroll
     for (int j = 0; j < kEmitItems; ++j) {
-        if (a.gather_mask) m[j] = (l0 + j < n_valid) ? (uint32_t)__ldg(a.mask + idx[j]) : 0u;
+        if (a.gather_mask && !a.seq) m[j] = (l0 + j < n_valid) ? (uint32_t)__ldg(a.mask + idx[j]) : 0u;
         s.key[l0 + j] = key[j];
         s.idx[l0 + j] = idx[j];
     }
@@ -291,7 +301,9 @@ __global__ void __launch_bounds__(kEmitThreads, 4) k_emit(const __grid_constant_
                     const uint32_t j = j0 + u * kEmitThreads;
                     if (j < total4) {
                         const uint32_t e = j / 3u, part = j - e * 3u;
-                        r[u] = __ldg(a.world + (size_t)s.idx[s.list[v][e]] * kWorldStride + part);
+                        const uint32_t li = s.list[v][e];
+                        r[u] = __ldg(a.seq ? a.world + ((size_t)tile_base + li) * 3u + part
+                                           : a.world + (size_t)s.idx[li] * kWorldStride + part);
                     }
                 }
 #pragma unroll
@@ -338,7 +350,8 @@ __global__ void __launch_bounds__(kEmitThreads, 4) k_emit(const __grid_constant_
         for (int u = 0; u < kGatherBatch; ++u) {
             const uint32_t j = tid + (u0 + u) * kEmitThreads;
             const uint32_t e = j / 3u, part = j - e * 3u;
-            if (u0 + u < kParts && s.msk[e]) r[u] = __ldg(a.world + (size_t)s.idx[e] * kWorldStride + part);
+            if (u0 + u < kParts && s.msk[e])
+                r[u] = __ldg(a.seq ? a.world + ((size_t)tile_base + e) * 3u + part : a.world + (size_t)s.idx[e] * kWorldStride + part);
         }
 #pragma unroll
         for (int u = 0; u < kGatherBatch; ++u) {

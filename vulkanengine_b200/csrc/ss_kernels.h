@@ -122,6 +122,8 @@ struct EmitArgs {
     uint32_t idx_bits;             // > 0: sorted words are [key | mask | instance]
     uint32_t mask_bits;            // 8: a visibility byte sits above the instance index (layout of the word)
     uint32_t gather_mask;          // 1: read visibility from mask[] (no byte in the word, or a reused, stale one)
+    uint32_t seq;                  // 1: world rows (12 floats each) and masks lie in WORD order: entry j belongs to sorted
+                                   //    word j, so the "gather" is a sequential read (split pipeline, submit.cu)
     const uint8_t* mask;
     const float4* world;
     uint32_t n;
@@ -229,6 +231,7 @@ struct SubmitArgs {
     const SlotDev* slots;
     uint32_t n, n_views, idx_bits;
     int gather;                    // 1: record of word j is rec[instance]; 0: rec[j]
+    int rows_only;                 // 1: stop after the world rows and masks (word order); k_emit compacts them
     int has_box;
     ViewOut out[SS_MAX_VIEWS];
     uint32_t cap_visible, max_draws;

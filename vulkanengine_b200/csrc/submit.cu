@@ -81,6 +81,7 @@ __device__ __forceinline__ void warp_walk(const uint32_t* lb, uint32_t stride, i
     }
     while (open) {
         uint32_t v[kLbPerWarp];
+        bool progress = false;
 #pragma unroll
         for (int j = 0; j < kLbPerWarp; ++j) {
             const int64_t t = start[j] - lane;
@@ -96,12 +97,16 @@ __device__ __forceinline__ void warp_walk(const uint32_t* lb, uint32_t stride, i
                 const int first_prefix = has_p ? __ffs(has_p) - 1 : 32;
                 const int take = min(first_missing, first_prefix + 1);  // lanes [0, take) are usable
                 out[j] += __reduce_add_sync(0xffffffffu, lane < take ? (v[j] & kLbValue) : 0u);
+                progress = progress || take > 0;
                 if (first_prefix < first_missing)
                     open &= ~(1u << j);
                 else
                     start[j] -= take;  // take may be 0: the nearest element has not published yet, poll again
             }
         }
+        // nothing new was published: leave the issue slots to the warps that compute (a polling warp that spins at full
+        // rate slows down the very CTAs it is waiting for)
+        if (open && !progress) __nanosleep(256);
     }
 }
 

@@ -336,7 +336,12 @@ __global__ void __launch_bounds__(kSubThreads, 5) k_submit(const __grid_constant
         const uint32_t mask0 = live0 ? cm.x : 0u, mask1 = live1 ? cm.y : 0u;
 
         // ---- the tile staged one iteration ago leaves now: its prefixes had this tile's arithmetic to become known
-        if (k > 0) emit_staged_tile<HAS_PARENT>(a, s, s.words[(k - 1) & 1u], staged_tile, n_tiles, imask, tid, lane, wid);
+        if (a.rows_only) {
+            if (tid == 0) bulk_wait_read();  // the previous tile's bulk stores have read the staging buffers
+            __syncthreads();
+        } else if (k > 0) {
+            emit_staged_tile<HAS_PARENT>(a, s, s.words[(k - 1) & 1u], staged_tile, n_tiles, imask, tid, lane, wid);
+        }
 
         // ---- stage this tile: rows (48 B per item: a lane's three float4 stores hit distinct banks), masks, words
         uint64_t* sw = s.words[k & 1u];
@@ -364,6 +369,15 @@ __global__ void __launch_bounds__(kSubThreads, 5) k_submit(const __grid_constant
             }
             if (n_tile & 15)
                 for (int i = tid; i < n_tile; i += kSubThreads) a.mask_out[base + i] = s.msk[i];
+        }
+        if (a.rows_only) {  // split pipeline: k_emit compacts the rows from here
+            wc0 = wn0; wc1 = wn1;
+            pc0 = pn0; pc1 = pn1;
+            if (GATHER) {
+                wn0 = wf0;
+                wn1 = wf1;
+            }
+            continue;
         }
 
         // ---- ranks: thread t now owns items 2t and 2t + 1 of the tile (word order)
@@ -499,5 +513,9 @@ __global__ void __launch_bounds__(kSubThreads, 5) k_submit(const __grid_constant
         }
     }
     // the last staged tile
+    if (a.rows_only) {
+        if (tid == 0) bulk_wait_read();
+        return;
+    }
     if (k > 0) emit_staged_tile<HAS_PARENT>(a, s, s.words[(k - 1) & 1u], staged_tile, n_tiles, imask, tid, lane, wid);
 }

@@ -263,8 +263,12 @@ class SceneSubmit:
     def frame_stage_ms(self, slot):
         ms = (C.c_float * 5)()
         self._ck(self.lib.ss_frame_stage_ms(self.h, C.c_uint32(slot), ms))
-        # fused pipeline: "instances" = building the key words, "emit" = the fused transform+cull+compact+emit kernel
-        return dict(zip(("hierarchy", "instances", "sort", "emit", "draws"), (float(x) for x in ms)))
+        st = FrameStats()
+        self.lib.ss_frame_sync(self.h, C.c_uint32(slot), C.byref(st))
+        # the fused pipelines sort BEFORE they transform: {records, key words + sort, transform+cull, compact+emit, draws}
+        names = ("hierarchy", "instances", "sort", "emit", "draws") if st.pipeline == PIPELINE_LEGACY else \
+            ("hierarchy", "sort", "instances", "emit", "draws")
+        return dict(zip(names, (float(x) for x in ms)))
 
     # ---- outputs
     def map_outputs(self, slot, view):
