@@ -75,10 +75,6 @@ typedef enum ss_frame_flags {
     /* stage-wise parity: do not run the transform stage, cull/sort/emit from the world rows given
        to ss_upload_world_rows */
     SS_FRAME_WORLD_ROWS_GIVEN = 1,
-    /* the frame does not write the per-instance world rows and visibility bytes (ss_outputs.world_rows / masks,
-       ss_download_world / ss_download_masks): a host that only consumes the per-view lists saves their traffic
-       (49 B per instance).  Honoured by the fused pipeline; the three-kernel pipeline needs the rows itself. */
-    SS_FRAME_NO_WORLD_ROWS = 2,
     /* Batched multi-view work (many cameras over one scene, BASELINE configs[4]): views are processed
        SS_MAX_VIEWS at a time, one ss_frame per batch.  After a first, full frame the transforms have not
        changed, so later batches may keep the world rows of the previous frame (cull + emit only) ... */
@@ -91,22 +87,19 @@ typedef enum ss_frame_flags {
 /* ss_config.flags */
 typedef enum ss_config_flags {
     SS_CONFIG_DEFAULT = 0,
-    /* always run the three-kernel pipeline (transform+cull -> sort -> compact+gather) instead of the fused kernel;
-       for A/B measurements and parity tests of both */
-    SS_CONFIG_LEGACY_PIPELINE = 1,
     /* Draw-order-resident layout.  The sort keys are static between ss_set_* calls (in the reference the std::map nodes
        persist across frames too, VC/Scene/SceneRenderer.cpp:1559-1591), so the library sorts ONCE when a static stream
-       changes and keeps its instance records in (key, instance) order; a frame is then one streaming pass with no
-       sort and no gather.  Transform uploads are re-ordered into the records on the device.  Results are the same
-       lists, bit for bit. */
+       changes and keeps its per-instance streams in (key, instance) order; a frame is then two streaming passes with no
+       sort and no gather.  Transform uploads are re-ordered on the device.  Results are the same lists, bit for bit.
+       Applies to TRS-driven instances on an implicit node map with deterministic trig and a key that shares a word
+       with the instance index; other scenes silently take the general pipeline. */
     SS_CONFIG_DRAW_ORDER_RESIDENT = 2
 } ss_config_flags;
 
 /* which kernels produced a frame (ss_frame_stats.pipeline) */
 typedef enum ss_pipeline {
-    SS_PIPELINE_LEGACY = 0,         /* k_instances -> sort -> k_emit: explicit node maps, libm trig, given world rows, wide keys */
-    SS_PIPELINE_FUSED = 1,          /* key words -> sort -> k_submit (records gathered in draw order) */
-    SS_PIPELINE_FUSED_RESIDENT = 2  /* k_submit streaming draw-order-resident records */
+    SS_PIPELINE_GENERAL = 0,  /* transform+cull+key -> sort -> compact + gather, every frame */
+    SS_PIPELINE_RESIDENT = 2  /* transform+cull over draw-order streams -> compact (sequential); sorted at ss_set_* time */
 } ss_pipeline;
 
 typedef struct ss_ctx ss_ctx;
@@ -162,17 +155,16 @@ typedef struct ss_outputs {
     const ss_draw_cmd* draws;     /* [draws]        one per run of equal keys, in MeshKey order */
     const uint64_t* draw_keys;    /* [draws]        key of each draw (to bind mesh + material) */
     const uint32_t* counts;       /* device: {visible, draws} of this view */
-    /* Every instance's world rows and visibility byte.  NOT per slot: they belong to the most recent ss_frame of the
-       context and are overwritten by the next one (the per-view lists above are what stays valid per slot).
-       Three-kernel pipeline: entry i = instance i, world_stride = 16 floats (row-major 4x4, row 3 = 0,0,0,1).
-       Fused pipeline: entry j = the instance named by world_words[j] & ((1 << world_idx_bits) - 1), i.e. the arrays
-       lie in (key, instance) order, world_stride = 12 floats (TransformData); NULL after SS_FRAME_NO_WORLD_ROWS.
-       ss_download_world / ss_download_masks return instance order either way. */
+    /* Every instance's world rows (row-major 4x4 at a 64 B stride, row 3 = 0,0,0,1) and visibility byte.  NOT per
+       slot: they belong to the most recent ss_frame of the context and are overwritten by the next one (the per-view
+       lists above are what stays valid per slot).  General pipeline: entry i = instance i, world_words = NULL.
+       Draw-order-resident layout: entry j = the instance named by world_words[j] & ((1 << world_idx_bits) - 1), i.e.
+       the arrays lie in (key, instance) order.  ss_download_world / ss_download_masks return instance order either way. */
     const float* world_rows;
     const uint8_t* masks;         /* bit v = visible in view v */
     uint32_t visible;             /* host copies, valid after ss_frame_sync */
     uint32_t n_draws;
-    const uint64_t* world_words;  /* fused pipeline: [instances] sorted words [key | instance]; NULL otherwise */
+    const uint64_t* world_words;  /* resident layout: [instances] sorted words [key | instance]; NULL otherwise */
     uint32_t world_idx_bits;
     uint32_t world_stride;        /* floats per entry of world_rows */
 } ss_outputs;
@@ -279,8 +271,8 @@ SS_API ss_status ss_frame(ss_ctx* ctx, const ss_view* views, uint32_t n_views, u
 SS_API ss_status ss_frame_sync(ss_ctx* ctx, uint32_t slot, ss_frame_stats* stats_out);
 
 /* Device time of the slot's frame by stage, CUDA events on the context stream:
-   {clear + hierarchy levels, transform+cull+key, sort, compact+emit, draws + count read-back}; for the fused
-   pipelines {clear + hierarchy levels + record refresh, key words + sort, transform+cull, compact+emit, draws}.
+   {clear + hierarchy levels (+ re-ordering of changed streams in the resident layout), transform+cull+key, sort,
+   compact+emit, draws + count read-back}.
    The counterpart of the reference's per-pass timestamp queries
    (PV/VulkanRenderCommandBuffer.cpp:150-172). */
 SS_API ss_status ss_frame_stage_ms(ss_ctx* ctx, uint32_t slot, float ms_out[5]);

@@ -17,12 +17,10 @@ def oracle_views(n_views=5, **kw):
     return synth.make_views(lambda *a: O.camera_view_proj(*a), lambda *a: O.cascade_matrices(*a), n_views, **kw)
 
 
-# the three pipelines a frame can take (ss_config.flags): fused kernel over gathered records (default where the
-# scene is eligible), the three-kernel pipeline, the fused kernel over draw-order-resident records
-PIPELINES = [pytest.param(0, id="fused"), pytest.param(S.CONFIG_LEGACY_PIPELINE, id="legacy"),
-             pytest.param(S.CONFIG_DRAW_ORDER_RESIDENT, id="resident")]
-EXPECT_PIPELINE = {0: S.PIPELINE_FUSED, S.CONFIG_LEGACY_PIPELINE: S.PIPELINE_LEGACY,
-                   S.CONFIG_DRAW_ORDER_RESIDENT: S.PIPELINE_FUSED_RESIDENT}
+# the two pipelines a frame can take (ss_config.flags): the general one (transform -> sort -> gather, every frame) and the
+# draw-order-resident layout (sorted when a static stream changes; a frame streams)
+PIPELINES = [pytest.param(0, id="general"), pytest.param(S.CONFIG_DRAW_ORDER_RESIDENT, id="resident")]
+EXPECT_PIPELINE = {0: S.PIPELINE_GENERAL, S.CONFIG_DRAW_ORDER_RESIDENT: S.PIPELINE_RESIDENT}
 
 
 def run_gpu(sc, views, trig_mode=S.TRIG_DETERMINISTIC, flags=0, world=None, pipe=None, **cfg):
@@ -275,7 +273,7 @@ def test_full_size_16m_properties_and_mask_parity(pipe):
     st = ctx.frame_sync(slot)
     assert int(st.pipeline) == EXPECT_PIPELINE[pipe]
     masks = ctx.download_masks()
-    if "rows" not in _FULL_REF:  # one oracle run serves the three pipelines
+    if "rows" not in _FULL_REF:  # one oracle run serves both pipelines
         osc = O.OracleScene(sc, 0)
         import ctypes as C
         rows = np.empty((n, 12), np.float32)
@@ -385,7 +383,7 @@ _CFG2_REF = {}
 
 
 def _cfg2_reference(sc, views):
-    if "ref" not in _CFG2_REF:  # one oracle run serves the three pipelines
+    if "ref" not in _CFG2_REF:  # one oracle run serves both pipelines
         _CFG2_REF["ref"] = O.OracleScene(sc, 0).frame(views, threads=8)
     return _CFG2_REF["ref"]
 
@@ -524,7 +522,7 @@ def test_randomised_configurations(case):
             views["flags"][::2] = synth.VIEW_SKIP_NEAR
     osc = O.OracleScene(sc, 0)
     ref = osc.frame(views)
-    pipe = [0, S.CONFIG_LEGACY_PIPELINE, S.CONFIG_DRAW_ORDER_RESIDENT][(case // 3) % 3]
+    pipe = [0, S.CONFIG_DRAW_ORDER_RESIDENT][(case // 3) % 2]
     ctx = S.SceneSubmit(sc.n_nodes, sc.n_instances, len(sc.slots), max_views=n_views, frames_in_flight=int(rng.integers(1, 4)),
                         flags=pipe)
     ctx.load_scene(sc)

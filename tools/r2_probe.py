@@ -19,9 +19,7 @@ def main():
     n = 1 << log2n
     sc = synth.flat_scene(n)
     views = synth.make_views(S.camera_view_proj, S.cascade_matrices, 5)
-    cases = [("legacy", S.CONFIG_LEGACY_PIPELINE, 0), ("fused", 0, 0), ("fused, no world rows", 0, S.FRAME_NO_WORLD_ROWS),
-             ("fused, reuse sort", 0, S.FRAME_REUSE_SORT), ("resident", S.CONFIG_DRAW_ORDER_RESIDENT, 0),
-             ("resident, no world rows", S.CONFIG_DRAW_ORDER_RESIDENT, S.FRAME_NO_WORLD_ROWS)]
+    cases = [("general", 0, 0), ("general, reuse sort", 0, S.FRAME_REUSE_SORT), ("resident", S.CONFIG_DRAW_ORDER_RESIDENT, 0)]
     ref_vis = None
     for name, cflags, fflags in cases:
         if only and not any(o in name for o in only):

@@ -28,7 +28,7 @@ def main():
         c = S.SceneSubmit(sc.n_nodes, n, len(sc.slots), max_views=5, max_draws_per_view=1 << 16, flags=fl)
         c.load_scene(sc)
         return c
-    ref = make(S.CONFIG_LEGACY_PIPELINE)
+    ref = make(0)
     slot = ref.frame(views)
     st = ref.frame_sync(slot)
     rmask = ref.download_masks()
@@ -45,7 +45,7 @@ def main():
         if ok and f % 8 == 0:
             ok = np.array_equal(ctx.download_view(slot, 0, st)["idx"], ridx)
         bad += 0 if ok else 1
-    print(f"flags {flags} n {n} hier {hier} chunks {os.environ.get('SS_SEQ_CHUNKS', 'default')}: {bad} bad frames of {frames} "
+    print(f"flags {flags} n {n} hier {hier}: {bad} bad frames of {frames} "
           f"(pipeline {S.PIPELINE_NAMES[int(st.pipeline)]})", flush=True)
     ctx.close()
     return 1 if bad else 0

@@ -30,9 +30,9 @@ struct Slot {
     int launches = 0;
     ss_view views[SS_MAX_VIEWS];      // as given to ss_frame (ss_raster_view projects with them)
     int pipeline = 0;                 // ss_pipeline that produced the slot
-    const uint64_t* words_known = nullptr;  // fused pipeline: the sorted words, when the host knows the buffer
+    const uint64_t* words_known = nullptr;  // resident layout: the sorted words
     uint32_t idx_bits = 0;
-    bool world_rows = true;
+
     // pinned host mirror
     uint32_t* h_counts = nullptr;     // [max_views][2] + overflow + passes_run: mapped pinned, written by k_draws
     uint32_t* h_counts_dev = nullptr; // the same words as the device sees them
@@ -102,19 +102,19 @@ struct ss_ctx {
     uint64_t* d_seg_key = nullptr;
     uint32_t* d_seg_inst = nullptr;
 
-    // fused pipeline (submit.cu): one 64 B record per instance, sorted words, their inverse for the resident layout
-    InstRec* d_rec = nullptr;
-    int32_t* d_parent_rec = nullptr;       // resident layout: parent of record r
-    uint32_t* d_pos = nullptr;             // resident layout: pos[instance] = record
-    uint32_t* d_sub_lookback = nullptr;
-    bool rec_static_dirty = true;          // box / slot / order of the records is stale: rebuild them whole
-    uint32_t rec_trs_lo = 0, rec_trs_hi = 0;  // instance range whose TRS changed since the records were built (lo >= hi: none)
-    bool words_valid = false;              // the sort buffers hold the sorted words of the current static streams
-    bool resident_valid = false;           // the records lie in draw order (SS_CONFIG_DRAW_ORDER_RESIDENT)
+    // draw-order-resident layout (resident.cu): the per-instance streams once more, in (key, instance) order
+    float* d_trs_o = nullptr;
+    float* d_box_o = nullptr;
+    uint32_t* d_slot_o = nullptr;
+    uint32_t* d_matword_o = nullptr;
+    int32_t* d_parent_o = nullptr;
+    uint32_t* d_pos = nullptr;             // pos[instance] = sorted position
+    bool res_static_dirty = true;          // box / slot / material / parent / order of the permuted streams is stale
+    bool res_trs_dirty = true;             // transforms changed since the permuted TRS stream was built
+    bool resident_valid = false;           // the sort buffers hold the sorted words of the current static streams
     const uint64_t* d_words_resident = nullptr;
     uint32_t words_idx_bits = 0;
     int last_pipeline = 0;                 // ss_pipeline of the most recent frame
-    bool last_world_rows = true;           // ... and whether it wrote world rows / masks
     bool nodes_valid = false;              // d_node_world holds the parent levels of the current transforms
 
     std::vector<Slot> slots;
@@ -221,27 +221,12 @@ void planes_from_view_proj(const float* vp, ViewPlanes& out)
 // Implicit node map (instance i sits on node node_base + i) under a parent chain: ss_frame composes the levels ABOVE
 // node_base with k_node_level and the instance kernel composes the instances' own level from world[parent], so every
 // instance node must belong to the last level.  Without parents every node is a root and any range is fine.
-// a static stream changed: kept world rows, sorted orders and instance records are all stale
+// a static stream changed: kept world rows, sorted orders and the draw-order streams are all stale
 void invalidate_static(ss_ctx* c)
 {
     c->world_valid = c->sort_valid = c->nodes_valid = false;
-    c->words_valid = c->resident_valid = false;
-    c->rec_static_dirty = true;
-}
-
-// TRS of nodes [first, first + count) changed: the records of the instances on them must be refreshed
-void mark_trs_dirty(ss_ctx* c, uint64_t first, uint64_t count)
-{
-    const uint64_t nb = c->node_base, n = c->n_instances;
-    const uint64_t lo = first > nb ? first - nb : 0, hi = std::min<uint64_t>(first + count > nb ? first + count - nb : 0, n);
-    if (lo >= hi) return;
-    if (c->rec_trs_lo >= c->rec_trs_hi) {
-        c->rec_trs_lo = (uint32_t)lo;
-        c->rec_trs_hi = (uint32_t)hi;
-    } else {
-        c->rec_trs_lo = std::min<uint32_t>(c->rec_trs_lo, (uint32_t)lo);
-        c->rec_trs_hi = std::max<uint32_t>(c->rec_trs_hi, (uint32_t)hi);
-    }
+    c->resident_valid = false;
+    c->res_static_dirty = true;
 }
 
 bool implicit_nodes_in_last_level(const ss_ctx* c, uint32_t node_base, uint32_t n)
@@ -300,7 +285,7 @@ SS_API ss_status ss_create(const ss_config* cfg, ss_ctx** out)
     if (cfg->struct_size != sizeof(ss_config) || cfg->max_views < 1 || cfg->max_views > SS_MAX_VIEWS ||
         cfg->max_instances == 0 || cfg->max_nodes == 0 || cfg->max_submesh_slots == 0 ||
         cfg->max_instances >= (1u << 30) || cfg->trig_mode > SS_TRIG_LIBM ||
-        (cfg->flags & ~(uint32_t)(SS_CONFIG_LEGACY_PIPELINE | SS_CONFIG_DRAW_ORDER_RESIDENT))) {
+        (cfg->flags & ~(uint32_t)SS_CONFIG_DRAW_ORDER_RESIDENT)) {
         g_create_error = "ss_create: invalid ss_config (struct_size, capacities 1..2^30-1, max_views 1..8, trig_mode, flags)";
         return SS_ERR_INVALID;
     }
@@ -350,7 +335,7 @@ SS_API ss_status ss_create(const ss_config* cfg, ss_ctx** out)
     TRY(dev_alloc(c, &c->d_trs_buf[0], NN * 9));
     TRY(dev_alloc(c, &c->d_trs_buf[1], NN * 9));
     c->d_trs = c->d_trs_buf[0];
-    TRY(dev_alloc(c, &c->d_parent, NN + kSubPad));
+    TRY(dev_alloc(c, &c->d_parent, NN));
     TRY(dev_alloc(c, &c->d_node_world, NN * 3));
     TRY(dev_alloc(c, &c->d_node, N));
     TRY(dev_alloc(c, &c->d_slot, N));
@@ -359,22 +344,24 @@ SS_API ss_status ss_create(const ss_config* cfg, ss_ctx** out)
     TRY(dev_alloc(c, &c->d_slots, (size_t)cfg->max_submesh_slots));
     TRY(dev_alloc(c, &c->d_world, N * kWorldStride));
     TRY(dev_alloc(c, &c->d_mask, N));
-    TRY(dev_alloc(c, &c->d_keys_a, N + kSubPad));  // padded: the fused kernel copies whole tiles
-    TRY(dev_alloc(c, &c->d_keys_b, N + kSubPad));
-    TRY(dev_alloc(c, &c->d_rec, N + kSubPad));
+    TRY(dev_alloc(c, &c->d_keys_a, N));
+    TRY(dev_alloc(c, &c->d_keys_b, N));
     if (cfg->flags & SS_CONFIG_DRAW_ORDER_RESIDENT) {
-        TRY(dev_alloc(c, &c->d_parent_rec, N + kSubPad));
+        TRY(dev_alloc(c, &c->d_trs_o, N * 9));
+        TRY(dev_alloc(c, &c->d_box_o, N * 6));
+        TRY(dev_alloc(c, &c->d_slot_o, N));
+        TRY(dev_alloc(c, &c->d_matword_o, N));
+        TRY(dev_alloc(c, &c->d_parent_o, N));
         TRY(dev_alloc(c, &c->d_pos, N));
     }
     TRY(dev_alloc(c, &c->d_vals_a, N));
     TRY(dev_alloc(c, &c->d_vals_b, N));
     TRY(dev_alloc(c, reinterpret_cast<unsigned char**>(&c->d_sort_scratch), sort_scratch_bytes(N)));
 
-    const size_t lb_bytes = (std::max(emit_lookback_bytes(N), submit_lookback_bytes(N)) + 255) & ~size_t(255);
+    const size_t lb_bytes = (emit_lookback_bytes(N) + 255) & ~size_t(255);
     c->emit_zero_bytes = lb_bytes + 256;
     TRY(dev_alloc(c, &c->d_emit_zero, c->emit_zero_bytes));
     c->d_lookback = reinterpret_cast<uint32_t*>(c->d_emit_zero);
-    c->d_sub_lookback = c->d_lookback;  // the two pipelines never run in the same frame
     c->d_ticket = reinterpret_cast<uint32_t*>(c->d_emit_zero + lb_bytes);
     c->d_totals = c->d_ticket + 16;
     c->d_overflow = c->d_ticket + 32;
@@ -540,7 +527,7 @@ SS_API ss_status ss_set_instances(ss_ctx* c, uint32_t n, const uint32_t* node, u
 SS_API ss_status ss_set_instance_aabbs(ss_ctx* c, uint32_t first, uint32_t count, const float* minmax6)
 {
     if (!c) return SS_ERR_INVALID;
-    c->rec_static_dirty = true;  // the records carry the boxes
+    c->res_static_dirty = true;  // the draw-order streams carry the boxes
     if (!minmax6) {
         c->has_inst_aabb = false;
         return SS_OK;
@@ -584,7 +571,7 @@ SS_API ss_status ss_upload_trs(ss_ctx* c, uint32_t first, uint32_t count, const 
     SS_CUDA(c, cudaSetDevice(c->device));
     if (!count) return SS_OK;
     c->world_valid = c->nodes_valid = false;  // transforms changed
-    mark_trs_dirty(c, first, count);
+    c->res_trs_dirty = true;
     if (first == 0 && count == c->n_nodes && count >= kAsyncUploadMinNodes) {
         const int tgt = c->trs_cur ^ 1;
         SS_CUDA(c, cudaStreamWaitEvent(c->upload_stream, c->ev_trs_read[tgt], 0));  // its last reader is past the transform stage
@@ -637,14 +624,7 @@ SS_API ss_status ss_upload_trs_sparse(ss_ctx* c, uint32_t count, const uint32_t*
         hi[j] = node_index[k];
     }
     c->world_valid = c->nodes_valid = false;  // transforms changed
-    {
-        uint32_t mn = 0xffffffffu, mx = 0;
-        for (uint32_t k = 0; k < count; ++k) {
-            mn = std::min(mn, node_index[k]);
-            mx = std::max(mx, node_index[k]);
-        }
-        mark_trs_dirty(c, mn, (uint64_t)mx - mn + 1);
-    }
+    c->res_trs_dirty = true;
     SS_CUDA(c, adopt_pending_upload(c));  // lands on top of whatever whole-stream upload came before it
     SS_CUDA(c, cudaMemcpyAsync(c->d_sparse, c->h_sparse, (size_t)kept * 40, cudaMemcpyHostToDevice, c->stream));
     SS_CUDA(c, cudaEventRecord(c->ev_sparse, c->stream));
@@ -731,15 +711,14 @@ SS_API ss_status ss_frame(ss_ctx* c, const ss_view* views, uint32_t n_views, uin
     while (idx_bits < 32 && (1ull << idx_bits) < (uint64_t)n) ++idx_bits;
     const bool packed = idx_bits + key_bits <= 64;
 
-    // Which pipeline.  The fused kernel (submit.cu) serves TRS-driven instances with an implicit node map and
-    // deterministic trig whose key and index share a word; everything else takes the three-kernel pipeline.
-    const bool fused = !(c->cfg.flags & SS_CONFIG_LEGACY_PIPELINE) && !c->has_node_map &&
-                       c->cfg.trig_mode == SS_TRIG_DETERMINISTIC && !(flags & SS_FRAME_WORLD_ROWS_GIVEN) && n > 0 && packed;
-    const bool resident = fused && (c->cfg.flags & SS_CONFIG_DRAW_ORDER_RESIDENT);
+    // Which pipeline.  The draw-order-resident layout serves TRS-driven instances with an implicit node map and
+    // deterministic trig whose key and index share a word; everything else takes the general three-kernel pipeline.
+    const bool resident = (c->cfg.flags & SS_CONFIG_DRAW_ORDER_RESIDENT) && !c->has_node_map &&
+                          c->cfg.trig_mode == SS_TRIG_DETERMINISTIC && !(flags & SS_FRAME_WORLD_ROWS_GIVEN) && n > 0 && packed;
     // world rows already on the device: uploaded for stage-wise parity, or kept from the previous frame
-    const bool world_given = !fused && ((flags & SS_FRAME_WORLD_ROWS_GIVEN) || ((flags & SS_FRAME_REUSE_WORLD) && c->world_valid));
-    const bool nodes_kept = fused && (flags & SS_FRAME_REUSE_WORLD) && c->nodes_valid;  // node rows of the parent levels
-    const bool reuse_sort = !fused && (flags & SS_FRAME_REUSE_SORT) && c->sort_valid;
+    const bool world_given = !resident && ((flags & SS_FRAME_WORLD_ROWS_GIVEN) || ((flags & SS_FRAME_REUSE_WORLD) && c->world_valid));
+    const bool nodes_kept = resident && (flags & SS_FRAME_REUSE_WORLD) && c->nodes_valid;  // node rows of the parent levels
+    const bool reuse_sort = !resident && (flags & SS_FRAME_REUSE_SORT) && c->sort_valid;
 
     SS_CUDA(c, adopt_pending_upload(c));
     SS_CUDA(c, cudaEventRecord(s.start, st));
@@ -764,15 +743,16 @@ SS_API ss_status ss_frame(ss_ctx* c, const ss_view* views, uint32_t n_views, uin
     }
 
     const size_t seg_words = (size_t)c->cfg.max_views * c->max_draws;
-    const uint32_t* words_sel = nullptr;      // device word telling which sort buffer holds the fused pipeline's words
-    const uint64_t* words_known = nullptr;    // ... or the buffer itself, when the host knows it
+    const uint64_t* words_known = nullptr;    // resident layout: the sorted words
 
-    if (fused) {
+    if (resident) {
+        // Draw-order-resident layout: the sort runs when a static stream changes, not per frame; the streams are kept
+        // in sorted order, so the instance kernel writes world rows and masks in draw order and k_emit streams them.
         const int begin_bit = idx_bits, end_bit = idx_bits + key_bits;
         const SortPlan plan = sort_plan(begin_bit, end_bit);
         const uint64_t imask = (1ull << idx_bits) - 1ull;
         SortControl* ctl = reinterpret_cast<SortControl*>(c->d_sort_scratch);
-        auto sort_words = [&]() -> ss_status {
+        if (!c->resident_valid) {
             const bool with_hist = plan.n_passes <= 3;
             WordsArgs wa;
             memset(&wa, 0, sizeof wa);
@@ -796,140 +776,87 @@ SS_API ss_status ss_frame(ss_ctx* c, const ss_view* views, uint32_t n_views, uin
             ++launches;
             SS_CUDA(c, sort_async(c->d_keys_a, nullptr, c->d_keys_b, nullptr, n, begin_bit, end_bit, c->d_sort_scratch, st,
                                   &launches, with_hist));
-            return SS_OK;
-        };
-        PackArgs pa;
-        memset(&pa, 0, sizeof pa);
-        pa.rec = c->d_rec;
-        pa.trs = c->d_trs + (size_t)c->node_base * 9;
-        pa.inst_aabb = c->has_inst_aabb ? c->d_inst_aabb : nullptr;
-        pa.slot = c->d_slot;
-        pa.parent = c->has_parent ? c->d_parent + c->node_base : nullptr;
-        pa.idx_mask = imask;
-        pa.n = n;
-        pa.lo = 0;
-        pa.hi = n;
-        const bool trs_dirty = c->rec_trs_lo < c->rec_trs_hi;
-        if (resident) {
-            // Draw-order-resident layout: the sort runs when a static stream changes, not per frame; the records
-            // (and the parents) are kept in sorted order, so the kernel streams them.
-            if (!c->resident_valid) {
-                ss_status rs = sort_words();
-                if (rs != SS_OK) return rs;
-                uint32_t sel = 0;
-                SS_CUDA(c, cudaMemcpyAsync(&sel, &ctl->src_sel[plan.n_passes], sizeof sel, cudaMemcpyDeviceToHost, st));
-                SS_CUDA(c, cudaStreamSynchronize(st));
-                c->d_words_resident = sel ? c->d_keys_b : c->d_keys_a;
-                c->resident_valid = true;
-                c->rec_static_dirty = true;
-            }
+            uint32_t sel = 0;
+            SS_CUDA(c, cudaMemcpyAsync(&sel, &ctl->src_sel[plan.n_passes], sizeof sel, cudaMemcpyDeviceToHost, st));
+            SS_CUDA(c, cudaStreamSynchronize(st));
+            c->d_words_resident = sel ? c->d_keys_b : c->d_keys_a;
+            c->resident_valid = true;
+            c->res_static_dirty = true;
+        }
+        if (c->res_static_dirty || c->res_trs_dirty) {
+            PermuteArgs pa;
+            memset(&pa, 0, sizeof pa);
             pa.order = c->d_words_resident;
-            pa.pos = c->d_pos;
-            pa.parent_out = c->d_parent_rec;
-            if (c->rec_static_dirty || trs_dirty) {
-                pa.trs_only = c->rec_static_dirty ? 0 : 1;
-                launch_pack_records(pa, st);
-                ++launches;
-            }
-            words_known = c->d_words_resident;
-        } else {
-            if (c->rec_static_dirty) {
-                launch_pack_records(pa, st);
-                ++launches;
-            } else if (trs_dirty) {
-                pa.trs_only = 1;
-                pa.lo = c->rec_trs_lo;
-                pa.hi = c->rec_trs_hi;
-                launch_pack_records(pa, st);
-                ++launches;
-            }
-        }
-        c->rec_static_dirty = false;
-        c->rec_trs_lo = c->rec_trs_hi = 0;
-        SS_CUDA(c, cudaEventRecord(s.stage[0], st));
-        SS_CUDA(c, cudaEventRecord(c->ev_trs_read[c->trs_cur], st));  // the records hold the transforms now
-
-        if (resident) {
-        } else if ((flags & SS_FRAME_REUSE_SORT) && c->words_valid) {
-            words_sel = &ctl->src_sel[plan.n_passes];
-        } else {
-            ss_status rs = sort_words();
-            if (rs != SS_OK) return rs;
-            c->words_valid = true;
-            words_sel = &ctl->src_sel[plan.n_passes];
-        }
-        SS_CUDA(c, cudaEventRecord(s.stage[1], st));  // fused stages: records | key words + sort | transform + cull | compact + emit | draws
-
-        SubmitArgs sa;
-        memset(&sa, 0, sizeof sa);
-        sa.rec = c->d_rec;
-        sa.words_a = resident ? c->d_words_resident : c->d_keys_a;
-        sa.words_b = c->d_keys_b;
-        sa.sort_ctl = resident ? nullptr : ctl;
-        sa.sort_passes = (uint32_t)plan.n_passes;
-        sa.parent = !c->has_parent ? nullptr : resident ? c->d_parent_rec : c->d_parent + c->node_base;
-        sa.node_world = c->d_node_world;
-        sa.slots = c->d_slots;
-        sa.n = n;
-        sa.n_views = n_views;
-        sa.idx_bits = (uint32_t)idx_bits;
-        sa.gather = resident ? 0 : 1;
-        sa.has_box = c->has_inst_aabb ? 1 : 0;
-        for (uint32_t v = 0; v < n_views; ++v) sa.out[v] = s.out[v];
-        sa.cap_visible = c->cap_visible;
-        sa.max_draws = c->max_draws;
-        sa.lookback = c->d_sub_lookback;
-        sa.lb_stride = submit_lookback_stride(n);
-        sa.seg_count = c->d_seg_count + c->seg_parity * seg_words;
-        sa.seg_key = c->d_seg_key;
-        sa.seg_inst = c->d_seg_inst;
-        sa.totals = c->d_totals;
-        sa.overflow = c->d_overflow;
-        // Two ways from here.  Split (default): k_submit stops after the world rows and masks (word order) and k_emit
-        // compacts them with sequential reads; no tile of either kernel waits for another CTA's arithmetic.  Single
-        // kernel (SS_SUBMIT_SINGLE=1): k_submit also compacts and emits, one tile behind its arithmetic.
-        static const bool single = getenv("SS_SUBMIT_SINGLE") && atoi(getenv("SS_SUBMIT_SINGLE")) != 0;
-        const bool want_rows = !(flags & SS_FRAME_NO_WORLD_ROWS) || !single;
-        if (want_rows) {
-            sa.world_out = c->d_world;   // 48 B stride, word order
-            sa.mask_out = c->d_mask;
-        }
-        sa.rows_only = single ? 0 : 1;
-        SS_CUDA(c, launch_submit(sa, cp, st));
-        ++launches;
-        SS_CUDA(c, cudaEventRecord(s.stage[2], st));
-        if (!single) {
-            EmitArgs ea;
-            memset(&ea, 0, sizeof ea);
-            ea.keys_a = sa.words_a;
-            ea.keys_b = sa.words_b;
-            ea.sort_ctl = sa.sort_ctl;
-            ea.sort_passes = sa.sort_passes;
-            ea.idx_bits = (uint32_t)idx_bits;
-            ea.mask_bits = 0;
-            ea.seq = 1;
-            ea.mask = c->d_mask;
-            ea.world = c->d_world;
-            ea.n = n;
-            ea.n_views = n_views;
-            for (uint32_t v = 0; v < n_views; ++v) ea.out[v] = s.out[v];
-            ea.cap_visible = c->cap_visible;
-            ea.max_draws = c->max_draws;
-            ea.lookback = c->d_lookback;
-            ea.ticket = c->d_ticket;
-            ea.seg_count = sa.seg_count;
-            ea.seg_key = c->d_seg_key;
-            ea.seg_inst = c->d_seg_inst;
-            ea.totals = c->d_totals;
-            ea.overflow = c->d_overflow;
-            launch_emit(ea, st);
+            pa.idx_mask = imask;
+            pa.n = n;
+            pa.trs_only = c->res_static_dirty ? 0 : 1;
+            pa.trs = c->d_trs + (size_t)c->node_base * 9;
+            pa.box = c->has_inst_aabb ? c->d_inst_aabb : nullptr;
+            pa.slot = c->d_slot;
+            pa.matword = c->d_matword;
+            pa.parent = c->has_parent ? c->d_parent + c->node_base : nullptr;
+            pa.trs_out = c->d_trs_o;
+            pa.box_out = c->d_box_o;
+            pa.slot_out = c->d_slot_o;
+            pa.matword_out = c->d_matword_o;
+            pa.parent_out = c->d_parent_o;
+            pa.pos_out = c->d_pos;
+            launch_permute(pa, st);
             ++launches;
+            c->res_static_dirty = c->res_trs_dirty = false;
         }
+        SS_CUDA(c, cudaEventRecord(s.stage[0], st));
+        SS_CUDA(c, cudaEventRecord(c->ev_trs_read[c->trs_cur], st));  // the permuted stream holds the transforms now
+
+        InstanceArgs ia;
+        memset(&ia, 0, sizeof ia);
+        ia.trs = c->d_trs_o;
+        ia.parent = c->has_parent ? c->d_parent_o : nullptr;
+        ia.node_world = c->d_node_world;
+        ia.node = nullptr;
+        ia.node_base = 0;
+        ia.slot = c->d_slot_o;
+        ia.matword = c->d_matword_o;
+        ia.inst_aabb = c->has_inst_aabb ? c->d_box_o : nullptr;
+        ia.slots = c->d_slots;
+        ia.world = c->d_world;   // rows of sorted position j
+        ia.mask = c->d_mask;
+        ia.keys = nullptr;       // the order is kept: masks only
+        ia.vals = nullptr;
+        ia.n = n;
+        ia.tess_shift = tess_shift;
+        ia.trig_mode = (int)c->cfg.trig_mode;
+        launch_instances(ia, cp, st);
+        ++launches;
+        SS_CUDA(c, cudaEventRecord(s.stage[1], st));
+        SS_CUDA(c, cudaEventRecord(s.stage[2], st));  // no sort
+
+        EmitArgs ea;
+        memset(&ea, 0, sizeof ea);
+        ea.keys_a = c->d_words_resident;
+        ea.idx_bits = (uint32_t)idx_bits;
+        ea.seq = 1;
+        ea.mask = c->d_mask;
+        ea.world = c->d_world;
+        ea.n = n;
+        ea.n_views = n_views;
+        for (uint32_t v = 0; v < n_views; ++v) ea.out[v] = s.out[v];
+        ea.cap_visible = c->cap_visible;
+        ea.max_draws = c->max_draws;
+        ea.lookback = c->d_lookback;
+        ea.ticket = c->d_ticket;
+        ea.seg_count = c->d_seg_count + c->seg_parity * seg_words;
+        ea.seg_key = c->d_seg_key;
+        ea.seg_inst = c->d_seg_inst;
+        ea.totals = c->d_totals;
+        ea.overflow = c->d_overflow;
+        launch_emit(ea, st);
+        ++launches;
+        words_known = c->d_words_resident;
         c->nodes_valid = true;
-        c->world_valid = c->sort_valid = false;  // the instance-order rows / packed words of the other pipeline are gone
+        c->world_valid = c->sort_valid = false;  // the instance-order rows / packed words of the general pipeline are gone
         c->words_idx_bits = (uint32_t)idx_bits;
-        c->last_pipeline = resident ? SS_PIPELINE_FUSED_RESIDENT : SS_PIPELINE_FUSED;
-        c->last_world_rows = want_rows;
+        c->last_pipeline = SS_PIPELINE_RESIDENT;
         SS_CUDA(c, cudaEventRecord(s.stage[3], st));
     } else {
         SS_CUDA(c, cudaEventRecord(s.stage[0], st));
@@ -978,9 +905,8 @@ SS_API ss_status ss_frame(ss_ctx* c, const ss_view* views, uint32_t n_views, uin
         }
         c->world_valid = true;
         c->nodes_valid = true;
-        c->words_valid = c->resident_valid = false;  // the sort buffers now belong to this pipeline
-        c->last_pipeline = SS_PIPELINE_LEGACY;
-        c->last_world_rows = true;
+        c->resident_valid = false;  // the sort buffers now belong to this pipeline
+        c->last_pipeline = SS_PIPELINE_GENERAL;
         SS_CUDA(c, cudaEventRecord(s.stage[1], st));
         SS_CUDA(c, cudaEventRecord(c->ev_trs_read[c->trs_cur], st));  // the TRS buffer may be overwritten from here on
 
@@ -1036,7 +962,6 @@ SS_API ss_status ss_frame(ss_ctx* c, const ss_view* views, uint32_t n_views, uin
     da.runs_cur = c->d_seg_runs + c->seg_parity;
     da.runs_next = c->d_seg_runs + (c->seg_parity ^ 1u);
     da.passes_run = &reinterpret_cast<SortControl*>(c->d_sort_scratch)->passes_run;
-    da.words_sel = words_sel;
     da.host_stats = s.h_counts_dev;
     da.stats_views = c->cfg.max_views;
     c->seg_parity ^= 1u;
@@ -1059,8 +984,7 @@ SS_API ss_status ss_frame(ss_ctx* c, const ss_view* views, uint32_t n_views, uin
     s.launches = launches;
     s.pipeline = c->last_pipeline;
     s.words_known = words_known;
-    s.idx_bits = fused ? (uint32_t)idx_bits : 0u;
-    s.world_rows = c->last_world_rows;
+    s.idx_bits = resident ? (uint32_t)idx_bits : 0u;
     ++c->frame_no;
     if (slot_out) *slot_out = si;
     return SS_OK;
@@ -1112,17 +1036,16 @@ SS_API ss_status ss_map_outputs(ss_ctx* c, uint32_t slot, uint32_t view, ss_outp
     out->draws = s.out[view].draws;
     out->draw_keys = s.out[view].draw_keys;
     out->counts = s.out[view].counts;
-    out->world_rows = s.world_rows ? reinterpret_cast<const float*>(c->d_world) : nullptr;
-    out->masks = s.world_rows ? c->d_mask : nullptr;
+    out->world_rows = reinterpret_cast<const float*>(c->d_world);
+    out->masks = c->d_mask;
     out->visible = std::min(s.h_counts[view * 2 + 0], c->cap_visible);
     out->n_draws = s.h_counts[view * 2 + 1];
     out->world_words = nullptr;
     out->world_idx_bits = 0;
     out->world_stride = kWorldStride * 4;
-    if (s.pipeline != SS_PIPELINE_LEGACY) {
-        out->world_words = s.words_known ? s.words_known : (s.h_counts[c->cfg.max_views * 2 + 2] ? c->d_keys_b : c->d_keys_a);
+    if (s.pipeline == SS_PIPELINE_RESIDENT) {
+        out->world_words = s.words_known;
         out->world_idx_bits = s.idx_bits;
-        out->world_stride = 12;
     }
     return SS_OK;
 }
@@ -1163,26 +1086,16 @@ static ss_status download_range(ss_ctx* c, const void* src, size_t elem, uint32_
     return SS_OK;
 }
 
-// Fused pipeline: world rows and masks lie in word order; bring the rows / bytes of instances [first, first + count)
+// Draw-order-resident layout: world rows and masks lie in word order; bring the rows / bytes of instances [first, first + count)
 // back to instance order through a scratch buffer (a download is not a per-frame operation).
 static ss_status download_word_ordered(ss_ctx* c, uint32_t first, uint32_t count, float* rows12, uint8_t* masks)
 {
-    if (!c->last_world_rows)
-        return c->fail(SS_ERR_STATE, "the last frame ran with SS_FRAME_NO_WORLD_ROWS: there are no world rows / masks to read");
     SS_CUDA(c, cudaStreamSynchronize(c->stream));
     const uint64_t* words = c->d_words_resident;
-    if (c->last_pipeline == SS_PIPELINE_FUSED) {
-        const int key_bits = (int)(c->mesh_bits + c->submesh_bits + c->material_bits) + 2;
-        const int passes = sort_num_passes((int)c->words_idx_bits, (int)c->words_idx_bits + key_bits);
-        uint32_t sel = 0;
-        SS_CUDA(c, cudaMemcpy(&sel, &reinterpret_cast<SortControl*>(c->d_sort_scratch)->src_sel[passes], sizeof sel,
-                              cudaMemcpyDeviceToHost));
-        words = sel ? c->d_keys_b : c->d_keys_a;
-    }
     void* tmp = nullptr;
     SS_CUDA(c, cudaMalloc(&tmp, std::max<size_t>((size_t)count * (rows12 ? 48 : 1), 256)));
     launch_unpermute(words, (1ull << c->words_idx_bits) - 1ull, c->n_instances, first, count,
-                     reinterpret_cast<const float4*>(c->d_world), rows12 ? static_cast<float4*>(tmp) : nullptr, c->d_mask,
+                     reinterpret_cast<const float4*>(c->d_world), kWorldStride, rows12 ? static_cast<float4*>(tmp) : nullptr, c->d_mask,
                      masks ? static_cast<uint8_t*>(tmp) : nullptr, c->stream);
     cudaError_t e = cudaGetLastError();
     if (e == cudaSuccess)
@@ -1201,7 +1114,7 @@ SS_API ss_status ss_download_world(ss_ctx* c, uint32_t first, uint32_t count, fl
         return c->fail(SS_ERR_INVALID, "ss_download_world: range [%u, +%u) exceeds %u instances", first, count,
                        c->n_instances);
     SS_CUDA(c, cudaSetDevice(c->device));
-    if (count && c->last_pipeline != SS_PIPELINE_LEGACY) return download_word_ordered(c, first, count, rows12, nullptr);
+    if (count && c->last_pipeline == SS_PIPELINE_RESIDENT) return download_word_ordered(c, first, count, rows12, nullptr);
     if (count)  // device rows sit at a 64 B stride; the host gets them packed as TransformData
         SS_CUDA(c, cudaMemcpy2DAsync(rows12, 48, c->d_world + (size_t)first * kWorldStride, kWorldStride * 16, 48, count,
                                      cudaMemcpyDeviceToHost, c->stream));
@@ -1210,7 +1123,7 @@ SS_API ss_status ss_download_world(ss_ctx* c, uint32_t first, uint32_t count, fl
 }
 SS_API ss_status ss_download_masks(ss_ctx* c, uint32_t first, uint32_t count, uint8_t* masks)
 {
-    if (c && masks && count && (uint64_t)first + count <= c->n_instances && c->last_pipeline != SS_PIPELINE_LEGACY) {
+    if (c && masks && count && (uint64_t)first + count <= c->n_instances && c->last_pipeline == SS_PIPELINE_RESIDENT) {
         SS_CUDA(c, cudaSetDevice(c->device));
         return download_word_ordered(c, first, count, nullptr, masks);
     }

@@ -302,7 +302,7 @@ __global__ void __launch_bounds__(kEmitThreads, 4) k_emit(const __grid_constant_
                     if (j < total4) {
                         const uint32_t e = j / 3u, part = j - e * 3u;
                         const uint32_t li = s.list[v][e];
-                        r[u] = __ldg(a.seq ? a.world + ((size_t)tile_base + li) * 3u + part
+                        r[u] = __ldg(a.seq ? a.world + ((size_t)tile_base + li) * kWorldStride + part
                                            : a.world + (size_t)s.idx[li] * kWorldStride + part);
                     }
                 }
@@ -351,7 +351,7 @@ __global__ void __launch_bounds__(kEmitThreads, 4) k_emit(const __grid_constant_
             const uint32_t j = tid + (u0 + u) * kEmitThreads;
             const uint32_t e = j / 3u, part = j - e * 3u;
             if (u0 + u < kParts && s.msk[e])
-                r[u] = __ldg(a.seq ? a.world + ((size_t)tile_base + e) * 3u + part : a.world + (size_t)s.idx[e] * kWorldStride + part);
+                r[u] = __ldg(a.seq ? a.world + ((size_t)tile_base + e) * kWorldStride + part : a.world + (size_t)s.idx[e] * kWorldStride + part);
         }
 #pragma unroll
         for (int u = 0; u < kGatherBatch; ++u) {
@@ -406,7 +406,6 @@ __global__ void __launch_bounds__(kDrawThreads) k_draws(const __grid_constant__ 
         *a.runs_cur = n_segs;
         a.host_stats[a.stats_views * 2] = *a.overflow | over;
         a.host_stats[a.stats_views * 2 + 1] = *a.passes_run;
-        a.host_stats[a.stats_views * 2 + 2] = a.words_sel ? *a.words_sel : 0u;
     }
     // rows of views this frame does not use are cleaned all the same: the frame that filled the other buffer may
     // have run more views than this one (ss_frame takes any n_views up to max_views)

@@ -122,8 +122,8 @@ struct EmitArgs {
     uint32_t idx_bits;             // > 0: sorted words are [key | mask | instance]
     uint32_t mask_bits;            // 8: a visibility byte sits above the instance index (layout of the word)
     uint32_t gather_mask;          // 1: read visibility from mask[] (no byte in the word, or a reused, stale one)
-    uint32_t seq;                  // 1: world rows (12 floats each) and masks lie in WORD order: entry j belongs to sorted
-                                   //    word j, so the "gather" is a sequential read (split pipeline, submit.cu)
+    uint32_t seq;                  // 1: world rows and masks lie in WORD order: entry j belongs to sorted word j, so the
+                                   //    "gather" is a sequential read (draw-order-resident layout, resident.cu)
     const uint8_t* mask;
     const float4* world;
     uint32_t n;
@@ -158,7 +158,6 @@ struct DrawArgs {
     uint32_t* runs_cur;            // out: number of runs this frame put into seg_count
     const uint32_t* runs_next;     // runs the frame before last left in seg_count_next (bounds the zeroing)
     const uint32_t* passes_run;    // SortControl::passes_run, forwarded to the host
-    const uint32_t* words_sel;     // fused pipeline: which sort buffer holds the words (forwarded too), or nullptr
     uint32_t* host_stats;          // mapped pinned host words: [stats_views][2] visible/draws, overflow, passes_run
     uint32_t stats_views;
     const uint64_t* seg_key;
@@ -170,21 +169,7 @@ struct DrawArgs {
 };
 void launch_draws(const DrawArgs& a, cudaStream_t st);
 
-// ---- fused submission kernel (submit.cu) ---------------------------------------------------------
-// One 64 B record per instance: everything the transform + cull of an instance reads, in ONE aligned block, so
-// that fetching an instance in draw order costs one DRAM line instead of three (TRS, box, ids).
-struct InstRec {
-    float trs[9];    // TransformComponent of the instance's node
-    float box[6];    // per-instance local AABB {min, max} (unused when the submesh table's box applies)
-    uint32_t slot;   // submesh table row or SS_SLOT_NULL
-};
-static_assert(sizeof(InstRec) == 64, "InstRec layout");
-
-constexpr int kSubThreads = 128;
-constexpr int kSubTile = 2 * kSubThreads;     // instances per tile
-constexpr int kSubWords = SS_MAX_VIEWS + 1;   // look-back counters: V visible counts + runs
-constexpr int kSubPad = kSubTile;             // elements every array a full-tile bulk copy reads must be padded by
-
+// ---- draw-order-resident layout (resident.cu) -------------------------------------------------------
 // sort words [key | instance] from the static id streams (+ the sort's digit histograms)
 struct WordsArgs {
     const uint32_t* slot;
@@ -201,58 +186,30 @@ struct WordsArgs {
 };
 void launch_build_words(const WordsArgs& a, cudaStream_t st);
 
-// (Re)build instance records from the streams.  order == nullptr: record r describes instance r.  Otherwise record
-// r describes instance order[r] & idx_mask (draw-order-resident layout) and pos / parent_out are filled as well.
-struct PackArgs {
-    InstRec* rec;
-    const float* trs;          // node stream, already offset to the first instance node
-    const float* inst_aabb;    // [n][6] or nullptr
-    const uint32_t* slot;
-    const int32_t* parent;     // node stream, offset like trs, or nullptr
-    const uint64_t* order;     // sorted words or nullptr
+// streams in draw order: entry j of every *_out describes instance order[j] & idx_mask
+struct PermuteArgs {
+    const uint64_t* order;     // sorted words
     uint64_t idx_mask;
-    uint32_t* pos;             // out: pos[instance] = r (with order), or nullptr
-    int32_t* parent_out;       // out: parent of record r (with order), or nullptr
     uint32_t n;
-    uint32_t lo, hi;           // instance range to refresh (identity order only; with an order the whole stream)
-    int trs_only;
+    int trs_only;              // 1: only the transforms changed
+    const float* trs;          // node stream, already offset to the first instance node
+    const float* box;          // [n][6] or nullptr
+    const uint32_t* slot;
+    const uint32_t* matword;
+    const int32_t* parent;     // node stream, offset like trs, or nullptr
+    float* trs_out;
+    float* box_out;
+    uint32_t* slot_out;
+    uint32_t* matword_out;
+    int32_t* parent_out;
+    uint32_t* pos_out;         // pos[instance] = j
 };
-void launch_pack_records(const PackArgs& a, cudaStream_t st);
-
-struct SubmitArgs {
-    const InstRec* rec;
-    const uint64_t* words_a;
-    const uint64_t* words_b;
-    const SortControl* sort_ctl;   // nullptr: the words are words_a
-    uint32_t sort_passes;
-    const int32_t* parent;         // gather: node stream offset to the first instance node, indexed by instance;
-                                   // resident: parent of record r; nullptr: no parent chain
-    const float4* node_world;
-    const SlotDev* slots;
-    uint32_t n, n_views, idx_bits;
-    int gather;                    // 1: record of word j is rec[instance]; 0: rec[j]
-    int rows_only;                 // 1: stop after the world rows and masks (word order); k_emit compacts them
-    int has_box;
-    ViewOut out[SS_MAX_VIEWS];
-    uint32_t cap_visible, max_draws;
-    uint32_t* lookback;            // [kSubWords][lb_stride], zeroed per frame
-    uint32_t lb_stride;
-    uint32_t* seg_count;
-    uint64_t* seg_key;
-    uint32_t* seg_inst;
-    uint32_t* totals;
-    uint32_t* overflow;
-    float4* world_out;             // [n][3] world rows in word order, or nullptr
-    uint8_t* mask_out;             // [n] visibility bytes in word order, or nullptr
-};
-size_t submit_lookback_bytes(uint64_t n);
-uint32_t submit_lookback_stride(uint64_t n);
-cudaError_t launch_submit(const SubmitArgs& a, const CullParams& cp, cudaStream_t st);
+void launch_permute(const PermuteArgs& a, cudaStream_t st);
 
 // rows / bytes of instances [first, first + count) out of word-ordered arrays (downloads, parity tests)
 void launch_unpermute(const uint64_t* words, uint64_t idx_mask, uint32_t n, uint32_t first, uint32_t count,
-                      const float4* world_words, float4* rows_out, const uint8_t* mask_words, uint8_t* mask_out,
-                      cudaStream_t st);
+                      const float4* world_words, uint32_t stride4, float4* rows_out, const uint8_t* mask_words,
+                      uint8_t* mask_out, cudaStream_t st);
 
 // ---- depth + id rasterisation of a view's compacted list (raster.cu) -------------------------------
 struct RasterArgs {

@@ -14,13 +14,11 @@ LIB_PATH = os.path.join(_HERE, "libscenesubmit.so")
 SS_OK, SS_ERR_INVALID, SS_ERR_CUDA, SS_ERR_CAPACITY, SS_ERR_STATE, SS_ERR_NOMEM = range(6)
 TRIG_DETERMINISTIC, TRIG_LIBM = 0, 1
 FRAME_WORLD_ROWS_GIVEN = 1
-FRAME_NO_WORLD_ROWS = 2
 FRAME_REUSE_WORLD = 4
 FRAME_REUSE_SORT = 8
-CONFIG_LEGACY_PIPELINE = 1
 CONFIG_DRAW_ORDER_RESIDENT = 2
-PIPELINE_LEGACY, PIPELINE_FUSED, PIPELINE_FUSED_RESIDENT = 0, 1, 2
-PIPELINE_NAMES = {0: "legacy", 1: "fused", 2: "fused_resident"}
+PIPELINE_GENERAL, PIPELINE_RESIDENT = 0, 2
+PIPELINE_NAMES = {0: "general", 2: "resident"}
 MAX_VIEWS = 8
 SLOT_NULL = 0xFFFFFFFF
 
@@ -263,12 +261,7 @@ class SceneSubmit:
     def frame_stage_ms(self, slot):
         ms = (C.c_float * 5)()
         self._ck(self.lib.ss_frame_stage_ms(self.h, C.c_uint32(slot), ms))
-        st = FrameStats()
-        self.lib.ss_frame_sync(self.h, C.c_uint32(slot), C.byref(st))
-        # the fused pipelines sort BEFORE they transform: {records, key words + sort, transform+cull, compact+emit, draws}
-        names = ("hierarchy", "instances", "sort", "emit", "draws") if st.pipeline == PIPELINE_LEGACY else \
-            ("hierarchy", "sort", "instances", "emit", "draws")
-        return dict(zip(names, (float(x) for x in ms)))
+        return dict(zip(("hierarchy", "instances", "sort", "emit", "draws"), (float(x) for x in ms)))
 
     # ---- outputs
     def map_outputs(self, slot, view):
