@@ -10,7 +10,7 @@ NVFLAGS  := $(ARCH) -O3 -std=c++17 -lineinfo -fmad=false $(EXTRA) \
 CSRC     := vulkanengine_b200/csrc
 OBJDIR   := build
 LIB      := vulkanengine_b200/libscenesubmit.so
-CU       := $(CSRC)/transform_cull.cu $(CSRC)/transform_cull_x2.cu $(CSRC)/radix_sort.cu $(CSRC)/emit.cu $(CSRC)/resident.cu $(CSRC)/raster.cu $(CSRC)/context.cu
+CU       := $(CSRC)/transform_cull.cu $(CSRC)/transform_cull_x2.cu $(CSRC)/radix_sort.cu $(CSRC)/emit.cu $(CSRC)/resident.cu $(CSRC)/merge.cu $(CSRC)/raster.cu $(CSRC)/context.cu
 CPP      := $(CSRC)/host_views.cpp
 OBJS     := $(patsubst $(CSRC)/%.cu,$(OBJDIR)/%.o,$(CU)) $(patsubst $(CSRC)/%.cpp,$(OBJDIR)/%.o,$(CPP))
 HDRS     := $(wildcard $(CSRC)/*.h $(CSRC)/*.cuh include/*.h)

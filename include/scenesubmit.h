@@ -359,6 +359,45 @@ SS_API ss_status ss_merge_place_peers(void* cuda_stream, const int32_t* const* r
                                       const int64_t* seg_out, const int64_t* seg_src, const int64_t* seg_add,
                                       const int64_t* seg_key, uint32_t n_segs, int32_t* out_idx, int64_t* out_keys);
 
+/* The whole merge as one library call (no Python, no framework tensors): every rank runs it and gets the merged list of
+   every view, equal to what ONE context holding all shards would have produced (the single-GPU stable order).
+   Peers: for every (view, rank) the device pointers of that rank's outputs of one finished frame slot as THIS process
+   sees them: its own from ss_map_outputs, the others' opened once from ss_export_slot_buffers handles (ss_ipc_open),
+   or, for several contexts in one process, every rank's ss_map_outputs pointers directly.  instance_base is the global
+   number of the rank's instance 0.  The caller makes sure (a barrier of its own) that every rank's frame of the slot
+   has completed and that no rank reuses the slot while another still merges from it.  Four kernels on cuda_stream for
+   all views together: fetch of the ranks' draws (KBs), a K-way merge of the sorted draw keys by bisection, segment
+   prefix + merged indirect draws, and a placement kernel that reads every rank's instance list in place over NVLink
+   (plain per-thread loads).  No host synchronisation until ss_merge_map reads the sizes.
+   No counterpart in the reference (one list on one CPU, VC/Scene/SceneRenderer.cpp:1336,1368,1381). */
+typedef struct ss_merge ss_merge;
+typedef struct ss_merge_peer {
+    const uint32_t* idx;          /* ss_outputs.instance_idx of the rank's view */
+    const ss_draw_cmd* draws;     /* ss_outputs.draws */
+    const uint64_t* draw_keys;    /* ss_outputs.draw_keys */
+    const uint32_t* counts;       /* ss_outputs.counts: {visible, draws} on the device */
+    uint64_t instance_base;
+} ss_merge_peer;
+typedef struct ss_merged_view {
+    const uint32_t* instance_idx; /* [visible] global instance numbers, draw order */
+    const uint64_t* keys;         /* [visible] */
+    const ss_draw_cmd* draws;     /* [n_draws] one per distinct key over all ranks */
+    const uint64_t* draw_keys;    /* [n_draws] */
+    uint32_t visible, n_draws;    /* host copies */
+} ss_merged_view;
+SS_API ss_status ss_merge_create(int device, uint32_t n_ranks, uint32_t n_views, uint32_t max_draws_per_rank,
+                                 uint64_t max_visible_per_view, ss_merge** out);
+SS_API void ss_merge_destroy(ss_merge* m);
+/* peers: host array [n_views][n_ranks]; asynchronous on cuda_stream */
+SS_API ss_status ss_merge_views(ss_merge* m, void* cuda_stream, const ss_merge_peer* peers);
+/* waits for cuda_stream, returns the view's merged buffers (library-owned, valid until the next ss_merge_views) */
+SS_API ss_status ss_merge_map(ss_merge* m, void* cuda_stream, uint32_t view, ss_merged_view* out);
+SS_API const char* ss_merge_last_error(const ss_merge* m);
+/* CUDA IPC handles of every buffer a peer needs of this context, for ss_ipc_open in another process:
+   [frames_in_flight][max_views][3] in the order idx, draws, draw_keys, then [frames_in_flight] counts blocks
+   (counts of view v of a slot = block + 2 * v words).  count_out = handles written. */
+SS_API ss_status ss_export_slot_buffers(ss_ctx* ctx, ss_ipc_handle* handles_out, uint32_t capacity, uint32_t* count_out);
+
 /* ---- the sort on its own ---------------------------------------------------------------------- */
 
 /* Stable LSD radix sort (onesweep) of (uint64 key, uint32 value) pairs on bits [begin_bit, end_bit).

@@ -103,3 +103,66 @@ def test_merge_place_kernel_against_numpy():
     torch.cuda.synchronize()
     assert np.array_equal(out_i.cpu().numpy().astype(np.int64), want_i)
     assert np.array_equal(out_k.cpu().numpy(), want_k)
+
+
+def dev_to_numpy(ptr, n, dtype):
+    """n elements of `dtype` at device address ptr, through torch (bytes, then reinterpreted)."""
+    nbytes = n * dtype.itemsize
+    if nbytes == 0:
+        return np.empty(0, dtype)
+
+    class _Dev:
+        __cuda_array_interface__ = {"shape": (nbytes,), "typestr": "|u1", "data": (int(ptr), False), "version": 2}
+    return torch.as_tensor(_Dev(), device="cuda").cpu().numpy().view(dtype).copy()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("shards,pipe", [(2, 0), (3, 0), (4, 2)])
+def test_merge_views_equals_single_context(shards, pipe):
+    """ss_merge_views: the merged lists of G entity-wise shards (G contexts on one GPU standing in for G ranks; the
+    pointers are the ranks' own output buffers) equal what ONE context holding the whole scene produces: instance
+    order, keys, indirect draws, draw keys, every view, in one library call."""
+    import ctypes as C
+
+    import numpy as np
+
+    from vulkanengine_b200 import scenesubmit as S
+    from vulkanengine_b200 import synth
+
+    n_total, n_views = 90_000, 5
+    views = synth.make_views(S.camera_view_proj, S.cascade_matrices, n_views)
+    whole = synth.flat_scene(n_total, n_keys=300)
+    one = S.SceneSubmit(whole.n_nodes, n_total, len(whole.slots), max_views=n_views, flags=pipe)
+    one.load_scene(whole)
+    slot1 = one.frame(views)
+    st1 = one.frame_sync(slot1)
+    ref = [one.download_view(slot1, v, st1) for v in range(n_views)]
+
+    bounds = [n_total * r // shards for r in range(shards + 1)]
+    ctxs, slots = [], []
+    for r in range(shards):
+        n = bounds[r + 1] - bounds[r]
+        sc = synth.flat_scene(n, first=bounds[r], n_keys=300)
+        c = S.SceneSubmit(sc.n_nodes, n, len(sc.slots), max_views=n_views, flags=pipe)
+        c.load_scene(sc)
+        slots.append(c.frame(views))
+        c.frame_sync(slots[-1])
+        ctxs.append(c)
+    peers = [[S.peer_of_outputs(ctxs[r].map_outputs(slots[r], v), bounds[r]) for r in range(shards)] for v in range(n_views)]
+    mg = S.Merger(shards, n_views, max_draws_per_rank=1 << 12, max_visible_per_view=n_total)
+    for _ in range(2):  # twice: the tables are reused
+        mg.merge(peers)
+    for v in range(n_views):
+        o = mg.map(v)
+        assert o.visible == len(ref[v]["idx"]) and o.n_draws == len(ref[v]["draws"]), v
+
+        def dl(ptr, n, dt):
+            return dev_to_numpy(ptr, n, np.dtype(dt))
+        assert np.array_equal(dl(o.instance_idx, o.visible, np.uint32), ref[v]["idx"]), f"view {v}: merged instance order"
+        assert np.array_equal(dl(o.keys, o.visible, np.uint64), ref[v]["keys"]), f"view {v}: merged keys"
+        assert np.array_equal(dl(o.draws, o.n_draws, S.DRAW_DTYPE), ref[v]["draws"]), f"view {v}: merged draws"
+        assert np.array_equal(dl(o.draw_keys, o.n_draws, np.uint64), ref[v]["draw_keys"]), f"view {v}: merged draw keys"
+    mg.close()
+    for c in ctxs:
+        c.close()
+    one.close()

@@ -1288,6 +1288,31 @@ SS_API ss_status ss_export_idx_lists(ss_ctx* c, ss_ipc_handle* handles_out, void
     return SS_OK;
 }
 
+SS_API ss_status ss_export_slot_buffers(ss_ctx* c, ss_ipc_handle* handles_out, uint32_t capacity, uint32_t* count_out)
+{
+    if (!c || !handles_out || !count_out) return SS_ERR_INVALID;
+    const uint32_t V = c->cfg.max_views, F = (uint32_t)c->slots.size(), need = F * V * 3 + F;
+    *count_out = need;
+    if (capacity < need) return c->fail(SS_ERR_INVALID, "ss_export_slot_buffers: %u handles, room for %u", need, capacity);
+    SS_CUDA(c, cudaSetDevice(c->device));
+    uint32_t k = 0;
+    for (uint32_t si = 0; si < F; ++si)
+        for (uint32_t v = 0; v < V; ++v) {
+            const void* bufs[3] = {c->slots[si].out[v].idx, c->slots[si].out[v].draws, c->slots[si].out[v].draw_keys};
+            for (const void* b : bufs) {
+                cudaIpcMemHandle_t h;
+                SS_CUDA(c, cudaIpcGetMemHandle(&h, const_cast<void*>(b)));
+                memcpy(&handles_out[k++], &h, sizeof h);
+            }
+        }
+    for (uint32_t si = 0; si < F; ++si) {
+        cudaIpcMemHandle_t h;
+        SS_CUDA(c, cudaIpcGetMemHandle(&h, c->slots[si].counts_dev));
+        memcpy(&handles_out[k++], &h, sizeof h);
+    }
+    return SS_OK;
+}
+
 SS_API ss_status ss_ipc_open(int device, const ss_ipc_handle* handle, void** device_ptr_out)
 {
     if (!handle || !device_ptr_out) return SS_ERR_INVALID;

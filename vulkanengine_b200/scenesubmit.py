@@ -30,7 +30,9 @@ EXPORTS = ["ss_create", "ss_destroy", "ss_last_error", "ss_version", "ss_set_key
            "ss_sort_pairs_host", "ss_sort_pairs_static", "ss_camera_view_proj", "ss_cascade_matrices",
            "ss_set_geometry", "ss_raster_view", "ss_map_raster", "ss_download_raster", "ss_read_pixel",
            "ss_cascade_matrices_batch", "ss_upload_trs_sparse", "ss_merge_place",
-           "ss_export_idx_lists", "ss_ipc_open", "ss_ipc_close", "ss_merge_place_peers"]
+           "ss_export_idx_lists", "ss_ipc_open", "ss_ipc_close", "ss_merge_place_peers",
+           "ss_merge_create", "ss_merge_destroy", "ss_merge_views", "ss_merge_map", "ss_merge_last_error",
+           "ss_export_slot_buffers"]
 RASTER_DEPTH_CLAMP = 1
 RASTER_EMPTY = 0xFFFFFFFFFFFFFFFF
 
@@ -61,6 +63,16 @@ class Outputs(C.Structure):
                 ("world_idx_bits", C.c_uint32), ("world_stride", C.c_uint32)]
 
 
+class MergePeer(C.Structure):
+    _fields_ = [("idx", C.c_void_p), ("draws", C.c_void_p), ("draw_keys", C.c_void_p), ("counts", C.c_void_p),
+                ("instance_base", C.c_uint64)]
+
+
+class MergedView(C.Structure):
+    _fields_ = [("instance_idx", C.c_void_p), ("keys", C.c_void_p), ("draws", C.c_void_p), ("draw_keys", C.c_void_p),
+                ("visible", C.c_uint32), ("n_draws", C.c_uint32)]
+
+
 _lib = None
 
 
@@ -80,6 +92,10 @@ def load_library():
         lib.ss_sort_scratch_bytes.argtypes = [C.c_uint64]
         lib.ss_destroy.argtypes = [C.c_void_p]
         lib.ss_destroy.restype = None
+        lib.ss_merge_destroy.argtypes = [C.c_void_p]
+        lib.ss_merge_destroy.restype = None
+        lib.ss_merge_last_error.argtypes = [C.c_void_p]
+        lib.ss_merge_last_error.restype = C.c_char_p
         _lib = lib
     return _lib
 
@@ -150,6 +166,49 @@ def sort_pairs_host(keys, vals, begin_bit=0, end_bit=64, device=0):
     if st != SS_OK:
         raise SceneSubmitError(st, lib.ss_last_error(None).decode())
     return ko, vo
+
+
+class Merger:
+    """ss_merge_*: merged draw lists of several shards (ranks), every view in one call."""
+
+    def __init__(self, n_ranks, n_views, max_draws_per_rank, max_visible_per_view, device=0):
+        self.lib = load_library()
+        self.n_ranks, self.n_views = n_ranks, n_views
+        h = C.c_void_p()
+        st = self.lib.ss_merge_create(C.c_int(device), C.c_uint32(n_ranks), C.c_uint32(n_views), C.c_uint32(max_draws_per_rank),
+                                      C.c_uint64(max_visible_per_view), C.byref(h))
+        if st != SS_OK:
+            raise SceneSubmitError(st, self.lib.ss_last_error(None).decode())
+        self.h = h
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.lib.ss_merge_destroy(self.h)
+            self.h = None
+
+    __del__ = close
+
+    def merge(self, peers, stream=None):
+        """peers[v][r] = (idx_ptr, draws_ptr, draw_keys_ptr, counts_ptr, instance_base); asynchronous on `stream`."""
+        arr = (MergePeer * (self.n_views * self.n_ranks))()
+        for v in range(self.n_views):
+            for r in range(self.n_ranks):
+                arr[v * self.n_ranks + r] = MergePeer(*peers[v][r])
+        st = self.lib.ss_merge_views(self.h, C.c_void_p(stream), arr)
+        if st != SS_OK:
+            raise SceneSubmitError(st, self.lib.ss_merge_last_error(self.h).decode())
+
+    def map(self, view, stream=None):
+        out = MergedView()
+        st = self.lib.ss_merge_map(self.h, C.c_void_p(stream), C.c_uint32(view), C.byref(out))
+        if st != SS_OK:
+            raise SceneSubmitError(st, self.lib.ss_merge_last_error(self.h).decode())
+        return out
+
+
+def peer_of_outputs(o, instance_base):
+    """(idx, draws, draw_keys, counts, base) of an Outputs struct from SceneSubmit.map_outputs."""
+    return (o.instance_idx, o.draws, o.draw_keys, o.counts, instance_base)
 
 
 class SceneSubmit:
@@ -310,6 +369,16 @@ class SceneSubmit:
         self._ck(self.lib.ss_export_idx_lists(self.h, handles, ptrs, C.c_uint32(cap), C.byref(count)))
         raw = bytes(handles)
         return [raw[64 * k: 64 * (k + 1)] for k in range(count.value)], [int(ptrs[k] or 0) for k in range(count.value)]
+
+    def export_slot_buffers(self):
+        """CUDA IPC handles (64 bytes each) of every buffer a peer needs for ss_merge_views:
+        [frames_in_flight][max_views][idx, draws, draw_keys], then [frames_in_flight] counts blocks."""
+        cap = 256
+        handles = (C.c_ubyte * (64 * cap))()
+        count = C.c_uint32()
+        self._ck(self.lib.ss_export_slot_buffers(self.h, handles, C.c_uint32(cap), C.byref(count)))
+        raw = bytes(handles)
+        return [raw[64 * k: 64 * (k + 1)] for k in range(count.value)]
 
     # ---- consumer pass: depth + id rasterisation of a view's lists ----
     def set_geometry(self, positions, indices):
