@@ -166,3 +166,24 @@ def test_merge_views_equals_single_context(shards, pipe):
     for c in ctxs:
         c.close()
     one.close()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("pipe", [0, 2])
+def test_merge_views_across_gpus(pipe):
+    """The same over real peers: one process per GPU (torch.distributed.run), shards on different GPUs, the other ranks'
+    buffers opened over CUDA IPC and read across NVLink by ss_merge_views.  Needs two GPUs; skipped on one."""
+    import subprocess
+    n_gpus = torch.cuda.device_count()
+    if n_gpus < 2:
+        pytest.skip("one GPU: the multi-GPU merge check needs two")
+    world = min(n_gpus, 4)
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        port = s.getsockname()[1]
+    env = dict(os.environ, SS_MERGE_PIPE=str(pipe))
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}", "--master-addr", "127.0.0.1",
+           "--master-port", str(port), os.path.join(os.path.dirname(os.path.abspath(__file__)), "multi_gpu_merge_worker.py")]
+    r = subprocess.run(cmd, env=env, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+    assert "identical to one context" in r.stdout
