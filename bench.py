@@ -47,6 +47,7 @@ def parse():
                     help="instances in the CPU sample (0: the whole scene for --impl reference, 2^20 for the cpu_baseline leg)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-extras", action="store_true", help="skip steady state, strong scaling, cfg5 and the other configs")
     return ap.parse_args()
 
 
@@ -140,7 +141,10 @@ def ncu_traffic(n, n_views):
         return out
     try:
         import csv
-        rows = list(csv.reader(open(os.path.join(ROOT, "profiles", "r01_ncu_full_summary.csv"))))
+        name = "r02_ncu_full_summary.csv" if os.path.exists(os.path.join(ROOT, "profiles", "r02_ncu_full_summary.csv")) else \
+            "r01_ncu_full_summary.csv"
+        out["source"] = f"profiles/{name} (one ncu --set full capture of this workload; not re-measured in this run)"
+        rows = list(csv.reader(open(os.path.join(ROOT, "profiles", name))))
         hdr = rows[0]
         ir, iw = hdr.index("dram__bytes_read.sum"), hdr.index("dram__bytes_write.sum")
         for r in rows[2:]:
@@ -218,6 +222,127 @@ def cpu_reference(sc, views, sample, threads, min_seconds=10.0):
     return n / best, "port", best, n
 
 
+def timed_frames(torch, ctx, stream, views, steps, flags=0):
+    """`steps` frames back to back through the slot ring, CUDA events on the library's stream; (ms total, slots)."""
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    slots = []
+    with torch.cuda.stream(stream):
+        ev0.record(stream)
+        for _ in range(steps):
+            slots.append(ctx.frame(views, flags))
+        ev1.record(stream)
+    ev1.synchronize()
+    return ev0.elapsed_time(ev1), slots
+
+
+def max_over_ranks(torch, dist, world, x):
+    t = torch.tensor([x], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return float(t.item())
+
+
+def open_merge_peers(S, dist, ctx, local_rank, rank, world, max_views, fif=3):
+    """peer[r][slot][view] = (idx, draws, draw_keys, counts) pointers of rank r's outputs as this process sees them
+    (CUDA IPC, opened once); None for this rank itself."""
+    everyone = [None] * world
+    dist.all_gather_object(everyone, ctx.export_slot_buffers())
+    table = []
+    for r in range(world):
+        if r == rank:
+            table.append(None)
+            continue
+        ptrs = [S.ipc_open(local_rank, h) for h in everyone[r]]
+        table.append([[(ptrs[(si * max_views + v) * 3], ptrs[(si * max_views + v) * 3 + 1], ptrs[(si * max_views + v) * 3 + 2],
+                        ptrs[fif * max_views * 3 + si] + 8 * v) for v in range(max_views)] for si in range(fif)])
+    return table
+
+
+def close_merge_peers(S, local_rank, table, max_views, fif=3):
+    for per_rank in table:
+        if per_rank is None:
+            continue
+        for si in range(fif):
+            for v in range(max_views):
+                for ptr in per_rank[si][v][:3]:
+                    S.ipc_close(local_rank, ptr)
+            S.ipc_close(local_rank, per_rank[si][0][3])
+
+
+def bench_merge(torch, dist, S, ctx, views, n, rank, local_rank, world, n_views):
+    """The one communicating step: ss_merge_views builds the merged list of every view on every rank, reading the other
+    ranks' instance lists in place over NVLink.  Timed on the device, max over ranks; not part of `value`."""
+    table = open_merge_peers(S, dist, ctx, local_rank, rank, world, n_views)
+    mg = S.Merger(world, n_views, max_draws_per_rank=1 << 16, max_visible_per_view=min(world * n, (1 << 32) - 1), device=local_rank)
+    slot = ctx.frame(views)
+    st = ctx.frame_sync(slot)
+    dist.barrier()
+    peers = [[S.peer_of_outputs(ctx.map_outputs(slot, v), r * n) if r == rank else (*table[r][slot][v], r * n)
+              for r in range(world)] for v in range(n_views)]
+    mg.merge(peers)  # warm-up
+    torch.cuda.synchronize()
+    dist.barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    reps = 5
+    e0.record()
+    for _ in range(reps):
+        mg.merge(peers, stream=torch.cuda.current_stream().cuda_stream)
+    e1.record()
+    e1.synchronize()
+    ms = max_over_ranks(torch, dist, world, e0.elapsed_time(e1) / reps)
+    merged = [mg.map(v) for v in range(n_views)]
+    total = sum(int(m.visible) for m in merged)
+    mine = sum(int(st.visible[v]) for v in range(n_views))
+    t = torch.tensor([mine], dtype=torch.int64, device="cuda")
+    dist.all_reduce(t)
+    remote_bytes = (total - mine) * 4
+    dist.barrier()
+    mg.close()
+    close_merge_peers(S, local_rank, table, n_views)
+    return {"ms": ms, "merged_elements": total, "equals_sum_of_ranks": bool(int(t.item()) == total),
+            "list_bytes_over_nvlink_per_rank": int(remote_bytes),
+            "nvlink_gbs_per_rank": remote_bytes / (ms * 1e-3) / 1e9 if ms > 0 else None,
+            "note": "ss_merge_views (C ABI, four kernels for all views, no host sync): every rank ends with the merged list of "
+                    "every view; instance lists are read in place over NVLink (CUDA IPC peers); not part of `value`"}
+
+
+def bench_cfg5(torch, S, synth, local_rank, rank, world, total_views=4096):
+    """configs[4]: 4096 camera views x 2^20 instances (3-level hierarchy), sharded by VIEW: this rank takes its share
+    of the cameras, 8 per frame; after the first frame the transforms and the order are kept (SS_FRAME_REUSE_*)."""
+    sc = synth.hierarchy_scene()
+    cams = synth.fibonacci_cameras(S.camera_view_proj, total_views)
+    lo, hi = total_views * rank // world, total_views * (rank + 1) // world
+    mine = cams[lo:hi]
+    ctx = S.SceneSubmit(sc.n_nodes, sc.n_instances, len(sc.slots), max_views=8, device=local_rank, max_draws_per_view=1 << 16)
+    ctx.load_scene(sc)
+    batches = [np.ascontiguousarray(mine[b:b + 8]) for b in range(0, len(mine), 8)]
+    reuse = S.FRAME_REUSE_WORLD | S.FRAME_REUSE_SORT
+    for b in batches[:3]:
+        ctx.frame_sync(ctx.frame(b))
+    stream = torch.cuda.ExternalStream(ctx.stream, device=local_rank)
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    slots = []
+    with torch.cuda.stream(stream):
+        ev0.record(stream)
+        for i, b in enumerate(batches):
+            slots.append(ctx.frame(b, 0 if i == 0 else reuse))
+        ev1.record(stream)
+    ev1.synchronize()
+    ms = ev0.elapsed_time(ev1)
+    vis, out_bytes = [], 0
+    for i in range(max(0, len(batches) - 3), len(batches)):
+        st = ctx.frame_sync(slots[i])
+        vis += [int(st.visible[v]) for v in range(len(batches[i]))]
+    stage = ctx.frame_stage_ms(slots[-1])
+    mean_vis = float(np.mean(vis)) if vis else 0.0
+    # per batch of 8 views: masks pass reads 64 B rows + writes 1 B; emit reads 8 B words + rows of visible items, writes 60 B each
+    n = sc.n_instances
+    batch_bytes = n * (64 + 1 + 8) + 8 * mean_vis * 60 + min(n, 8 * mean_vis) * 48
+    ctx.close()
+    return {"views": len(mine), "ms_total": ms, "ms_per_batch": ms / max(len(batches), 1), "mean_visible_per_view": mean_vis,
+            "stage_ms_last_batch": {k: round(float(v), 4) for k, v in stage.items()}, "batch_algorithmic_bytes": batch_bytes, "n": n}
+
+
 def main():
     a = parse()
     rank = int(os.environ.get("RANK", "0"))
@@ -282,21 +407,25 @@ def main():
     sc = synth.flat_scene(n, first=rank * n)
     views = synth.make_views(S.camera_view_proj, S.cascade_matrices, a.views)
     trig = S.TRIG_DETERMINISTIC if a.trig == "deterministic" else S.TRIG_LIBM
-    ctx = S.SceneSubmit(sc.n_nodes, n, len(sc.slots), max_views=a.views, device=local_rank, trig_mode=trig,
-                        max_draws_per_view=1 << 16)
-    ctx.load_scene(sc)
+
+    def make_ctx(scene, flags=0, n_views=a.views):
+        c = S.SceneSubmit(scene.n_nodes, scene.n_instances, len(scene.slots), max_views=n_views, device=local_rank,
+                          trig_mode=trig, max_draws_per_view=1 << 16, flags=flags)
+        c.load_scene(scene)
+        return c
 
     def barrier():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
 
-    # ---- device-resident timing -----------------------------------------------------------------
+    ctx = make_ctx(sc)
+
+    # ---- device-resident timing: the general pipeline (transform -> sort -> compact, every frame) ----------------
     for _ in range(max(a.warmup, 3)):
         st = ctx.frame_sync(ctx.frame(views))
     launches_per_frame = int(st.kernel_launches)
     stream = torch.cuda.ExternalStream(ctx.stream, device=local_rank)
-    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     # clocks are sampled DURING load: the sampler runs through an untimed stretch of identical frames
     # (a frame is ~2 ms, nvidia-smi samples every 100 ms) and through the timed region that follows directly
     sampler = ClockSampler(local_rank)
@@ -305,104 +434,33 @@ def main():
     while time.perf_counter() - t_load < 1.2:
         ctx.frame_sync(ctx.frame(views))
     barrier()
-    slots = []
-    with torch.cuda.stream(stream):
-        ev0.record(stream)
-        for _ in range(a.steps):
-            slots.append(ctx.frame(views))
-        ev1.record(stream)
-    ev1.synchronize()
+    ms_total, slots = timed_frames(torch, ctx, stream, views, a.steps)
     barrier()
     clocks = sampler.stop()
-    ms_total = ev0.elapsed_time(ev1)
     st = ctx.frame_sync(slots[-1])
-    stage = ctx.frame_stage_ms(slots[-1])
-    # per-stage times averaged over the last frames_in_flight frames still in their slots
-    stages = [ctx.frame_stage_ms(s) for s in sorted(set(slots[-3:]))]
-    stage = {k: float(np.mean([x[k] for x in stages])) for k in stage}
+    stages = [ctx.frame_stage_ms(s_) for s_ in sorted(set(slots[-3:]))]
+    stage = {k: float(np.mean([x[k] for x in stages])) for k in stages[0]}
     visible = [int(st.visible[v]) for v in range(a.views)]
     draws = [int(st.draws[v]) for v in range(a.views)]
-
-    t = torch.tensor([ms_total], dtype=torch.float64, device="cuda")
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ms_step = float(t.item()) / a.steps
+    ms_step = max_over_ranks(torch, dist, world, ms_total) / a.steps
     value = world * n / (ms_step * 1e-3)
+    masks = ctx.download_masks() if rank == 0 else None
 
-    # ---- merged draw list (only where one list is needed): all-gather over NCCL, timed separately ------
-    merge = None
-    if world > 1:
-        from vulkanengine_b200 import sharding
+    merge = bench_merge(torch, dist, S, ctx, views, n, rank, local_rank, world, a.views) if world > 1 else None
 
-        class _Dev:
-            def __init__(self, ptr, n, typestr):
-                self.__cuda_array_interface__ = {"shape": (n,), "typestr": typestr, "data": (ptr, False), "version": 2}
-
-        def dev_tensor(ptr, n, typestr):
-            if n == 0:
-                return torch.empty(0, dtype=torch.int64 if typestr == "<i8" else torch.int32, device="cuda")
-            return torch.as_tensor(_Dev(ptr, n, typestr), device="cuda")
-
-        def merge_all_views(slot_, st_):
-            lists = []
-            for v in range(a.views):
-                o = ctx.map_outputs(slot_, v)
-                # the whole device buffer (capacity n): ranks gather equal-length slices, nothing is copied to pad
-                idx = dev_tensor(o.instance_idx, n, "<i4")
-                dk = dev_tensor(o.draw_keys, o.n_draws, "<i8")
-                draws = dev_tensor(o.draws, o.n_draws * 5, "<i4").view(-1, 5)
-                lists.append((idx, dk, draws[:, 1].contiguous()))
-            merged = sharding.merge_view_lists(lists, rank * n, peers=peers, frame_slot=slot_)
-            return sum(m[1].numel() * 4 for m in merged)  # instance indices crossing NVLink (keys are rebuilt from the runs)
-
-        s_ = ctx.frame(views)
-        st_ = ctx.frame_sync(s_)
-        peers = None
-        merge_all_views(s_, st_)  # warm-up (NCCL channels, allocator)
-        barrier()
-        g0, g1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        g0.record()
-        merge_all_views(s_, st_)
-        g1.record()
-        g1.synchronize()
-        gt = torch.tensor([g0.elapsed_time(g1)], dtype=torch.float64, device="cuda")
-        dist.all_reduce(gt, op=dist.ReduceOp.MAX)
-        # the same with every rank reading its peers' lists in place over NVLink (CUDA IPC) instead of an all-gathered copy
-        peers = sharding.PeerLists(ctx, local_rank)
-        merge_all_views(s_, st_)
-        barrier()
-        m0, m1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        m0.record()
-        merged_bytes = merge_all_views(s_, st_)
-        m1.record()
-        m1.synchronize()
-        mt = torch.tensor([m0.elapsed_time(m1)], dtype=torch.float64, device="cuda")
-        dist.all_reduce(mt, op=dist.ReduceOp.MAX)
-        barrier()
-        peers.close()
-        merge = {"ms": float(mt.item()), "ms_with_all_gather": float(gt.item()), "list_bytes_over_nvlink": int(merged_bytes),
-                 "note": "sizes and draws all-gathered (KBs); each rank's placement kernel reads the peers' instance lists in "
-                         "place over NVLink (ms) or from an NCCL all-gathered copy (ms_with_all_gather); not part of the "
-                         "sharded phase timed in value"}
-
-    # ---- end to end through the C ABI from host buffers --------------------------------------------
+    # ---- end to end through the C ABI from host buffers ----------------------------------------------------------
     e2e = None
     if not a.no_e2e:
         host_trs = torch.from_numpy(sc.trs).pin_memory()
         h2d = host_trs.numel() * 4 + views.nbytes
-        d2h = 0
         for _ in range(2):
             ctx.upload_trs_ptr(host_trs.data_ptr(), n)
             s_ = ctx.frame(views)
             st_ = ctx.frame_sync(s_)
             for v in range(a.views):
                 ctx.download_draws(s_, v, st_)
-        barrier()
-        t0 = time.perf_counter()
         e_steps = max(3, min(a.steps, 30))
-        # Pipelined the way a host with frames in flight runs it: step k's upload and ss_frame are issued, then step
-        # k-1's result is fenced and read.  A whole-stream TRS upload goes to the library's second TRS buffer on its own
-        # stream, so the copy for step k+1 overlaps step k's kernels; every step still moves all of its inputs.
+
         def consume(slot_):
             st_k = ctx.frame_sync(slot_)
             nbytes = C.sizeof(S.FrameStats)
@@ -410,28 +468,134 @@ def main():
                 dr, dk = ctx.download_draws(slot_, v, st_k)
                 nbytes += dr.nbytes + dk.nbytes
             return nbytes
-        prev = None
-        for _ in range(e_steps):
-            ctx.upload_trs_ptr(host_trs.data_ptr(), n)
-            s_ = ctx.frame(views)
-            if prev is not None:
-                d2h = consume(prev)
-            prev = s_
-        d2h = consume(prev)
-        torch.cuda.synchronize()
-        dt = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device="cuda")
-        if world > 1:
-            dist.all_reduce(dt, op=dist.ReduceOp.MAX)
-        e2e = {"value": world * n * e_steps / float(dt.item()), "unit": "instances/s", "h2d_bytes_per_step": int(h2d),
-               "d2h_bytes_per_step": int(d2h), "ms_per_step": float(dt.item()) / e_steps * 1e3, "host_binding": numa,
+
+        def run_e2e(upload):
+            # Pipelined the way a host with frames in flight runs it: step k's upload and ss_frame are issued, then
+            # step k-1's result is fenced and read.  Every step still moves all of its inputs.
+            barrier()
+            t0 = time.perf_counter()
+            prev, d2h_ = None, 0
+            for _ in range(e_steps):
+                upload()
+                s_k = ctx.frame(views)
+                if prev is not None:
+                    d2h_ = consume(prev)
+                prev = s_k
+            d2h_ = consume(prev)
+            torch.cuda.synchronize()
+            return max_over_ranks(torch, dist, world, time.perf_counter() - t0), d2h_
+
+        dt, d2h = run_e2e(lambda: ctx.upload_trs_ptr(host_trs.data_ptr(), n))
+        e2e = {"value": world * n * e_steps / dt, "unit": "instances/s", "h2d_bytes_per_step": int(h2d),
+               "d2h_bytes_per_step": int(d2h), "ms_per_step": dt / e_steps * 1e3, "host_binding": numa,
+               "h2d_gbs_per_rank": h2d / (dt / e_steps) / 1e9,
                "note": "pinned TRS (36 B/instance) + views in; counts, indirect draws and draw keys of every view out; "
-                       "compacted instance rows stay in HBM for the GPU consumer; two frames in flight (step k's result "
-                       "is read after step k+1 is issued)"}
+                       "compacted instance rows stay in HBM for the GPU consumer (the renderer); two frames in flight "
+                       "(step k's result is read after step k+1 is issued); bound by the host-to-device copy"}
+        # the shape of a physics tick (JoltPhysicsWorld.cpp:112-128): a tenth of the entities moved, sent as sparse records
+        n_dirty = n // 10
+        dirty = np.sort(np.random.default_rng(7).choice(n, n_dirty, replace=False)).astype(np.uint32)
+        dirty_t = torch.from_numpy(dirty.view(np.int32)).pin_memory()
+        recs_t = torch.from_numpy(np.ascontiguousarray(sc.trs[dirty])).pin_memory()
+        dt_s, _ = run_e2e(lambda: ctx.upload_trs_sparse_ptr(dirty_t.data_ptr(), recs_t.data_ptr(), n_dirty))
+        e2e["dirty_tenth"] = {"value": world * n * e_steps / dt_s, "ms_per_step": dt_s / e_steps * 1e3,
+                              "h2d_bytes_per_step": int(n_dirty * 40 + views.nbytes),
+                              "note": "the same loop when 10 % of the transforms change per step (ss_upload_trs_sparse); "
+                                      "beside the full-upload number, not instead of it"}
+        del host_trs, dirty_t, recs_t
+    ctx.close()
+
+    # ---- steady state: the draw-order-resident layout (sorted when the static streams change, not per frame) -----
+    steady = None
+    if not a.no_extras:
+        rctx = make_ctx(sc, flags=S.CONFIG_DRAW_ORDER_RESIDENT)
+        st0 = rctx.frame_sync(rctx.frame(views))  # builds the layout: key words + sort + permutation of every stream
+        relayout_ms = float(st0.gpu_ms)
+        for _ in range(4):
+            rctx.frame_sync(rctx.frame(views))
+        rstream = torch.cuda.ExternalStream(rctx.stream, device=local_rank)
+        barrier()
+        rms, rslots = timed_frames(torch, rctx, rstream, views, a.steps)
+        barrier()
+        rst = rctx.frame_sync(rslots[-1])
+        rstage = rctx.frame_stage_ms(rslots[-1])
+        rctx.upload_trs(sc.trs)  # every transform changed: the permuted stream is rebuilt inside the next frame
+        rctx.flush_uploads()
+        rst2 = rctx.frame_sync(rctx.frame(views))
+        rms_step = max_over_ranks(torch, dist, world, rms) / a.steps
+        steady = {"ms_per_frame": rms_step, "value": world * n / (rms_step * 1e-3), "unit": "instances/s",
+                  "pipeline": S.PIPELINE_NAMES[int(rst.pipeline)], "stage_ms": {k: round(float(v), 4) for k, v in rstage.items()},
+                  "same_lists": [int(rst.visible[v]) for v in range(a.views)] == visible,
+                  "relayout_ms": relayout_ms, "frame_after_full_trs_upload_ms": float(rst2.gpu_ms),
+                  "note": "SS_CONFIG_DRAW_ORDER_RESIDENT: streams kept in (key, instance) order, a frame is two streaming "
+                          "passes (no sort, no gather); relayout_ms = first frame (key words + sort + permutation), paid when "
+                          "ss_set_* changes a static stream; reported beside `value`, which sorts every frame"}
+        rctx.close()
+
+    # ---- strong scaling on configs[3]: 2^26 instances over the ranks ---------------------------------------------
+    strong = None
+    if world > 1 and not a.no_extras:
+        n64 = (1 << 26) // world
+        sc64 = synth.flat_scene(n64, first=rank * n64)
+        c64 = make_ctx(sc64)
+        for _ in range(3):
+            c64.frame_sync(c64.frame(views))
+        s64 = torch.cuda.ExternalStream(c64.stream, device=local_rank)
+        barrier()
+        ms64, sl64 = timed_frames(torch, c64, s64, views, a.steps)
+        barrier()
+        c64.frame_sync(sl64[-1])
+        ms64 = max_over_ranks(torch, dist, world, ms64) / a.steps
+        strong = {"instances_total": n64 * world, "instances_per_rank": n64, "ms_per_frame": ms64,
+                  "value": n64 * world / (ms64 * 1e-3), "unit": "instances/s",
+                  "one_gpu_estimate_ms": ms_step * (1 << 26) / n,
+                  "speedup_vs_estimate": ms_step * (1 << 26) / n / ms64,
+                  "note": "configs[3] (64M instances, entity-wise shards, no collective in the sharded phase); the one-GPU time is "
+                          "this rank count's 2^24 frame time scaled by 4 (2^26 instances do not fit the per-view capacity "
+                          "budget of one context at full size), so the speed-up includes nothing but that linear estimate"}
+        c64.close()
+        del sc64
+
+    # ---- configs[4]: 4096 cameras x 2^20 instances, sharded by view ----------------------------------------------
+    cfg5 = None
+    if not a.no_extras:
+        barrier()
+        r5 = bench_cfg5(torch, S, synth, local_rank, rank, world)
+        ms5 = max_over_ranks(torch, dist, world, r5["ms_total"])
+        peak5, _ = peaks()
+        cfg5 = {"views_total": 4096, "views_per_rank": r5["views"], "ms_total": ms5, "ms_per_batch_of_8": r5["ms_per_batch"],
+                "views_per_s": 4096 / (ms5 * 1e-3), "instance_views_per_s": 4096 * r5["n"] / (ms5 * 1e-3),
+                "mean_visible_per_view": r5["mean_visible_per_view"], "stage_ms_last_batch": r5["stage_ms_last_batch"],
+                "roofline": {"bound": "hbm", "achieved": r5["batch_algorithmic_bytes"] / (r5["ms_per_batch"] * 1e-3) / 1e9,
+                             "peak": peak5, "unit": "GB/s",
+                             "frac": r5["batch_algorithmic_bytes"] / (r5["ms_per_batch"] * 1e-3) / 1e9 / peak5,
+                             "note": "per batch of 8 views: rows + words in, masks out, 60 B per visible (instance, view) out; "
+                                     "the batch is emit/HBM-bound, not FP32-issue-bound"},
+                "note": "sharded by view, no exchange; SS_FRAME_REUSE_WORLD | SS_FRAME_REUSE_SORT after the first batch"}
+
+    # ---- the other single-GPU configs (rank 0, one GPU only): configs[1] and the hierarchy variant of configs[2] ---
+    other = None
+    if world == 1 and not a.no_extras:
+        other = {}
+        for name, scene, nv in (("cfg2_1m_hierarchy_1_camera", synth.hierarchy_scene(), 1),
+                                ("cfg3_hierarchy_variant_16m", synth.hierarchy_scene(n_roots=1 << 14, seed=synth.SEED_BASE + 3), a.views)):
+            vws = synth.make_views(S.camera_view_proj, S.cascade_matrices, nv)
+            for label, flags in (("general", 0), ("resident", S.CONFIG_DRAW_ORDER_RESIDENT)):
+                c2 = make_ctx(scene, flags=flags, n_views=nv)
+                for _ in range(4):
+                    c2.frame_sync(c2.frame(vws))
+                s2 = torch.cuda.ExternalStream(c2.stream, device=local_rank)
+                ms2, sl2 = timed_frames(torch, c2, s2, vws, a.steps)
+                st2 = c2.frame_sync(sl2[-1])
+                other[f"{name}_{label}"] = {"ms_per_frame": ms2 / a.steps, "instances_per_s": scene.n_instances / (ms2 / a.steps * 1e-3),
+                                            "nodes": scene.n_nodes, "visible": [int(st2.visible[v]) for v in range(nv)],
+                                            "stage_ms": {k: round(float(v), 4) for k, v in c2.frame_stage_ms(sl2[-1]).items()}}
+                c2.close()
+            del scene
 
     if rank == 0:
         peak, peak_src = peaks()
         # per-kernel rooflines: algorithmic bytes of the launch / its CUDA-event time (ss_frame_stage_ms)
-        masks = ctx.download_masks()
         unique_visible = int(np.count_nonzero(masks))
         traffic = ncu_traffic(n, a.views)
         kb = instances_kernel_bytes(n, a.views, False)
@@ -441,25 +605,33 @@ def main():
                                         ("k_instances_x2 (transform+cull+key)", "k_instances", kb, stage["instances"])):
             ach = nbytes / (ms_k * 1e-3) / 1e9
             roofs.append({"kernel": name, "bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
-                          "traffic": traffic.get(key), "peak_source": peak_src, "algorithmic_bytes_per_launch": nbytes,
-                          "kernel_ms": ms_k})
+                          "traffic": traffic.get(key), "traffic_source": traffic.get("source"), "peak_source": peak_src,
+                          "algorithmic_bytes_per_launch": nbytes, "kernel_ms": ms_k})
         roofs.sort(key=lambda r: -r["kernel_ms"])  # the dominant kernel first
         balg = algorithmic_bytes(n, a.views, visible, draws, False)
         line = {"metric": "culled+compacted instances/sec", "value": value, "unit": "instances/s", "n_gpus": world,
                 "steps": a.steps, "warmup": max(a.warmup, 3), "ms_per_step": ms_step, "higher_is_better": True,
                 "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-                "config": {"workload": WORKLOAD, "instances_per_gpu": n, "views": a.views, "keys": 4096,
-                           "trig": a.trig, "seed": int(sc.seed), "l2": "inputs_exceed_l2 (2 GB of streams per frame)",
-                           "sharding": "entity-wise, no collective in the sharded phase" if world > 1 else "none"},
+                "config": bench_config(n, a.views, int(sc.seed), world), "trig": TRIG_NOTE,
+                "pipeline": "general: transform+cull+key -> onesweep sort -> compact+gather, all per frame",
                 "ms_per_frame": ms_step, "visible_per_view": visible, "draws_per_view": draws,
                 "stage_ms": stage, "sort_passes_run": int(st.sort_passes_run),
                 "frame_algorithmic_gb": balg / 1e9, "frame_frac_of_hbm_peak": balg / (ms_step * 1e-3) / 1e9 / peak,
                 "roofline": roofs[0], "roofline_other_kernels": roofs[1:],
                 "gpu_launches": launches_per_frame * a.steps, "clocks": clocks}
+        if steady:
+            steady["frame_frac_of_hbm_peak"] = balg / (steady["ms_per_frame"] * 1e-3) / 1e9 / peak
+            line["steady_state"] = steady
         if e2e:
             line["e2e"] = e2e
         if merge:
             line["merge"] = merge
+        if strong:
+            line["strong_64m"] = strong
+        if cfg5:
+            line["cfg5"] = cfg5
+        if other:
+            line["other_configs"] = other
         if not a.no_cpu_baseline and world == 1:
             os.sched_setaffinity(0, all_cpus)  # the CPU baseline gets every core again
             cores = os.cpu_count() or 1
@@ -471,7 +643,6 @@ def main():
                                               f"({secs * 1e3:.1f} ms best of repeats)",
                                     "single_thread_value": ips1}
         print(json.dumps(line), flush=True)
-    ctx.close()
     if world > 1:
         dist.destroy_process_group()
 

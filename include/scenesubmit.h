@@ -240,7 +240,9 @@ SS_API ss_status ss_upload_trs(ss_ctx* ctx, uint32_t first, uint32_t count, cons
    leaves behind — the physics write-back loop (Platform/JoltPhysics/JoltPhysicsWorld.cpp:112-127, translation and
    rotation of every rigid body) or a gizmo edit (VulkanEditor/src/EditorLayer.cpp:593-603).  node_index[k] names the
    node trs9[k] belongs to; a node named twice keeps the later record.  The records cross the bus packed
-   (40 B per node) and a kernel scatters them into the TRS stream. */
+   (40 B per node) and a kernel scatters them into the TRS stream.  A strictly ascending node list in PINNED memory is
+   read by the copy engine where it lies (keep both arrays unchanged until ss_flush_uploads or the next frame's
+   ss_frame_sync); anything else is staged before the call returns. */
 SS_API ss_status ss_upload_trs_sparse(ss_ctx* ctx, uint32_t count, const uint32_t* node_index, const float* trs9);
 
 /* World rows (TransformData, 48 B each) of EXTERNAL nodes: nodes numbered past the last level given to

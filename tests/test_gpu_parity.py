@@ -657,3 +657,144 @@ def test_implicit_node_map_must_stay_in_last_level():
     with pytest.raises(S.SceneSubmitError):
         ctx.set_key_layout(1, 1, 1)
     ctx.close()
+
+
+def _ref_flat_frame(sc, views, trig_mode):
+    """oracle/_ref (the reference's own GLM): per-instance masks and world rows of a flat or hierarchical scene."""
+    import ctypes as C
+
+    class Flat(C.Structure):
+        _fields_ = [("n", C.c_uint32), ("trs", C.c_void_p), ("parent", C.c_void_p), ("n_nodes", C.c_uint32),
+                    ("node_base", C.c_uint32), ("slot", C.c_void_p), ("matword", C.c_void_p), ("inst_aabb", C.c_void_p),
+                    ("slot_local", C.c_void_p), ("slot_mesh_handle", C.c_void_p), ("slot_submesh", C.c_void_p),
+                    ("material_handle", C.c_void_p), ("trig_mode", C.c_int)]
+    n = sc.n_instances
+    keep = [np.ascontiguousarray(x) for x in (sc.trs, sc.slot, sc.matword, sc.inst_aabb, sc.slots["local"],
+                                              sc.mesh_handles[sc.slots["mesh_rank"]], sc.slots["submesh_index"], sc.material_handles)]
+    parent = None if sc.parent is None else np.ascontiguousarray(sc.parent)
+    p = lambda a: None if a is None else a.ctypes.data_as(C.c_void_p)
+    f = Flat(n, p(keep[0]), p(parent), sc.n_nodes, sc.node_base, p(keep[1]), p(keep[2]), p(keep[3]), p(keep[4]), p(keep[5]),
+             p(keep[6]), p(keep[7]), trig_mode)
+    vps, vfl = np.ascontiguousarray(views["view_proj"]), np.ascontiguousarray(views["flags"])
+    vis, drw = np.zeros(len(views), np.uint32), np.zeros(len(views), np.uint32)
+    masks, rows = np.zeros(n, np.uint8), np.zeros((n, 12), np.float32)
+    O.ref().ssr_flat_frame(C.byref(f), p(vps), p(vfl), C.c_uint32(len(views)), C.c_int(os.cpu_count() or 1), p(vis), p(drw),
+                           p(masks), p(rows))
+    return masks, rows, vis
+
+
+@pytest.mark.skipif(not O.ref_available(), reason="oracle/_ref/libss_ref.so (the reference's GLM build) is not here")
+def test_default_mode_against_the_reference_libm_arithmetic_at_full_size():
+    """SURVEY §7 hard part 1 (iii), configs[2] at full size: the library's DEFAULT mode (deterministic trig) against the
+    reference as it really computes (glm -> libm sinf/cosf, oracle/_ref).  World rows within 1e-6 relative; every
+    visibility bit that differs is listed with the signed distance of the box from the deciding plane, which must be a
+    rounding-sized sliver (|d| <= 1e-5 of the magnitudes that were added up)."""
+    n = 1 << 24
+    sc = synth.flat_scene(n)
+    views = oracle_views(5)
+    ref_masks, ref_rows, ref_vis = _ref_flat_frame(sc, views, trig_mode=1)
+    ctx = S.SceneSubmit(sc.n_nodes, n, len(sc.slots), max_views=5, max_draws_per_view=1 << 16)
+    ctx.load_scene(sc)
+    st = ctx.frame_sync(ctx.frame(views))
+    rows, masks = ctx.download_world(), ctx.download_masks()
+    ctx.close()
+    live = sc.slot != synth.SLOT_NULL
+    scale = np.maximum(np.abs(ref_rows).max(axis=1, keepdims=True), 1e-30)
+    rel = (np.abs(rows - ref_rows) / scale)[live]
+    assert rel.max() <= 1e-6, f"world rows: {rel.max():.3g} relative"
+    diff = np.flatnonzero(masks != ref_masks)
+    assert len(diff) < n * 1e-4, f"{len(diff)} instances differ in visibility"
+    worst = 0.0
+    lines = []
+    for i in diff:
+        R = ref_rows[i].astype(np.float64).reshape(3, 4)
+        mn, mx = sc.inst_aabb[i, :3].astype(np.float64), sc.inst_aabb[i, 3:].astype(np.float64)
+        cl, el = (mn + mx) * 0.5, (mx - mn) * 0.5
+        cw, ew = R[:, :3] @ cl + R[:, 3], np.abs(R[:, :3]) @ el
+        for v in range(5):
+            if ((int(masks[i]) ^ int(ref_masks[i])) >> v) & 1:
+                planes = O.planes_from_view_proj(views["view_proj"][v]).astype(np.float64).reshape(6, 4)
+                if views["flags"][v] & synth.VIEW_SKIP_NEAR:
+                    planes = np.delete(planes, 4, axis=0)
+                s = planes[:, :3] @ cw + planes[:, 3]
+                r = np.abs(planes[:, :3]) @ ew
+                mag = np.abs(planes[:, :3]) @ np.abs(cw) + np.abs(planes[:, 3]) + r
+                k = int(np.argmin(np.abs(s + r) / mag))      # the plane that decides: the one nearest to the box's far corner
+                d = float((s + r)[k] / mag[k])
+                worst = max(worst, abs(d))
+                lines.append(f"instance {i} view {v}: gpu {(int(masks[i]) >> v) & 1} reference {(int(ref_masks[i]) >> v) & 1} "
+                             f"plane {k} signed distance {float((s + r)[k]):+.3e} ({d:+.2e} of the summed magnitudes)")
+    print(f"{len(diff)} of {n} instances differ in a visibility bit (deterministic trig vs glm/libm); worst relative distance {worst:.2e}")
+    for ln in lines[:40]:
+        print("  " + ln)
+    assert worst <= 1e-5, "a visibility bit differs on a box that is not borderline"
+    # the lists' sizes move by exactly the listed bits
+    for v in range(5):
+        flips = int((((masks[diff] >> v) & 1).astype(np.int64) - ((ref_masks[diff] >> v) & 1).astype(np.int64)).sum())
+        assert int(st.visible[v]) - int(ref_vis[v]) == flips
+
+
+_HIER_REF = {}
+
+
+@pytest.mark.parametrize("pipe", PIPELINES)
+def test_full_size_hierarchy_variant_16m(pipe):
+    """The 3-level variant of configs[2] at full size (2^24 leaves under 2^14 roots x 32 x 32, 17.3 M nodes, 5 views):
+    world rows, masks bit-exact against the oracle; the lists sorted by (key, instance) and exactly the visible set."""
+    sc = synth.hierarchy_scene(n_roots=1 << 14, seed=synth.SEED_BASE + 3)
+    n = sc.n_instances
+    views = oracle_views(5)
+    ctx = S.SceneSubmit(sc.n_nodes, n, len(sc.slots), max_views=5, max_draws_per_view=1 << 16, flags=pipe)
+    ctx.load_scene(sc)
+    slot = ctx.frame(views)
+    st = ctx.frame_sync(slot)
+    assert int(st.pipeline) == EXPECT_PIPELINE[pipe]
+    if "rows" not in _HIER_REF:
+        import ctypes as C
+        osc = O.OracleScene(sc, 0)
+        rows = np.empty((n, 12), np.float32)
+        nw = osc.node_worlds()
+        O.lib().sso_instance_rows(C.byref(osc.s), nw.ctypes.data_as(C.c_void_p), rows.ctypes.data_as(C.c_void_p))
+        del nw
+        _HIER_REF.update(rows=rows, omask=osc.cull(rows, views), okeys=osc.keys())
+    rows, omask, okeys = _HIER_REF["rows"], _HIER_REF["omask"], _HIER_REF["okeys"]
+    masks = ctx.download_masks()
+    assert np.array_equal(masks, omask)
+    world = ctx.download_world()
+    assert np.array_equal(world, rows)
+    for v in range(5):
+        got = ctx.download_view(slot, v, st)
+        vis = np.flatnonzero((masks >> v) & 1).astype(np.uint32)
+        assert np.array_equal(np.sort(got["idx"]), vis), f"view {v}: not exactly the visible set"
+        assert np.array_equal(got["keys"], okeys[got["idx"]]), f"view {v}: keys"
+        k, i = got["keys"], got["idx"].astype(np.int64)
+        assert np.all((k[1:] > k[:-1]) | ((k[1:] == k[:-1]) & (i[1:] > i[:-1]))), f"view {v}: not sorted by (key, instance)"
+        assert np.array_equal(got["rows"], world[got["idx"]]), f"view {v}: rows"
+        d = got["draws"]
+        assert int(d["instance_count"].sum()) == len(vis)
+    ctx.close()
+
+
+def test_lists_belong_to_their_slot_world_rows_to_the_last_frame():
+    """The contract of ss_outputs with frames in flight: the per-view lists of slot f stay as they are while frames
+    f+1, f+2 are issued (FramesInFlight, VC/Renderer/Renderer.h:28); the per-instance world rows and masks are ONE
+    array that always holds the most recent frame."""
+    sc = synth.flat_scene(30_000, n_keys=128)
+    views = oracle_views(5)
+    ctx = S.SceneSubmit(sc.n_nodes, sc.n_instances, len(sc.slots), max_views=5)
+    ctx.load_scene(sc)
+    variants, slots = [], []
+    for k in range(3):  # three frames issued back to back on different transforms, nothing read in between
+        t = sc.trs.copy()
+        t[:, 0] += np.float32(40.0 * k)
+        variants.append(t)
+        ctx.upload_trs(t)
+        slots.append(ctx.frame(views))
+    refs = [O.OracleScene(synth.SceneArrays(**{**sc.__dict__, "trs": t}), 0).frame(views) for t in variants]
+    for k in (0, 1, 2):
+        st = ctx.frame_sync(slots[k])
+        for v in range(5):
+            got = ctx.download_view(slots[k], v, st)
+            assert np.array_equal(got["idx"], refs[k]["views"][v]["idx"]) and np.array_equal(got["rows"], refs[k]["views"][v]["rows"])
+    assert np.array_equal(ctx.download_world(), refs[2]["rows"]) and np.array_equal(ctx.download_masks(), refs[2]["masks"])
+    ctx.close()

@@ -609,24 +609,51 @@ SS_API ss_status ss_upload_trs_sparse(ss_ctx* c, uint32_t count, const uint32_t*
     } else {
         SS_CUDA(c, cudaEventSynchronize(c->ev_sparse));  // the previous call's copy must have left the staging buffer
     }
-    // pack: indices, then records, keeping only the LAST record of a node named more than once
+    // pack: indices, then records, keeping only the LAST record of a node named more than once.  Strictly ascending
+    // node lists (what a producer walking its bodies in order sends) cannot hold duplicates: two memcpys.
     uint32_t* hi = reinterpret_cast<uint32_t*>(c->h_sparse);
-    std::unordered_map<uint32_t, uint32_t> last;
-    last.reserve(count * 2);
-    for (uint32_t k = 0; k < count; ++k) last[node_index[k]] = k;
+    bool ascending = true;
+    for (uint32_t k = 1; k < count && ascending; ++k) ascending = node_index[k] > node_index[k - 1];
     uint32_t kept = 0;
-    for (uint32_t k = 0; k < count; ++k)
-        if (last[node_index[k]] == k) hi[kept++] = k;          // source positions for now
-    float* hr = reinterpret_cast<float*>(c->h_sparse + (size_t)kept * 4);
-    for (uint32_t j = 0; j < kept; ++j) {
-        const uint32_t k = hi[j];
-        memcpy(hr + (size_t)j * 9, trs9 + (size_t)k * 9, 36);
-        hi[j] = node_index[k];
+    const void* src_idx = c->h_sparse;
+    const void* src_rec = nullptr;
+    if (ascending) {
+        kept = count;
+        // pinned caller memory is read by the copy engine where it lies (same rule as ss_upload_trs: unchanged until
+        // ss_flush_uploads or the next frame's ss_frame_sync); pageable memory is staged
+        cudaPointerAttributes pa_i{}, pa_r{};
+        const bool pinned = cudaPointerGetAttributes(&pa_i, node_index) == cudaSuccess && pa_i.type == cudaMemoryTypeHost &&
+                            cudaPointerGetAttributes(&pa_r, trs9) == cudaSuccess && pa_r.type == cudaMemoryTypeHost;
+        cudaGetLastError();
+        if (pinned) {
+            src_idx = node_index;
+            src_rec = trs9;
+        } else {
+            memcpy(hi, node_index, (size_t)count * 4);
+            memcpy(c->h_sparse + (size_t)count * 4, trs9, (size_t)count * 36);
+        }
+    } else {
+        std::unordered_map<uint32_t, uint32_t> last;
+        last.reserve(count * 2);
+        for (uint32_t k = 0; k < count; ++k) last[node_index[k]] = k;
+        for (uint32_t k = 0; k < count; ++k)
+            if (last[node_index[k]] == k) hi[kept++] = k;          // source positions for now
+        float* hr = reinterpret_cast<float*>(c->h_sparse + (size_t)kept * 4);
+        for (uint32_t j = 0; j < kept; ++j) {
+            const uint32_t k = hi[j];
+            memcpy(hr + (size_t)j * 9, trs9 + (size_t)k * 9, 36);
+            hi[j] = node_index[k];
+        }
     }
     c->world_valid = c->nodes_valid = false;  // transforms changed
     c->res_trs_dirty = true;
     SS_CUDA(c, adopt_pending_upload(c));  // lands on top of whatever whole-stream upload came before it
-    SS_CUDA(c, cudaMemcpyAsync(c->d_sparse, c->h_sparse, (size_t)kept * 40, cudaMemcpyHostToDevice, c->stream));
+    if (src_rec) {
+        SS_CUDA(c, cudaMemcpyAsync(c->d_sparse, src_idx, (size_t)kept * 4, cudaMemcpyHostToDevice, c->stream));
+        SS_CUDA(c, cudaMemcpyAsync(c->d_sparse + (size_t)kept * 4, src_rec, (size_t)kept * 36, cudaMemcpyHostToDevice, c->stream));
+    } else {
+        SS_CUDA(c, cudaMemcpyAsync(c->d_sparse, c->h_sparse, (size_t)kept * 40, cudaMemcpyHostToDevice, c->stream));
+    }
     SS_CUDA(c, cudaEventRecord(c->ev_sparse, c->stream));
     launch_trs_scatter(c->d_trs, reinterpret_cast<const uint32_t*>(c->d_sparse),
                        reinterpret_cast<const float*>(c->d_sparse + (size_t)kept * 4), kept, c->stream);

@@ -290,6 +290,10 @@ class SceneSubmit:
         assert len(node_index) == len(trs)
         self._ck(self.lib.ss_upload_trs_sparse(self.h, C.c_uint32(len(trs)), _p(node_index), _p(trs)))
 
+    def upload_trs_sparse_ptr(self, node_index_ptr, trs_ptr, count):
+        """Raw host pointers (pinned tensors): ascending node lists are copied straight from them."""
+        self._ck(self.lib.ss_upload_trs_sparse(self.h, C.c_uint32(count), C.c_void_p(node_index_ptr), C.c_void_p(trs_ptr)))
+
     def upload_trs_ptr(self, host_ptr, count, first=0):
         """Raw host pointer (e.g. a pinned torch tensor's data_ptr())."""
         self._ck(self.lib.ss_upload_trs(self.h, C.c_uint32(first), C.c_uint32(count), C.c_void_p(host_ptr)))
