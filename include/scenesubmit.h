@@ -453,6 +453,14 @@ SS_API ss_status ss_cascade_matrices(const float view_proj[16], float z_near, fl
                                      const float light_dir[3], float splits_out[4],
                                      float light_matrices_out[4][16]);
 
+/* The same with CascadeOffset set (VC/Scene/SceneRenderer.cpp:662-679, an ImGui toggle at :987-1000): each cascade's
+   projection is shifted so that CascadeOrigin projects onto the texel grid of a map_size x map_size shadow map
+   (CSMSettings::MapSize, SceneRenderer.h:179).  cascade_origin == NULL gives ss_cascade_matrices. */
+SS_API ss_status ss_cascade_matrices_snapped(const float view_proj[16], float z_near, float z_far,
+                                             float split_lambda, float near_offset, float far_offset,
+                                             const float light_dir[3], const float cascade_origin[3], float map_size,
+                                             float splits_out[4], float light_matrices_out[4][16]);
+
 /* The same for many cameras at once, on the GPU (batched multi-camera work needs a cascade set per
    camera).  view_proj: [n_cameras][16], light_matrices_out: [n_cameras][4][16], host pointers; the split distances
    depend on the clip range only and come back once.  The per-camera arithmetic is the text ss_cascade_matrices

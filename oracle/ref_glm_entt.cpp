@@ -158,10 +158,11 @@ void ssr_camera_view_proj(float fov, float aspect, float zn, float zf, const flo
     store_mat4(P * V, view_proj);
 }
 
-// SceneRenderer::UpdateCascadeMap (VulkanCore/src/VulkanCore/Scene/SceneRenderer.cpp:579-687),
-// CascadeOffset == 0, evaluated with the same glm calls in the same order.
-void ssr_cascade_matrices(const float* view_proj, float zn, float zf, float lambda, float near_off,
-                          float far_off, const float* light_dir, float* splits, float* light_mats)
+// SceneRenderer::UpdateCascadeMap (VulkanCore/src/VulkanCore/Scene/SceneRenderer.cpp:579-687), evaluated with the same
+// glm calls in the same order.  cascade_origin == nullptr: CascadeOffset == 0; otherwise the texel-snap branch (:662-679).
+void ssr_cascade_matrices_snapped(const float* view_proj, float zn, float zf, float lambda, float near_off,
+                                  float far_off, const float* light_dir, const float* cascade_origin, float map_size,
+                                  float* splits, float* light_mats)
 {
     const glm::mat4 VP = load_mat4(view_proj);
     const float clipRange = zf - zn;
@@ -200,10 +201,31 @@ void ssr_cascade_matrices(const float* view_proj, float zn, float zf, float lamb
         glm::vec3 ld = glm::normalize(glm::vec3(light_dir[0], light_dir[1], light_dir[2]));
         glm::mat4 lv = glm::lookAt(center - ld * -minE.z, center, glm::vec3(0.0f, 1.0f, 0.0f));
         glm::mat4 lo = glm::ortho(minE.x, maxE.x, minE.y, maxE.y, near_off, maxE.z - minE.z + far_off);
+        if (cascade_origin) {
+            float shadowMapSize = map_size;
+            glm::mat4 shadowMatrix = lo * lv;
+            glm::vec4 shadowOrigin = glm::vec4(glm::vec3(cascade_origin[0], cascade_origin[1], cascade_origin[2]), 1.0f);
+            shadowOrigin = shadowMatrix * shadowOrigin;
+            shadowOrigin = shadowOrigin * shadowMapSize / 2.0f;
+            glm::vec4 roundedOrigin = glm::round(shadowOrigin);
+            glm::vec4 roundOffset = roundedOrigin - shadowOrigin;
+            roundOffset = roundOffset * 2.0f / shadowMapSize;
+            roundOffset.z = 0.0f;
+            roundOffset.w = 0.0f;
+            glm::mat4 shadowProj = lo;
+            shadowProj[3] += roundOffset;
+            lo = shadowProj;
+        }
         splits[i] = (zn + split * clipRange) * -1.0f;
         store_mat4(lo * lv, light_mats + i * 16);
         last = cs[i];
     }
+}
+
+void ssr_cascade_matrices(const float* view_proj, float zn, float zf, float lambda, float near_off,
+                          float far_off, const float* light_dir, float* splits, float* light_mats)
+{
+    ssr_cascade_matrices_snapped(view_proj, zn, zf, lambda, near_off, far_off, light_dir, nullptr, 0.0f, splits, light_mats);
 }
 
 // One pass of the reference's submission over an entt registry, then grouped output.

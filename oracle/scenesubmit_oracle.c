@@ -556,10 +556,11 @@ void sso_camera_view_proj(float fov_y, float aspect, float z_near, float z_far,
     sso_mat4_mul(proj, view, view_proj);
 }
 
-/* VC/Scene/SceneRenderer.cpp:579-687 (CascadeOffset == 0 branch). */
-void sso_cascade_matrices(const float view_proj[16], float z_near, float z_far, float lambda,
-                          float near_offset, float far_offset, const float light_dir[3],
-                          float splits[4], float light_matrices[64])
+/* VC/Scene/SceneRenderer.cpp:579-687.  cascade_origin == NULL: CascadeOffset == 0; otherwise the texel-snap branch
+   (:662-679) with CascadeOrigin and MapSize. */
+void sso_cascade_matrices_snapped(const float view_proj[16], float z_near, float z_far, float lambda,
+                                  float near_offset, float far_offset, const float light_dir[3],
+                                  const float* cascade_origin, float map_size, float splits[4], float light_matrices[64])
 {
     float cascadeSplits[4];
     float clipRange = z_far - z_near;
@@ -646,10 +647,33 @@ void sso_cascade_matrices(const float view_proj[16], float z_near, float z_far, 
         M(lo, 3, 1) = -(top + bottom) / (top - bottom);
         M(lo, 3, 2) = -zn / (zf - zn);
 
+        if (cascade_origin) {
+            /* shadowOrigin = (lo * lv) * vec4(origin, 1); glm mat4 * vec4: (m0*x + m1*y) + (m2*z + m3*w) */
+            float sm[16];
+            sso_mat4_mul(lo, lv, sm);
+            const float ov[4] = {cascade_origin[0], cascade_origin[1], cascade_origin[2], 1.0f};
+            for (int r = 0; r < 2; ++r) { /* z and w of the offset are zeroed (:674-675) */
+                float a = M(sm, 0, r) * ov[0] + M(sm, 1, r) * ov[1];
+                float b = M(sm, 2, r) * ov[2] + M(sm, 3, r) * ov[3];
+                float so = a + b;
+                so = so * map_size / 2.0f;
+                float off = roundf(so) - so; /* glm::round = round half away from zero */
+                off = off * 2.0f / map_size;
+                M(lo, 3, r) = M(lo, 3, r) + off;
+            }
+        }
         splits[i] = (z_near + splitDist * clipRange) * -1.0f;
         sso_mat4_mul(lo, lv, light_matrices + i * 16);
         lastSplitDist = cascadeSplits[i];
     }
+}
+
+void sso_cascade_matrices(const float view_proj[16], float z_near, float z_far, float lambda,
+                          float near_offset, float far_offset, const float light_dir[3],
+                          float splits[4], float light_matrices[64])
+{
+    sso_cascade_matrices_snapped(view_proj, z_near, z_far, lambda, near_offset, far_offset, light_dir, NULL, 0.0f, splits,
+                                 light_matrices);
 }
 
 /* ---- depth + id rasterisation --------------------------------------------------------------------

@@ -30,7 +30,7 @@ def main():
     np.savez_compressed(os.path.join(HERE, "trs_to_mat4.npz"), trs=trs, mat_det=mats[0], mat_libm=mats[1])
 
     # A9: EditorCamera view-projection + UpdateCascadeMap through glm
-    cams, outs = [], []
+    cams, outs, snapped = [], [], []
     for _ in range(64):
         fov = rng.uniform(0.5, 1.6)
         aspect = rng.uniform(0.8, 2.2)
@@ -44,8 +44,12 @@ def main():
         splits, lm = O.cascade_matrices(vp, zn, zf, lam, -75.0, 75.0, light, "ref")
         cams.append(np.concatenate([[fov, aspect, zn, zf], pos, [pitch, yaw, lam], light]).astype(np.float32))
         outs.append(np.concatenate([v, p, vp, splits, lm.reshape(-1)]).astype(np.float32))
+        # the CascadeOffset branch (SceneRenderer.cpp:662-679): CascadeOrigin at the world origin and at the camera, 4096^2 map
+        for org in (np.zeros(3, np.float32), pos):
+            s2, lm2 = O.cascade_matrices(vp, zn, zf, lam, -75.0, 75.0, light, "ref", origin=org, map_size=4096.0)
+            snapped.append(np.concatenate([org, s2, lm2.reshape(-1)]).astype(np.float32))
     # the reference's own defaults (EditorLayer.cpp:75, SceneRenderer.h:173-181, Components.h:144)
-    np.savez_compressed(os.path.join(HERE, "views.npz"), cams=np.stack(cams), outs=np.stack(outs))
+    np.savez_compressed(os.path.join(HERE, "views.npz"), cams=np.stack(cams), outs=np.stack(outs), snapped=np.stack(snapped))
 
     # A2/A4/A6: a whole submission pass over an entt registry with std::map<MeshKey> grouping
     packs = {}

@@ -167,14 +167,16 @@ def camera_view_proj(fov, aspect, zn, zf, pos, pitch, yaw, which="oracle"):
     return v, p, vp
 
 
-def cascade_matrices(vp, zn, zf, lam, near_off, far_off, light_dir, which="oracle"):
+def cascade_matrices(vp, zn, zf, lam, near_off, far_off, light_dir, which="oracle", origin=None, map_size=0.0):
+    """origin given: the CascadeOffset branch (texel snap of CascadeOrigin on a map_size^2 shadow map)."""
     vp = np.ascontiguousarray(vp, np.float32)
     ld = np.asarray(light_dir, np.float32)
+    org = None if origin is None else np.ascontiguousarray(origin, np.float32)
     splits = np.empty(4, np.float32)
     mats = np.empty((4, 16), np.float32)
-    fn = lib().sso_cascade_matrices if which == "oracle" else ref().ssr_cascade_matrices
+    fn = lib().sso_cascade_matrices_snapped if which == "oracle" else ref().ssr_cascade_matrices_snapped
     fn(_ptr(vp), C.c_float(zn), C.c_float(zf), C.c_float(lam), C.c_float(near_off), C.c_float(far_off),
-       _ptr(ld), _ptr(splits), _ptr(mats))
+       _ptr(ld), _ptr(org), C.c_float(map_size), _ptr(splits), _ptr(mats))
     return splits, mats
 
 

@@ -33,7 +33,7 @@ def test_det_sincos_close_to_libm():
 @pytest.mark.parametrize("which", ["oracle", "product"])
 def test_views_golden(which):
     g = np.load(os.path.join(GOLD, "views.npz"))
-    for cam, out in zip(g["cams"], g["outs"]):
+    for k, (cam, out) in enumerate(zip(g["cams"], g["outs"])):
         fov, aspect, zn, zf = (float(x) for x in cam[:4])
         pos, pitch, yaw, lam, light = cam[4:7], float(cam[7]), float(cam[8]), float(cam[9]), cam[10:13]
         if which == "oracle":
@@ -44,6 +44,10 @@ def test_views_golden(which):
             splits, lm = S.cascade_matrices(vp, zn, zf, lam, -75.0, 75.0, light)
         got = np.concatenate([v, p, vp, splits, lm.reshape(-1)]).astype(np.float32)
         assert got.tobytes() == out.tobytes()
+        for snap in g["snapped"][2 * k: 2 * k + 2]:  # the CascadeOffset branch, two origins per camera
+            fn = O.cascade_matrices if which == "oracle" else S.cascade_matrices
+            s2, lm2 = fn(vp, zn, zf, lam, -75.0, 75.0, light, origin=snap[:3], map_size=4096.0)
+            assert np.concatenate([s2, lm2.reshape(-1)]).astype(np.float32).tobytes() == snap[3:].tobytes()
 
 
 @pytest.mark.parametrize("name", ["small", "medium", "hier"])

@@ -31,6 +31,12 @@ def test_camera_and_cascades_match_glm_bitwise():
         ca = O.cascade_matrices(a[2], 0.1, args[3], 0.92, -75.0, 75.0, light, "oracle")
         cb = O.cascade_matrices(a[2], 0.1, args[3], 0.92, -75.0, 75.0, light, "ref")
         assert ca[0].tobytes() == cb[0].tobytes() and ca[1].tobytes() == cb[1].tobytes()
+        org = rng.uniform(-300, 300, 3)  # the CascadeOffset branch
+        for size in (1024.0, 4096.0):
+            sa = O.cascade_matrices(a[2], 0.1, args[3], 0.92, -75.0, 75.0, light, "oracle", origin=org, map_size=size)
+            sb = O.cascade_matrices(a[2], 0.1, args[3], 0.92, -75.0, 75.0, light, "ref", origin=org, map_size=size)
+            assert sa[1].tobytes() == sb[1].tobytes()
+            assert sa[1].tobytes() != ca[1].tobytes()  # the snap really moves the projection
 
 
 @pytest.mark.parametrize("name", ["small", "medium", "hier"])

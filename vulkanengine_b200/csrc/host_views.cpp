@@ -152,8 +152,11 @@ M4 translation(V3 t)
 // slice the frustum, bound it with a sphere snapped to 1/16, look along the light, orthographic projection.
 // Host and device compile this same text (-fmad=false / -ffp-contract=off, IEEE division and square root on both),
 // so the batched device version gives the host version's bits.
+// snap_size > 0: the CascadeOffset branch (SceneRenderer.cpp:662-679): the projection is shifted so that CascadeOrigin
+// lands on a texel centre grid of a snap_size^2 map.
 SS_HD void cascades_from_splits(const M4& vp, const float split[4], float z_near, float clip_range, float near_offset,
-                                float far_offset, V3 light_in, float splits_out[4], float* light_matrices_out /* [4][16] */)
+                                float far_offset, V3 light_in, float splits_out[4], float* light_matrices_out /* [4][16] */,
+                                V3 snap_origin = {0.f, 0.f, 0.f}, float snap_size = 0.0f)
 {
     const float ndc[8][3] = {{-1, 1, 0}, {1, 1, 0}, {1, -1, 0}, {-1, -1, 0}, {-1, 1, 1}, {1, 1, 1}, {1, -1, 1}, {-1, -1, 1}};
     const V3 light = normalize(light_in);
@@ -208,6 +211,17 @@ SS_HD void cascades_from_splits(const M4& vp, const float split[4], float z_near
         lo_m.c[3][1] = -(hi + lo) / (hi - lo);
         lo_m.c[3][2] = -zn / (zf - zn);
 
+        if (snap_size > 0.0f) {
+            const M4 shadow = matmul(lo_m, lv);
+            const float o[4] = {snap_origin.x, snap_origin.y, snap_origin.z, 1.0f};
+            float so[4];
+            mulvec(shadow, o, so);
+            for (int r = 0; r < 2; ++r) {  // the z and w components of the offset are zeroed
+                const float v = so[r] * snap_size / 2.0f;
+                const float off = (roundf(v) - v) * 2.0f / snap_size;  // glm::round: half away from zero
+                lo_m.c[3][r] = lo_m.c[3][r] + off;
+            }
+        }
         splits_out[i] = (z_near + split[i] * clip_range) * -1.0f;
         const M4 lm = matmul(lo_m, lv);
         for (int q = 0; q < 16; ++q) light_matrices_out[i * 16 + q] = (&lm.c[0][0])[q];
@@ -242,11 +256,12 @@ SS_API ss_status ss_camera_view_proj(float fov_y, float aspect, float z_near, fl
     return SS_OK;
 }
 
-SS_API ss_status ss_cascade_matrices(const float view_proj[16], float z_near, float z_far, float split_lambda,
-                                     float near_offset, float far_offset, const float light_dir[3],
-                                     float splits_out[4], float light_matrices_out[4][16])
+SS_API ss_status ss_cascade_matrices_snapped(const float view_proj[16], float z_near, float z_far, float split_lambda,
+                                             float near_offset, float far_offset, const float light_dir[3],
+                                             const float cascade_origin[3], float map_size, float splits_out[4],
+                                             float light_matrices_out[4][16])
 {
-    if (!view_proj || !light_dir || !splits_out || !light_matrices_out) return SS_ERR_INVALID;
+    if (!view_proj || !light_dir || !splits_out || !light_matrices_out || (cascade_origin && !(map_size > 0.0f))) return SS_ERR_INVALID;
     M4 vp;
     std::memcpy(&vp, view_proj, 64);
     const float clip_range = z_far - z_near;
@@ -262,9 +277,18 @@ SS_API ss_status ss_cascade_matrices(const float view_proj[16], float z_near, fl
         split[i] = (d - z_near) / clip_range;
     }
 
+    const V3 origin = cascade_origin ? V3{cascade_origin[0], cascade_origin[1], cascade_origin[2]} : V3{0.f, 0.f, 0.f};
     cascades_from_splits(vp, split, z_near, clip_range, near_offset, far_offset, {light_dir[0], light_dir[1], light_dir[2]}, splits_out,
-                         &light_matrices_out[0][0]);
+                         &light_matrices_out[0][0], origin, cascade_origin ? map_size : 0.0f);
     return SS_OK;
+}
+
+SS_API ss_status ss_cascade_matrices(const float view_proj[16], float z_near, float z_far, float split_lambda,
+                                     float near_offset, float far_offset, const float light_dir[3],
+                                     float splits_out[4], float light_matrices_out[4][16])
+{
+    return ss_cascade_matrices_snapped(view_proj, z_near, z_far, split_lambda, near_offset, far_offset, light_dir, nullptr, 0.0f,
+                                       splits_out, light_matrices_out);
 }
 
 }  // extern "C"

@@ -32,7 +32,7 @@ EXPORTS = ["ss_create", "ss_destroy", "ss_last_error", "ss_version", "ss_set_key
            "ss_cascade_matrices_batch", "ss_upload_trs_sparse", "ss_merge_place",
            "ss_export_idx_lists", "ss_ipc_open", "ss_ipc_close", "ss_merge_place_peers",
            "ss_merge_create", "ss_merge_destroy", "ss_merge_views", "ss_merge_map", "ss_merge_last_error",
-           "ss_export_slot_buffers"]
+           "ss_export_slot_buffers", "ss_cascade_matrices_snapped"]
 RASTER_DEPTH_CLAMP = 1
 RASTER_EMPTY = 0xFFFFFFFFFFFFFFFF
 
@@ -115,14 +115,15 @@ def camera_view_proj(fov, aspect, zn, zf, pos, pitch, yaw):
     return v, p, vp
 
 
-def cascade_matrices(vp, zn, zf, lam, near_off, far_off, light_dir):
+def cascade_matrices(vp, zn, zf, lam, near_off, far_off, light_dir, origin=None, map_size=0.0):
     lib = load_library()
     vp = np.ascontiguousarray(vp, np.float32)
     ld = np.asarray(light_dir, np.float32)
+    org = None if origin is None else np.ascontiguousarray(origin, np.float32)
     splits = np.empty(4, np.float32)
     mats = np.empty((4, 16), np.float32)
-    st = lib.ss_cascade_matrices(_p(vp), C.c_float(zn), C.c_float(zf), C.c_float(lam), C.c_float(near_off),
-                                 C.c_float(far_off), _p(ld), _p(splits), _p(mats))
+    st = lib.ss_cascade_matrices_snapped(_p(vp), C.c_float(zn), C.c_float(zf), C.c_float(lam), C.c_float(near_off),
+                                         C.c_float(far_off), _p(ld), _p(org), C.c_float(map_size), _p(splits), _p(mats))
     if st != SS_OK:
         raise SceneSubmitError(st, "ss_cascade_matrices")
     return splits, mats
