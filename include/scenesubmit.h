@@ -245,6 +245,13 @@ SS_API ss_status ss_upload_trs(ss_ctx* ctx, uint32_t first, uint32_t count, cons
    ss_frame_sync); anything else is staged before the call returns. */
 SS_API ss_status ss_upload_trs_sparse(ss_ctx* ctx, uint32_t count, const uint32_t* node_index, const float* trs9);
 
+/* The physics write-back itself (Platform/JoltPhysics/JoltPhysicsWorld.cpp:112-127): pose7[k] = body position xyz and
+   rotation quaternion xyzw of node node_index[k].  A kernel turns the quaternion into Euler angles the way
+   JPH::Quat::GetEulerAngles does (vendor/JoltPhysics/Jolt/Math/Quat.inl:185-203) and writes Translation and Rotation of
+   the node's TransformComponent; Scale stays.  32 B per body over the bus instead of the 40 B of a finished record, and
+   no trigonometry on the host.  Angles agree with Jolt's to 1e-6 (Jolt's ATan2/ASin are its own polynomials). */
+SS_API ss_status ss_upload_pose_sparse(ss_ctx* ctx, uint32_t count, const uint32_t* node_index, const float* pose7);
+
 /* World rows (TransformData, 48 B each) of EXTERNAL nodes: nodes numbered past the last level given to
    ss_set_nodes are never composed from TRS.  This is how the ad-hoc submitters that hand the renderer
    a finished glm::mat4 keep working: SceneRenderer::SubmitMesh / SubmitSelectedMesh
@@ -292,6 +299,18 @@ SS_API ss_status ss_download_view(ss_ctx* ctx, uint32_t slot, uint32_t view, flo
                                   uint64_t* draw_keys);
 SS_API ss_status ss_download_world(ss_ctx* ctx, uint32_t first, uint32_t count, float* rows12);
 SS_API ss_status ss_download_masks(ss_ctx* ctx, uint32_t first, uint32_t count, uint8_t* masks);
+
+/* ---- selection pass ------------------------------------------------------------ */
+
+/* Entity id of every instance: what Scene::OnSelectGeometry hands to SubmitSelectedMesh per entity
+   (VC/Scene/Scene.cpp:149-160, (int)(entt::entity)ent).  Optional; without it ss_select_view reports -1. */
+SS_API ss_status ss_set_instance_entities(ss_ctx* ctx, uint32_t first, uint32_t count, const int32_t* entity_ids);
+/* The instance stream of the selection pass for one view of a finished slot: SelectTransformData
+   {vec4 MRow[3]; int EntityID}, 52 B per visible instance, in draw order (VC/Core/Components.h:100-104,
+   VC/Scene/SceneRenderer.cpp:1169-1204), so the pass's vertex stage needs no table on the host.  device_out receives a
+   library-owned device buffer (valid until the next ss_select_view); host_out, when not NULL, gets a copy of
+   `visible` records (capacity in records is the caller's business: ss_frame_sync reported the count). */
+SS_API ss_status ss_select_view(ss_ctx* ctx, uint32_t slot, uint32_t view, const void** device_out, void* host_out);
 
 /* The CUDA stream (cudaStream_t) frames run on, so a consumer can order its own work after them. */
 SS_API void* ss_stream(ss_ctx* ctx);
@@ -437,6 +456,34 @@ SS_API ss_status ss_sort_pairs_host(int device, const uint64_t* keys_in, const u
 SS_API ss_status ss_sort_pairs_static(void* cuda_stream, uint64_t* keys_a, uint32_t* vals_a,
                                       uint64_t* keys_b, uint32_t* vals_b, uint64_t n, int begin_bit,
                                       int end_bit, int* sorted_in_b);
+
+/* ---- light submission ----------------------------------------------------------------- */
+
+/* Scene::UpdateLightsBuffer and Scene::OnUpdateLights (VC/Scene/Scene.cpp:167-264) for lights whose TransformComponent
+   lives in the library's TRS stream (after ss_upload_pose_sparse the host no longer holds the Euler angles): a kernel
+   reads Translation / Rotation of each light's node and fills the uniform blocks the shaders read, byte for byte:
+     ub_point_out  UBPointLights  (VC/Core/Components.h:229-234): int LightCount, vec3 pad, PointLightComponent[10]
+                   {vec4(Translation, 1), Color, Radius, Falloff}, 48 B each (alignas 16)                  = 496 B
+     ub_spot_out   UBSpotLights   (:236-241): int LightCount, vec3 pad, SpotLightComponent[10]
+                   {vec4(Translation, 1), Color, normalize(Rotation), InnerCutoff, OuterCutoff, Radius, Falloff}, 64 B = 656 B
+     positions_out [n_point + n_spot][4]: vec4(Translation, Radius), point lights first (OnUpdateLights, :167-198)
+   Lights are given in view order (the host mirror's Registry::view); at most 10 of each kind, as in the reference's
+   arrays.  Any output may be NULL.  Synchronous (a few hundred bytes). */
+typedef struct ss_point_light {
+    uint32_t node;
+    float color[4];
+    float radius, falloff;
+} ss_point_light;
+typedef struct ss_spot_light {
+    uint32_t node;
+    float color[4];
+    float inner_cutoff, outer_cutoff, radius, falloff;
+} ss_spot_light;
+#define SS_MAX_LIGHTS 10u
+#define SS_UB_POINT_LIGHTS_BYTES 496u
+#define SS_UB_SPOT_LIGHTS_BYTES 656u
+SS_API ss_status ss_pack_lights(ss_ctx* ctx, const ss_point_light* point, uint32_t n_point, const ss_spot_light* spot,
+                                uint32_t n_spot, void* ub_point_out, void* ub_spot_out, float* positions_out);
 
 /* ---- host-side view matrices (stay on the host) --------------------------------- */
 

@@ -458,3 +458,82 @@ double ssr_flat_frame(const ssr_flat* f, const float* view_projs /* [nv][16] */,
 }
 
 } // extern "C"
+
+// JPH::Quat::GetEulerAngles through the reference's own Jolt headers (vendor/JoltPhysics/Jolt/Math/Quat.inl:185-203):
+// what JoltPhysicsWorld::Update (Platform/JoltPhysics/JoltPhysicsWorld.cpp:121-122) writes into TransformComponent::Rotation.
+#ifdef SSR_WITH_JOLT
+#include <Jolt/Jolt.h>
+#include <Jolt/Math/Quat.h>
+extern "C" void ssr_jolt_euler(const float* quat_xyzw, uint32_t n, float* euler_out)
+{
+    for (uint32_t i = 0; i < n; ++i) {
+        const float* q4 = quat_xyzw + (size_t)i * 4;
+        JPH::Quat q(q4[0], q4[1], q4[2], q4[3]);
+        JPH::Vec3 e = q.GetEulerAngles();
+        euler_out[i * 3 + 0] = e.GetX();
+        euler_out[i * 3 + 1] = e.GetY();
+        euler_out[i * 3 + 2] = e.GetZ();
+    }
+}
+#endif
+
+// Scene::UpdateLightsBuffer / OnUpdateLights (VulkanCore/src/VulkanCore/Scene/Scene.cpp:167-264) with the reference's own
+// light structs restated field for field (VulkanCore/src/VulkanCore/Core/Components.h:106-139, 229-241; the header itself
+// drags in the asset system) and its glm calls.  trs: [n_nodes][9] TransformComponent memory; lights in view order.
+namespace ssr_lights {
+struct alignas(16) PointLightComponent { glm::vec4 Position{0.0f}; glm::vec4 Color{0.0f}; float Radius = 0.1f; float Falloff = 1.0f; };
+struct alignas(8) SpotLightComponent {
+    glm::vec4 Position{0.0f}; glm::vec4 Color{1.0f}; glm::vec3 Direction{1.0f};
+    float InnerCutoff = 0.174f; float OuterCutoff = 0.261f; float Radius = 0.1f; float Falloff = 1.0f;
+};
+struct UBPointLights { int LightCount; glm::vec3 Padding{}; PointLightComponent PointLights[10]; };
+struct UBSpotLights { int LightCount; glm::vec3 Padding{}; SpotLightComponent SpotLights[10]; };
+static_assert(sizeof(UBPointLights) == 496 && sizeof(UBSpotLights) == 656, "uniform block sizes");
+}  // namespace ssr_lights
+extern "C" void ssr_pack_lights(const float* trs, const uint32_t* point_node, const float* point_par /* [n][6] color4 radius falloff */,
+                                uint32_t n_point, const uint32_t* spot_node, const float* spot_par /* [n][8] color4 inner outer radius falloff */,
+                                uint32_t n_spot, void* ub_point, void* ub_spot, float* positions)
+{
+    using namespace ssr_lights;
+    UBPointLights pl;
+    UBSpotLights sl;
+    memset(&pl, 0, sizeof pl);
+    memset(&sl, 0, sizeof sl);
+    int li = 0;
+    for (uint32_t k = 0; k < n_point; ++k) {
+        const float* t = trs + (size_t)point_node[k] * 9;
+        const float* q = point_par + k * 6;
+        glm::vec3 Translation(t[0], t[1], t[2]);
+        PointLightComponent c;
+        c.Position = glm::vec4(Translation, 1.0f);
+        c.Color = glm::vec4(q[0], q[1], q[2], q[3]);
+        c.Radius = q[4];
+        c.Falloff = q[5];
+        memcpy(&pl.PointLights[li++], &c, 40);  // the bytes the aggregate initialisation sets; padding stays zero
+        glm::vec4 position = glm::vec4(Translation, q[4]);
+        memcpy(positions + k * 4, &position, 16);
+    }
+    pl.LightCount = li;
+    li = 0;
+    for (uint32_t k = 0; k < n_spot; ++k) {
+        const float* t = trs + (size_t)spot_node[k] * 9;
+        const float* q = spot_par + k * 8;
+        glm::vec3 Translation(t[0], t[1], t[2]), Rotation(t[3], t[4], t[5]);
+        glm::vec3 direction = glm::normalize(Rotation);
+        SpotLightComponent c;
+        c.Position = glm::vec4(Translation, 1.0f);
+        c.Color = glm::vec4(q[0], q[1], q[2], q[3]);
+        c.Direction = direction;
+        c.InnerCutoff = q[4];
+        c.OuterCutoff = q[5];
+        c.Radius = q[6];
+        c.Falloff = q[7];
+        memcpy(&sl.SpotLights[li++], &c, 60);
+        glm::vec4 position = glm::vec4(Translation, q[6]);
+        memcpy(positions + (n_point + k) * 4, &position, 16);
+    }
+    sl.LightCount = li;
+    memcpy(ub_point, &pl, sizeof pl);
+    memcpy(ub_spot, &sl, sizeof sl);
+}
+

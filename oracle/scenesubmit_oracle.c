@@ -862,3 +862,63 @@ void sso_raster_view(const float* rows12, const uint32_t* instance_idx, uint32_t
         }
     }
 }
+
+/* JPH::Quat::GetEulerAngles (VulkanCore/vendor/JoltPhysics/Jolt/Math/Quat.inl:185-203), the conversion
+   JoltPhysicsWorld::Update applies to every body (Platform/JoltPhysics/JoltPhysicsWorld.cpp:121-127).  Jolt's ATan2 / ASin
+   are its own polynomial approximations; libm stands in for them here (agreement to ~1e-6, checked against the Jolt
+   build in tests/test_oracle_vs_ref.py). */
+void sso_quat_to_euler(const float* quat_xyzw, uint32_t n, float* euler_out)
+{
+    for (uint32_t i = 0; i < n; ++i) {
+        const float x = quat_xyzw[i * 4 + 0], y = quat_xyzw[i * 4 + 1], z = quat_xyzw[i * 4 + 2], w = quat_xyzw[i * 4 + 3];
+        float y_sq = y * y;
+        float t0 = 2.0f * (w * x + y * z);
+        float t1 = 1.0f - 2.0f * (x * x + y_sq);
+        float t2 = 2.0f * (w * y - z * x);
+        t2 = t2 > 1.0f ? 1.0f : t2;
+        t2 = t2 < -1.0f ? -1.0f : t2;
+        float t3 = 2.0f * (w * z + x * y);
+        float t4 = 1.0f - 2.0f * (y_sq + z * z);
+        euler_out[i * 3 + 0] = atan2f(t0, t1);
+        euler_out[i * 3 + 1] = asinf(t2);
+        euler_out[i * 3 + 2] = atan2f(t3, t4);
+    }
+}
+
+/* Scene::UpdateLightsBuffer + OnUpdateLights (VC/Scene/Scene.cpp:167-264): uniform blocks UBPointLights (496 B) and
+   UBSpotLights (656 B) of VC/Core/Components.h:229-241, and vec4(Translation, Radius) per light.  Offsets in floats:
+   block = {count, pad x3, lights...}; point light 12 floats {pos4, color4, radius, falloff, pad x2}; spot light 16 floats
+   {pos4, color4, dir3, inner, outer, radius, falloff, pad}.  glm::normalize(v) = v * (1 / sqrt(dot(v, v))). */
+void sso_pack_lights(const float* trs, const uint32_t* point_node, const float* point_par, uint32_t n_point,
+                     const uint32_t* spot_node, const float* spot_par, uint32_t n_spot, void* ub_point, void* ub_spot,
+                     float* positions)
+{
+    float* p = (float*)ub_point;
+    float* s = (float*)ub_spot;
+    memset(p, 0, 496);
+    memset(s, 0, 656);
+    ((int*)p)[0] = (int)n_point;
+    ((int*)s)[0] = (int)n_spot;
+    for (uint32_t k = 0; k < n_point; ++k) {
+        const float* t = trs + (size_t)point_node[k] * 9;
+        const float* q = point_par + k * 6;
+        float* o = p + 4 + k * 12;
+        o[0] = t[0]; o[1] = t[1]; o[2] = t[2]; o[3] = 1.0f;
+        for (int c = 0; c < 4; ++c) o[4 + c] = q[c];
+        o[8] = q[4]; o[9] = q[5];
+        positions[k * 4 + 0] = t[0]; positions[k * 4 + 1] = t[1]; positions[k * 4 + 2] = t[2]; positions[k * 4 + 3] = q[4];
+    }
+    for (uint32_t k = 0; k < n_spot; ++k) {
+        const float* t = trs + (size_t)spot_node[k] * 9;
+        const float* q = spot_par + k * 8;
+        float* o = s + 4 + k * 16;
+        const float inv = 1.0f / sqrtf(t[3] * t[3] + t[4] * t[4] + t[5] * t[5]);
+        o[0] = t[0]; o[1] = t[1]; o[2] = t[2]; o[3] = 1.0f;
+        for (int c = 0; c < 4; ++c) o[4 + c] = q[c];
+        o[8] = t[3] * inv; o[9] = t[4] * inv; o[10] = t[5] * inv;
+        o[11] = q[4]; o[12] = q[5]; o[13] = q[6]; o[14] = q[7];
+        float* w = positions + (n_point + k) * 4;
+        w[0] = t[0]; w[1] = t[1]; w[2] = t[2]; w[3] = q[6];
+    }
+}
+

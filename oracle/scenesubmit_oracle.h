@@ -109,6 +109,10 @@ double sso_frame(const sso_scene* sc, const sso_view* views, uint32_t n_views, i
 void sso_camera_view_proj(float fov_y, float aspect, float z_near, float z_far,
                           const float position[3], float pitch, float yaw, float view[16],
                           float proj[16], float view_proj[16]);
+void sso_pack_lights(const float* trs, const uint32_t* point_node, const float* point_par, uint32_t n_point,
+                     const uint32_t* spot_node, const float* spot_par, uint32_t n_spot, void* ub_point, void* ub_spot,
+                     float* positions);
+void sso_quat_to_euler(const float* quat_xyzw, uint32_t n, float* euler_out);
 void sso_cascade_matrices_snapped(const float view_proj[16], float z_near, float z_far, float lambda,
                                   float near_offset, float far_offset, const float light_dir[3],
                                   const float* cascade_origin, float map_size, float splits[4], float light_matrices[64]);

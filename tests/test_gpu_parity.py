@@ -798,3 +798,91 @@ def test_lists_belong_to_their_slot_world_rows_to_the_last_frame():
             assert np.array_equal(got["idx"], refs[k]["views"][v]["idx"]) and np.array_equal(got["rows"], refs[k]["views"][v]["rows"])
     assert np.array_equal(ctx.download_world(), refs[2]["rows"]) and np.array_equal(ctx.download_masks(), refs[2]["masks"])
     ctx.close()
+
+
+def test_pose_upload_physics_write_back():
+    """SURVEY 8f-2, the producer's arithmetic on the device: (position, quaternion) of moved bodies ->
+    TransformComponent translation + Euler rotation (JPH::Quat::GetEulerAngles), scale kept.  The frame that follows
+    must equal the oracle's frame on transforms converted by the oracle's restatement, to the tolerance of the two
+    libms (angles to 1e-6, rows to 1e-5 relative)."""
+    import ctypes as C
+    n = 70_000
+    sc = synth.flat_scene(n, n_keys=50)
+    views = oracle_views(5)
+    ctx = S.SceneSubmit(sc.n_nodes, n, len(sc.slots), max_views=5)
+    ctx.load_scene(sc)
+    rng = np.random.default_rng(21)
+    k = 20_000
+    nodes = np.sort(rng.choice(n, k, replace=False)).astype(np.uint32)
+    quat = rng.normal(size=(k, 4)).astype(np.float32)
+    quat /= np.linalg.norm(quat, axis=1, keepdims=True).astype(np.float32)
+    pos = rng.uniform(-400, 400, (k, 3)).astype(np.float32)
+    ctx.upload_pose_sparse(nodes, np.concatenate([pos, quat], axis=1))
+    st = ctx.frame_sync(ctx.frame(views))
+    euler = np.empty((k, 3), np.float32)
+    O.lib().sso_quat_to_euler(quat.ctypes.data_as(C.c_void_p), C.c_uint32(k), euler.ctypes.data_as(C.c_void_p))
+    trs = sc.trs.copy()
+    trs[nodes, 0:3] = pos
+    trs[nodes, 3:6] = euler
+    ref = O.OracleScene(synth.SceneArrays(**{**sc.__dict__, "trs": trs}), 0).frame(views)
+    world = ctx.download_world()
+    live = sc.slot != synth.SLOT_NULL
+    scale = np.maximum(np.abs(ref["rows"]).max(axis=1, keepdims=True), 1e-30)
+    assert (np.abs(world - ref["rows"]) <= 1e-5 * scale)[live].all()
+    untouched = np.ones(n, bool)
+    untouched[nodes] = False
+    assert np.array_equal(world[untouched], ref["rows"][untouched])  # the others are bit-identical
+    assert (ctx.download_masks() != ref["masks"]).mean() < 1e-3
+    assert all(abs(int(st.visible[v]) - len(ref["views"][v]["idx"])) <= 20 for v in range(5))
+    with pytest.raises(S.SceneSubmitError):
+        ctx.upload_pose_sparse(np.array([n], np.uint32), np.zeros((1, 7), np.float32))
+    ctx.close()
+
+
+def test_pack_lights_from_device_transforms():
+    """ss_pack_lights: the uniform blocks of Scene::UpdateLightsBuffer from the device-resident TRS stream, after a pose
+    upload moved two of the lights (the host never saw their Euler angles): identical bytes to the oracle on the same
+    transforms; more than ten lights of a kind are refused (the reference's arrays hold ten)."""
+    import ctypes as C
+
+    from test_oracle_vs_ref import _light_case, pack_lights_cpu
+    sc = synth.flat_scene(2000, n_keys=16)
+    ctx = S.SceneSubmit(sc.n_nodes, sc.n_instances, len(sc.slots), max_views=1)
+    ctx.load_scene(sc)
+    _, pn, pp, sn, spp = _light_case(3, n_nodes=sc.n_nodes)
+    trs = sc.trs.copy()
+    moved = np.unique(np.concatenate([pn[:1], sn[:1]])).astype(np.uint32)
+    rec = trs[moved].copy()
+    rec[:, :6] += np.float32(0.5)
+    ctx.upload_trs_sparse(moved, rec)
+    trs[moved] = rec
+    got = ctx.pack_lights(pn, pp, sn, spp)
+    ref = pack_lights_cpu(O.lib().sso_pack_lights, trs, pn, pp, sn, spp)
+    for g, r in zip(got, ref):
+        assert g.tobytes() == r.tobytes()
+    with pytest.raises(S.SceneSubmitError):
+        ctx.pack_lights(np.zeros(11, np.uint32), np.zeros((11, 6), np.float32), sn, spp)
+    ctx.close()
+
+
+@pytest.mark.parametrize("pipe", PIPELINES)
+def test_select_view_records_carry_entity_ids(pipe):
+    """SubmitSelectedMesh's instance stream (SelectTransformData, 52 B: rows + EntityID, Components.h:100-104) built on
+    the device from a view's compacted list and the per-instance entity stream."""
+    sc = synth.flat_scene(40_000, n_keys=100)
+    views = oracle_views(5)
+    ref = O.OracleScene(sc, 0).frame(views)
+    ctx = S.SceneSubmit(sc.n_nodes, sc.n_instances, len(sc.slots), max_views=5, flags=pipe)
+    ctx.load_scene(sc)
+    ent = (np.arange(sc.n_instances, dtype=np.int64) * 7 + 3).astype(np.int32)  # any host numbering
+    slot = ctx.frame(views)
+    st = ctx.frame_sync(slot)
+    rec = ctx.select_view(slot, 0, st)
+    assert (rec["entity"] == -1).all() and np.array_equal(rec["rows"], ref["views"][0]["rows"])  # no entity stream yet
+    ctx.set_instance_entities(ent)
+    for v in (0, 4):
+        rec = ctx.select_view(slot, v, st)
+        assert rec.dtype.itemsize == 52
+        assert np.array_equal(rec["rows"], ref["views"][v]["rows"])
+        assert np.array_equal(rec["entity"], ent[ref["views"][v]["idx"]])
+    ctx.close()

@@ -83,3 +83,50 @@ def test_flat_frame_of_ref_matches_oracle_masks_and_counts():
         assert np.array_equal(rows[live], res["rows"][live])
         assert [int(x) for x in vis] == [len(v["idx"]) for v in res["views"]]
         assert [int(x) for x in drw] == [len(v["draws"]) for v in res["views"]]
+
+
+def test_quat_to_euler_matches_jolt():
+    """The oracle's restatement of JPH::Quat::GetEulerAngles against the reference's own Jolt headers: same formula,
+    Jolt evaluates ATan2 / ASin with its own polynomials, libm here: agreement to 1e-6 (absolute, radians)."""
+    import ctypes as C
+    rng = np.random.default_rng(31)
+    q = rng.normal(size=(20000, 4)).astype(np.float32)
+    q /= np.linalg.norm(q, axis=1, keepdims=True).astype(np.float32)
+    q[0] = [0, 0, 0, 1]
+    q[1] = [0, 0.70710678, 0, 0.70710678]  # pitch of 90 degrees: the clamped asin branch
+    a, b = np.empty((len(q), 3), np.float32), np.empty((len(q), 3), np.float32)
+    p = lambda x: x.ctypes.data_as(C.c_void_p)
+    O.lib().sso_quat_to_euler(p(q), C.c_uint32(len(q)), p(a))
+    O.ref().ssr_jolt_euler(p(q), C.c_uint32(len(q)), p(b))
+    assert np.abs(a - b).max() <= 2e-6, np.abs(a - b).max()
+
+
+def _light_case(seed, n_nodes=50):
+    rng = np.random.default_rng(seed)
+    trs = np.concatenate([rng.uniform(-100, 100, (n_nodes, 3)), rng.uniform(-3, 3, (n_nodes, 3)), rng.uniform(0.5, 2, (n_nodes, 3))],
+                         axis=1).astype(np.float32)
+    n_pt, n_sp = int(rng.integers(0, 11)), int(rng.integers(0, 11))
+    pn, sn = rng.integers(0, n_nodes, n_pt).astype(np.uint32), rng.integers(0, n_nodes, n_sp).astype(np.uint32)
+    pp, spp = rng.uniform(0, 5, (n_pt, 6)).astype(np.float32), rng.uniform(0, 5, (n_sp, 8)).astype(np.float32)
+    return trs, pn, pp, sn, spp
+
+
+def pack_lights_cpu(fn, trs, pn, pp, sn, spp):
+    import ctypes as C
+    p = lambda x: x.ctypes.data_as(C.c_void_p)
+    ubp, ubs = np.zeros(496, np.uint8), np.zeros(656, np.uint8)
+    pos = np.zeros((len(pn) + len(sn) + 1, 4), np.float32)
+    fn(p(np.ascontiguousarray(trs)), p(pn), p(np.ascontiguousarray(pp)), C.c_uint32(len(pn)), p(sn), p(np.ascontiguousarray(spp)),
+       C.c_uint32(len(sn)), p(ubp), p(ubs), p(pos))
+    return ubp, ubs, pos[:len(pn) + len(sn)]
+
+
+def test_pack_lights_matches_reference_structs_bytewise():
+    """UBPointLights / UBSpotLights as Scene::UpdateLightsBuffer fills them (reference structs + glm::normalize in
+    oracle/_ref) against the oracle's float-offset restatement: identical bytes, padding included."""
+    for seed in range(40):
+        case = _light_case(seed)
+        a = pack_lights_cpu(O.lib().sso_pack_lights, *case)
+        b = pack_lights_cpu(O.ref().ssr_pack_lights, *case)
+        for x, y in zip(a, b):
+            assert x.tobytes() == y.tobytes()

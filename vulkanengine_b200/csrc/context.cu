@@ -90,6 +90,9 @@ struct ss_ctx {
     unsigned char* d_sparse = nullptr;
     size_t sparse_cap = 0;
     cudaEvent_t ev_sparse = nullptr;   // the staging buffer's last copy has left the host
+    int32_t* d_entity = nullptr;       // ss_set_instance_entities (allocated on first use)
+    uint32_t* d_select = nullptr;      // ss_select_view: SelectTransformData records of one view (allocated on first use)
+    unsigned char* d_lights = nullptr; // ss_pack_lights: light descriptions in, uniform blocks out
     // geometry + raster target of the consumer pass (ss_set_geometry / ss_raster_view); allocated on first use
     float* d_positions = nullptr;
     uint32_t* d_indices = nullptr;
@@ -265,6 +268,9 @@ SS_API void ss_destroy(ss_ctx* c)
     if (c->h_sparse) cudaFreeHost(c->h_sparse);
     if (c->d_sparse) cudaFree(c->d_sparse);
     if (c->ev_sparse) cudaEventDestroy(c->ev_sparse);
+    if (c->d_lights) cudaFree(c->d_lights);
+    if (c->d_entity) cudaFree(c->d_entity);
+    if (c->d_select) cudaFree(c->d_select);
     if (c->d_positions) cudaFree(c->d_positions);
     if (c->d_indices) cudaFree(c->d_indices);
     for (unsigned long long* p : c->d_raster)
@@ -585,16 +591,19 @@ SS_API ss_status ss_upload_trs(ss_ctx* c, uint32_t first, uint32_t count, const 
     return SS_OK;
 }
 
-SS_API ss_status ss_upload_trs_sparse(ss_ctx* c, uint32_t count, const uint32_t* node_index, const float* trs9)
+// Shared path of the sparse uploads: (node, record of R floats) pairs, staged and copied packed (4 + 4R bytes per node),
+// then scattered by a kernel.  R = 9: TransformComponent records; R = 7: physics poses (position + quaternion).
+static ss_status upload_sparse_records(ss_ctx* c, uint32_t count, const uint32_t* node_index, const float* recs, uint32_t R,
+                                       const char* who)
 {
     if (!c) return SS_ERR_INVALID;
-    if (count && (!node_index || !trs9)) return c->fail(SS_ERR_INVALID, "ss_upload_trs_sparse: null array");
+    if (count && (!node_index || !recs)) return c->fail(SS_ERR_INVALID, "%s: null array", who);
     if (!count) return SS_OK;
     for (uint32_t k = 0; k < count; ++k)
         if (node_index[k] >= c->n_nodes)
-            return c->fail(SS_ERR_INVALID, "ss_upload_trs_sparse: record %u names node %u of %u", k, node_index[k], c->n_nodes);
+            return c->fail(SS_ERR_INVALID, "%s: record %u names node %u of %u", who, k, node_index[k], c->n_nodes);
     SS_CUDA(c, cudaSetDevice(c->device));
-    const size_t bytes = (size_t)count * 40;
+    const size_t rec_bytes = (size_t)R * 4, bytes = (size_t)count * (4 + rec_bytes);
     if (!c->ev_sparse) SS_CUDA(c, cudaEventCreateWithFlags(&c->ev_sparse, cudaEventDisableTiming));
     if (bytes > c->sparse_cap) {
         SS_CUDA(c, cudaStreamSynchronize(c->stream));
@@ -623,14 +632,14 @@ SS_API ss_status ss_upload_trs_sparse(ss_ctx* c, uint32_t count, const uint32_t*
         // ss_flush_uploads or the next frame's ss_frame_sync); pageable memory is staged
         cudaPointerAttributes pa_i{}, pa_r{};
         const bool pinned = cudaPointerGetAttributes(&pa_i, node_index) == cudaSuccess && pa_i.type == cudaMemoryTypeHost &&
-                            cudaPointerGetAttributes(&pa_r, trs9) == cudaSuccess && pa_r.type == cudaMemoryTypeHost;
+                            cudaPointerGetAttributes(&pa_r, recs) == cudaSuccess && pa_r.type == cudaMemoryTypeHost;
         cudaGetLastError();
         if (pinned) {
             src_idx = node_index;
-            src_rec = trs9;
+            src_rec = recs;
         } else {
             memcpy(hi, node_index, (size_t)count * 4);
-            memcpy(c->h_sparse + (size_t)count * 4, trs9, (size_t)count * 36);
+            memcpy(c->h_sparse + (size_t)count * 4, recs, (size_t)count * rec_bytes);
         }
     } else {
         std::unordered_map<uint32_t, uint32_t> last;
@@ -641,7 +650,7 @@ SS_API ss_status ss_upload_trs_sparse(ss_ctx* c, uint32_t count, const uint32_t*
         float* hr = reinterpret_cast<float*>(c->h_sparse + (size_t)kept * 4);
         for (uint32_t j = 0; j < kept; ++j) {
             const uint32_t k = hi[j];
-            memcpy(hr + (size_t)j * 9, trs9 + (size_t)k * 9, 36);
+            memcpy(hr + (size_t)j * R, recs + (size_t)k * R, rec_bytes);
             hi[j] = node_index[k];
         }
     }
@@ -650,14 +659,60 @@ SS_API ss_status ss_upload_trs_sparse(ss_ctx* c, uint32_t count, const uint32_t*
     SS_CUDA(c, adopt_pending_upload(c));  // lands on top of whatever whole-stream upload came before it
     if (src_rec) {
         SS_CUDA(c, cudaMemcpyAsync(c->d_sparse, src_idx, (size_t)kept * 4, cudaMemcpyHostToDevice, c->stream));
-        SS_CUDA(c, cudaMemcpyAsync(c->d_sparse + (size_t)kept * 4, src_rec, (size_t)kept * 36, cudaMemcpyHostToDevice, c->stream));
+        SS_CUDA(c, cudaMemcpyAsync(c->d_sparse + (size_t)kept * 4, src_rec, (size_t)kept * rec_bytes, cudaMemcpyHostToDevice, c->stream));
     } else {
-        SS_CUDA(c, cudaMemcpyAsync(c->d_sparse, c->h_sparse, (size_t)kept * 40, cudaMemcpyHostToDevice, c->stream));
+        SS_CUDA(c, cudaMemcpyAsync(c->d_sparse, c->h_sparse, (size_t)kept * (4 + rec_bytes), cudaMemcpyHostToDevice, c->stream));
     }
     SS_CUDA(c, cudaEventRecord(c->ev_sparse, c->stream));
-    launch_trs_scatter(c->d_trs, reinterpret_cast<const uint32_t*>(c->d_sparse),
-                       reinterpret_cast<const float*>(c->d_sparse + (size_t)kept * 4), kept, c->stream);
+    const uint32_t* d_idx = reinterpret_cast<const uint32_t*>(c->d_sparse);
+    const float* d_rec = reinterpret_cast<const float*>(c->d_sparse + (size_t)kept * 4);
+    if (R == 9)
+        launch_trs_scatter(c->d_trs, d_idx, d_rec, kept, c->stream);
+    else
+        launch_pose_scatter(c->d_trs, d_idx, d_rec, kept, c->stream);
     SS_CUDA(c, cudaGetLastError());
+    return SS_OK;
+}
+
+SS_API ss_status ss_upload_trs_sparse(ss_ctx* c, uint32_t count, const uint32_t* node_index, const float* trs9)
+{
+    return upload_sparse_records(c, count, node_index, trs9, 9, "ss_upload_trs_sparse");
+}
+
+SS_API ss_status ss_upload_pose_sparse(ss_ctx* c, uint32_t count, const uint32_t* node_index, const float* pose7)
+{
+    return upload_sparse_records(c, count, node_index, pose7, 7, "ss_upload_pose_sparse");
+}
+
+SS_API ss_status ss_pack_lights(ss_ctx* c, const ss_point_light* point, uint32_t n_point, const ss_spot_light* spot, uint32_t n_spot,
+                                void* ub_point_out, void* ub_spot_out, float* positions_out)
+{
+    if (!c) return SS_ERR_INVALID;
+    if (n_point > SS_MAX_LIGHTS || n_spot > SS_MAX_LIGHTS || (n_point && !point) || (n_spot && !spot))
+        return c->fail(SS_ERR_INVALID, "ss_pack_lights: at most %u lights of a kind (the reference's uniform arrays)", SS_MAX_LIGHTS);
+    for (uint32_t k = 0; k < n_point; ++k)
+        if (point[k].node >= c->n_nodes) return c->fail(SS_ERR_INVALID, "ss_pack_lights: point light %u names node %u of %u", k, point[k].node, c->n_nodes);
+    for (uint32_t k = 0; k < n_spot; ++k)
+        if (spot[k].node >= c->n_nodes) return c->fail(SS_ERR_INVALID, "ss_pack_lights: spot light %u names node %u of %u", k, spot[k].node, c->n_nodes);
+    SS_CUDA(c, cudaSetDevice(c->device));
+    constexpr size_t kIn = SS_MAX_LIGHTS * (sizeof(ss_point_light) + sizeof(ss_spot_light));
+    constexpr size_t kOut = SS_UB_POINT_LIGHTS_BYTES + SS_UB_SPOT_LIGHTS_BYTES + 2 * SS_MAX_LIGHTS * 16;
+    if (!c->d_lights) SS_CUDA(c, cudaMalloc(reinterpret_cast<void**>(&c->d_lights), kIn + kOut));
+    SS_CUDA(c, adopt_pending_upload(c));  // the newest transforms
+    unsigned char* d_out = c->d_lights + kIn;
+    ss_point_light* d_point = reinterpret_cast<ss_point_light*>(c->d_lights);
+    ss_spot_light* d_spot = reinterpret_cast<ss_spot_light*>(c->d_lights + SS_MAX_LIGHTS * sizeof(ss_point_light));
+    SS_CUDA(c, cudaMemsetAsync(d_out, 0, kOut, c->stream));
+    if (n_point) SS_CUDA(c, cudaMemcpyAsync(d_point, point, n_point * sizeof(ss_point_light), cudaMemcpyHostToDevice, c->stream));
+    if (n_spot) SS_CUDA(c, cudaMemcpyAsync(d_spot, spot, n_spot * sizeof(ss_spot_light), cudaMemcpyHostToDevice, c->stream));
+    launch_pack_lights(c->d_trs, d_point, n_point, d_spot, n_spot, d_out, c->stream);
+    SS_CUDA(c, cudaGetLastError());
+    unsigned char host[kOut];
+    SS_CUDA(c, cudaMemcpyAsync(host, d_out, kOut, cudaMemcpyDeviceToHost, c->stream));
+    SS_CUDA(c, cudaStreamSynchronize(c->stream));
+    if (ub_point_out) memcpy(ub_point_out, host, SS_UB_POINT_LIGHTS_BYTES);
+    if (ub_spot_out) memcpy(ub_spot_out, host + SS_UB_POINT_LIGHTS_BYTES, SS_UB_SPOT_LIGHTS_BYTES);
+    if (positions_out) memcpy(positions_out, host + SS_UB_POINT_LIGHTS_BYTES + SS_UB_SPOT_LIGHTS_BYTES, (size_t)(n_point + n_spot) * 16);
     return SS_OK;
 }
 
@@ -1370,6 +1425,39 @@ SS_API ss_status ss_merge_place_peers(void* cuda_stream, const int32_t* const* r
     launch_merge_place_peers(rank_lists, seg_rank, seg_out, seg_src, seg_add, seg_key, n_segs, out_idx, out_keys,
                              static_cast<cudaStream_t>(cuda_stream));
     return cudaGetLastError() == cudaSuccess ? SS_OK : SS_ERR_CUDA;
+}
+
+SS_API ss_status ss_set_instance_entities(ss_ctx* c, uint32_t first, uint32_t count, const int32_t* entity_ids)
+{
+    if (!c) return SS_ERR_INVALID;
+    if (!entity_ids || (uint64_t)first + count > c->n_instances)
+        return c->fail(SS_ERR_INVALID, "ss_set_instance_entities: range [%u, +%u) exceeds %u instances", first, count, c->n_instances);
+    SS_CUDA(c, cudaSetDevice(c->device));
+    if (!c->d_entity) {
+        SS_CUDA(c, cudaMalloc(reinterpret_cast<void**>(&c->d_entity), std::max<size_t>((size_t)c->cfg.max_instances * 4, 256)));
+        SS_CUDA(c, cudaMemsetAsync(c->d_entity, 0xFF, (size_t)c->cfg.max_instances * 4, c->stream));  // -1: no entity
+    }
+    if (count) {
+        SS_CUDA(c, cudaMemcpyAsync(c->d_entity + first, entity_ids, (size_t)count * 4, cudaMemcpyHostToDevice, c->stream));
+        SS_CUDA(c, cudaStreamSynchronize(c->stream));
+    }
+    return SS_OK;
+}
+
+SS_API ss_status ss_select_view(ss_ctx* c, uint32_t slot, uint32_t view, const void** device_out, void* host_out)
+{
+    ss_outputs o;
+    ss_status st = ss_map_outputs(c, slot, view, &o);  // fences the frame: counts are on the host
+    if (st != SS_OK) return st;
+    if (!c->d_select) SS_CUDA(c, cudaMalloc(reinterpret_cast<void**>(&c->d_select), std::max<size_t>((size_t)c->cap_visible * 52, 256)));
+    launch_select_records(reinterpret_cast<const float4*>(o.instance_rows), o.instance_idx, c->d_entity, o.visible, c->d_select,
+                          c->stream);
+    SS_CUDA(c, cudaGetLastError());
+    if (host_out && o.visible)
+        SS_CUDA(c, cudaMemcpyAsync(host_out, c->d_select, (size_t)o.visible * 52, cudaMemcpyDeviceToHost, c->stream));
+    SS_CUDA(c, cudaStreamSynchronize(c->stream));
+    if (device_out) *device_out = c->d_select;
+    return SS_OK;
 }
 
 SS_API void* ss_stream(ss_ctx* c) { return c ? c->stream : nullptr; }

@@ -23,6 +23,8 @@ struct NodeLevelArgs {
 void launch_node_level(const NodeLevelArgs& a, cudaStream_t st);
 // TRS records of scattered nodes: trs[node_index[k]] = records[k] for k in order (a later record wins)
 void launch_trs_scatter(float* trs, const uint32_t* node_index, const float* records, uint32_t count, cudaStream_t st);
+// physics poses {position xyz, quaternion xyzw} of scattered nodes -> Translation and Rotation (Euler) of their TRS records
+void launch_pose_scatter(float* trs, const uint32_t* node_index, const float* poses, uint32_t count, cudaStream_t st);
 
 struct InstanceArgs {
     const float* trs;
@@ -56,6 +58,13 @@ bool launch_instances(const InstanceArgs& a, const CullParams& cp, cudaStream_t 
 // persistent TMA + packed-FP32 fast path, two instances per thread (transform_cull_x2.cu); same results bit for bit
 bool instances_x2_eligible(const InstanceArgs& a);
 void launch_instances_x2(const InstanceArgs& a, const CullParams& cp, cudaStream_t st);
+
+// SelectTransformData records {rows 48 B, entity id} of a view's compacted list (transform_cull.cu)
+void launch_select_records(const float4* rows, const uint32_t* idx, const int32_t* entity, uint32_t visible, uint32_t* out13,
+                           cudaStream_t st);
+// light uniform blocks from the TRS stream (transform_cull.cu); out = [496 B UBPointLights | 656 B UBSpotLights | positions]
+void launch_pack_lights(const float* trs, const ss_point_light* point, uint32_t n_point, const ss_spot_light* spot,
+                        uint32_t n_spot, unsigned char* out, cudaStream_t st);
 
 // ---- onesweep radix sort (radix_sort.cu) -------------------------------------------------------
 constexpr int kMaxRadixBits = 9;

@@ -5,6 +5,7 @@
 // memory with 128-bit coalesced loads, each thread then reads its own record at an odd word stride
 // (bank-conflict free), computes, and the 48 B output rows leave through shared memory as 128-bit
 // coalesced stores.  No tensor cores: a 4x4 affine product per instance is not a dense contraction.
+#include <algorithm>
 #include <cstdlib>
 
 #include "ss_kernels.h"
@@ -234,7 +235,105 @@ __global__ void k_trs_scatter(float* trs, const uint32_t* node_index, const floa
     const uint32_t k = g / 9u, f = g - k * 9u;
     if (k < count) trs[(size_t)node_index[k] * 9 + f] = records[(size_t)k * 9 + f];
 }
+// The physics write-back loop (Platform/JoltPhysics/JoltPhysicsWorld.cpp:112-127) on the device: body position and
+// rotation quaternion -> TransformComponent::Translation and ::Rotation; Scale is left as it is.  The Euler angles are
+// JPH::Quat::GetEulerAngles (vendor/JoltPhysics/Jolt/Math/Quat.inl:185-203) in its operation order; Jolt evaluates
+// ATan2 / ASin with its own polynomials, here they are CUDA's atan2f / asinf (a few ulp apart: the angles agree to
+// 1e-6, they are not bit-identical).
+__global__ void k_pose_scatter(float* trs, const uint32_t* node_index, const float* poses, uint32_t count)
+{
+    const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= count) return;
+    const float* p = poses + (size_t)k * 7;
+    const float x = p[3], y = p[4], z = p[5], w = p[6];
+    const float y_sq = y * y;
+    const float t0 = 2.0f * (w * x + y * z);
+    const float t1 = 1.0f - 2.0f * (x * x + y_sq);
+    float t2 = 2.0f * (w * y - z * x);
+    t2 = t2 > 1.0f ? 1.0f : t2;
+    t2 = t2 < -1.0f ? -1.0f : t2;
+    const float t3 = 2.0f * (w * z + x * y);
+    const float t4 = 1.0f - 2.0f * (y_sq + z * z);
+    float* t = trs + (size_t)node_index[k] * 9;
+    t[0] = p[0];
+    t[1] = p[1];
+    t[2] = p[2];
+    t[3] = atan2f(t0, t1);
+    t[4] = asinf(t2);
+    t[5] = atan2f(t3, t4);
+}
 }  // namespace
+
+namespace {
+// Scene::UpdateLightsBuffer / OnUpdateLights (VC/Scene/Scene.cpp:167-264): one thread per light
+__global__ void k_pack_lights(const float* trs, const ss_point_light* point, uint32_t n_point, const ss_spot_light* spot,
+                              uint32_t n_spot, unsigned char* out)
+{
+    const uint32_t t = threadIdx.x;
+    float* ubp = reinterpret_cast<float*>(out);
+    float* ubs = reinterpret_cast<float*>(out + SS_UB_POINT_LIGHTS_BYTES);
+    float* posv = reinterpret_cast<float*>(out + SS_UB_POINT_LIGHTS_BYTES + SS_UB_SPOT_LIGHTS_BYTES);
+    if (t == 0) {
+        reinterpret_cast<int*>(ubp)[0] = (int)n_point;
+        reinterpret_cast<int*>(ubs)[0] = (int)n_spot;
+    }
+    if (t < n_point) {
+        const ss_point_light L = point[t];
+        const float* tr = trs + (size_t)L.node * 9;
+        float* o = ubp + 4 + t * 12;
+        o[0] = tr[0]; o[1] = tr[1]; o[2] = tr[2]; o[3] = 1.0f;
+        o[4] = L.color[0]; o[5] = L.color[1]; o[6] = L.color[2]; o[7] = L.color[3];
+        o[8] = L.radius; o[9] = L.falloff;
+        float* q = posv + t * 4;
+        q[0] = tr[0]; q[1] = tr[1]; q[2] = tr[2]; q[3] = L.radius;
+    } else if (t >= 16 && t - 16 < n_spot) {
+        const uint32_t k = t - 16;
+        const ss_spot_light L = spot[k];
+        const float* tr = trs + (size_t)L.node * 9;
+        // glm::normalize(Rotation) = v * inversesqrt(dot(v, v)), inversesqrt(x) = 1 / sqrt(x) (GLM/detail/func_exponential.inl)
+        const float rx = tr[3], ry = tr[4], rz = tr[5];
+        const float inv = 1.0f / sqrtf(rx * rx + ry * ry + rz * rz);
+        float* o = ubs + 4 + k * 16;
+        o[0] = tr[0]; o[1] = tr[1]; o[2] = tr[2]; o[3] = 1.0f;
+        o[4] = L.color[0]; o[5] = L.color[1]; o[6] = L.color[2]; o[7] = L.color[3];
+        o[8] = rx * inv; o[9] = ry * inv; o[10] = rz * inv;
+        o[11] = L.inner_cutoff; o[12] = L.outer_cutoff; o[13] = L.radius; o[14] = L.falloff;
+        float* q = posv + (n_point + k) * 4;
+        q[0] = tr[0]; q[1] = tr[1]; q[2] = tr[2]; q[3] = L.radius;
+    }
+}
+}  // namespace
+
+void launch_pack_lights(const float* trs, const ss_point_light* point, uint32_t n_point, const ss_spot_light* spot, uint32_t n_spot,
+                        unsigned char* out, cudaStream_t st)
+{
+    k_pack_lights<<<1, 32, 0, st>>>(trs, point, n_point, spot, n_spot, out);
+}
+
+namespace {
+// one thread per 32-bit word of the 52 B records: words 0..11 = the instance rows, word 12 = the entity id
+__global__ void k_select_records(const uint32_t* __restrict__ rows, const uint32_t* __restrict__ idx, const int32_t* __restrict__ entity,
+                                 uint32_t visible, uint32_t* __restrict__ out)
+{
+    const uint64_t total = (uint64_t)visible * 13u, step = (uint64_t)gridDim.x * blockDim.x;
+    for (uint64_t g = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; g < total; g += step) {
+        const uint32_t e = (uint32_t)(g / 13u), w = (uint32_t)(g - (uint64_t)e * 13u);
+        out[g] = w < 12 ? rows[(size_t)e * 12 + w] : (entity ? (uint32_t)entity[idx[e]] : 0xFFFFFFFFu);
+    }
+}
+}  // namespace
+
+void launch_select_records(const float4* rows, const uint32_t* idx, const int32_t* entity, uint32_t visible, uint32_t* out13, cudaStream_t st)
+{
+    if (!visible) return;
+    const uint64_t want = ((uint64_t)visible * 13 + 255) / 256;
+    k_select_records<<<(unsigned)std::min<uint64_t>(want, 148 * 16), 256, 0, st>>>(reinterpret_cast<const uint32_t*>(rows), idx, entity, visible, out13);
+}
+
+void launch_pose_scatter(float* trs, const uint32_t* node_index, const float* poses, uint32_t count, cudaStream_t st)
+{
+    if (count) k_pose_scatter<<<(count + 255u) / 256u, 256, 0, st>>>(trs, node_index, poses, count);
+}
 
 void launch_trs_scatter(float* trs, const uint32_t* node_index, const float* records, uint32_t count, cudaStream_t st)
 {

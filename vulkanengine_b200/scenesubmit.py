@@ -32,7 +32,7 @@ EXPORTS = ["ss_create", "ss_destroy", "ss_last_error", "ss_version", "ss_set_key
            "ss_cascade_matrices_batch", "ss_upload_trs_sparse", "ss_merge_place",
            "ss_export_idx_lists", "ss_ipc_open", "ss_ipc_close", "ss_merge_place_peers",
            "ss_merge_create", "ss_merge_destroy", "ss_merge_views", "ss_merge_map", "ss_merge_last_error",
-           "ss_export_slot_buffers", "ss_cascade_matrices_snapped"]
+           "ss_export_slot_buffers", "ss_cascade_matrices_snapped", "ss_upload_pose_sparse", "ss_pack_lights", "ss_set_instance_entities", "ss_select_view"]
 RASTER_DEPTH_CLAMP = 1
 RASTER_EMPTY = 0xFFFFFFFFFFFFFFFF
 
@@ -290,6 +290,37 @@ class SceneSubmit:
         trs = np.ascontiguousarray(trs, np.float32).reshape(-1, 9)
         assert len(node_index) == len(trs)
         self._ck(self.lib.ss_upload_trs_sparse(self.h, C.c_uint32(len(trs)), _p(node_index), _p(trs)))
+
+    def upload_pose_sparse(self, node_index, pose7):
+        """(position xyz, quaternion xyzw) per node: the physics write-back, converted to Euler angles on the device."""
+        node_index = np.ascontiguousarray(node_index, np.uint32)
+        pose7 = np.ascontiguousarray(pose7, np.float32).reshape(-1, 7)
+        assert len(node_index) == len(pose7)
+        self._ck(self.lib.ss_upload_pose_sparse(self.h, C.c_uint32(len(pose7)), _p(node_index), _p(pose7)))
+
+    def set_instance_entities(self, entity_ids, first=0):
+        e = np.ascontiguousarray(entity_ids, np.int32)
+        self._ck(self.lib.ss_set_instance_entities(self.h, C.c_uint32(first), C.c_uint32(len(e)), _p(e)))
+
+    def select_view(self, slot, view, stats):
+        """SelectTransformData records (rows [12] + entity id) of the view, draw order."""
+        m = int(stats.visible[view])
+        rec = np.empty(m, np.dtype([("rows", "<f4", (12,)), ("entity", "<i4")]))
+        ptr = C.c_void_p()
+        self._ck(self.lib.ss_select_view(self.h, C.c_uint32(slot), C.c_uint32(view), C.byref(ptr), _p(rec)))
+        return rec
+
+    def pack_lights(self, point_nodes, point_par, spot_nodes, spot_par):
+        """point_par [n][6] = color rgba, radius, falloff; spot_par [n][8] = color rgba, inner, outer, radius, falloff.
+        Returns (UBPointLights bytes, UBSpotLights bytes, positions [n_point + n_spot][4])."""
+        pt = np.zeros(len(point_nodes), np.dtype([("node", "<u4"), ("par", "<f4", (6,))]))
+        pt["node"], pt["par"] = point_nodes, np.asarray(point_par, np.float32).reshape(-1, 6)
+        sp = np.zeros(len(spot_nodes), np.dtype([("node", "<u4"), ("par", "<f4", (8,))]))
+        sp["node"], sp["par"] = spot_nodes, np.asarray(spot_par, np.float32).reshape(-1, 8)
+        ubp, ubs = np.zeros(496, np.uint8), np.zeros(656, np.uint8)
+        pos = np.zeros((len(pt) + len(sp), 4), np.float32)
+        self._ck(self.lib.ss_pack_lights(self.h, _p(pt), C.c_uint32(len(pt)), _p(sp), C.c_uint32(len(sp)), _p(ubp), _p(ubs), _p(pos)))
+        return ubp, ubs, pos
 
     def upload_trs_sparse_ptr(self, node_index_ptr, trs_ptr, count):
         """Raw host pointers (pinned tensors): ascending node lists are copied straight from them."""
