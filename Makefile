@@ -19,14 +19,20 @@ HOSTBIN  := vulkanengine_b200/host/host_cli.bin
 HOSTSRC  := vulkanengine_b200/host/Scene.cpp vulkanengine_b200/host/SceneSerializer.cpp vulkanengine_b200/host/MeshImporter.cpp vulkanengine_b200/host/host_cli.cpp
 HOSTHDR  := $(wildcard vulkanengine_b200/host/*.h) include/scenesubmit.h
 
-all: $(LIB) $(HOSTBIN)
+MERGEBIN := vulkanengine_b200/host/merge_cli.bin
+
+all: $(LIB) $(HOSTBIN) $(MERGEBIN)
 
 # C++ host mirror of Scene / SceneRenderer: plain g++, links the C ABI only
 $(HOSTBIN): $(HOSTSRC) $(HOSTHDR) $(LIB)
 	g++ -std=c++17 -O2 -Wall -ffp-contract=off -o $@ $(HOSTSRC) -Lvulkanengine_b200 -lscenesubmit -lz \
 	    -Wl,-rpath,'$$ORIGIN/..'
 
-host: $(HOSTBIN)
+# merged draw lists of several shards from a C++ host (C ABI only)
+$(MERGEBIN): vulkanengine_b200/host/merge_cli.cpp include/scenesubmit.h $(LIB)
+	g++ -std=c++17 -O2 -Wall -o $@ vulkanengine_b200/host/merge_cli.cpp -Lvulkanengine_b200 -lscenesubmit -Wl,-rpath,'$$ORIGIN/..'
+
+host: $(HOSTBIN) $(MERGEBIN)
 
 $(OBJDIR)/%.o: $(CSRC)/%.cu $(HDRS)
 	@mkdir -p $(OBJDIR)

@@ -413,6 +413,9 @@ SS_API void ss_merge_destroy(ss_merge* m);
 SS_API ss_status ss_merge_views(ss_merge* m, void* cuda_stream, const ss_merge_peer* peers);
 /* waits for cuda_stream, returns the view's merged buffers (library-owned, valid until the next ss_merge_views) */
 SS_API ss_status ss_merge_map(ss_merge* m, void* cuda_stream, uint32_t view, ss_merged_view* out);
+/* host copies of a merged view (any pointer may be NULL; sizes from a first call with NULL pointers) */
+SS_API ss_status ss_merge_download(ss_merge* m, void* cuda_stream, uint32_t view, uint32_t* instance_idx, uint64_t* keys,
+                                   ss_draw_cmd* draws, uint64_t* draw_keys, uint32_t* visible_out, uint32_t* draws_out);
 SS_API const char* ss_merge_last_error(const ss_merge* m);
 /* CUDA IPC handles of every buffer a peer needs of this context, for ss_ipc_open in another process:
    [frames_in_flight][max_views][3] in the order idx, draws, draw_keys, then [frames_in_flight] counts blocks

@@ -100,3 +100,14 @@ def test_mirror_render_scene_matches_oracle(name, tmp_path):
             assert (int(dl[d, 0]), int(dl[d, 1]), int(dl[d, 2]), int(dl[d, 3])) == (mesh, mat, sub, tess)
             assert int(dl[d, 5]) == int(r["draws"]["instance_count"][d]) and int(dl[d, 8]) == int(r["draws"]["first_instance"][d])
             assert int(dl[d, 4]) == int(r["draws"]["index_count"][d]) and int(dl[d, 6]) == int(r["draws"]["first_index"][d])
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("mode", ["", "resident"])
+def test_merge_from_a_cpp_host(mode):
+    """ss_merge_views called from C++ through the C ABI alone (vulkanengine_b200/host/merge_cli.cpp): the merged lists of
+    three shards equal one context holding the scene."""
+    exe = os.path.join(ROOT, "vulkanengine_b200", "host", "merge_cli.bin")
+    r = subprocess.run([exe, "150000", "3"] + ([mode] if mode else []), capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stdout + r.stderr
+    assert "merge identical" in r.stdout

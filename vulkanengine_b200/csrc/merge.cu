@@ -359,6 +359,29 @@ SS_API ss_status ss_merge_map(ss_merge* m, void* cuda_stream, uint32_t view, ss_
     return SS_OK;
 }
 
+SS_API ss_status ss_merge_download(ss_merge* m, void* cuda_stream, uint32_t view, uint32_t* instance_idx, uint64_t* keys,
+                                   ss_draw_cmd* draws, uint64_t* draw_keys, uint32_t* visible_out, uint32_t* draws_out)
+{
+    ss_merged_view o;
+    const ss_status st = ss_merge_map(m, cuda_stream, view, &o);
+    if (st != SS_OK) return st;
+    cudaStream_t s = static_cast<cudaStream_t>(cuda_stream);
+    cudaError_t e = cudaSuccess;
+    if (instance_idx && o.visible) e = cudaMemcpyAsync(instance_idx, o.instance_idx, (size_t)o.visible * 4, cudaMemcpyDeviceToHost, s);
+    if (e == cudaSuccess && keys && o.visible) e = cudaMemcpyAsync(keys, o.keys, (size_t)o.visible * 8, cudaMemcpyDeviceToHost, s);
+    if (e == cudaSuccess && draws && o.n_draws)
+        e = cudaMemcpyAsync(draws, o.draws, (size_t)o.n_draws * sizeof(ss_draw_cmd), cudaMemcpyDeviceToHost, s);
+    if (e == cudaSuccess && draw_keys && o.n_draws) e = cudaMemcpyAsync(draw_keys, o.draw_keys, (size_t)o.n_draws * 8, cudaMemcpyDeviceToHost, s);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(s);
+    if (e != cudaSuccess) {
+        m->err = std::string("ss_merge_download: ") + cudaGetErrorString(e);
+        return SS_ERR_CUDA;
+    }
+    if (visible_out) *visible_out = o.visible;
+    if (draws_out) *draws_out = o.n_draws;
+    return SS_OK;
+}
+
 SS_API const char* ss_merge_last_error(const ss_merge* m) { return m ? m->err.c_str() : ""; }
 
 }  // extern "C"

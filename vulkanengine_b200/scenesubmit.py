@@ -31,7 +31,7 @@ EXPORTS = ["ss_create", "ss_destroy", "ss_last_error", "ss_version", "ss_set_key
            "ss_set_geometry", "ss_raster_view", "ss_map_raster", "ss_download_raster", "ss_read_pixel",
            "ss_cascade_matrices_batch", "ss_upload_trs_sparse", "ss_merge_place",
            "ss_export_idx_lists", "ss_ipc_open", "ss_ipc_close", "ss_merge_place_peers",
-           "ss_merge_create", "ss_merge_destroy", "ss_merge_views", "ss_merge_map", "ss_merge_last_error",
+           "ss_merge_create", "ss_merge_destroy", "ss_merge_views", "ss_merge_map", "ss_merge_last_error", "ss_merge_download",
            "ss_export_slot_buffers", "ss_cascade_matrices_snapped", "ss_upload_pose_sparse", "ss_pack_lights", "ss_set_instance_entities", "ss_select_view"]
 RASTER_DEPTH_CLAMP = 1
 RASTER_EMPTY = 0xFFFFFFFFFFFFFFFF
