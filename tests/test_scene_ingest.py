@@ -223,3 +223,36 @@ def test_loaded_mini_scene_selection_and_shadow_passes(tmp_path):
     hovered = int(np.frombuffer(b2[9 + 17 + 11], np.int32)[0])
     inst = int(covered[y, x] & np.uint64(0xFFFFFFFF))
     assert hovered == int(f["entity"][inst])
+
+
+def test_submesh_tables_against_the_reference_assimp_import():
+    """tests/golden/vkmeshes_assimp.json is the submesh table the REFERENCE's importer path gives for the bundled FBX
+    sources: its vendored Assimp compiled by oracle/Makefile (`make -C oracle assimp`) with Mesh.cpp:62-72's flags, then
+    MeshSource / TraverseNodes bookkeeping (oracle/ref_assimp.cpp).  The headless reader (host/MeshImporter.cpp, pinned to
+    tests/golden/vkmeshes.json by the tests above) must agree on everything the submission path reads:
+      exact      number and order of submeshes, BaseIndex, IndexCount, MaterialIndex
+      1e-6       LocalTransform (Assimp accumulates in float, the reader in double), local bounds
+      different  VertexCount / BaseVertex: Assimp's JoinIdenticalVertices welds corners that share every attribute
+                 (after CalcTangentSpace); the reader keeps one vertex per polygon corner, so its counts are >= Assimp's
+                 and its vertex_offset refers to its own (unwelded) vertex arena, which is what its index buffer indexes."""
+    import json
+    here = os.path.dirname(os.path.abspath(__file__))
+    ours = json.load(open(os.path.join(here, "golden", "vkmeshes.json")))["sources"]
+    ref = json.load(open(os.path.join(here, "golden", "vkmeshes_assimp.json")))["sources"]
+    assert len(ref) >= 11
+    for src, table in ref.items():
+        mine = ours[src]
+        assert len(mine) == len(table), src
+        base_vertex = 0
+        for a, b in zip(table, mine):
+            for f in ("BaseIndex", "IndexCount", "MaterialIndex"):
+                assert a[f] == b[f], (src, f)
+            la, lb = np.array(a["LocalTransform"]), np.array(b["LocalTransform"])
+            assert np.abs(la - lb).max() <= 1e-6 * max(np.abs(la).max(), 1.0), src
+            for f in ("BoundsMin", "BoundsMax"):
+                xa, xb = np.array(a[f]), np.array(b[f])
+                assert np.abs(xa - xb).max() <= 1e-6 * max(np.abs(xa).max(), 1e-30), (src, f)
+            assert b["VertexCount"] >= a["VertexCount"] and b["BaseVertex"] >= a["BaseVertex"]
+            assert b["VertexCount"] <= a["IndexCount"]          # never more than one vertex per corner
+            assert b["BaseVertex"] == base_vertex                # the reader's own arena is dense
+            base_vertex += b["VertexCount"]
