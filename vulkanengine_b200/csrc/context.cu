@@ -1,6 +1,7 @@
 // libscenesubmit C ABI: context, device streams, frame orchestration.  See include/scenesubmit.h for the
 // contract and the reference code each entry point replaces.
 #include <cuda_runtime.h>
+#include <nvtx3/nvToolsExt.h>
 
 #include <algorithm>
 #include <cstdarg>
@@ -802,6 +803,15 @@ SS_API ss_status ss_frame(ss_ctx* c, const ss_view* views, uint32_t n_views, uin
     const bool nodes_kept = resident && (flags & SS_FRAME_REUSE_WORLD) && c->nodes_valid;  // node rows of the parent levels
     const bool reuse_sort = !resident && (flags & SS_FRAME_REUSE_SORT) && c->sort_valid;
 
+    // NVTX ranges carry the names of the reference's Optick scopes around the loops this frame replaces:
+    // "Submit-SceneRenderer" (VC/Scene/SceneRenderer.cpp:1062), "Submit-SubmitMeshes" (VC/Scene/Scene.cpp:137),
+    // "SubmitMesh" (SceneRenderer.cpp:1126)
+    struct NvtxScope {
+        bool open = true;
+        explicit NvtxScope(const char* name) { nvtxRangePushA(name); }
+        void end() { if (open) nvtxRangePop(); open = false; }
+        ~NvtxScope() { end(); }
+    } nvtx_frame("Submit-SceneRenderer");
     SS_CUDA(c, adopt_pending_upload(c));
     SS_CUDA(c, cudaEventRecord(s.start, st));
     SS_CUDA(c, cudaMemsetAsync(c->d_emit_zero, 0, c->emit_zero_bytes, st));
@@ -827,6 +837,7 @@ SS_API ss_status ss_frame(ss_ctx* c, const ss_view* views, uint32_t n_views, uin
     const size_t seg_words = (size_t)c->cfg.max_views * c->max_draws;
     const uint64_t* words_known = nullptr;    // resident layout: the sorted words
 
+    NvtxScope nvtx_meshes("Submit-SubmitMeshes");
     if (resident) {
         // Draw-order-resident layout: the sort runs when a static stream changes, not per frame; the streams are kept
         // in sorted order, so the instance kernel writes world rows and masks in draw order and k_emit streams them.
@@ -1034,6 +1045,7 @@ SS_API ss_status ss_frame(ss_ctx* c, const ss_view* views, uint32_t n_views, uin
         SS_CUDA(c, cudaEventRecord(s.stage[3], st));
     }
 
+    nvtx_meshes.end();
     DrawArgs da;
     memset(&da, 0, sizeof da);
     da.n_views = n_views;

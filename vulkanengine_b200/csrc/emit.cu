@@ -601,9 +601,27 @@ size_t emit_lookback_bytes(uint64_t n)
     return (size_t)(tiles ? tiles : 1) * kEmitWords * sizeof(uint32_t);
 }
 
+namespace {
+int device_sm_count()
+{
+    static int sms[64] = {0};
+    int dev = 0;
+    cudaGetDevice(&dev);
+    int& n = sms[dev & 63];
+    if (!n && cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess) n = 148;
+    return n;
+}
+}  // namespace
+
 void launch_emit(const EmitArgs& a, cudaStream_t st)
 {
-    cudaFuncSetAttribute(k_emit, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(EmitSmem));
+    static bool attr_set[64] = {false};
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (!attr_set[dev & 63]) {
+        cudaFuncSetAttribute(k_emit, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(EmitSmem));
+        attr_set[dev & 63] = true;
+    }
     const uint32_t tiles = (a.n + kEmitTile - 1) / kEmitTile;
     if (tiles) k_emit<<<tiles, kEmitThreads, sizeof(EmitSmem), st>>>(a);
 }
@@ -618,7 +636,7 @@ void launch_draws(const DrawArgs& a, cudaStream_t st)
 void launch_merge_place(const int32_t* lists, const int64_t* seg_out, const int64_t* seg_src, const int64_t* seg_add,
                         const int64_t* seg_key, uint32_t n_segs, int32_t* out_idx, int64_t* out_keys, cudaStream_t st)
 {
-    if (n_segs) k_merge_place<<<148 * 8, 256, 0, st>>>(lists, seg_out, seg_src, seg_add, seg_key, n_segs, out_idx, out_keys);
+    if (n_segs) k_merge_place<<<device_sm_count() * 8, 256, 0, st>>>(lists, seg_out, seg_src, seg_add, seg_key, n_segs, out_idx, out_keys);
 }
 
 void launch_merge_place_peers(const int32_t* const* rank_lists, const int32_t* seg_rank, const int64_t* seg_out,
@@ -626,7 +644,7 @@ void launch_merge_place_peers(const int32_t* const* rank_lists, const int32_t* s
                               int32_t* out_idx, int64_t* out_keys, cudaStream_t st)
 {
     if (n_segs)
-        k_merge_place_peers<<<148 * 8, 256, 0, st>>>(rank_lists, seg_rank, seg_out, seg_src, seg_add, seg_key, n_segs, out_idx, out_keys);
+        k_merge_place_peers<<<device_sm_count() * 8, 256, 0, st>>>(rank_lists, seg_rank, seg_out, seg_src, seg_add, seg_key, n_segs, out_idx, out_keys);
 }
 
 }  // namespace ss

@@ -320,18 +320,30 @@ void launch_instances_x2(const InstanceArgs& a, const CullParams& cp, cudaStream
     nz.neg_one = ((uint64_t)neg_one << 32) | neg_one;
     nz.neg_zero = ((uint64_t)neg_zero << 32) | neg_zero;
     const uint32_t n_tiles = (a.n + kTile2 - 1) / kTile2;
-    int dev = 0, sms = 148;
+    // attribute + occupancy are looked up once per device and kernel variant, not per frame
+    struct PerDevice {
+        int sms = 0, per_sm[2] = {0, 0};
+    };
+    static PerDevice cache[64];
+    int dev = 0;
     cudaGetDevice(&dev);
-    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    PerDevice& pd = cache[dev & 63];
     const size_t smem = sizeof(Smem2);
-    int per_sm = 1;
-    if (a.parent) {
-        cudaFuncSetAttribute(k_instances_x2<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_instances_x2<true>, kThreads2, smem);
-    } else {
-        cudaFuncSetAttribute(k_instances_x2<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_instances_x2<false>, kThreads2, smem);
+    const int which = a.parent ? 1 : 0;
+    if (!pd.per_sm[which]) {
+        int sms_q = 148, per = 1;
+        cudaDeviceGetAttribute(&sms_q, cudaDevAttrMultiProcessorCount, dev);
+        if (a.parent) {
+            cudaFuncSetAttribute(k_instances_x2<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+            cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per, k_instances_x2<true>, kThreads2, smem);
+        } else {
+            cudaFuncSetAttribute(k_instances_x2<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+            cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per, k_instances_x2<false>, kThreads2, smem);
+        }
+        pd.sms = sms_q;
+        pd.per_sm[which] = std::max(per, 1);
     }
+    const int sms = pd.sms, per_sm = pd.per_sm[which];
     // persistent: one resident wave; a multiple of the SM count
     const uint32_t grid = std::min<uint32_t>(n_tiles, (uint32_t)(sms * std::max(per_sm, 1)));
     if (a.parent)
