@@ -117,13 +117,26 @@ __global__ void __launch_bounds__(kSegThreads) k_merge_segments(const __grid_con
         t.n_segs[v] = n_segs;
     }
     __syncthreads();
-    for (uint32_t s0 = 0; s0 < n_segs; s0 += kSegThreads) {
-        const uint32_t s = s0 + tid;
-        const bool ok = s < n_segs;
-        const uint32_t c = ok ? t.seg_cnt[vb + s] : 0u;
-        const uint64_t key = ok ? t.seg_key[vb + s] : 0ull;
-        const bool head = ok && (s == 0 || t.seg_key[vb + s - 1] != key);
-        uint32_t xc = c, xh = head ? 1u : 0u;
+    constexpr int kIt = 8;  // consecutive segments per thread and step
+    for (uint32_t s0 = 0; s0 < n_segs; s0 += kSegThreads * kIt) {
+        const uint32_t first = s0 + tid * kIt;
+        uint32_t c[kIt];
+        uint64_t key[kIt];
+        bool head[kIt];
+        uint64_t prev_key = (first > 0 && first <= n_segs) ? t.seg_key[vb + first - 1] : 0ull;
+        uint32_t tc = 0, th = 0;
+#pragma unroll
+        for (int j = 0; j < kIt; ++j) {
+            const uint32_t s = first + j;
+            const bool ok = s < n_segs;
+            c[j] = ok ? t.seg_cnt[vb + s] : 0u;
+            key[j] = ok ? t.seg_key[vb + s] : 0ull;
+            head[j] = ok && (s == 0 || key[j] != prev_key);
+            prev_key = key[j];
+            tc += c[j];
+            th += head[j] ? 1u : 0u;
+        }
+        uint32_t xc = tc, xh = th;
 #pragma unroll
         for (int o = 1; o < 32; o <<= 1) {
             const uint32_t yc = __shfl_up_sync(0xffffffffu, xc, o), yh = __shfl_up_sync(0xffffffffu, xh, o);
@@ -142,15 +155,21 @@ __global__ void __launch_bounds__(kSegThreads) k_merge_segments(const __grid_con
             bc += warp_c[w];
             bh += warp_h[w];
         }
-        const uint32_t excl_c = bc + xc - c, draw_no = bh + xh - (head ? 1u : 0u);
-        if (ok) {
-            t.seg_out[(size_t)v * (t.n_ranks * t.max_draws + 1) + s] = excl_c;
-            if (head) {  // the merged draw of this key: its instances start here; the count is filled below
-                ss_draw_cmd d = t.seg_draw[vb + s];
-                d.first_instance = excl_c;
-                d.instance_count = 0;
-                t.out_draws[vb + draw_no] = d;
-                t.out_draw_keys[vb + draw_no] = key;
+        uint32_t excl_c = bc + xc - tc, draw_no = bh + xh - th;
+#pragma unroll
+        for (int j = 0; j < kIt; ++j) {
+            const uint32_t s = first + j;
+            if (s < n_segs) {
+                t.seg_out[(size_t)v * (t.n_ranks * t.max_draws + 1) + s] = excl_c;
+                if (head[j]) {  // the merged draw of this key: its instances start here; the count is filled below
+                    ss_draw_cmd d = t.seg_draw[vb + s];
+                    d.first_instance = excl_c;
+                    d.instance_count = 0;
+                    t.out_draws[vb + draw_no] = d;
+                    t.out_draw_keys[vb + draw_no] = key[j];
+                    ++draw_no;
+                }
+                excl_c += c[j];
             }
         }
         __syncthreads();
@@ -175,48 +194,62 @@ __global__ void __launch_bounds__(kSegThreads) k_merge_segments(const __grid_con
     }
 }
 
-// Persistent warps over the merged list of every view (grid.y = view), 128 positions per warp and round: a warp bisects
-// the segment prefix once and its lanes walk on from there; four independent peer reads per lane are in flight.
+// Persistent warps over the merged list of every view (grid.y = view), kChunk = 512 consecutive positions per warp and
+// step.  A warp bisects the segment prefix once per chunk; every lane then keeps the segment it is in (its end, its source
+// pointer, key and instance base) in registers and only re-reads the tables when it walks past the segment's end, so the
+// steady state per element is one peer read (four in flight per lane) and two coalesced stores.
 __global__ void __launch_bounds__(256) k_merge_place(const __grid_constant__ PeerTable pt, const __grid_constant__ MergeTables t)
 {
-    constexpr int kRounds = 4;
+    constexpr int kBatch = 4, kRoundsPerChunk = 16, kChunk = 32 * kRoundsPerChunk;
     const uint32_t v = blockIdx.y;
     const int lane = threadIdx.x & 31;
     const size_t vb = (size_t)v * t.n_ranks * t.max_draws;
     const uint32_t n_segs = t.n_segs[v];
-    const uint32_t* seg_out = t.seg_out + (size_t)v * (t.n_ranks * t.max_draws + 1);
+    const uint32_t* __restrict__ seg_out = t.seg_out + (size_t)v * (t.n_ranks * t.max_draws + 1);
     const uint32_t total = min(seg_out[n_segs], t.cap_visible);
-    uint32_t* out_idx = t.out_idx + (size_t)v * t.cap_visible;
-    uint64_t* out_keys = t.out_keys + (size_t)v * t.cap_visible;
+    uint32_t* __restrict__ out_idx = t.out_idx + (size_t)v * t.cap_visible;
+    uint64_t* __restrict__ out_keys = t.out_keys + (size_t)v * t.cap_visible;
     const uint32_t warps = (gridDim.x * blockDim.x) >> 5, warp_id = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    for (uint64_t g0 = (uint64_t)warp_id * (32 * kRounds); g0 < total; g0 += (uint64_t)warps * (32 * kRounds)) {
+    for (uint64_t g0 = (uint64_t)warp_id * kChunk; g0 < total; g0 += (uint64_t)warps * kChunk) {
         uint32_t lo = 0, hi = n_segs;
         while (hi - lo > 1) {
             const uint32_t mid = (lo + hi) >> 1;
             if (seg_out[mid] <= g0) lo = mid; else hi = mid;
         }
-        uint32_t val[kRounds];
-        uint64_t key[kRounds];
-        uint32_t sI = lo;
+        // the lane's current segment, cached
+        uint32_t cur = lo, seg_begin = 0, seg_end = 0, ibase = 0;
+        const uint32_t* src = nullptr;
+        uint64_t key = 0;
+        auto load_segment = [&](uint32_t sI) {
+            seg_begin = seg_out[sI];
+            seg_end = seg_out[sI + 1];
+            const ss_merge_peer& p = pt.p[v][t.seg_rank[vb + sI]];
+            src = p.idx + t.seg_src[vb + sI];
+            ibase = (uint32_t)p.instance_base;
+            key = t.seg_key[vb + sI];
+        };
+        load_segment(cur);
+        for (int r0 = 0; r0 < kRoundsPerChunk; r0 += kBatch) {
+            uint32_t val[kBatch];
+            uint64_t kk[kBatch];
 #pragma unroll
-        for (int r = 0; r < kRounds; ++r) {
-            const uint64_t e = g0 + r * 32 + lane;
-            val[r] = 0;
-            key[r] = 0;
-            if (e < total) {
-                while (seg_out[sI + 1] <= e) ++sI;
-                const uint32_t rk = t.seg_rank[vb + sI];
-                const ss_merge_peer& p = pt.p[v][rk];
-                val[r] = p.idx[t.seg_src[vb + sI] + (uint32_t)(e - seg_out[sI])] + (uint32_t)p.instance_base;
-                key[r] = t.seg_key[vb + sI];
+            for (int r = 0; r < kBatch; ++r) {
+                const uint64_t e = g0 + (uint64_t)(r0 + r) * 32 + lane;
+                val[r] = 0;
+                kk[r] = 0;
+                if (e < total) {
+                    while (e >= seg_end) load_segment(++cur);  // empty segments are stepped over
+                    val[r] = src[(uint32_t)e - seg_begin] + ibase;
+                    kk[r] = key;
+                }
             }
-        }
 #pragma unroll
-        for (int r = 0; r < kRounds; ++r) {
-            const uint64_t e = g0 + r * 32 + lane;
-            if (e < total) {
-                out_idx[e] = val[r];
-                out_keys[e] = key[r];
+            for (int r = 0; r < kBatch; ++r) {
+                const uint64_t e = g0 + (uint64_t)(r0 + r) * 32 + lane;
+                if (e < total) {
+                    out_idx[e] = val[r];
+                    out_keys[e] = kk[r];
+                }
             }
         }
     }
@@ -322,7 +355,7 @@ SS_API ss_status ss_merge_views(ss_merge* m, void* cuda_stream, const ss_merge_p
     k_merge_fetch<<<dim3(std::min<uint32_t>(chunks, 8), t.n_views, t.n_ranks), 256, 0, st>>>(pt, t);
     k_merge_rank<<<dim3((t.n_ranks * t.max_draws + 255) / 256, t.n_views), 256, 0, st>>>(t);
     k_merge_segments<<<t.n_views, kSegThreads, 0, st>>>(t);
-    k_merge_place<<<dim3((unsigned)m->sms * 2, t.n_views), 256, 0, st>>>(pt, t);
+    k_merge_place<<<dim3((unsigned)m->sms * 4, t.n_views), 256, 0, st>>>(pt, t);
     const cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) {
         m->err = std::string("ss_merge_views: ") + cudaGetErrorString(e);

@@ -43,7 +43,7 @@ int make_ctx(const SceneData& sc, size_t lo, size_t hi, const std::vector<ss_sub
     cfg.max_instances = n;
     cfg.max_submesh_slots = (uint32_t)table.size();
     cfg.max_views = 5;
-    cfg.max_draws_per_view = 4096;
+    cfg.max_draws_per_view = 16384;
     cfg.flags = flags;
     ss_ctx* ctx = nullptr;
     CK(ss_create(&cfg, &ctx));
@@ -131,7 +131,7 @@ int main(int argc, char** argv)
             peers[v * shards + r] = {o.instance_idx, o.draws, o.draw_keys, o.counts, (uint64_t)lo[r]};
         }
     ss_merge* mg = nullptr;
-    if (ss_merge_create(0, shards, 5, 4096, n, &mg) != SS_OK) { std::fprintf(stderr, "ss_merge_create: %s\n", ss_last_error(nullptr)); return 2; }
+    if (ss_merge_create(0, shards, 5, 16384, n, &mg) != SS_OK) { std::fprintf(stderr, "ss_merge_create: %s\n", ss_last_error(nullptr)); return 2; }
     if (ss_merge_views(mg, nullptr, peers.data()) != SS_OK) { std::fprintf(stderr, "ss_merge_views: %s\n", ss_merge_last_error(mg)); return 2; }
     bool same = true;
     for (uint32_t v = 0; v < 5; ++v) {
