@@ -147,9 +147,13 @@ def ncu_traffic(n, n_views):
         rows = list(csv.reader(open(os.path.join(ROOT, "profiles", name))))
         hdr = rows[0]
         ir, iw = hdr.index("dram__bytes_read.sum"), hdr.index("dram__bytes_write.sum")
+        iname = hdr.index("Kernel Name") if "Kernel Name" in hdr else 0
+        irep = hdr.index("report") if "report" in hdr else None
         for r in rows[2:]:
+            if irep is not None and "general" not in r[irep]:
+                continue  # the capture of the general pipeline's frame (the resident frame is in the same file)
             for key in ("k_instances", "k_emit"):
-                if key in r[0] and key not in out:
+                if key in r[iname] and key not in out:
                     out[key] = int((float(r[ir]) + float(r[iw])) * 1e9)
     except Exception:
         pass

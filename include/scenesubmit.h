@@ -155,7 +155,8 @@ typedef struct ss_outputs {
     const ss_draw_cmd* draws;     /* [draws]        one per run of equal keys, in MeshKey order */
     const uint64_t* draw_keys;    /* [draws]        key of each draw (to bind mesh + material) */
     const uint32_t* counts;       /* device: {visible, draws} of this view */
-    /* Every instance's world rows (row-major 4x4 at a 64 B stride, row 3 = 0,0,0,1) and visibility byte.  NOT per
+    /* Every instance's world rows (world_stride floats apart: 16 = row-major 4x4 with row 3 = 0,0,0,1 in the general
+       pipeline, 12 = packed TransformData in the resident layout) and visibility byte.  NOT per
        slot: they belong to the most recent ss_frame of the context and are overwritten by the next one (the per-view
        lists above are what stays valid per slot).  General pipeline: entry i = instance i, world_words = NULL.
        Draw-order-resident layout: entry j = the instance named by world_words[j] & ((1 << world_idx_bits) - 1), i.e.

@@ -912,7 +912,8 @@ SS_API ss_status ss_frame(ss_ctx* c, const ss_view* views, uint32_t n_views, uin
         ia.matword = c->d_matword_o;
         ia.inst_aabb = c->has_inst_aabb ? c->d_box_o : nullptr;
         ia.slots = c->d_slots;
-        ia.world = c->d_world;   // rows of sorted position j
+        ia.world = c->d_world;   // rows of sorted position j, packed 48 B apart: their only reader streams them
+        ia.world_stride = 3;
         ia.mask = c->d_mask;
         ia.keys = nullptr;       // the order is kept: masks only
         ia.vals = nullptr;
@@ -929,6 +930,7 @@ SS_API ss_status ss_frame(ss_ctx* c, const ss_view* views, uint32_t n_views, uin
         ea.keys_a = c->d_words_resident;
         ea.idx_bits = (uint32_t)idx_bits;
         ea.seq = 1;
+        ea.world_stride = 3;
         ea.mask = c->d_mask;
         ea.world = c->d_world;
         ea.n = n;
@@ -965,6 +967,7 @@ SS_API ss_status ss_frame(ss_ctx* c, const ss_view* views, uint32_t n_views, uin
         ia.inst_aabb = c->has_inst_aabb ? c->d_inst_aabb : nullptr;
         ia.slots = c->d_slots;
         ia.world = c->d_world;
+        ia.world_stride = kWorldStride;
         ia.mask = c->d_mask;
         ia.keys = c->d_keys_a;
         ia.vals = c->d_vals_a;
@@ -1026,6 +1029,7 @@ SS_API ss_status ss_frame(ss_ctx* c, const ss_view* views, uint32_t n_views, uin
         ea.gather_mask = (!packed || ia.mask_bits == 0 || reuse_sort) ? 1u : 0u;
         ea.mask = c->d_mask;
         ea.world = c->d_world;
+        ea.world_stride = kWorldStride;
         ea.n = n;
         ea.n_views = n_views;
         for (uint32_t v = 0; v < n_views; ++v) ea.out[v] = s.out[v];
@@ -1140,6 +1144,7 @@ SS_API ss_status ss_map_outputs(ss_ctx* c, uint32_t slot, uint32_t view, ss_outp
     if (s.pipeline == SS_PIPELINE_RESIDENT) {
         out->world_words = s.words_known;
         out->world_idx_bits = s.idx_bits;
+        out->world_stride = 12;
     }
     return SS_OK;
 }
@@ -1189,7 +1194,7 @@ static ss_status download_word_ordered(ss_ctx* c, uint32_t first, uint32_t count
     void* tmp = nullptr;
     SS_CUDA(c, cudaMalloc(&tmp, std::max<size_t>((size_t)count * (rows12 ? 48 : 1), 256)));
     launch_unpermute(words, (1ull << c->words_idx_bits) - 1ull, c->n_instances, first, count,
-                     reinterpret_cast<const float4*>(c->d_world), kWorldStride, rows12 ? static_cast<float4*>(tmp) : nullptr, c->d_mask,
+                     reinterpret_cast<const float4*>(c->d_world), 3u, rows12 ? static_cast<float4*>(tmp) : nullptr, c->d_mask,
                      masks ? static_cast<uint8_t*>(tmp) : nullptr, c->stream);
     cudaError_t e = cudaGetLastError();
     if (e == cudaSuccess)

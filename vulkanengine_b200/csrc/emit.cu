@@ -289,8 +289,8 @@ __global__ void __launch_bounds__(kEmitThreads, 4) k_emit(const __grid_constant_
                 const uint32_t li = s.list[v][e];
                 const uint32_t g = base + e;
                 if (g < a.cap_visible) {
-                    o.keys[g] = s.key[li];
-                    o.idx[g] = s.idx[li];
+                    __stcs(reinterpret_cast<unsigned long long*>(o.keys + g), (unsigned long long)s.key[li]);
+                    __stcs(o.idx + g, s.idx[li]);
                 }
             }
             const uint32_t total4 = cnt * 3u;
@@ -302,7 +302,7 @@ __global__ void __launch_bounds__(kEmitThreads, 4) k_emit(const __grid_constant_
                     if (j < total4) {
                         const uint32_t e = j / 3u, part = j - e * 3u;
                         const uint32_t li = s.list[v][e];
-                        r[u] = __ldg(a.seq ? a.world + ((size_t)tile_base + li) * kWorldStride + part
+                        r[u] = __ldg(a.seq ? a.world + ((size_t)tile_base + li) * a.world_stride + part
                                            : a.world + (size_t)s.idx[li] * kWorldStride + part);
                     }
                 }
@@ -311,7 +311,7 @@ __global__ void __launch_bounds__(kEmitThreads, 4) k_emit(const __grid_constant_
                     const uint32_t j = j0 + u * kEmitThreads;
                     if (j < total4) {
                         const uint32_t e = j / 3u;
-                        if (base + e < a.cap_visible) o.rows[(size_t)base * 3u + j] = r[u];
+                        if (base + e < a.cap_visible) __stcs(o.rows + (size_t)base * 3u + j, r[u]);  // written once, read by another kernel
                     }
                 }
             }
@@ -351,7 +351,7 @@ __global__ void __launch_bounds__(kEmitThreads, 4) k_emit(const __grid_constant_
             const uint32_t j = tid + (u0 + u) * kEmitThreads;
             const uint32_t e = j / 3u, part = j - e * 3u;
             if (u0 + u < kParts && s.msk[e])
-                r[u] = __ldg(a.seq ? a.world + ((size_t)tile_base + e) * kWorldStride + part : a.world + (size_t)s.idx[e] * kWorldStride + part);
+                r[u] = __ldg(a.seq ? a.world + ((size_t)tile_base + e) * a.world_stride + part : a.world + (size_t)s.idx[e] * kWorldStride + part);
         }
 #pragma unroll
         for (int u = 0; u < kGatherBatch; ++u) {

@@ -36,7 +36,9 @@ struct InstanceArgs {
     const uint32_t* matword;
     const float* inst_aabb;    // [n][6] or nullptr
     const SlotDev* slots;
-    float4* world;             // [n][kWorldStride] in/out
+    float4* world;             // [n][world_stride] in/out
+    uint32_t world_stride;     // float4 per instance: kWorldStride (4: one aligned 64 B block per row set, what the sorted-order
+                               // gather wants) or 3 (packed TransformData, for the sequential reader of the resident layout)
     uint8_t* mask;
     uint64_t* keys;
     uint32_t* vals;            // iota payload for the sort
@@ -131,6 +133,7 @@ struct EmitArgs {
     uint32_t idx_bits;             // > 0: sorted words are [key | mask | instance]
     uint32_t mask_bits;            // 8: a visibility byte sits above the instance index (layout of the word)
     uint32_t gather_mask;          // 1: read visibility from mask[] (no byte in the word, or a reused, stale one)
+    uint32_t world_stride;         // float4 per entry of `world`
     uint32_t seq;                  // 1: world rows and masks lie in WORD order: entry j belongs to sorted word j, so the
                                    //    "gather" is a sequential read (draw-order-resident layout, resident.cu)
     const uint8_t* mask;

@@ -136,7 +136,7 @@ __global__ void __launch_bounds__(kTile) k_instances(InstanceArgs a, const __gri
     if (from_trs) tile_load_f32<9>(s_trs, a.trs + ((size_t)a.node_base + base) * 9, n_tile);
     if (a.inst_aabb) tile_load_f32<6>(s_box, a.inst_aabb + (size_t)base * 6, n_tile);
     if (a.world_given) {
-        const float4* src = a.world + (size_t)base * kWorldStride;
+        const float4* src = a.world + (size_t)base * kWorldStride;  // given rows always come at the 64 B stride
         for (int k = tid; k < n_tile * kWorldStride; k += kTile) s_rows[row_slot(k)] = ld_nc_f4(src + k);
     }
     uint32_t slot = SS_SLOT_NULL, mw = 0;
@@ -204,11 +204,16 @@ __global__ void __launch_bounds__(kTile) k_instances(InstanceArgs a, const __gri
             s_rows[row_slot(tid * kWorldStride + 3)] = make_float4(0.f, 0.f, 0.f, 1.f);
         }
         __syncthreads();
-        float4* dst = a.world + (size_t)base * kWorldStride;
+        if (a.world_stride == 3) {  // packed TransformData: rows 0..2 of every instance, 48 B apart
+            float4* dst = a.world + (size_t)base * 3;
+            for (int k = tid; k < n_tile * 3; k += kTile) dst[k] = s_rows[row_slot((k / 3) * kWorldStride + k % 3)];
+        } else {
+            float4* dst = a.world + (size_t)base * kWorldStride;
 #pragma unroll
-        for (int u = 0; u < kWorldStride; ++u) {
-            const int k = tid + u * kTile;
-            if (k < n_tile * kWorldStride) dst[k] = s_rows[row_slot(k)];
+            for (int u = 0; u < kWorldStride; ++u) {
+                const int k = tid + u * kTile;
+                if (k < n_tile * kWorldStride) dst[k] = s_rows[row_slot(k)];
+            }
         }
     }
     if (valid) {

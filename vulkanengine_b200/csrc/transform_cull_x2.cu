@@ -209,31 +209,35 @@ __global__ void __launch_bounds__(kThreads2, HAS_PARENT ? 8 : 10) k_instances_x2
         }
         aff_mul2(m, node, loc, w);  // VC/Scene/SceneRenderer.cpp:1150
 
-        // ---- world rows to HBM, 64 B per instance.  A lane's four rows are contiguous but the lanes of a warp
-        // sit 64 B apart, so they are transposed through a warp-private shared buffer (no block barrier) and
-        // leave as four fully coalesced 512 B stores per group of 32 instances.
+        // ---- world rows to HBM, 64 B (or, world_stride == 3, 48 B) per instance.  A lane's rows are contiguous but
+        // the lanes of a warp sit a whole instance apart, so they are transposed through a warp-private shared buffer
+        // (no block barrier) and leave as fully coalesced 512 B stores per group of 32 instances.
         {
             float4* tr = s.tr[tid >> 5];
             const int lane = tid & 31;
             const float4 zero = make_float4(0.f, 0.f, 0.f, 0.f), last = make_float4(0.f, 0.f, 0.f, 1.f);
+            const bool packed_rows = a.world_stride == 3;
 #pragma unroll
             for (int h = 0; h < 2; ++h) {
                 const bool live = h ? live1 : live0;
                 const int first = (h ? t1 : t0) - lane;  // first instance of this warp's group inside the tile
 #pragma unroll
-                for (int r = 0; r < 3; ++r)
-                    tr[row_slot2(lane * 4 + r)] =
-                        !live ? zero
-                              : (h ? make_float4(hi(w.r[r][0]), hi(w.r[r][1]), hi(w.r[r][2]), hi(w.r[r][3]))
-                                   : make_float4(lo(w.r[r][0]), lo(w.r[r][1]), lo(w.r[r][2]), lo(w.r[r][3])));
-                tr[row_slot2(lane * 4 + 3)] = last;
+                for (int r = 0; r < 3; ++r) {
+                    const float4 row = !live ? zero
+                                             : (h ? make_float4(hi(w.r[r][0]), hi(w.r[r][1]), hi(w.r[r][2]), hi(w.r[r][3]))
+                                                  : make_float4(lo(w.r[r][0]), lo(w.r[r][1]), lo(w.r[r][2]), lo(w.r[r][3])));
+                    // 48 B stride: 12 words per lane, eight consecutive lanes cover all 32 banks as they are
+                    tr[packed_rows ? lane * 3 + r : row_slot2(lane * 4 + r)] = row;
+                }
+                if (!packed_rows) tr[row_slot2(lane * 4 + 3)] = last;
                 __syncwarp();
-                float4* dst = a.world + ((size_t)base + first) * kWorldStride;
-                const int n_rows = min(max(n_tile - first, 0), 32) * kWorldStride;
+                const int per = packed_rows ? 3 : kWorldStride;
+                float4* dst = a.world + ((size_t)base + first) * per;
+                const int n_rows = min(max(n_tile - first, 0), 32) * per;
 #pragma unroll
                 for (int j = 0; j < 4; ++j) {
                     const int k = j * 32 + lane;
-                    if (k < n_rows) dst[k] = tr[row_slot2(k)];
+                    if (k < n_rows) __stcs(dst + k, tr[packed_rows ? k : row_slot2(k)]);  // read once, by a later kernel
                 }
                 __syncwarp();
             }
