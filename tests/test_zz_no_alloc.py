@@ -81,3 +81,31 @@ def test_static_scratch_sort_rejects_sizes_beyond_its_maximum():
     st = lib.ss_sort_pairs_static(None, None, _dev(va), _dev(kb), _dev(vb), C.c_uint64(8), C.c_int(0), C.c_int(64),
                                   C.byref(in_b))
     assert st == S.SS_ERR_INVALID
+
+
+def test_static_scratch_sort_on_a_second_device_and_stream_ownership():
+    """The built-in scratch exists once per GPU that loads the library and its address is looked up per device: a
+    sort on device 1 must work after sorts on device 0, and a stream of another device than the current one is
+    refused instead of running kernels where the looked-up address means nothing.  Needs two GPUs."""
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("one GPU")
+    lib = S.load_library()
+    n = 50_000
+    keys = np.random.default_rng(3).integers(0, 2**64, size=n, dtype=np.uint64)
+    with torch.cuda.device(1):
+        dev = torch.device("cuda", 1)
+        ka = torch.from_numpy(keys.view(np.int64).copy()).to(dev)
+        va = torch.arange(n, dtype=torch.int32, device=dev)
+        kb, vb = torch.empty_like(ka), torch.empty_like(va)
+        in_b = C.c_int(-1)
+        stream = C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+        st = lib.ss_sort_pairs_static(stream, _dev(ka), _dev(va), _dev(kb), _dev(vb), C.c_uint64(n), C.c_int(0), C.c_int(64),
+                                      C.byref(in_b))
+        assert st == S.SS_OK, lib.ss_last_error(None).decode()
+        v = (vb if in_b.value else va).cpu().numpy().view(np.uint32)
+        assert np.array_equal(v, np.argsort(keys, kind="stable").astype(np.uint32))
+        other = torch.cuda.Stream(device=0)
+        st = lib.ss_sort_pairs_static(C.c_void_p(other.cuda_stream), _dev(ka), _dev(va), _dev(kb), _dev(vb), C.c_uint64(n),
+                                      C.c_int(0), C.c_int(64), C.byref(in_b))
+        assert st == S.SS_ERR_INVALID
