@@ -86,11 +86,16 @@ struct ss_ctx {
     uint32_t* d_overflow = nullptr;
     uint32_t* d_seg_count = nullptr;   // [2][max_views][max_draws]: per-view run counters, double-buffered by frame
     uint32_t* d_seg_runs = nullptr;    // [2] runs left in each buffer
-    // staging of ss_upload_trs_sparse: pinned host + device, [count] indices then [count][9] records; grows on demand
+    // staging of the sparse uploads: [count] indices then [count][R] records; grows on demand.  One pinned host buffer
+    // (pageable callers only) and two device buffers, so that the copy of one call (upload stream) runs under the frame
+    // issued before it while the scatter of the call before still reads the other buffer.
     unsigned char* h_sparse = nullptr;
-    unsigned char* d_sparse = nullptr;
+    unsigned char* d_sparse[2] = {nullptr, nullptr};
     size_t sparse_cap = 0;
-    cudaEvent_t ev_sparse = nullptr;   // the staging buffer's last copy has left the host
+    int sparse_cur = 0;
+    cudaEvent_t ev_sparse = nullptr;             // the host staging buffer's last copy has left the host
+    cudaEvent_t ev_sparse_copied = nullptr;      // upload stream: this call's records are in d_sparse[cur]
+    cudaEvent_t ev_sparse_scattered[2] = {nullptr, nullptr};  // frame stream: the scatter that read d_sparse[b] is done
     int32_t* d_entity = nullptr;       // ss_set_instance_entities (allocated on first use)
     uint32_t* d_select = nullptr;      // ss_select_view: SelectTransformData records of one view (allocated on first use)
     unsigned char* d_lights = nullptr; // ss_pack_lights: light descriptions in, uniform blocks out
@@ -267,8 +272,12 @@ SS_API void ss_destroy(ss_ctx* c)
     }
     for (void* p : c->allocs) cudaFree(p);
     if (c->h_sparse) cudaFreeHost(c->h_sparse);
-    if (c->d_sparse) cudaFree(c->d_sparse);
+    for (int b = 0; b < 2; ++b) {
+        if (c->d_sparse[b]) cudaFree(c->d_sparse[b]);
+        if (c->ev_sparse_scattered[b]) cudaEventDestroy(c->ev_sparse_scattered[b]);
+    }
     if (c->ev_sparse) cudaEventDestroy(c->ev_sparse);
+    if (c->ev_sparse_copied) cudaEventDestroy(c->ev_sparse_copied);
     if (c->d_lights) cudaFree(c->d_lights);
     if (c->d_entity) cudaFree(c->d_entity);
     if (c->d_select) cudaFree(c->d_select);
@@ -600,78 +609,98 @@ static ss_status upload_sparse_records(ss_ctx* c, uint32_t count, const uint32_t
     if (!c) return SS_ERR_INVALID;
     if (count && (!node_index || !recs)) return c->fail(SS_ERR_INVALID, "%s: null array", who);
     if (!count) return SS_OK;
-    for (uint32_t k = 0; k < count; ++k)
-        if (node_index[k] >= c->n_nodes)
-            return c->fail(SS_ERR_INVALID, "%s: record %u names node %u of %u", who, k, node_index[k], c->n_nodes);
+    // one pass over the list: bounds and strict ascent (what a producer walking its bodies in order sends)
+    uint32_t over = node_index[0] >= c->n_nodes, not_asc = 0;
+    for (uint32_t k = 1; k < count; ++k) {
+        over |= node_index[k] >= c->n_nodes;
+        not_asc |= node_index[k] <= node_index[k - 1];
+    }
+    if (over)
+        for (uint32_t k = 0; k < count; ++k)
+            if (node_index[k] >= c->n_nodes)
+                return c->fail(SS_ERR_INVALID, "%s: record %u names node %u of %u", who, k, node_index[k], c->n_nodes);
+    const bool ascending = !not_asc;
     SS_CUDA(c, cudaSetDevice(c->device));
     const size_t rec_bytes = (size_t)R * 4, bytes = (size_t)count * (4 + rec_bytes);
-    if (!c->ev_sparse) SS_CUDA(c, cudaEventCreateWithFlags(&c->ev_sparse, cudaEventDisableTiming));
+    if (!c->ev_sparse) {
+        SS_CUDA(c, cudaEventCreateWithFlags(&c->ev_sparse, cudaEventDisableTiming));
+        SS_CUDA(c, cudaEventCreateWithFlags(&c->ev_sparse_copied, cudaEventDisableTiming));
+        for (int b = 0; b < 2; ++b) SS_CUDA(c, cudaEventCreateWithFlags(&c->ev_sparse_scattered[b], cudaEventDisableTiming));
+    }
     if (bytes > c->sparse_cap) {
+        SS_CUDA(c, cudaStreamSynchronize(c->upload_stream));
         SS_CUDA(c, cudaStreamSynchronize(c->stream));
         if (c->h_sparse) cudaFreeHost(c->h_sparse);
-        if (c->d_sparse) cudaFree(c->d_sparse);
-        c->h_sparse = c->d_sparse = nullptr;
+        for (int b = 0; b < 2; ++b) {
+            if (c->d_sparse[b]) cudaFree(c->d_sparse[b]);
+            c->d_sparse[b] = nullptr;
+        }
+        c->h_sparse = nullptr;
         c->sparse_cap = 0;
         const size_t cap = std::max<size_t>(bytes * 2, 1 << 16);
         SS_CUDA(c, cudaHostAlloc(reinterpret_cast<void**>(&c->h_sparse), cap, cudaHostAllocDefault));
-        SS_CUDA(c, cudaMalloc(reinterpret_cast<void**>(&c->d_sparse), cap));
+        for (int b = 0; b < 2; ++b) SS_CUDA(c, cudaMalloc(reinterpret_cast<void**>(&c->d_sparse[b]), cap));
         c->sparse_cap = cap;
-    } else {
-        SS_CUDA(c, cudaEventSynchronize(c->ev_sparse));  // the previous call's copy must have left the staging buffer
     }
-    // pack: indices, then records, keeping only the LAST record of a node named more than once.  Strictly ascending
-    // node lists (what a producer walking its bodies in order sends) cannot hold duplicates: two memcpys.
-    uint32_t* hi = reinterpret_cast<uint32_t*>(c->h_sparse);
-    bool ascending = true;
-    for (uint32_t k = 1; k < count && ascending; ++k) ascending = node_index[k] > node_index[k - 1];
-    uint32_t kept = 0;
-    const void* src_idx = c->h_sparse;
-    const void* src_rec = nullptr;
+    // Pinned caller memory with an ascending list (no duplicates possible) is read by the copy engine where it lies (same
+    // rule as ss_upload_trs: unchanged until ss_flush_uploads or the next frame's ss_frame_sync).  Anything else is packed
+    // into the pinned staging buffer, keeping only the LAST record of a node named more than once.
+    bool in_place = false;
     if (ascending) {
-        kept = count;
-        // pinned caller memory is read by the copy engine where it lies (same rule as ss_upload_trs: unchanged until
-        // ss_flush_uploads or the next frame's ss_frame_sync); pageable memory is staged
         cudaPointerAttributes pa_i{}, pa_r{};
-        const bool pinned = cudaPointerGetAttributes(&pa_i, node_index) == cudaSuccess && pa_i.type == cudaMemoryTypeHost &&
-                            cudaPointerGetAttributes(&pa_r, recs) == cudaSuccess && pa_r.type == cudaMemoryTypeHost;
+        in_place = cudaPointerGetAttributes(&pa_i, node_index) == cudaSuccess && pa_i.type == cudaMemoryTypeHost &&
+                   cudaPointerGetAttributes(&pa_r, recs) == cudaSuccess && pa_r.type == cudaMemoryTypeHost;
         cudaGetLastError();
-        if (pinned) {
-            src_idx = node_index;
-            src_rec = recs;
-        } else {
+    }
+    uint32_t kept = 0;
+    if (in_place) {
+        kept = count;
+    } else {
+        SS_CUDA(c, cudaEventSynchronize(c->ev_sparse));  // the previous staged copy must have left the staging buffer
+        uint32_t* hi = reinterpret_cast<uint32_t*>(c->h_sparse);
+        if (ascending) {
+            kept = count;
             memcpy(hi, node_index, (size_t)count * 4);
             memcpy(c->h_sparse + (size_t)count * 4, recs, (size_t)count * rec_bytes);
-        }
-    } else {
-        std::unordered_map<uint32_t, uint32_t> last;
-        last.reserve(count * 2);
-        for (uint32_t k = 0; k < count; ++k) last[node_index[k]] = k;
-        for (uint32_t k = 0; k < count; ++k)
-            if (last[node_index[k]] == k) hi[kept++] = k;          // source positions for now
-        float* hr = reinterpret_cast<float*>(c->h_sparse + (size_t)kept * 4);
-        for (uint32_t j = 0; j < kept; ++j) {
-            const uint32_t k = hi[j];
-            memcpy(hr + (size_t)j * R, recs + (size_t)k * R, rec_bytes);
-            hi[j] = node_index[k];
+        } else {
+            std::unordered_map<uint32_t, uint32_t> last;
+            last.reserve(count * 2);
+            for (uint32_t k = 0; k < count; ++k) last[node_index[k]] = k;
+            for (uint32_t k = 0; k < count; ++k)
+                if (last[node_index[k]] == k) hi[kept++] = k;          // source positions for now
+            float* hr = reinterpret_cast<float*>(c->h_sparse + (size_t)kept * 4);
+            for (uint32_t j = 0; j < kept; ++j) {
+                const uint32_t k = hi[j];
+                memcpy(hr + (size_t)j * R, recs + (size_t)k * R, rec_bytes);
+                hi[j] = node_index[k];
+            }
         }
     }
     c->world_valid = c->nodes_valid = false;  // transforms changed
     c->res_trs_dirty = true;
     SS_CUDA(c, adopt_pending_upload(c));  // lands on top of whatever whole-stream upload came before it
-    if (src_rec) {
-        SS_CUDA(c, cudaMemcpyAsync(c->d_sparse, src_idx, (size_t)kept * 4, cudaMemcpyHostToDevice, c->stream));
-        SS_CUDA(c, cudaMemcpyAsync(c->d_sparse + (size_t)kept * 4, src_rec, (size_t)kept * rec_bytes, cudaMemcpyHostToDevice, c->stream));
+    // copy on the upload stream (under the frames already issued), scatter on the frame stream once the copy is in
+    const int b = c->sparse_cur;
+    c->sparse_cur ^= 1;
+    unsigned char* dst = c->d_sparse[b];
+    SS_CUDA(c, cudaStreamWaitEvent(c->upload_stream, c->ev_sparse_scattered[b], 0));
+    if (in_place) {
+        SS_CUDA(c, cudaMemcpyAsync(dst, node_index, (size_t)kept * 4, cudaMemcpyHostToDevice, c->upload_stream));
+        SS_CUDA(c, cudaMemcpyAsync(dst + (size_t)kept * 4, recs, (size_t)kept * rec_bytes, cudaMemcpyHostToDevice, c->upload_stream));
     } else {
-        SS_CUDA(c, cudaMemcpyAsync(c->d_sparse, c->h_sparse, (size_t)kept * (4 + rec_bytes), cudaMemcpyHostToDevice, c->stream));
+        SS_CUDA(c, cudaMemcpyAsync(dst, c->h_sparse, (size_t)kept * (4 + rec_bytes), cudaMemcpyHostToDevice, c->upload_stream));
+        SS_CUDA(c, cudaEventRecord(c->ev_sparse, c->upload_stream));
     }
-    SS_CUDA(c, cudaEventRecord(c->ev_sparse, c->stream));
-    const uint32_t* d_idx = reinterpret_cast<const uint32_t*>(c->d_sparse);
-    const float* d_rec = reinterpret_cast<const float*>(c->d_sparse + (size_t)kept * 4);
+    SS_CUDA(c, cudaEventRecord(c->ev_sparse_copied, c->upload_stream));
+    SS_CUDA(c, cudaStreamWaitEvent(c->stream, c->ev_sparse_copied, 0));
+    const uint32_t* d_idx = reinterpret_cast<const uint32_t*>(dst);
+    const float* d_rec = reinterpret_cast<const float*>(dst + (size_t)kept * 4);
     if (R == 9)
         launch_trs_scatter(c->d_trs, d_idx, d_rec, kept, c->stream);
     else
         launch_pose_scatter(c->d_trs, d_idx, d_rec, kept, c->stream);
     SS_CUDA(c, cudaGetLastError());
+    SS_CUDA(c, cudaEventRecord(c->ev_sparse_scattered[b], c->stream));
     return SS_OK;
 }
 
