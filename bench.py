@@ -7,13 +7,21 @@ synthetic scene of configs[2] ("synthetic 16M instances, main camera + 4 cascade
 frusta"), 2^24 instances per GPU.  N > 1 GPUs: entity-wise shards, 2^24 instances per rank (weak
 scaling; N = 4 is configs[3]'s 64M), no data-path collective in the sharded phase.
 
-  value      instances/s with every input stream resident in HBM (CUDA events, max over ranks)
+  value      instances/s with every input stream resident in HBM, general pipeline: the keys are sorted
+             every frame (CUDA events on the frame stream, max over ranks)
   e2e        the same metric through the C ABI from HOST buffers: pinned TRS upload (36 B/instance) +
-             view matrices in, per-view indirect draws + draw keys + counts out, every step
-  roofline   the dominant kernel (transform+cull+key) against the measured HBM peak
+             view matrices in, per-view indirect draws + draw keys + counts out, every step; beside it
+             e2e.dirty_tenth (a tenth of the transforms sent as sparse records) and e2e.h2d_probe (the
+             host's copy bandwidth with all ranks copying at once: the ceiling of the full upload)
+  roofline   the frame's longest kernel (k_emit: compaction + gather of the world rows) against the
+             measured HBM peak; roofline_other_kernels holds the transform+cull+key kernel the same way
+  steady_state   the draw-order-resident layout (SS_CONFIG_DRAW_ORDER_RESIDENT): sorted when the static
+             streams change, not per frame.  Reported beside `value`, never instead of it
+  merge      N > 1: one globally sorted list per view (ss_merge_views over CUDA IPC peer mappings)
+  strong_64m, cfg5, other_configs   configs[3] over the N GPUs, configs[4] (64 views), configs[0/1]
   cpu_baseline / --impl reference
              the reference's CPU path (entt-order walk, glm T*R*S, std::map<MeshKey> grouping, plus
-             the same cull) from oracle/_ref on the box's host cores, on a bounded sample
+             the same cull) from oracle/_ref on the box's host cores (--impl reference: the whole scene)
 """
 import argparse
 import ctypes as C
@@ -508,7 +516,21 @@ def main():
                               "h2d_bytes_per_step": int(n_dirty * 40 + views.nbytes),
                               "note": "the same loop when 10 % of the transforms change per step (ss_upload_trs_sparse); "
                                       "beside the full-upload number, not instead of it"}
-        del host_trs, dirty_t, recs_t
+        # the ceiling of the full-upload number: every rank copies the same pinned stream at once, nothing else running
+        dev_probe = torch.empty(host_trs.numel(), dtype=torch.float32, device=dev)
+        dev_probe.copy_(host_trs, non_blocking=True)
+        torch.cuda.synchronize()
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(3):
+            dev_probe.copy_(host_trs, non_blocking=True)
+        torch.cuda.synchronize()
+        dt_p = max_over_ranks(torch, dist, world, time.perf_counter() - t0) / 3
+        e2e["h2d_probe"] = {"gbs_per_rank": host_trs.numel() * 4 / dt_p / 1e9, "gbs_all_ranks": world * host_trs.numel() * 4 / dt_p / 1e9,
+                            "ceiling_instances_per_s": world * n / dt_p,
+                            "note": "plain pinned host-to-device copies of the TRS stream on all ranks at once (max over ranks): "
+                                    "what the full-upload e2e number cannot exceed on this host"}
+        del host_trs, dirty_t, recs_t, dev_probe
     ctx.close()
 
     # ---- steady state: the draw-order-resident layout (sorted when the static streams change, not per frame) -----
