@@ -106,6 +106,8 @@ struct ss_ctx {
     unsigned long long* d_raster[SS_MAX_VIEWS] = {};  // one target per view: [raster_h[v]][raster_w[v]]
     unsigned long long* d_raster_pairs = nullptr;  // [max_draws + 1]
     uint32_t* d_raster_queue = nullptr;            // works | tile entries | 2 counters (kRasterQueueWorks / kRasterQueueTiles)
+    uint32_t* d_raster_hiz = nullptr;              // coarse depth of the pass being drawn (raster_hiz_words of the largest target)
+    size_t raster_hiz_cap = 0;
     uint32_t raster_w[SS_MAX_VIEWS] = {}, raster_h[SS_MAX_VIEWS] = {};
     uint32_t seg_parity = 0;
     uint64_t* d_seg_key = nullptr;
@@ -287,6 +289,7 @@ SS_API void ss_destroy(ss_ctx* c)
         if (p) cudaFree(p);
     if (c->d_raster_pairs) cudaFree(c->d_raster_pairs);
     if (c->d_raster_queue) cudaFree(c->d_raster_queue);
+    if (c->d_raster_hiz) cudaFree(c->d_raster_hiz);
     if (c->stream) cudaStreamDestroy(c->stream);
     delete c;
 }
@@ -1342,6 +1345,16 @@ SS_API ss_status ss_raster_view(ss_ctx* c, uint32_t slot, uint32_t view, uint32_
     ra.height = height;
     ra.flags = flags;
     ra.target = c->d_raster[view];
+    const size_t hiz_words = raster_hiz_words(width, height);
+    if (hiz_words > c->raster_hiz_cap) {
+        SS_CUDA(c, cudaStreamSynchronize(c->stream));
+        if (c->d_raster_hiz) cudaFree(c->d_raster_hiz);
+        c->d_raster_hiz = nullptr;
+        c->raster_hiz_cap = 0;
+        SS_CUDA(c, cudaMalloc(&c->d_raster_hiz, hiz_words * sizeof(uint32_t)));
+        c->raster_hiz_cap = hiz_words;
+    }
+    ra.hiz = c->d_raster_hiz;
     launch_raster_clear(ra.target, layer, c->stream);
     launch_raster(ra, c->stream);
     SS_CUDA(c, cudaGetLastError());

@@ -601,7 +601,6 @@ size_t emit_lookback_bytes(uint64_t n)
     return (size_t)(tiles ? tiles : 1) * kEmitWords * sizeof(uint32_t);
 }
 
-namespace {
 int device_sm_count()
 {
     static int sms[64] = {0};
@@ -611,7 +610,6 @@ int device_sm_count()
     if (!n && cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess) n = 148;
     return n;
 }
-}  // namespace
 
 void launch_emit(const EmitArgs& a, cudaStream_t st)
 {

@@ -18,6 +18,9 @@
 //      whole target
 // Every float operation is written out in a fixed order (-fmad=false), the order the tests' CPU restatement uses:
 // the two agree bit for bit.  The reference's own rasteriser is the Vulkan device: unavailable on this box.
+#include <algorithm>
+#include <cmath>
+
 #include "ss_kernels.h"
 
 namespace ss {
@@ -122,6 +125,20 @@ __device__ __forceinline__ void put(unsigned long long* target, uint32_t width, 
     atomicMin(target + (size_t)j * width + i, ((unsigned long long)__float_as_uint(depth) << 32) | inst);
 }
 
+// Conservative lower bound of every depth a snapped triangle can store, as float bits (0: no bound).  A sample's depth
+// is fl(fl(fl(z0 l0) + fl(z1 l1)) + fl(z2 l2)) with l_q = fl(fl(e_q) / fl(area)), e_q >= 0 and sum e_q = area: for
+// z_q >= 0 that is at least min z * (1 - 9 * 2^-24).  With DepthClamp the bound stops at 1, the largest depth stored.
+__device__ __forceinline__ uint32_t depth_floor_bits(float z0, float z1, float z2, bool clamp_depth)
+{
+    const float lo = fminf(fminf(z0, z1), z2);
+    if (!(lo > 0.f)) return 0u;
+    float zc = lo * 0.99999905f;  // 1 - 2^-20
+    if (clamp_depth) zc = fminf(zc, 1.0f);
+    return __float_as_uint(zc);
+}
+
+constexpr int kCellShift = 3;  // coarse depth cells of 8 x 8 samples
+
 // what the sample loop needs, derived once per triangle
 struct Prep {
     int x[3], y[3], dx[3], dy[3];  // mode 0; edge q runs from vertex q+1 to vertex q+2 (opposite vertex q); dx, dy carry the
@@ -129,6 +146,11 @@ struct Prep {
     float fa, zn[3];
     float a[3], b[3], c[3], z[3], det, sf;  // mode 1
 };
+
+__device__ __forceinline__ uint32_t work_depth_floor(const Work& t, bool clamp_depth)
+{
+    return t.mode == 0 ? depth_floor_bits(__uint_as_float(t.w[6]), __uint_as_float(t.w[7]), __uint_as_float(t.w[8]), clamp_depth) : 0u;
+}
 
 __device__ __forceinline__ Prep prepare(const Work& t)
 {
@@ -199,6 +221,78 @@ __device__ __forceinline__ void shade(const Prep& p, int mode, int i, int j, boo
         if (!inside) return;
         if (!(p.sf * ((e[0] + e[1]) + e[2]) > 0.f)) return;  // 1 / w at the sample must be positive
         put(target, width, i, j, ((p.z[0] * e[0] + p.z[1] * e[1]) + p.z[2] * e[2]) / p.det, clamp_depth, inst);
+    }
+}
+
+// True when the samples x0..x1 x y0..y1 all lie outside one edge of a snapped triangle.  Exact: an edge function is
+// linear, so it is negative over the rectangle iff it is negative at the corner it favours (a sample ON an edge may
+// belong to the triangle, hence < and not <=).
+__device__ __forceinline__ bool rect_outside(const Prep& p, int x0, int x1, int y0, int y1)
+{
+    bool out = false;
+#pragma unroll
+    for (int q = 0; q < 3; ++q) {
+        const int p0 = (q + 1) % 3;
+        // E = dx (py - y0) - dy (px - x0) is largest where dx favours py and -dy favours px
+        const int py = 256 * (p.dx[q] >= 0 ? y1 : y0) + 128, px = 256 * (p.dy[q] <= 0 ? x1 : x0) + 128;
+        const long long best = (long long)p.dx[q] * (py - p.y[p0]) - (long long)p.dy[q] * (px - p.x[p0]);
+        out = out || best < 0;
+    }
+    return out;
+}
+
+// One warp samples the rectangle x0..x1 x y0..y1 of one triangle, coarse cell by coarse cell: the lanes first sort out
+// which cells can matter (a cell whose coarse depth lies in front of everything the triangle can store, or that lies
+// outside an edge, is skipped whole), then take the samples of each remaining cell two apiece.  `zc` = 0 or no coarse
+// buffer: every cell is sampled.  Skipping never changes the target: a skipped sample could not have won its cell.
+__device__ __forceinline__ void warp_sample_rect(const Prep& p, int mode, int x0, int x1, int y0, int y1, uint32_t zc,
+                                                 bool clamp_depth, uint32_t inst, const RasterArgs& a, int lane)
+{
+    const int cx0 = x0 >> kCellShift, cy0 = y0 >> kCellShift;
+    const int ncx = (x1 >> kCellShift) - cx0 + 1, ncy = (y1 >> kCellShift) - cy0 + 1;
+    const int n_cells = ncx * ncy;
+    for (int base = 0; base < n_cells; base += 32) {
+        const int c = base + lane;
+        bool alive = c < n_cells;
+        int cx = 0, cy = 0;
+        if (alive) {
+            cy = c / ncx;
+            cx = cx0 + (c - cy * ncx);
+            cy += cy0;
+            if (a.hiz && zc > __ldg(a.hiz + (size_t)cy * a.hiz_w + cx)) alive = false;
+            if (alive && mode == 0)
+                alive = !rect_outside(p, max(x0, cx << kCellShift), min(x1, (cx << kCellShift) + 7), max(y0, cy << kCellShift),
+                                      min(y1, (cy << kCellShift) + 7));
+        }
+        uint32_t todo = __ballot_sync(0xffffffffu, alive);
+        while (todo) {
+            const int src = __ffs(todo) - 1;
+            todo &= todo - 1;
+            const int ccx = __shfl_sync(0xffffffffu, cx, src), ccy = __shfl_sync(0xffffffffu, cy, src);
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+                const int sidx = lane + 32 * h;
+                const int i = (ccx << kCellShift) + (sidx & 7), j = (ccy << kCellShift) + (sidx >> 3);
+                if (i >= x0 && i <= x1 && j >= y0 && j <= y1) shade(p, mode, i, j, clamp_depth, inst, a.target, a.width);
+            }
+        }
+    }
+}
+
+// hiz[cell] = the largest depth bits among the cell's samples (all ones while any of them is empty).  The target's
+// words only ever fall, so the value stays an upper bound for as long as it is used.
+__global__ void __launch_bounds__(256) k_raster_hiz(const unsigned long long* __restrict__ target, uint32_t width, uint32_t height,
+                                                    uint32_t* __restrict__ hiz, uint32_t hiz_w, uint32_t hiz_h)
+{
+    const uint32_t n = hiz_w * hiz_h;
+    for (uint32_t c = blockIdx.x * blockDim.x + threadIdx.x; c < n; c += gridDim.x * blockDim.x) {
+        const uint32_t cy = c / hiz_w, cx = c - cy * hiz_w;
+        const uint32_t x0 = cx << kCellShift, y0 = cy << kCellShift;
+        uint32_t m = 0;
+        const uint32_t x1 = min(x0 + 8u, width), y1 = min(y0 + 8u, height);
+        for (uint32_t j = y0; j < y1; ++j)
+            for (uint32_t i = x0; i < x1; ++i) m = max(m, (uint32_t)(__ldcg(target + (size_t)j * width + i) >> 32));
+        hiz[c] = m;
     }
 }
 
@@ -316,11 +410,14 @@ __global__ void __launch_bounds__(kRasterThreads, 4) k_raster(const __grid_const
     __shared__ uint32_t s_pre[kRasterThreads / 32][32];                     // samples before each lane's
     const int lane = threadIdx.x & 31;
     const uint32_t n_draws = min(a.counts[1], a.max_draws);
-    const unsigned long long total = a.pairs[n_draws];
+    const unsigned long long all_pairs = a.pairs[n_draws];
     const bool clamp_depth = (a.flags & SS_RASTER_DEPTH_CLAMP) != 0;
     const unsigned long long warps = ((unsigned long long)gridDim.x * kRasterThreads) >> 5;
     const unsigned long long warp_id = ((unsigned long long)blockIdx.x * kRasterThreads + threadIdx.x) >> 5;
-    for (unsigned long long g0 = warp_id * 32ull; g0 < total; g0 += warps * 32ull) {
+    // this launch's part of the pairs (the pass is drawn in phases, the coarse depth refreshed in between)
+    const unsigned long long first = (unsigned long long)(((unsigned __int128)all_pairs * a.phase_lo) >> 16);
+    const unsigned long long total = (unsigned long long)(((unsigned __int128)all_pairs * a.phase_hi) >> 16);
+    for (unsigned long long g0 = first + warp_id * 32ull; g0 < total; g0 += warps * 32ull) {
         // the last draw whose first pair is <= g0
         uint32_t lo = 0, hi = n_draws;
         while (hi - lo > 1) {
@@ -369,10 +466,26 @@ __global__ void __launch_bounds__(kRasterThreads, 4) k_raster(const __grid_const
             }
         }
         // from here on: uncut, snapped triangles only
-        const long long samples = t.mode == 0 ? (long long)(t.x1 - t.x0 + 1) * (t.y1 - t.y0 + 1) : 0;
+        long long samples = t.mode == 0 ? (long long)(t.x1 - t.x0 + 1) * (t.y1 - t.y0 + 1) : 0;
         if (samples > kHugeSamples) {
             queue_or_walk(t, inst, a);
             t.mode = -1;
+            samples = 0;
+        }
+        // a small triangle that lies behind the coarse depth of every cell it touches is dropped here (larger ones are
+        // sorted out cell by cell where they are sampled)
+        const uint32_t zc = work_depth_floor(t, clamp_depth);
+        if (a.hiz && zc && samples > 0 && samples <= kCoopSamples) {
+            const int cx0 = t.x0 >> kCellShift, cx1 = t.x1 >> kCellShift, cy0 = t.y0 >> kCellShift, cy1 = t.y1 >> kCellShift;
+            if ((cx1 - cx0 + 1) * (cy1 - cy0 + 1) <= 16) {
+                uint32_t far = 0;
+                for (int cy = cy0; cy <= cy1; ++cy)
+                    for (int cx = cx0; cx <= cx1; ++cx) far = max(far, __ldg(a.hiz + (size_t)cy * a.hiz_w + cx));
+                if (zc > far) {
+                    t.mode = -1;
+                    samples = 0;
+                }
+            }
         }
         // The samples of the warp's 32 triangles, dealt out evenly: each lane leaves its triangle's record in shared
         // memory and the lanes then take the samples of all bounds 32 at a time, whoever's they are.  (Sampling one's
@@ -396,14 +509,7 @@ __global__ void __launch_bounds__(kRasterThreads, 4) k_raster(const __grid_const
             w.mode = 0;
             const uint32_t w_inst = __shfl_sync(0xffffffffu, inst, src);
             const Prep p = prepare(w);
-            const int bw = w.x1 - w.x0 + 1;
-            int i = w.x0 + lane, j = w.y0;
-            while (i > w.x1) { i -= bw; ++j; }
-            while (j <= w.y1) {
-                shade(p, 0, i, j, clamp_depth, w_inst, a.target, a.width);
-                i += 32;
-                while (i > w.x1) { i -= bw; ++j; }
-            }
+            warp_sample_rect(p, 0, w.x0, w.x1, w.y0, w.y1, __shfl_sync(0xffffffffu, zc, src), clamp_depth, w_inst, a, lane);
         }
         const uint32_t most = __reduce_max_sync(0xffffffffu, count);
         if (most <= 2u) {  // nothing to balance
@@ -490,26 +596,7 @@ __global__ void __launch_bounds__(kRasterThreads) k_raster_tiles(const __grid_co
         // the tile's samples that lie inside the triangle's bounds
         const int x0 = max(w.x0, tx << 6), x1 = min(w.x1, (tx << 6) + 63), y0 = max(w.y0, ty << 6), y1 = min(w.y1, (ty << 6) + 63);
         const Prep p = prepare(w);
-        if (w.mode == 0) {
-            bool out = false;
-#pragma unroll
-            for (int q = 0; q < 3; ++q) {
-                const int p0 = (q + 1) % 3;
-                // E = dx (py - y0) - dy (px - x0) is largest where dx favours py and -dy favours px
-                const int py = 256 * (p.dx[q] >= 0 ? y1 : y0) + 128, px = 256 * (p.dy[q] <= 0 ? x1 : x0) + 128;
-                const long long best = (long long)p.dx[q] * (py - p.y[p0]) - (long long)p.dy[q] * (px - p.x[p0]);
-                out = out || best < 0;
-            }
-            if (out) continue;
-        }
-        const int bw = x1 - x0 + 1;
-        int i = x0 + lane, j = y0;
-        while (i > x1) { i -= bw; ++j; }
-        while (j <= y1) {
-            shade(p, w.mode, i, j, clamp_depth, inst, a.target, a.width);
-            i += 32;
-            while (i > x1) { i -= bw; ++j; }
-        }
+        warp_sample_rect(p, w.mode, x0, x1, y0, y1, work_depth_floor(w, clamp_depth), clamp_depth, inst, a, lane);
     }
 }
 
@@ -525,13 +612,41 @@ void launch_raster_clear(unsigned long long* target, size_t n, cudaStream_t st)
     if (n) k_raster_clear<<<148 * 4, 256, 0, st>>>(target, n);
 }
 
-void launch_raster(const RasterArgs& a, cudaStream_t st)
+size_t raster_hiz_words(uint32_t width, uint32_t height)
 {
-    if (!a.visible) return;
+    return (size_t)((width + 7) >> kCellShift) * ((height + 7) >> kCellShift);
+}
+
+// The pairs are drawn in phases whose cumulative share grows by sqrt(2): after each, the coarse depth is rebuilt from
+// the target, so that a later phase skips what the earlier ones already hide (draw order is by key, i.e. any prefix of
+// the pairs is a spatially uniform sample of the view).  A view of a few instances is drawn in one phase.
+void launch_raster(const RasterArgs& a_in, cudaStream_t st)
+{
+    if (!a_in.visible) return;
+    RasterArgs a = a_in;
     k_raster_pairs<<<1, 1024, 0, st>>>(a.draws, a.counts, a.max_draws, a.pairs);
-    if (a.queue_works) cudaMemsetAsync(a.queue_counts, 0, 2 * sizeof(uint32_t), st);
-    k_raster<<<148 * 12, kRasterThreads, 0, st>>>(a);  // persistent warps striding over the pairs
-    if (a.queue_works) k_raster_tiles<<<148 * 12, kRasterThreads, 0, st>>>(a);  // ... and over the queued tiles
+    constexpr int kPhases = 12;
+    const int phases = (a.hiz && a.visible >= 256) ? kPhases : 1;
+    if (phases == 1) a.hiz = nullptr;
+    a.hiz_w = (a.width + 7) >> kCellShift;
+    a.hiz_h = (a.height + 7) >> kCellShift;
+    const size_t cells = (size_t)a.hiz_w * a.hiz_h;
+    if (a.hiz) cudaMemsetAsync(a.hiz, 0xFF, cells * sizeof(uint32_t), st);
+    const int sms = device_sm_count();
+    uint32_t lo = 0;
+    for (int ph = 0; ph < phases; ++ph) {
+        const uint32_t hi = ph + 1 == phases ? 65536u : (uint32_t)(65536.0 * exp2(-0.5 * (phases - 1 - ph)));
+        a.phase_lo = lo;
+        a.phase_hi = hi;
+        lo = hi;
+        if (a.queue_works) cudaMemsetAsync(a.queue_counts, 0, 2 * sizeof(uint32_t), st);
+        k_raster<<<sms * 12, kRasterThreads, 0, st>>>(a);  // persistent warps striding over the pairs
+        if (a.queue_works) k_raster_tiles<<<sms * 12, kRasterThreads, 0, st>>>(a);  // ... and over the queued tiles
+        if (a.hiz && ph + 1 < phases) {
+            const size_t want = (cells + 255) / 256;
+            k_raster_hiz<<<(unsigned)std::min<size_t>(want, (size_t)sms * 8), 256, 0, st>>>(a.target, a.width, a.height, a.hiz, a.hiz_w, a.hiz_h);
+        }
+    }
 }
 
 }  // namespace ss

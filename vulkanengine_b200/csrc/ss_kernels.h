@@ -244,7 +244,14 @@ struct RasterArgs {
     uint32_t* queue_tiles;     // [queue_tile_cap] owner work of each 64 x 64 tile entry
     uint32_t* queue_counts;    // {works, tile entries}
     uint32_t queue_work_cap, queue_tile_cap;
+    // coarse depth: per 8 x 8-sample cell an upper bound of the depth bits its samples hold (all ones: unknown), refreshed
+    // between the phases the pairs are drawn in; nullptr: none.  phase_lo/hi: this launch's part of the pairs, 16.16
+    uint32_t* hiz;
+    uint32_t hiz_w, hiz_h;
+    uint32_t phase_lo, phase_hi;
 };
+size_t raster_hiz_words(uint32_t width, uint32_t height);
+int device_sm_count();  // SMs of the current device, cached per device
 void launch_raster_clear(unsigned long long* target, size_t n, cudaStream_t st);
 void launch_raster(const RasterArgs& a, cudaStream_t st);
 
