@@ -104,9 +104,9 @@ struct ss_ctx {
     uint32_t* d_indices = nullptr;
     uint32_t n_vertices = 0, n_indices = 0;
     unsigned long long* d_raster[SS_MAX_VIEWS] = {};  // one target per view: [raster_h[v]][raster_w[v]]
-    unsigned long long* d_raster_pairs = nullptr;  // [max_draws + 1]
+    void* d_raster_order = nullptr;                // depth-order scratch of the raster pass (raster_order_bytes(n_instances))
     uint32_t* d_raster_queue = nullptr;            // works | tile entries | 2 counters (kRasterQueueWorks / kRasterQueueTiles)
-    uint32_t* d_raster_hiz = nullptr;              // coarse depth of the pass being drawn (raster_hiz_words of the largest target)
+    unsigned long long* d_raster_hiz = nullptr;              // coarse depth of the pass being drawn (raster_hiz_words of the largest target)
     size_t raster_hiz_cap = 0;
     uint32_t raster_w[SS_MAX_VIEWS] = {}, raster_h[SS_MAX_VIEWS] = {};
     uint32_t seg_parity = 0;
@@ -287,7 +287,7 @@ SS_API void ss_destroy(ss_ctx* c)
     if (c->d_indices) cudaFree(c->d_indices);
     for (unsigned long long* p : c->d_raster)
         if (p) cudaFree(p);
-    if (c->d_raster_pairs) cudaFree(c->d_raster_pairs);
+    if (c->d_raster_order) cudaFree(c->d_raster_order);
     if (c->d_raster_queue) cudaFree(c->d_raster_queue);
     if (c->d_raster_hiz) cudaFree(c->d_raster_hiz);
     if (c->stream) cudaStreamDestroy(c->stream);
@@ -1325,11 +1325,11 @@ SS_API ss_status ss_raster_view(ss_ctx* c, uint32_t slot, uint32_t view, uint32_
     ra.draws = o.draws;
     ra.counts = o.counts;
     ra.max_draws = c->max_draws;
-    if (!c->d_raster_pairs) SS_CUDA(c, cudaMalloc(&c->d_raster_pairs, ((size_t)c->max_draws + 1) * sizeof(unsigned long long)));
-    ra.pairs = c->d_raster_pairs;
+    if (!c->d_raster_order) SS_CUDA(c, cudaMalloc(&c->d_raster_order, raster_order_bytes(c->n_instances)));
+    raster_order_carve(c->d_raster_order, c->n_instances, &ra);
     constexpr uint32_t kRasterQueueWorks = 1u << 19, kRasterQueueTiles = 1u << 23;  // 40 MB + 32 MB, on first use
     if (!c->d_raster_queue)
-        SS_CUDA(c, cudaMalloc(&c->d_raster_queue, ((size_t)kRasterQueueWorks * 20 + kRasterQueueTiles + 2) * sizeof(uint32_t)));
+        SS_CUDA(c, cudaMalloc(&c->d_raster_queue, ((size_t)kRasterQueueWorks * 20 + kRasterQueueTiles + 4) * sizeof(uint32_t)));
     ra.queue_works = c->d_raster_queue;
     ra.queue_tiles = c->d_raster_queue + (size_t)kRasterQueueWorks * 20;
     ra.queue_counts = ra.queue_tiles + kRasterQueueTiles;
@@ -1351,7 +1351,7 @@ SS_API ss_status ss_raster_view(ss_ctx* c, uint32_t slot, uint32_t view, uint32_
         if (c->d_raster_hiz) cudaFree(c->d_raster_hiz);
         c->d_raster_hiz = nullptr;
         c->raster_hiz_cap = 0;
-        SS_CUDA(c, cudaMalloc(&c->d_raster_hiz, hiz_words * sizeof(uint32_t)));
+        SS_CUDA(c, cudaMalloc(&c->d_raster_hiz, hiz_words * sizeof(unsigned long long)));
         c->raster_hiz_cap = hiz_words;
     }
     ra.hiz = c->d_raster_hiz;

@@ -20,6 +20,8 @@
 // the two agree bit for bit.  The reference's own rasteriser is the Vulkan device: unavailable on this box.
 #include <algorithm>
 #include <cmath>
+#include <cstdio>
+#include <vector>
 
 #include "ss_kernels.h"
 
@@ -30,6 +32,7 @@ namespace {
 constexpr int kRasterThreads = 128;
 constexpr int kCoopSamples = 192;             // bounds holding more samples than this get the whole warp to themselves
 constexpr long long kHugeSamples = 16384;      // beyond this a triangle is queued and spread over the grid, tile by tile
+constexpr int kChunkPairs = 1024;             // pairs a warp takes at a time, at most (a short phase is cut finer)
 constexpr int kWorkWords = 20;                // queue record: Work::w[13], x0, x1, y0, y1, mode, instance, first tile entry
 constexpr float kSubpixel = 256.0f;
 constexpr float kSnapLimit = 268435456.0f;    // 2^28 sub-pixel units = 2^20 pixels
@@ -117,11 +120,20 @@ __device__ __forceinline__ Work setup(const float c[3][4], int width, int height
     return t;
 }
 
+// -DSS_RASTER_STATS: counters of what the pass did, printed by launch_raster (a debugging build, never the shipped one)
+#ifdef SS_RASTER_STATS
+__device__ unsigned long long g_rstats[12];
+#define RSTAT(i, v) atomicAdd(&g_rstats[i], (unsigned long long)(v))
+#else
+#define RSTAT(i, v)
+#endif
+
 __device__ __forceinline__ void put(unsigned long long* target, uint32_t width, int i, int j, float depth, bool clamp_depth,
                                     uint32_t inst)
 {
     if (clamp_depth) depth = depth < 0.f ? 0.f : (depth > 1.f ? 1.f : depth);  // a NaN stays one and is dropped
     if (!(depth >= 0.f && depth <= 1.f)) return;
+    RSTAT(7, 1);
     atomicMin(target + (size_t)j * width + i, ((unsigned long long)__float_as_uint(depth) << 32) | inst);
 }
 
@@ -243,9 +255,10 @@ __device__ __forceinline__ bool rect_outside(const Prep& p, int x0, int x1, int 
 
 // One warp samples the rectangle x0..x1 x y0..y1 of one triangle, coarse cell by coarse cell: the lanes first sort out
 // which cells can matter (a cell whose coarse depth lies in front of everything the triangle can store, or that lies
-// outside an edge, is skipped whole), then take the samples of each remaining cell two apiece.  `zc` = 0 or no coarse
-// buffer: every cell is sampled.  Skipping never changes the target: a skipped sample could not have won its cell.
-__device__ __forceinline__ void warp_sample_rect(const Prep& p, int mode, int x0, int x1, int y0, int y1, uint32_t zc,
+// outside an edge, is skipped whole), then take the samples of each remaining cell two apiece.  `floor_word` bounds
+// every word the triangle can store from below ([depth floor | instance]); without a coarse buffer every cell is
+// sampled.  Skipping never changes the target: a skipped sample could not have won its place.
+__device__ __forceinline__ void warp_sample_rect(const Prep& p, int mode, int x0, int x1, int y0, int y1, unsigned long long floor_word,
                                                  bool clamp_depth, uint32_t inst, const RasterArgs& a, int lane)
 {
     const int cx0 = x0 >> kCellShift, cy0 = y0 >> kCellShift;
@@ -259,12 +272,14 @@ __device__ __forceinline__ void warp_sample_rect(const Prep& p, int mode, int x0
             cy = c / ncx;
             cx = cx0 + (c - cy * ncx);
             cy += cy0;
-            if (a.hiz && zc > __ldg(a.hiz + (size_t)cy * a.hiz_w + cx)) alive = false;
+            if (a.hiz && floor_word > __ldg(a.hiz + (size_t)cy * a.hiz_w + cx)) alive = false;
             if (alive && mode == 0)
                 alive = !rect_outside(p, max(x0, cx << kCellShift), min(x1, (cx << kCellShift) + 7), max(y0, cy << kCellShift),
                                       min(y1, (cy << kCellShift) + 7));
         }
         uint32_t todo = __ballot_sync(0xffffffffu, alive);
+        RSTAT(5, c < n_cells);
+        RSTAT(6, alive);
         while (todo) {
             const int src = __ffs(todo) - 1;
             todo &= todo - 1;
@@ -279,52 +294,163 @@ __device__ __forceinline__ void warp_sample_rect(const Prep& p, int mode, int x0
     }
 }
 
-// hiz[cell] = the largest depth bits among the cell's samples (all ones while any of them is empty).  The target's
-// words only ever fall, so the value stays an upper bound for as long as it is used.
+// hiz[cell] = the largest word among the cell's samples (all ones while any of them is empty).  The target's words
+// only ever fall, so the value stays an upper bound for as long as it is used.
 __global__ void __launch_bounds__(256) k_raster_hiz(const unsigned long long* __restrict__ target, uint32_t width, uint32_t height,
-                                                    uint32_t* __restrict__ hiz, uint32_t hiz_w, uint32_t hiz_h)
+                                                    unsigned long long* __restrict__ hiz, uint32_t hiz_w, uint32_t hiz_h)
 {
     const uint32_t n = hiz_w * hiz_h;
     for (uint32_t c = blockIdx.x * blockDim.x + threadIdx.x; c < n; c += gridDim.x * blockDim.x) {
         const uint32_t cy = c / hiz_w, cx = c - cy * hiz_w;
         const uint32_t x0 = cx << kCellShift, y0 = cy << kCellShift;
-        uint32_t m = 0;
+        unsigned long long m = 0;
         const uint32_t x1 = min(x0 + 8u, width), y1 = min(y0 + 8u, height);
         for (uint32_t j = y0; j < y1; ++j)
-            for (uint32_t i = x0; i < x1; ++i) m = max(m, (uint32_t)(__ldcg(target + (size_t)j * width + i) >> 32));
+            for (uint32_t i = x0; i < x1; ++i) m = max(m, __ldcg(target + (size_t)j * width + i));
         hiz[c] = m;
     }
 }
 
-// pairs[d] = number of (instance, triangle) pairs of the draws before d; pairs[n_draws] = all of them
-__global__ void __launch_bounds__(1024) k_raster_pairs(const ss_draw_cmd* draws, const uint32_t* counts, uint32_t max_draws,
-                                                       unsigned long long* pairs)
+__global__ void __launch_bounds__(256) k_raster_hiz2(const unsigned long long* __restrict__ hiz, uint32_t hiz_w, uint32_t hiz_h,
+                                                     unsigned long long* __restrict__ hiz2, uint32_t hiz2_w, uint32_t hiz2_h)
 {
-    __shared__ unsigned long long warp_sum[32];
-    __shared__ unsigned long long carry;
-    const uint32_t n_draws = min(counts[1], max_draws);
-    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
-    if (tid == 0) carry = 0;
-    __syncthreads();
-    for (uint32_t d0 = 0; d0 < n_draws; d0 += 1024) {
-        const uint32_t d = d0 + tid;
-        const unsigned long long mine = d < n_draws ? (unsigned long long)draws[d].instance_count * (draws[d].index_count / 3u) : 0ull;
-        unsigned long long x = mine;
-#pragma unroll
-        for (int o = 1; o < 32; o <<= 1) {
-            const unsigned long long y = __shfl_up_sync(0xffffffffu, x, o);
-            if (lane >= o) x += y;
-        }
-        if (lane == 31) warp_sum[wid] = x;
-        __syncthreads();
-        unsigned long long base = carry;
-        for (int w = 0; w < wid; ++w) base += warp_sum[w];
-        if (d < n_draws) pairs[d] = base + x - mine;
-        __syncthreads();
-        if (tid == 1023) carry = base + x;
-        __syncthreads();
+    const uint32_t n = hiz2_w * hiz2_h;
+    for (uint32_t c = blockIdx.x * blockDim.x + threadIdx.x; c < n; c += gridDim.x * blockDim.x) {
+        const uint32_t ty = c / hiz2_w, tx = c - ty * hiz2_w;
+        unsigned long long m = 0;
+        for (uint32_t cy = ty * 8; cy < min(ty * 8 + 8u, hiz_h); ++cy)
+            for (uint32_t cx = tx * 8; cx < min(tx * 8 + 8u, hiz_w); ++cx) m = max(m, hiz[(size_t)cy * hiz_w + cx]);
+        hiz2[c] = m;
     }
-    if (tid == 0) pairs[n_draws] = carry;
+}
+
+// ---- the order the pass is drawn in: front to back ---------------------------------------------------------------
+// Every row of the view gets the depth of its transform's origin as a sort key; the rows are sorted by it (the library's
+// own radix sort) and the triangles before every rank are counted, so that a (rank, triangle) pair has a number and any
+// range of those numbers can be found again by bisection.  The order only decides how much the coarse depth can skip.
+constexpr uint32_t kNoDraw = 0xFFFFFFFFu;
+constexpr int kScanThreads = 1024, kScanItems = 4, kScanTile = kScanThreads * kScanItems;
+
+__device__ __forceinline__ const unsigned long long* sorted_order(const RasterArgs& a)
+{
+    const SortControl* ctl = static_cast<const SortControl*>(a.sort_scratch);
+    return ctl->src_sel[a.sort_passes] ? a.order_b : a.order_a;
+}
+
+__global__ void __launch_bounds__(256) k_raster_keys(const __grid_constant__ RasterArgs a)
+{
+    const uint32_t n_draws = min(a.counts[1], a.max_draws);
+    for (uint32_t k = blockIdx.x * blockDim.x + threadIdx.x; k < a.visible; k += gridDim.x * blockDim.x) {
+        // the last draw that starts at or before row k (the draws of a view lie in row order)
+        uint32_t d = kNoDraw;
+        if (n_draws) {
+            uint32_t lo = 0, hi = n_draws;
+            while (hi - lo > 1) {
+                const uint32_t mid = (lo + hi) >> 1;
+                if (a.draws[mid].first_instance <= k) lo = mid; else hi = mid;
+            }
+            const uint32_t fi = a.draws[lo].first_instance;
+            if (k >= fi && k - fi < a.draws[lo].instance_count) d = lo;
+        }
+        const float tx = a.rows[(size_t)k * 3 + 0].w, ty = a.rows[(size_t)k * 3 + 1].w, tz = a.rows[(size_t)k * 3 + 2].w;
+        const float z = (a.vp[2] * tx + a.vp[6] * ty) + (a.vp[10] * tz + a.vp[14]);
+        const float w = (a.vp[3] * tx + a.vp[7] * ty) + (a.vp[11] * tz + a.vp[15]);
+        float key = w > 0.f ? z / w : -1.f;  // at or behind the eye: first
+        uint32_t low = k;
+        if (a.flags & SS_RASTER_DEPTH_CLAMP) {
+            // everything in front of the near plane is stored at depth 0 and the lowest instance wins there: those rows
+            // are drawn in instance order (the sort then runs over all 64 bits)
+            key = key > 0.f ? fminf(key, 1.0f) : 0.f;
+            low = a.idx[k];
+            a.row_of[low] = k;
+        }
+        const uint32_t bits = __float_as_uint(key);
+        const uint32_t sortable = bits ^ ((bits >> 31) ? 0xFFFFFFFFu : 0x80000000u);
+        a.order_a[k] = ((unsigned long long)sortable << 32) | low;
+        a.draw_of[k] = d;
+    }
+}
+
+__device__ __forceinline__ uint32_t row_at_rank(const RasterArgs& a, const unsigned long long* order, uint32_t r)
+{
+    const uint32_t low = (uint32_t)order[r];
+    return (a.flags & SS_RASTER_DEPTH_CLAMP) ? a.row_of[low] : low;
+}
+
+__device__ __forceinline__ uint32_t triangles_at_rank(const RasterArgs& a, const unsigned long long* order, uint32_t r)
+{
+    const uint32_t d = a.draw_of[row_at_rank(a, order, r)];
+    return d == kNoDraw ? 0u : a.draws[d].index_count / 3u;
+}
+
+__device__ __forceinline__ unsigned long long block_exclusive_scan(unsigned long long mine, unsigned long long* total)
+{
+    __shared__ unsigned long long warp_sum[kScanThreads / 32];
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    unsigned long long x = mine;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const unsigned long long y = __shfl_up_sync(0xffffffffu, x, o);
+        if (lane >= o) x += y;
+    }
+    __syncthreads();  // warp_sum may still be read by the previous call
+    if (lane == 31) warp_sum[wid] = x;
+    __syncthreads();
+    unsigned long long base = 0, all = 0;
+    for (int w = 0; w < kScanThreads / 32; ++w) {
+        const unsigned long long v = warp_sum[w];
+        if (w < wid) base += v;
+        all += v;
+    }
+    *total = all;
+    return base + x - mine;
+}
+
+__global__ void __launch_bounds__(kScanThreads) k_raster_scan_sums(const __grid_constant__ RasterArgs a)
+{
+    const unsigned long long* order = sorted_order(a);
+    const uint32_t r0 = blockIdx.x * kScanTile + threadIdx.x * kScanItems;
+    unsigned long long mine = 0;
+#pragma unroll
+    for (int q = 0; q < kScanItems; ++q)
+        if (r0 + q < a.visible) mine += triangles_at_rank(a, order, r0 + q);
+    unsigned long long all;
+    block_exclusive_scan(mine, &all);
+    if (threadIdx.x == 0) a.block_sums[blockIdx.x] = all;
+}
+
+__global__ void __launch_bounds__(kScanThreads) k_raster_scan_top(unsigned long long* block_sums, uint32_t n_blocks)
+{
+    unsigned long long carry = 0;
+    for (uint32_t b0 = 0; b0 < n_blocks; b0 += kScanThreads) {
+        const uint32_t b = b0 + threadIdx.x;
+        const unsigned long long mine = b < n_blocks ? block_sums[b] : 0ull;
+        unsigned long long all;
+        const unsigned long long ex = block_exclusive_scan(mine, &all);
+        if (b < n_blocks) block_sums[b] = carry + ex;
+        carry += all;
+    }
+}
+
+__global__ void __launch_bounds__(kScanThreads) k_raster_scan_apply(const __grid_constant__ RasterArgs a)
+{
+    const unsigned long long* order = sorted_order(a);
+    const uint32_t r0 = blockIdx.x * kScanTile + threadIdx.x * kScanItems;
+    uint32_t cnt[kScanItems];
+    unsigned long long mine = 0;
+#pragma unroll
+    for (int q = 0; q < kScanItems; ++q) {
+        cnt[q] = r0 + q < a.visible ? triangles_at_rank(a, order, r0 + q) : 0u;
+        mine += cnt[q];
+    }
+    unsigned long long all;
+    unsigned long long at = a.block_sums[blockIdx.x] + block_exclusive_scan(mine, &all);
+#pragma unroll
+    for (int q = 0; q < kScanItems; ++q) {
+        if (r0 + q < a.visible) a.tri_prefix[r0 + q] = at;
+        at += cnt[q];
+        if (r0 + q + 1 == a.visible) a.tri_prefix[a.visible] = at;
+    }
 }
 
 // A triangle its thread does not sample itself: queued for k_raster_tiles (one entry per 64 x 64-sample tile of its
@@ -345,7 +471,14 @@ __device__ __noinline__ void queue_or_walk(const Work& t, uint32_t inst, const R
                 for (int q = 0; q < 13; ++q) rec[q] = t.w[q];
                 rec[13] = (uint32_t)t.x0; rec[14] = (uint32_t)t.x1; rec[15] = (uint32_t)t.y0; rec[16] = (uint32_t)t.y1;
                 rec[17] = (uint32_t)t.mode; rec[18] = inst; rec[19] = base_t;
-                for (uint32_t k = 0; k < n_tiles; ++k) a.queue_tiles[base_t + k] = slot_w;
+                // an entry whose tile already lies in front of everything the triangle can store is nobody's
+                const unsigned long long floor_word = ((unsigned long long)work_depth_floor(t, clamp_depth) << 32) | inst;
+                const uint32_t tnx = (uint32_t)((t.x1 >> 6) - tx0 + 1);
+                for (uint32_t k = 0; k < n_tiles; ++k) {
+                    const uint32_t ty = (uint32_t)ty0 + k / tnx, tx = (uint32_t)tx0 + k % tnx;
+                    const bool hidden = a.hiz2 && floor_word > __ldg(a.hiz2 + (size_t)ty * a.hiz2_w + tx);
+                    a.queue_tiles[base_t + k] = hidden ? 0xFFFFFFFFu : slot_w;
+                }
                 return;
             }
             // the tile list is full: the part of the range that exists is marked as nobody's
@@ -409,164 +542,202 @@ __global__ void __launch_bounds__(kRasterThreads, 4) k_raster(const __grid_const
     __shared__ __align__(16) uint32_t s_rec[kRasterThreads / 32][32][20];  // per lane: x, y, dx, dy, zn, fa, x0, y0, width, instance
     __shared__ uint32_t s_pre[kRasterThreads / 32][32];                     // samples before each lane's
     const int lane = threadIdx.x & 31;
-    const uint32_t n_draws = min(a.counts[1], a.max_draws);
-    const unsigned long long all_pairs = a.pairs[n_draws];
+    const unsigned long long* order = sorted_order(a);
+    const unsigned long long all_pairs = a.tri_prefix[a.visible];
     const bool clamp_depth = (a.flags & SS_RASTER_DEPTH_CLAMP) != 0;
-    const unsigned long long warps = ((unsigned long long)gridDim.x * kRasterThreads) >> 5;
-    const unsigned long long warp_id = ((unsigned long long)blockIdx.x * kRasterThreads + threadIdx.x) >> 5;
-    // this launch's part of the pairs (the pass is drawn in phases, the coarse depth refreshed in between)
+    // this launch's part of the pairs (the pass is drawn in phases, the coarse depth rebuilt in between), handed out to
+    // the warps in chunks: one bisection per chunk, the lanes walk on from there
     const unsigned long long first = (unsigned long long)(((unsigned __int128)all_pairs * a.phase_lo) >> 16);
-    const unsigned long long total = (unsigned long long)(((unsigned __int128)all_pairs * a.phase_hi) >> 16);
-    for (unsigned long long g0 = first + warp_id * 32ull; g0 < total; g0 += warps * 32ull) {
-        // the last draw whose first pair is <= g0
-        uint32_t lo = 0, hi = n_draws;
-        while (hi - lo > 1) {
-            const uint32_t mid = (lo + hi) >> 1;
-            if (a.pairs[mid] <= g0) lo = mid; else hi = mid;
-        }
-        const unsigned long long g = g0 + (unsigned long long)lane;
-        Work t;
-        t.mode = -1;
-        t.x0 = t.y0 = 0;
-        t.x1 = t.y1 = -1;
-        uint32_t inst = 0;
-        if (g < total) {
-            uint32_t d = lo;
-            while (a.pairs[d + 1] <= g) ++d;  // draws without pairs are stepped over
-            const ss_draw_cmd dc = a.draws[d];
-            const uint32_t tris = dc.index_count / 3u;
-            const unsigned long long local = g - a.pairs[d];
-            const uint32_t ki = (uint32_t)(local / tris), tI = (uint32_t)(local - (unsigned long long)ki * tris);
-            const uint32_t k = dc.first_instance + ki;
-            const float4 r0 = a.rows[(size_t)k * 3 + 0], r1 = a.rows[(size_t)k * 3 + 1], r2 = a.rows[(size_t)k * 3 + 2];
-            inst = a.idx[k];
-            // 1: the triangle in clip space
-            float c[3][4], dd[3];
-            bool in_range = true;
-#pragma unroll
-            for (int v = 0; v < 3; ++v) {
-                const uint64_t ii = (uint64_t)dc.first_index + (uint64_t)tI * 3u + (uint64_t)v;
-                if (ii >= a.n_indices) { in_range = false; break; }
-                const int64_t vi = (int64_t)dc.vertex_offset + (int64_t)a.indices[ii];
-                if (vi < 0 || vi >= (int64_t)a.n_vertices) { in_range = false; break; }
-                clip_of(a.vp, r0, r1, r2, a.positions + (size_t)vi * 3, c[v]);
+    const unsigned long long last = (unsigned long long)(((unsigned __int128)all_pairs * a.phase_hi) >> 16);
+    // at least four chunks per warp of the grid, so that a short phase (or a view of few, large triangles) still
+    // spreads over all of it
+    const unsigned long long grid_warps = ((unsigned long long)gridDim.x * kRasterThreads) >> 5;
+    const unsigned long long chunk_pairs =
+        max(32ull, min((unsigned long long)kChunkPairs, ((last - first) / (grid_warps * 4ull)) & ~31ull));
+    const unsigned long long n_chunks = (last - first + chunk_pairs - 1) / chunk_pairs;
+    // a phase too short to occupy the grid (the nearest, largest triangles come first) hands everything a warp would
+    // have to itself to the queue instead, which spreads it tile by tile
+    const long long huge_samples = (last - first) < grid_warps * 64ull ? (long long)kCoopSamples : kHugeSamples;
+    for (;;) {
+        unsigned long long chunk = 0;
+        if (lane == 0) chunk = atomicAdd(a.queue_counts + 2, 1u);
+        chunk = __shfl_sync(0xffffffffu, chunk, 0);
+        if (chunk >= n_chunks) break;
+        const unsigned long long c0 = first + chunk * chunk_pairs;
+        const unsigned long long total = min(c0 + chunk_pairs, last);
+        // the last rank whose first pair is <= c0
+        uint32_t r_warp = 0;
+        {
+            uint32_t lo = 0, hi = a.visible;
+            while (hi - lo > 1) {
+                const uint32_t mid = (lo + hi) >> 1;
+                if (a.tri_prefix[mid] <= c0) lo = mid; else hi = mid;
             }
-            if (in_range) {  // a table that points outside the geometry draws nothing
-#pragma unroll
-                for (int v = 0; v < 3; ++v) dd[v] = clamp_depth ? c[v][3] - 1e-5f : c[v][2];
-                if (dd[0] >= 0.f && dd[1] >= 0.f && dd[2] >= 0.f) {
-                    t = setup(c, (int)a.width, (int)a.height);
-                    if (t.mode == 1) {  // not snappable: never sampled here
-                        queue_or_walk(t, inst, a);
-                        t.mode = -1;
-                    }
-                } else {
-                    cut_and_queue(c, dd, inst, a);
-                }
-            }
+            r_warp = lo;
         }
-        // from here on: uncut, snapped triangles only
-        long long samples = t.mode == 0 ? (long long)(t.x1 - t.x0 + 1) * (t.y1 - t.y0 + 1) : 0;
-        if (samples > kHugeSamples) {
-            queue_or_walk(t, inst, a);
+        for (unsigned long long g0 = c0; g0 < total; g0 += 32ull) {
+            const unsigned long long g = g0 + (unsigned long long)lane;
+            Work t;
             t.mode = -1;
-            samples = 0;
-        }
-        // a small triangle that lies behind the coarse depth of every cell it touches is dropped here (larger ones are
-        // sorted out cell by cell where they are sampled)
-        const uint32_t zc = work_depth_floor(t, clamp_depth);
-        if (a.hiz && zc && samples > 0 && samples <= kCoopSamples) {
-            const int cx0 = t.x0 >> kCellShift, cx1 = t.x1 >> kCellShift, cy0 = t.y0 >> kCellShift, cy1 = t.y1 >> kCellShift;
-            if ((cx1 - cx0 + 1) * (cy1 - cy0 + 1) <= 16) {
-                uint32_t far = 0;
-                for (int cy = cy0; cy <= cy1; ++cy)
-                    for (int cx = cx0; cx <= cx1; ++cx) far = max(far, __ldg(a.hiz + (size_t)cy * a.hiz_w + cx));
-                if (zc > far) {
-                    t.mode = -1;
-                    samples = 0;
+            t.x0 = t.y0 = 0;
+            t.x1 = t.y1 = -1;
+            uint32_t inst = 0;
+            uint32_t r = r_warp;
+            if (g < total) {
+                while (a.tri_prefix[r + 1] <= g) ++r;  // ranks without triangles are stepped over
+                const uint32_t k = row_at_rank(a, order, r);
+                const ss_draw_cmd dc = a.draws[a.draw_of[k]];
+                const uint32_t tI = (uint32_t)(g - a.tri_prefix[r]);
+                const float4 r0 = a.rows[(size_t)k * 3 + 0], r1 = a.rows[(size_t)k * 3 + 1], r2 = a.rows[(size_t)k * 3 + 2];
+                inst = a.idx[k];
+                // 1: the triangle in clip space
+                float c[3][4], dd[3];
+                bool in_range = true;
+    #pragma unroll
+                for (int v = 0; v < 3; ++v) {
+                    const uint64_t ii = (uint64_t)dc.first_index + (uint64_t)tI * 3u + (uint64_t)v;
+                    if (ii >= a.n_indices) { in_range = false; break; }
+                    const int64_t vi = (int64_t)dc.vertex_offset + (int64_t)a.indices[ii];
+                    if (vi < 0 || vi >= (int64_t)a.n_vertices) { in_range = false; break; }
+                    clip_of(a.vp, r0, r1, r2, a.positions + (size_t)vi * 3, c[v]);
+                }
+                if (in_range) {  // a table that points outside the geometry draws nothing
+    #pragma unroll
+                    for (int v = 0; v < 3; ++v) dd[v] = clamp_depth ? c[v][3] - 1e-5f : c[v][2];
+                    if (dd[0] >= 0.f && dd[1] >= 0.f && dd[2] >= 0.f) {
+                        t = setup(c, (int)a.width, (int)a.height);
+                        if (t.mode == 1) {  // not snappable: never sampled here
+                            queue_or_walk(t, inst, a);
+                            t.mode = -1;
+                        }
+                    } else {
+                        cut_and_queue(c, dd, inst, a);
+                    }
                 }
             }
-        }
-        // The samples of the warp's 32 triangles, dealt out evenly: each lane leaves its triangle's record in shared
-        // memory and the lanes then take the samples of all bounds 32 at a time, whoever's they are.  (Sampling one's
-        // own triangle would cost the warp as many rounds as its largest triangle has samples, with most lanes idle:
-        // measured 14 of 32 lanes busy and 10 K instructions per 32 triangles on the camera view of cfg 3.)
-        // A triangle of more than kCoopSamples keeps the warp to itself instead (its record is broadcast once and the
-        // lanes stride over its bounds: no owner search and no division per sample).
-        const bool coop = t.mode == 0 && samples > kCoopSamples;
-        const uint32_t count = (t.mode == 0 && !coop) ? (uint32_t)samples : 0u;
-        uint32_t todo = __ballot_sync(0xffffffffu, coop);
-        while (todo) {
-            const int src = __ffs(todo) - 1;
-            todo &= todo - 1;
-            Work w;
-#pragma unroll
-            for (int q = 0; q < 9; ++q) w.w[q] = __shfl_sync(0xffffffffu, t.w[q], src);
-            w.x0 = __shfl_sync(0xffffffffu, t.x0, src);
-            w.x1 = __shfl_sync(0xffffffffu, t.x1, src);
-            w.y0 = __shfl_sync(0xffffffffu, t.y0, src);
-            w.y1 = __shfl_sync(0xffffffffu, t.y1, src);
-            w.mode = 0;
-            const uint32_t w_inst = __shfl_sync(0xffffffffu, inst, src);
-            const Prep p = prepare(w);
-            warp_sample_rect(p, 0, w.x0, w.x1, w.y0, w.y1, __shfl_sync(0xffffffffu, zc, src), clamp_depth, w_inst, a, lane);
-        }
-        const uint32_t most = __reduce_max_sync(0xffffffffu, count);
-        if (most <= 2u) {  // nothing to balance
+            r_warp = __shfl_sync(0xffffffffu, r, 31);  // where the next 32 pairs start looking
+            // from here on: uncut, snapped triangles only
+            long long samples = t.mode == 0 ? (long long)(t.x1 - t.x0 + 1) * (t.y1 - t.y0 + 1) : 0;
+            const unsigned long long floor_word = ((unsigned long long)work_depth_floor(t, clamp_depth) << 32) | inst;
+            // a large triangle that lies behind the coarse depth of every 64 x 64 tile it touches is dropped here
+            if (a.hiz2 && samples > kCoopSamples) {
+                const int tx0 = t.x0 >> 6, tx1 = t.x1 >> 6, ty0 = t.y0 >> 6, ty1 = t.y1 >> 6;
+                if ((tx1 - tx0 + 1) * (ty1 - ty0 + 1) <= 16) {
+                    unsigned long long far = 0;
+                    for (int ty = ty0; ty <= ty1; ++ty)
+                        for (int tx = tx0; tx <= tx1; ++tx) far = max(far, __ldg(a.hiz2 + (size_t)ty * a.hiz2_w + tx));
+                    if (floor_word > far) {
+                        t.mode = -1;
+                        samples = 0;
+                    }
+                }
+            }
+            if (samples > huge_samples) {
+                queue_or_walk(t, inst, a);
+                t.mode = -1;
+                samples = 0;
+            }
+            // a small triangle that lies behind the coarse depth of every cell it touches is dropped here (the others are
+            // sorted out cell by cell where they are sampled)
+            if (a.hiz && samples > 0 && samples <= kCoopSamples) {
+                const int cx0 = t.x0 >> kCellShift, cx1 = t.x1 >> kCellShift, cy0 = t.y0 >> kCellShift, cy1 = t.y1 >> kCellShift;
+                if ((cx1 - cx0 + 1) * (cy1 - cy0 + 1) <= 16) {
+                    unsigned long long far = 0;
+                    for (int cy = cy0; cy <= cy1; ++cy)
+                        for (int cx = cx0; cx <= cx1; ++cx) far = max(far, __ldg(a.hiz + (size_t)cy * a.hiz_w + cx));
+                    RSTAT(2, floor_word > far);
+                    if (floor_word > far) {
+                        t.mode = -1;
+                        samples = 0;
+                    }
+                }
+            }
+            // The samples of the warp's 32 triangles, dealt out evenly: each lane leaves its triangle's record in shared
+            // memory and the lanes then take the samples of all bounds 32 at a time, whoever's they are.  (Sampling one's
+            // own triangle would cost the warp as many rounds as its largest triangle has samples, with most lanes idle:
+            // measured 14 of 32 lanes busy and 10 K instructions per 32 triangles on the camera view of cfg 3.)
+            // A triangle of more than kCoopSamples keeps the warp to itself instead (its record is broadcast once and the
+            // lanes stride over its bounds: no owner search and no division per sample).
+            const bool coop = t.mode == 0 && samples > kCoopSamples;
+            RSTAT(0, g < total);
+            RSTAT(1, t.mode == 0 && samples > 0);
+            if (t.mode == 0 && !coop) RSTAT(3, samples);
+            RSTAT(4, coop);
+            RSTAT(8, t.mode == 0 && samples > 0 && (floor_word >> 32) == 0u);
+            const uint32_t count = (t.mode == 0 && !coop) ? (uint32_t)samples : 0u;
+            uint32_t todo = __ballot_sync(0xffffffffu, coop);
+            while (todo) {
+                const int src = __ffs(todo) - 1;
+                todo &= todo - 1;
+                Work w;
+    #pragma unroll
+                for (int q = 0; q < 9; ++q) w.w[q] = __shfl_sync(0xffffffffu, t.w[q], src);
+                w.x0 = __shfl_sync(0xffffffffu, t.x0, src);
+                w.x1 = __shfl_sync(0xffffffffu, t.x1, src);
+                w.y0 = __shfl_sync(0xffffffffu, t.y0, src);
+                w.y1 = __shfl_sync(0xffffffffu, t.y1, src);
+                w.mode = 0;
+                const uint32_t w_inst = __shfl_sync(0xffffffffu, inst, src);
+                const Prep p = prepare(w);
+                warp_sample_rect(p, 0, w.x0, w.x1, w.y0, w.y1, __shfl_sync(0xffffffffu, floor_word, src), clamp_depth, w_inst, a, lane);
+            }
+            const uint32_t most = __reduce_max_sync(0xffffffffu, count);
+            if (most <= 2u) {  // nothing to balance
+                if (count) {
+                    const Prep p = prepare(t);
+                    for (int j = t.y0; j <= t.y1; ++j)
+                        for (int i = t.x0; i <= t.x1; ++i) shade(p, 0, i, j, clamp_depth, inst, a.target, a.width);
+                }
+                continue;
+            }
+            uint32_t incl = count;
+    #pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const uint32_t y = __shfl_up_sync(0xffffffffu, incl, o);
+                if (lane >= o) incl += y;
+            }
+            const uint32_t all = __shfl_sync(0xffffffffu, incl, 31);
+            uint32_t* rec = s_rec[threadIdx.x >> 5][lane];
+            uint32_t* pre = s_pre[threadIdx.x >> 5];
+            pre[lane] = incl - count;
             if (count) {
                 const Prep p = prepare(t);
-                for (int j = t.y0; j <= t.y1; ++j)
-                    for (int i = t.x0; i <= t.x1; ++i) shade(p, 0, i, j, clamp_depth, inst, a.target, a.width);
+    #pragma unroll
+                for (int q = 0; q < 3; ++q) {
+                    rec[q] = (uint32_t)p.x[q];
+                    rec[3 + q] = (uint32_t)p.y[q];
+                    rec[6 + q] = (uint32_t)p.dx[q];
+                    rec[9 + q] = (uint32_t)p.dy[q];
+                    rec[12 + q] = __float_as_uint(p.zn[q]);
+                }
+                rec[15] = __float_as_uint(p.fa);
+                rec[16] = (uint32_t)t.x0;
+                rec[17] = (uint32_t)t.y0;
+                rec[18] = (uint32_t)(t.x1 - t.x0 + 1);
+                rec[19] = inst;
             }
-            continue;
-        }
-        uint32_t incl = count;
-#pragma unroll
-        for (int o = 1; o < 32; o <<= 1) {
-            const uint32_t y = __shfl_up_sync(0xffffffffu, incl, o);
-            if (lane >= o) incl += y;
-        }
-        const uint32_t all = __shfl_sync(0xffffffffu, incl, 31);
-        uint32_t* rec = s_rec[threadIdx.x >> 5][lane];
-        uint32_t* pre = s_pre[threadIdx.x >> 5];
-        pre[lane] = incl - count;
-        if (count) {
-            const Prep p = prepare(t);
-#pragma unroll
-            for (int q = 0; q < 3; ++q) {
-                rec[q] = (uint32_t)p.x[q];
-                rec[3 + q] = (uint32_t)p.y[q];
-                rec[6 + q] = (uint32_t)p.dx[q];
-                rec[9 + q] = (uint32_t)p.dy[q];
-                rec[12 + q] = __float_as_uint(p.zn[q]);
+            __syncwarp();
+            for (uint32_t sIdx = lane; sIdx < all; sIdx += 32) {
+                // the last lane whose first sample is <= sIdx (lanes without samples share their successor's start)
+                int owner = 0;
+    #pragma unroll
+                for (int step = 16; step > 0; step >>= 1)
+                    if (pre[owner + step] <= sIdx) owner += step;
+                const uint4* r4 = reinterpret_cast<const uint4*>(s_rec[threadIdx.x >> 5][owner]);
+                const uint4 q0 = r4[0], q1 = r4[1], q2 = r4[2], q3 = r4[3], q4 = r4[4];
+                Prep p;
+                p.x[0] = (int)q0.x; p.x[1] = (int)q0.y; p.x[2] = (int)q0.z;
+                p.y[0] = (int)q0.w; p.y[1] = (int)q1.x; p.y[2] = (int)q1.y;
+                p.dx[0] = (int)q1.z; p.dx[1] = (int)q1.w; p.dx[2] = (int)q2.x;
+                p.dy[0] = (int)q2.y; p.dy[1] = (int)q2.z; p.dy[2] = (int)q2.w;
+                p.zn[0] = __uint_as_float(q3.x); p.zn[1] = __uint_as_float(q3.y); p.zn[2] = __uint_as_float(q3.z);
+                p.fa = __uint_as_float(q3.w);
+                const uint32_t local = sIdx - pre[owner], bw = q4.z;
+                const uint32_t row = local / bw;
+                shade(p, 0, (int)(q4.x + (local - row * bw)), (int)(q4.y + row), clamp_depth, q4.w, a.target, a.width);
             }
-            rec[15] = __float_as_uint(p.fa);
-            rec[16] = (uint32_t)t.x0;
-            rec[17] = (uint32_t)t.y0;
-            rec[18] = (uint32_t)(t.x1 - t.x0 + 1);
-            rec[19] = inst;
+            __syncwarp();  // the records are rewritten on the next round
         }
-        __syncwarp();
-        for (uint32_t sIdx = lane; sIdx < all; sIdx += 32) {
-            // the last lane whose first sample is <= sIdx (lanes without samples share their successor's start)
-            int owner = 0;
-#pragma unroll
-            for (int step = 16; step > 0; step >>= 1)
-                if (pre[owner + step] <= sIdx) owner += step;
-            const uint4* r4 = reinterpret_cast<const uint4*>(s_rec[threadIdx.x >> 5][owner]);
-            const uint4 q0 = r4[0], q1 = r4[1], q2 = r4[2], q3 = r4[3], q4 = r4[4];
-            Prep p;
-            p.x[0] = (int)q0.x; p.x[1] = (int)q0.y; p.x[2] = (int)q0.z;
-            p.y[0] = (int)q0.w; p.y[1] = (int)q1.x; p.y[2] = (int)q1.y;
-            p.dx[0] = (int)q1.z; p.dx[1] = (int)q1.w; p.dx[2] = (int)q2.x;
-            p.dy[0] = (int)q2.y; p.dy[1] = (int)q2.z; p.dy[2] = (int)q2.w;
-            p.zn[0] = __uint_as_float(q3.x); p.zn[1] = __uint_as_float(q3.y); p.zn[2] = __uint_as_float(q3.z);
-            p.fa = __uint_as_float(q3.w);
-            const uint32_t local = sIdx - pre[owner], bw = q4.z;
-            const uint32_t row = local / bw;
-            shade(p, 0, (int)(q4.x + (local - row * bw)), (int)(q4.y + row), clamp_depth, q4.w, a.target, a.width);
-        }
-        __syncwarp();  // the records are rewritten on the next round
     }
 }
 
@@ -596,7 +767,7 @@ __global__ void __launch_bounds__(kRasterThreads) k_raster_tiles(const __grid_co
         // the tile's samples that lie inside the triangle's bounds
         const int x0 = max(w.x0, tx << 6), x1 = min(w.x1, (tx << 6) + 63), y0 = max(w.y0, ty << 6), y1 = min(w.y1, (ty << 6) + 63);
         const Prep p = prepare(w);
-        warp_sample_rect(p, w.mode, x0, x1, y0, y1, work_depth_floor(w, clamp_depth), clamp_depth, inst, a, lane);
+        warp_sample_rect(p, w.mode, x0, x1, y0, y1, ((unsigned long long)work_depth_floor(w, clamp_depth) << 32) | inst, clamp_depth, inst, a, lane);
     }
 }
 
@@ -614,38 +785,94 @@ void launch_raster_clear(unsigned long long* target, size_t n, cudaStream_t st)
 
 size_t raster_hiz_words(uint32_t width, uint32_t height)
 {
-    return (size_t)((width + 7) >> kCellShift) * ((height + 7) >> kCellShift);
+    return (size_t)((width + 7) >> kCellShift) * ((height + 7) >> kCellShift) + (size_t)((width + 63) >> 6) * ((height + 63) >> 6);
 }
 
-// The pairs are drawn in phases whose cumulative share grows by sqrt(2): after each, the coarse depth is rebuilt from
-// the target, so that a later phase skips what the earlier ones already hide (draw order is by key, i.e. any prefix of
-// the pairs is a spatially uniform sample of the view).  A view of a few instances is drawn in one phase.
+size_t raster_order_bytes(uint32_t n)
+{
+    auto up = [](size_t x) { return (x + 255) & ~size_t(255); };
+    const size_t n1 = (size_t)(n ? n : 1);
+    return 2 * up(n1 * 8) + up((n1 + 1) * 8) + 2 * up(n1 * 4) + up(((n1 + kScanTile - 1) / kScanTile) * 8) + up(sort_scratch_bytes(n1));
+}
+
+void raster_order_carve(void* blob, uint32_t n, RasterArgs* a)
+{
+    auto up = [](size_t x) { return (x + 255) & ~size_t(255); };
+    const size_t n1 = (size_t)(n ? n : 1);
+    unsigned char* p = static_cast<unsigned char*>(blob);
+    a->order_a = reinterpret_cast<unsigned long long*>(p); p += up(n1 * 8);
+    a->order_b = reinterpret_cast<unsigned long long*>(p); p += up(n1 * 8);
+    a->tri_prefix = reinterpret_cast<unsigned long long*>(p); p += up((n1 + 1) * 8);
+    a->draw_of = reinterpret_cast<uint32_t*>(p); p += up(n1 * 4);
+    a->row_of = reinterpret_cast<uint32_t*>(p); p += up(n1 * 4);
+    a->block_sums = reinterpret_cast<unsigned long long*>(p); p += up(((n1 + kScanTile - 1) / kScanTile) * 8);
+    a->sort_scratch = p;
+}
+
+// The pairs are drawn front to back in phases whose cumulative share doubles; after each, the coarse depth is
+// rebuilt from the target, so that a later phase skips what the earlier, nearer ones already hide.  A view of a few
+// instances is drawn in one phase.
 void launch_raster(const RasterArgs& a_in, cudaStream_t st)
 {
     if (!a_in.visible) return;
     RasterArgs a = a_in;
-    k_raster_pairs<<<1, 1024, 0, st>>>(a.draws, a.counts, a.max_draws, a.pairs);
+    const int sms = device_sm_count();
+    const unsigned row_grid = (unsigned)std::min<size_t>(((size_t)a.visible + 255) / 256, (size_t)sms * 8);
+    const unsigned scan_grid = (a.visible + kScanTile - 1) / kScanTile;
+    const int sort_begin = (a.flags & SS_RASTER_DEPTH_CLAMP) ? 0 : 32;
+    a.sort_passes = sort_num_passes(sort_begin, 64);
+    k_raster_keys<<<row_grid, 256, 0, st>>>(a);
+    int sort_launches = 0;
+    sort_async(reinterpret_cast<uint64_t*>(a.order_a), nullptr, reinterpret_cast<uint64_t*>(a.order_b), nullptr, a.visible, sort_begin, 64,
+               a.sort_scratch, st, &sort_launches, false);
+    k_raster_scan_sums<<<scan_grid, kScanThreads, 0, st>>>(a);
+    k_raster_scan_top<<<1, kScanThreads, 0, st>>>(a.block_sums, scan_grid);
+    k_raster_scan_apply<<<scan_grid, kScanThreads, 0, st>>>(a);
     constexpr int kPhases = 12;
     const int phases = (a.hiz && a.visible >= 256) ? kPhases : 1;
     if (phases == 1) a.hiz = nullptr;
     a.hiz_w = (a.width + 7) >> kCellShift;
     a.hiz_h = (a.height + 7) >> kCellShift;
     const size_t cells = (size_t)a.hiz_w * a.hiz_h;
-    if (a.hiz) cudaMemsetAsync(a.hiz, 0xFF, cells * sizeof(uint32_t), st);
-    const int sms = device_sm_count();
+    a.hiz2_w = (a.width + 63) >> 6;
+    a.hiz2_h = (a.height + 63) >> 6;
+    const size_t tiles = (size_t)a.hiz2_w * a.hiz2_h;
+    a.hiz2 = a.hiz ? a.hiz + cells : nullptr;
+    if (a.hiz) cudaMemsetAsync(a.hiz, 0xFF, (cells + tiles) * sizeof(unsigned long long), st);
     uint32_t lo = 0;
     for (int ph = 0; ph < phases; ++ph) {
-        const uint32_t hi = ph + 1 == phases ? 65536u : (uint32_t)(65536.0 * exp2(-0.5 * (phases - 1 - ph)));
+        const uint32_t hi = ph + 1 == phases ? 65536u : (uint32_t)(65536u >> (phases - 1 - ph));
         a.phase_lo = lo;
         a.phase_hi = hi;
         lo = hi;
-        if (a.queue_works) cudaMemsetAsync(a.queue_counts, 0, 2 * sizeof(uint32_t), st);
-        k_raster<<<sms * 12, kRasterThreads, 0, st>>>(a);  // persistent warps striding over the pairs
-        if (a.queue_works) k_raster_tiles<<<sms * 12, kRasterThreads, 0, st>>>(a);  // ... and over the queued tiles
+        cudaMemsetAsync(a.queue_counts, 0, 4 * sizeof(uint32_t), st);  // queue fill and the next chunk of pairs
+        k_raster<<<sms * 12, kRasterThreads, 0, st>>>(a);  // persistent warps taking chunks of the phase's pairs
+        if (a.queue_works) k_raster_tiles<<<sms * 12, kRasterThreads, 0, st>>>(a);  // ... and striding over the queued tiles
         if (a.hiz && ph + 1 < phases) {
             const size_t want = (cells + 255) / 256;
             k_raster_hiz<<<(unsigned)std::min<size_t>(want, (size_t)sms * 8), 256, 0, st>>>(a.target, a.width, a.height, a.hiz, a.hiz_w, a.hiz_h);
+            k_raster_hiz2<<<(unsigned)((tiles + 255) / 256), 256, 0, st>>>(a.hiz, a.hiz_w, a.hiz_h, a.hiz2, a.hiz2_w, a.hiz2_h);
         }
+#ifdef SS_RASTER_STATS
+        {
+            unsigned long long h[12], z[12] = {};
+            uint32_t qc[4] = {};
+            cudaStreamSynchronize(st);
+            cudaMemcpyFromSymbol(h, g_rstats, sizeof h);
+            cudaMemcpyToSymbol(g_rstats, z, sizeof z);
+            cudaMemcpy(qc, a.queue_counts, 16, cudaMemcpyDeviceToHost);
+            if (a.hiz) {
+                std::vector<unsigned long long> hz(cells);
+                cudaMemcpy(hz.data(), a.hiz, cells * 8, cudaMemcpyDeviceToHost);
+                size_t ones = 0, zeros = 0, one_f = 0;
+                for (unsigned long long v : hz) { ones += v == ~0ull; zeros += (v >> 32) == 0u; one_f += (v >> 32) == 0x3F800000u; }
+                fprintf(stderr, "  hiz before the next phase: %zu cells, %zu open, %zu at depth 0, %zu at depth 1; no floor %llu\n", cells, ones, zeros, one_f, h[8]);
+            }
+            fprintf(stderr, "raster phase %2d [%5u, %5u): pairs %llu with_samples %llu small_rejected %llu balanced_samples %llu coop_tris %llu "
+                            "cells %llu alive %llu puts %llu queued %u tiles %u\n", ph, a.phase_lo, a.phase_hi, h[0], h[1], h[2], h[3], h[4],
+                    h[5], h[6], h[7], qc[0], qc[1]);
+        }
+#endif
     }
 }
 

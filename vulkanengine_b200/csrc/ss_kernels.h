@@ -230,7 +230,17 @@ struct RasterArgs {
     const ss_draw_cmd* draws;  // the view's indirect draws (index range + instance range of each run)
     const uint32_t* counts;    // {visible, draws} of the view, device side
     uint32_t max_draws;
-    unsigned long long* pairs; // scratch [max_draws + 1]: (instance, triangle) pairs before each draw
+    // scratch of the depth order the pass is drawn in (front to back): sort words [depth key : 32 | row : 32] in two
+    // buffers (the sort's control block says which one holds the result), the draw of every row, and the number of
+    // triangles before every rank of that order ([visible + 1])
+    unsigned long long* order_a;
+    unsigned long long* order_b;
+    void* sort_scratch;
+    int sort_passes;
+    uint32_t* draw_of;
+    uint32_t* row_of;          // [n_instances], DepthClamp passes: the sort word carries the instance, this maps it back to its row
+    unsigned long long* tri_prefix;
+    unsigned long long* block_sums;
     const float* positions;    // [n_vertices][3]
     const uint32_t* indices;   // [n_indices]
     uint32_t n_vertices, n_indices;
@@ -242,15 +252,19 @@ struct RasterArgs {
     // queue of huge triangles (nullptr: none, they are walked where they are found)
     uint32_t* queue_works;     // [queue_work_cap][20]
     uint32_t* queue_tiles;     // [queue_tile_cap] owner work of each 64 x 64 tile entry
-    uint32_t* queue_counts;    // {works, tile entries}
+    uint32_t* queue_counts;    // {works, tile entries, next chunk of pairs, unused}
     uint32_t queue_work_cap, queue_tile_cap;
-    // coarse depth: per 8 x 8-sample cell an upper bound of the depth bits its samples hold (all ones: unknown), refreshed
+    // coarse depth: per 8 x 8-sample cell an upper bound of the words its samples hold (all ones: unknown), refreshed
     // between the phases the pairs are drawn in; nullptr: none.  phase_lo/hi: this launch's part of the pairs, 16.16
-    uint32_t* hiz;
+    unsigned long long* hiz;
     uint32_t hiz_w, hiz_h;
+    unsigned long long* hiz2;  // the same per 64 x 64-sample tile (8 x 8 cells): one look for a large triangle or a queue entry
+    uint32_t hiz2_w, hiz2_h;
     uint32_t phase_lo, phase_hi;
 };
 size_t raster_hiz_words(uint32_t width, uint32_t height);
+size_t raster_order_bytes(uint32_t n_instances);  // one allocation, carved up by raster_order_carve
+void raster_order_carve(void* blob, uint32_t n_instances, RasterArgs* a);
 int device_sm_count();  // SMs of the current device, cached per device
 void launch_raster_clear(unsigned long long* target, size_t n, cudaStream_t st);
 void launch_raster(const RasterArgs& a, cudaStream_t st);
