@@ -19,6 +19,7 @@ scaling; N = 4 is configs[3]'s 64M), no data-path collective in the sharded phas
              streams change, not per frame.  Reported beside `value`, never instead of it
   merge      N > 1: one globally sorted list per view (ss_merge_views over CUDA IPC peer mappings)
   strong_64m, cfg5, other_configs   configs[3] over the N GPUs, configs[4] (64 views), configs[0/1]
+  raster     one GPU: the consumer pass over the frame's lists (id pass + cascade depth passes, csrc/raster.cu)
   cpu_baseline / --impl reference
              the reference's CPU path (entt-order walk, glm T*R*S, std::map<MeshKey> grouping, plus
              the same cull) from oracle/_ref on the box's host cores (--impl reference: the whole scene)
@@ -517,7 +518,7 @@ def main():
                               "note": "the same loop when 10 % of the transforms change per step (ss_upload_trs_sparse); "
                                       "beside the full-upload number, not instead of it"}
         # the ceiling of the full-upload number: every rank copies the same pinned stream at once, nothing else running
-        dev_probe = torch.empty(host_trs.numel(), dtype=torch.float32, device=dev)
+        dev_probe = torch.empty_like(host_trs, device=f"cuda:{local_rank}")
         dev_probe.copy_(host_trs, non_blocking=True)
         torch.cuda.synchronize()
         barrier()
@@ -621,6 +622,37 @@ def main():
                 c2.close()
             del scene
 
+    # ---- consumer of the lists: id pass of the camera view + depth passes of the cascades ----------
+    raster = None
+    if world == 1 and not a.no_extras and a.views == N_VIEWS:
+        pos, ind, box_slots = synth.box_geometry(sc.slots)
+        rsc = synth.SceneArrays(**{**sc.__dict__, "slots": box_slots})
+        rctx = make_ctx(rsc)
+        rctx.set_geometry(pos, ind)
+        rslot = rctx.frame(views)
+        rst = rctx.frame_sync(rslot)
+        rstream = torch.cuda.ExternalStream(rctx.stream, device=local_rank)
+        raster = {"note": "csrc/raster.cu over the frame's lists, one box (12 triangles) per instance: entity-id pass of the camera "
+                          "view at 1920x1080 (SelectionPass) and DepthClamp depth passes of the four cascades at 4096^2 (ShadowPass); "
+                          "bit-equal to the CPU restatement (tests/test_raster.py); the reference's rasteriser is the Vulkan device: "
+                          "unavailable on this box"}
+        for v, (w_, h_, fl_) in enumerate([(1920, 1080, 0)] + [(4096, 4096, S.RASTER_DEPTH_CLAMP)] * 4):
+            rctx.raster_view(rslot, v, w_, h_, fl_)  # allocates the target
+            ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            reps = 3
+            with torch.cuda.stream(rstream):
+                ev0.record(rstream)
+                for _ in range(reps):
+                    rctx.raster_view(rslot, v, w_, h_, fl_)
+                ev1.record(rstream)
+            ev1.synchronize()
+            ms_r = ev0.elapsed_time(ev1) / reps
+            n_vis = int(rst.visible[v])
+            raster[f"view{v}"] = {"target": [w_, h_], "instances": n_vis, "triangles": n_vis * 12, "ms": ms_r,
+                                  "mtri_per_s": n_vis * 12 / (ms_r * 1e-3) / 1e6}
+        rctx.close()
+        del rsc, pos, ind
+
     if rank == 0:
         peak, peak_src = peaks()
         # per-kernel rooflines: algorithmic bytes of the launch / its CUDA-event time (ss_frame_stage_ms)
@@ -660,6 +692,8 @@ def main():
             line["cfg5"] = cfg5
         if other:
             line["other_configs"] = other
+        if raster:
+            line["raster"] = raster
         if not a.no_cpu_baseline and world == 1:
             os.sched_setaffinity(0, all_cpus)  # the CPU baseline gets every core again
             cores = os.cpu_count() or 1

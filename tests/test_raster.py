@@ -190,3 +190,19 @@ def test_randomised_raster(case):
     for v, (img, want, _) in enumerate(out):
         assert np.array_equal(img, want), f"case {case} view {v}: {np.count_nonzero(img != want)} of {W * H} samples differ"
     ctx.close()
+
+
+@pytest.mark.parametrize("flags_name", ["default", "depth_clamp"])
+def test_heavy_overdraw_is_drawn_in_phases(flags_name):
+    """Thousands of boxes around the camera, each covering a good part of a small target: the pass runs front to back in
+    phases and skips what the coarse depth already hides (csrc/raster.cu, launch_raster).  What is skipped depends on
+    the order; the image must not — and with DepthClamp most of it sits at depth 0, where the lowest instance wins."""
+    flags = S.RASTER_DEPTH_CLAMP if flags_name == "depth_clamp" else 0
+    sc, pos, ind = close_up_scene(3000, spread=30.0, seed_shift=77)
+    views = synth.fibonacci_cameras(lambda *a: O.camera_view_proj(*a), 2, radius=10.0, seed=synth.SEED_BASE + 77)
+    ctx, slot, out = run(sc, pos, ind, views, 160, 120, lambda v: flags)
+    for v, (img, want, got_view) in enumerate(out):
+        assert len(got_view["idx"]) >= 256, "too few instances for more than one phase"
+        assert np.array_equal(img, want), f"view {v}: {np.count_nonzero(img != want)} samples differ"
+        assert np.count_nonzero(img != np.uint64(S.RASTER_EMPTY)) > 160 * 120 // 2
+    ctx.close()

@@ -537,7 +537,11 @@ __device__ __noinline__ void cut_and_queue(const float c[3][4], const float dd[3
 // up to 16 K samples — its warp, lanes striding over the bounds; more, or anything cut by the near plane or not
 // snappable — the queue, so that a view whose instances cover thousands of pixels each (the near shadow cascades)
 // is spread over the whole grid.
-__global__ void __launch_bounds__(kRasterThreads, 4) k_raster(const __grid_constant__ RasterArgs a)
+// 8 CTAs of 128 threads per SM (64 registers): the per-triangle set-up is a chain of dependent loads, and with most
+// triangles dropped by the coarse depth it is what the pass spends its time on; measured on cfg 3's far cascade
+// (199 M triangles) 31.8 ms at 4 CTAs, 26.4 at 6, 23.4 at 8.
+constexpr int kRasterCtasPerSm = 8;
+__global__ void __launch_bounds__(kRasterThreads, kRasterCtasPerSm) k_raster(const __grid_constant__ RasterArgs a)
 {
     __shared__ __align__(16) uint32_t s_rec[kRasterThreads / 32][32][20];  // per lane: x, y, dx, dy, zn, fa, x0, y0, width, instance
     __shared__ uint32_t s_pre[kRasterThreads / 32][32];                     // samples before each lane's
@@ -846,7 +850,7 @@ void launch_raster(const RasterArgs& a_in, cudaStream_t st)
         a.phase_hi = hi;
         lo = hi;
         cudaMemsetAsync(a.queue_counts, 0, 4 * sizeof(uint32_t), st);  // queue fill and the next chunk of pairs
-        k_raster<<<sms * 12, kRasterThreads, 0, st>>>(a);  // persistent warps taking chunks of the phase's pairs
+        k_raster<<<sms * 3 * kRasterCtasPerSm, kRasterThreads, 0, st>>>(a);  // persistent warps taking chunks of the phase's pairs
         if (a.queue_works) k_raster_tiles<<<sms * 12, kRasterThreads, 0, st>>>(a);  // ... and striding over the queued tiles
         if (a.hiz && ph + 1 < phases) {
             const size_t want = (cells + 255) / 256;
