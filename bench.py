@@ -303,6 +303,7 @@ def bench_merge(torch, dist, S, ctx, views, n, rank, local_rank, world, n_views)
     e1.record()
     e1.synchronize()
     ms = max_over_ranks(torch, dist, world, e0.elapsed_time(e1) / reps)
+    stage = mg.stage_ms()
     merged = [mg.map(v) for v in range(n_views)]
     total = sum(int(m.visible) for m in merged)
     mine = sum(int(st.visible[v]) for v in range(n_views))
@@ -312,7 +313,7 @@ def bench_merge(torch, dist, S, ctx, views, n, rank, local_rank, world, n_views)
     dist.barrier()
     mg.close()
     close_merge_peers(S, local_rank, table, n_views)
-    return {"ms": ms, "merged_elements": total, "equals_sum_of_ranks": bool(int(t.item()) == total),
+    return {"ms": ms, "stage_ms_rank0": stage, "merged_elements": total, "equals_sum_of_ranks": bool(int(t.item()) == total),
             "list_bytes_over_nvlink_per_rank": int(remote_bytes),
             "nvlink_gbs_per_rank": remote_bytes / (ms * 1e-3) / 1e9 if ms > 0 else None,
             "note": "ss_merge_views (C ABI, four kernels for all views, no host sync): every rank ends with the merged list of "

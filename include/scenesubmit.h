@@ -412,6 +412,8 @@ SS_API ss_status ss_merge_create(int device, uint32_t n_ranks, uint32_t n_views,
 SS_API void ss_merge_destroy(ss_merge* m);
 /* peers: host array [n_views][n_ranks]; asynchronous on cuda_stream */
 SS_API ss_status ss_merge_views(ss_merge* m, void* cuda_stream, const ss_merge_peer* peers);
+/* CUDA-event times of the last ss_merge_views' four kernels: fetch, rank, segments, placement (waits for them) */
+SS_API ss_status ss_merge_stage_ms(ss_merge* m, float ms_out[4]);
 /* waits for cuda_stream, returns the view's merged buffers (library-owned, valid until the next ss_merge_views) */
 SS_API ss_status ss_merge_map(ss_merge* m, void* cuda_stream, uint32_t view, ss_merged_view* out);
 /* host copies of a merged view (any pointer may be NULL; sizes from a first call with NULL pointers) */

@@ -195,14 +195,19 @@ __global__ void __launch_bounds__(kSegThreads) k_merge_segments(const __grid_con
 }
 
 // Persistent warps over the merged list of every view (grid.y = view), kChunk = 512 consecutive positions per warp and
-// step.  A warp bisects the segment prefix once per chunk; every lane then keeps the segment it is in (its end, its source
-// pointer, key and instance base) in registers and only re-reads the tables when it walks past the segment's end, so the
-// steady state per element is one peer read (four in flight per lane) and two coalesced stores.
-__global__ void __launch_bounds__(256) k_merge_place(const __grid_constant__ PeerTable pt, const __grid_constant__ MergeTables t)
+// step.  A warp bisects the segment prefix once per chunk; every lane then keeps the segment it is in (its end and its
+// source pointer) in registers and only re-reads the tables when it walks past the segment's end.  The peer reads of a
+// whole chunk are issued at once as 4-byte cp.async copies into shared memory (16 per lane in flight, no registers
+// held): over NVLink with every GPU reading every other one it is the bytes in flight that set the pace (four
+// register loads per lane: 2.33 ms for 187 M elements on 8 GPUs).  Then the chunk is added up and stored, coalesced.
+constexpr int kPlaceRounds = 16, kPlaceChunk = 32 * kPlaceRounds, kPlaceWarps = 8;
+
+__global__ void __launch_bounds__(kPlaceWarps * 32) k_merge_place(const __grid_constant__ PeerTable pt, const __grid_constant__ MergeTables t)
 {
-    constexpr int kBatch = 4, kRoundsPerChunk = 16, kChunk = 32 * kRoundsPerChunk;
+    __shared__ uint32_t s_val[kPlaceWarps][kPlaceChunk];
+    __shared__ uint32_t s_seg[kPlaceWarps][kPlaceChunk];
     const uint32_t v = blockIdx.y;
-    const int lane = threadIdx.x & 31;
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     const size_t vb = (size_t)v * t.n_ranks * t.max_draws;
     const uint32_t n_segs = t.n_segs[v];
     const uint32_t* __restrict__ seg_out = t.seg_out + (size_t)v * (t.n_ranks * t.max_draws + 1);
@@ -210,48 +215,47 @@ __global__ void __launch_bounds__(256) k_merge_place(const __grid_constant__ Pee
     uint32_t* __restrict__ out_idx = t.out_idx + (size_t)v * t.cap_visible;
     uint64_t* __restrict__ out_keys = t.out_keys + (size_t)v * t.cap_visible;
     const uint32_t warps = (gridDim.x * blockDim.x) >> 5, warp_id = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    for (uint64_t g0 = (uint64_t)warp_id * kChunk; g0 < total; g0 += (uint64_t)warps * kChunk) {
+    uint32_t* my_val = s_val[wid];
+    uint32_t* my_seg = s_seg[wid];
+    for (uint64_t g0 = (uint64_t)warp_id * kPlaceChunk; g0 < total; g0 += (uint64_t)warps * kPlaceChunk) {
         uint32_t lo = 0, hi = n_segs;
         while (hi - lo > 1) {
             const uint32_t mid = (lo + hi) >> 1;
             if (seg_out[mid] <= g0) lo = mid; else hi = mid;
         }
         // the lane's current segment, cached
-        uint32_t cur = lo, seg_begin = 0, seg_end = 0, ibase = 0;
+        uint32_t cur = lo, seg_begin = 0, seg_end = 0;
         const uint32_t* src = nullptr;
-        uint64_t key = 0;
         auto load_segment = [&](uint32_t sI) {
             seg_begin = seg_out[sI];
             seg_end = seg_out[sI + 1];
-            const ss_merge_peer& p = pt.p[v][t.seg_rank[vb + sI]];
-            src = p.idx + t.seg_src[vb + sI];
-            ibase = (uint32_t)p.instance_base;
-            key = t.seg_key[vb + sI];
+            src = pt.p[v][t.seg_rank[vb + sI]].idx + t.seg_src[vb + sI];
         };
         load_segment(cur);
-        for (int r0 = 0; r0 < kRoundsPerChunk; r0 += kBatch) {
-            uint32_t val[kBatch];
-            uint64_t kk[kBatch];
 #pragma unroll
-            for (int r = 0; r < kBatch; ++r) {
-                const uint64_t e = g0 + (uint64_t)(r0 + r) * 32 + lane;
-                val[r] = 0;
-                kk[r] = 0;
-                if (e < total) {
-                    while (e >= seg_end) load_segment(++cur);  // empty segments are stepped over
-                    val[r] = src[(uint32_t)e - seg_begin] + ibase;
-                    kk[r] = key;
-                }
-            }
-#pragma unroll
-            for (int r = 0; r < kBatch; ++r) {
-                const uint64_t e = g0 + (uint64_t)(r0 + r) * 32 + lane;
-                if (e < total) {
-                    out_idx[e] = val[r];
-                    out_keys[e] = kk[r];
-                }
+        for (int r = 0; r < kPlaceRounds; ++r) {
+            const uint64_t e = g0 + (uint64_t)r * 32 + lane;
+            if (e < total) {
+                while (e >= seg_end) load_segment(++cur);  // empty segments are stepped over
+                const uint32_t dst = (uint32_t)__cvta_generic_to_shared(my_val + r * 32 + lane);
+                asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(dst), "l"(src + ((uint32_t)e - seg_begin)) : "memory");
+                my_seg[r * 32 + lane] = cur;
             }
         }
+        asm volatile("cp.async.commit_group;" ::: "memory");
+        asm volatile("cp.async.wait_group 0;" ::: "memory");
+        __syncwarp();
+#pragma unroll 4
+        for (int r = 0; r < kPlaceRounds; ++r) {
+            const uint64_t e = g0 + (uint64_t)r * 32 + lane;
+            if (e < total) {
+                const uint32_t sI = my_seg[r * 32 + lane];
+                const uint32_t ibase = (uint32_t)pt.p[v][t.seg_rank[vb + sI]].instance_base;
+                __stcs(out_idx + e, my_val[r * 32 + lane] + ibase);  // written once, read by the consumer: keep them out of L2's way
+                __stcs(reinterpret_cast<unsigned long long*>(out_keys + e), (unsigned long long)t.seg_key[vb + sI]);
+            }
+        }
+        __syncwarp();  // the chunk buffer is refilled on the next step
     }
 }
 
@@ -265,6 +269,8 @@ struct ss_merge {
     MergeTables t{};
     std::vector<void*> allocs;
     std::string err;
+    cudaEvent_t ev[5] = {};  // around the four kernels of the last ss_merge_views
+    bool timed = false;
 };
 
 extern "C" {
@@ -331,6 +337,8 @@ SS_API void ss_merge_destroy(ss_merge* m)
     if (!m) return;
     cudaSetDevice(m->device);
     for (void* p : m->allocs) cudaFree(p);
+    for (cudaEvent_t e : m->ev)
+        if (e) cudaEventDestroy(e);
     delete m;
 }
 
@@ -352,15 +360,37 @@ SS_API ss_status ss_merge_views(ss_merge* m, void* cuda_stream, const ss_merge_p
     if (cudaSetDevice(m->device) != cudaSuccess) return SS_ERR_CUDA;
     cudaStream_t st = static_cast<cudaStream_t>(cuda_stream);
     const uint32_t chunks = (t.max_draws + 255) / 256;
+    if (!m->ev[0])
+        for (cudaEvent_t& e : m->ev)
+            if (cudaEventCreate(&e) != cudaSuccess) return SS_ERR_CUDA;
+    cudaEventRecord(m->ev[0], st);
     k_merge_fetch<<<dim3(std::min<uint32_t>(chunks, 8), t.n_views, t.n_ranks), 256, 0, st>>>(pt, t);
+    cudaEventRecord(m->ev[1], st);
     k_merge_rank<<<dim3((t.n_ranks * t.max_draws + 255) / 256, t.n_views), 256, 0, st>>>(t);
+    cudaEventRecord(m->ev[2], st);
     k_merge_segments<<<t.n_views, kSegThreads, 0, st>>>(t);
-    k_merge_place<<<dim3((unsigned)m->sms * 4, t.n_views), 256, 0, st>>>(pt, t);
+    cudaEventRecord(m->ev[3], st);
+    k_merge_place<<<dim3((unsigned)m->sms * 4, t.n_views), kPlaceWarps * 32, 0, st>>>(pt, t);
+    cudaEventRecord(m->ev[4], st);
+    m->timed = true;
     const cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) {
         m->err = std::string("ss_merge_views: ") + cudaGetErrorString(e);
         return SS_ERR_CUDA;
     }
+    return SS_OK;
+}
+
+SS_API ss_status ss_merge_stage_ms(ss_merge* m, float ms_out[4])
+{
+    if (!m || !ms_out) return SS_ERR_INVALID;
+    if (!m->timed) {
+        m->err = "ss_merge_stage_ms: no ss_merge_views yet";
+        return SS_ERR_STATE;
+    }
+    if (cudaSetDevice(m->device) != cudaSuccess || cudaEventSynchronize(m->ev[4]) != cudaSuccess) return SS_ERR_CUDA;
+    for (int i = 0; i < 4; ++i)
+        if (cudaEventElapsedTime(&ms_out[i], m->ev[i], m->ev[i + 1]) != cudaSuccess) return SS_ERR_CUDA;
     return SS_OK;
 }
 

@@ -31,7 +31,7 @@ EXPORTS = ["ss_create", "ss_destroy", "ss_last_error", "ss_version", "ss_set_key
            "ss_set_geometry", "ss_raster_view", "ss_map_raster", "ss_download_raster", "ss_read_pixel",
            "ss_cascade_matrices_batch", "ss_upload_trs_sparse", "ss_merge_place",
            "ss_export_idx_lists", "ss_ipc_open", "ss_ipc_close", "ss_merge_place_peers",
-           "ss_merge_create", "ss_merge_destroy", "ss_merge_views", "ss_merge_map", "ss_merge_last_error", "ss_merge_download",
+           "ss_merge_create", "ss_merge_destroy", "ss_merge_views", "ss_merge_stage_ms", "ss_merge_map", "ss_merge_last_error", "ss_merge_download",
            "ss_export_slot_buffers", "ss_cascade_matrices_snapped", "ss_upload_pose_sparse", "ss_pack_lights", "ss_set_instance_entities", "ss_select_view"]
 RASTER_DEPTH_CLAMP = 1
 RASTER_EMPTY = 0xFFFFFFFFFFFFFFFF
@@ -198,6 +198,14 @@ class Merger:
         st = self.lib.ss_merge_views(self.h, C.c_void_p(stream), arr)
         if st != SS_OK:
             raise SceneSubmitError(st, self.lib.ss_merge_last_error(self.h).decode())
+
+    def stage_ms(self):
+        """CUDA-event times of the last merge's kernels: fetch, rank, segments, placement."""
+        ms = (C.c_float * 4)()
+        st = self.lib.ss_merge_stage_ms(self.h, ms)
+        if st != SS_OK:
+            raise SceneSubmitError(st, self.lib.ss_merge_last_error(self.h).decode())
+        return dict(zip(("fetch", "rank", "segments", "place"), (float(x) for x in ms)))
 
     def map(self, view, stream=None):
         out = MergedView()
