@@ -27,8 +27,8 @@ def main():
         cols = [hdr.index(k) for k in KEEP if k in hdr]
         if first:
             w.writerow(["report"] + [hdr[c] for c in cols])
-            w.writerow([""] + [units[c] for c in cols])
             first = False
+        w.writerow(["units of " + rep.split("/")[-1]] + [units[c] for c in cols])  # ncu picks units per report
         for r in rows[2:]:
             w.writerow([rep.split("/")[-1]] + [r[c] for c in cols])
 
