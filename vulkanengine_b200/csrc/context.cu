@@ -1325,8 +1325,8 @@ SS_API ss_status ss_raster_view(ss_ctx* c, uint32_t slot, uint32_t view, uint32_
     ra.draws = o.draws;
     ra.counts = o.counts;
     ra.max_draws = c->max_draws;
-    if (!c->d_raster_order) SS_CUDA(c, cudaMalloc(&c->d_raster_order, raster_order_bytes(c->n_instances)));
-    raster_order_carve(c->d_raster_order, c->n_instances, &ra);
+    if (!c->d_raster_order) SS_CUDA(c, cudaMalloc(&c->d_raster_order, raster_order_bytes(c->n_instances, c->max_draws)));
+    raster_order_carve(c->d_raster_order, c->n_instances, c->max_draws, &ra);
     constexpr uint32_t kRasterQueueWorks = 1u << 19, kRasterQueueTiles = 1u << 23;  // 40 MB + 32 MB, on first use
     if (!c->d_raster_queue)
         SS_CUDA(c, cudaMalloc(&c->d_raster_queue, ((size_t)kRasterQueueWorks * 20 + kRasterQueueTiles + 4) * sizeof(uint32_t)));

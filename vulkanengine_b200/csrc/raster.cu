@@ -337,6 +337,108 @@ __device__ __forceinline__ const unsigned long long* sorted_order(const RasterAr
     return ctl->src_sel[a.sort_passes] ? a.order_b : a.order_a;
 }
 
+// Bounds of the vertices every draw's index range names (one CTA per draw at a time).  A vertex or an index outside the
+// geometry is left out: the triangle it belongs to is never drawn.
+__global__ void __launch_bounds__(128) k_raster_draw_bounds(const __grid_constant__ RasterArgs a)
+{
+    __shared__ float s_red[4][6];
+    const uint32_t n_draws = min(a.counts[1], a.max_draws);
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    for (uint32_t d = blockIdx.x; d < n_draws; d += gridDim.x) {
+        const ss_draw_cmd dc = a.draws[d];
+        float lo[3] = {INFINITY, INFINITY, INFINITY}, hi[3] = {-INFINITY, -INFINITY, -INFINITY};
+        for (uint32_t i = threadIdx.x; i < dc.index_count; i += blockDim.x) {
+            const uint64_t ii = (uint64_t)dc.first_index + i;
+            if (ii >= a.n_indices) continue;
+            const int64_t vi = (int64_t)dc.vertex_offset + (int64_t)a.indices[ii];
+            if (vi < 0 || vi >= (int64_t)a.n_vertices) continue;
+#pragma unroll
+            for (int q = 0; q < 3; ++q) {
+                const float p = a.positions[(size_t)vi * 3 + q];
+                lo[q] = fminf(lo[q], p);
+                hi[q] = fmaxf(hi[q], p);
+            }
+        }
+#pragma unroll
+        for (int q = 0; q < 3; ++q)
+            for (int o = 16; o > 0; o >>= 1) {
+                lo[q] = fminf(lo[q], __shfl_xor_sync(0xffffffffu, lo[q], o));
+                hi[q] = fmaxf(hi[q], __shfl_xor_sync(0xffffffffu, hi[q], o));
+            }
+        __syncthreads();  // s_red of the previous draw has been read
+        if (lane == 0)
+            for (int q = 0; q < 3; ++q) {
+                s_red[wid][q] = lo[q];
+                s_red[wid][3 + q] = hi[q];
+            }
+        __syncthreads();
+        if (threadIdx.x < 6) {
+            float v = s_red[0][threadIdx.x];
+            for (int w = 1; w < 4; ++w) v = threadIdx.x < 3 ? fminf(v, s_red[w][threadIdx.x]) : fmaxf(v, s_red[w][threadIdx.x]);
+            a.draw_aabb[(size_t)d * 6 + threadIdx.x] = v;
+        }
+    }
+}
+
+// Where on the target, and how near at the nearest, anything of one instance can land: the eight corners of its draw's
+// bounds through the same two products the triangles go through, with the rounding of every step accounted for.
+// A vertex is a convex combination of the corners; its clip coordinates, as k_raster computes them, lie within `err`
+// of the exact ones (each is a sum of products whose magnitudes are bounded by the corners': 2^-19 of that sum covers
+// the dozen roundings on the way twice over), so they lie in the hull of the corners' computed coordinates widened by
+// 2 err, and with w > 0 throughout a ratio x / w is extreme at an extreme point of that set.  The snap to 1/256 pixel
+// and the float evaluation of the viewport transform add at most 1/64 pixel + 2^-20 |x|.  No bound (whole target,
+// depth 0) when a corner may reach w <= 0 or lies beyond 2^19 pixels (triangles that cannot be snapped are sampled
+// with float edge functions, whose coverage is not exact).
+__device__ __forceinline__ uint4 instance_bound(const RasterArgs& a, float4 r0, float4 r1, float4 r2, const float* bb, uint32_t inst)
+{
+    const bool clamp_depth = (a.flags & SS_RASTER_DEPTH_CLAMP) != 0;
+    const int cxmax = (int)((a.width - 1) >> kCellShift), cymax = (int)((a.height - 1) >> kCellShift);
+    const uint4 whole = make_uint4((uint32_t)cxmax << 16, (uint32_t)cymax << 16, 0u, inst);
+    if (!(bb[0] <= bb[3])) return make_uint4(1u, 0u, 0u, inst);  // no valid vertex: nothing of it is ever drawn
+    const float half_w = 0.5f * (float)a.width, half_h = 0.5f * (float)a.height;
+    float sx_lo = INFINITY, sx_hi = -INFINITY, sy_lo = INFINITY, sy_hi = -INFINITY, zn_lo = INFINITY;
+    const float k = 1.9073486e-6f;  // 2^-19
+#pragma unroll
+    for (int c = 0; c < 8; ++c) {
+        const float px = bb[(c & 1) ? 3 : 0], py = bb[(c & 2) ? 4 : 1], pz = bb[(c & 4) ? 5 : 2];
+        const float wx = (r0.x * px + r0.y * py) + (r0.z * pz + r0.w);
+        const float wy = (r1.x * px + r1.y * py) + (r1.z * pz + r1.w);
+        const float wz = (r2.x * px + r2.y * py) + (r2.z * pz + r2.w);
+        const float mx = (fabsf(r0.x * px) + fabsf(r0.y * py)) + (fabsf(r0.z * pz) + fabsf(r0.w));
+        const float my = (fabsf(r1.x * px) + fabsf(r1.y * py)) + (fabsf(r1.z * pz) + fabsf(r1.w));
+        const float mz = (fabsf(r2.x * px) + fabsf(r2.y * py)) + (fabsf(r2.z * pz) + fabsf(r2.w));
+        float cl[4], er[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            cl[j] = (a.vp[j] * wx + a.vp[4 + j] * wy) + (a.vp[8 + j] * wz + a.vp[12 + j]);
+            er[j] = 2.f * k * ((fabsf(a.vp[j]) * mx + fabsf(a.vp[4 + j]) * my) + (fabsf(a.vp[8 + j]) * mz + fabsf(a.vp[12 + j])));
+        }
+        const float w_lo = cl[3] - er[3], w_hi = cl[3] + er[3];
+        if (!(w_lo > 0.f)) return whole;
+        const float xl = cl[0] - er[0], xh = cl[0] + er[0], yl = cl[1] - er[1], yh = cl[1] + er[1];
+        const float rxl = xl >= 0.f ? xl / w_hi : xl / w_lo, rxh = xh >= 0.f ? xh / w_lo : xh / w_hi;
+        const float ryl = yl >= 0.f ? yl / w_hi : yl / w_lo, ryh = yh >= 0.f ? yh / w_lo : yh / w_hi;
+        sx_lo = fminf(sx_lo, rxl * half_w + half_w);
+        sx_hi = fmaxf(sx_hi, rxh * half_w + half_w);
+        sy_lo = fminf(sy_lo, ryl * half_h + half_h);
+        sy_hi = fmaxf(sy_hi, ryh * half_h + half_h);
+        const float zl = cl[2] - er[2];
+        zn_lo = fminf(zn_lo, zl > 0.f ? zl / w_hi : 0.f);
+    }
+    const float far_out = 524288.f;  // 2^19 pixels
+    if (!(sx_lo > -far_out && sx_hi < far_out && sy_lo > -far_out && sy_hi < far_out)) return whole;
+    const float mgx = 0.015625f + fmaxf(fabsf(sx_lo), fabsf(sx_hi)) * 9.5367432e-7f;
+    const float mgy = 0.015625f + fmaxf(fabsf(sy_lo), fabsf(sy_hi)) * 9.5367432e-7f;
+    // sample i sits at i + 0.5
+    const int i0 = max((int)ceilf(sx_lo - mgx - 0.5f), 0), i1 = min((int)floorf(sx_hi + mgx - 0.5f), (int)a.width - 1);
+    const int j0 = max((int)ceilf(sy_lo - mgy - 0.5f), 0), j1 = min((int)floorf(sy_hi + mgy - 0.5f), (int)a.height - 1);
+    if (i0 > i1 || j0 > j1) return make_uint4(1u, 0u, 0u, inst);  // covers no sample
+    float zf = zn_lo > 0.f ? zn_lo * (1.f - k) : 0.f;
+    if (clamp_depth) zf = fminf(zf, 1.0f);
+    return make_uint4((uint32_t)(i0 >> kCellShift) | ((uint32_t)(i1 >> kCellShift) << 16),
+                      (uint32_t)(j0 >> kCellShift) | ((uint32_t)(j1 >> kCellShift) << 16), __float_as_uint(zf), inst);
+}
+
 __global__ void __launch_bounds__(256) k_raster_keys(const __grid_constant__ RasterArgs a)
 {
     const uint32_t n_draws = min(a.counts[1], a.max_draws);
@@ -368,6 +470,15 @@ __global__ void __launch_bounds__(256) k_raster_keys(const __grid_constant__ Ras
         const uint32_t sortable = bits ^ ((bits >> 31) ? 0xFFFFFFFFu : 0x80000000u);
         a.order_a[k] = ((unsigned long long)sortable << 32) | low;
         a.draw_of[k] = d;
+        const uint32_t inst = a.idx[k];
+        if (d == kNoDraw) {
+            a.bound[k] = make_uint4(1u, 0u, 0u, inst);
+        } else {
+            float bb[6];
+#pragma unroll
+            for (int q = 0; q < 6; ++q) bb[q] = a.draw_aabb[(size_t)d * 6 + q];
+            a.bound[k] = instance_bound(a, a.rows[(size_t)k * 3 + 0], a.rows[(size_t)k * 3 + 1], a.rows[(size_t)k * 3 + 2], bb, inst);
+        }
     }
 }
 
@@ -590,10 +701,32 @@ __global__ void __launch_bounds__(kRasterThreads, kRasterCtasPerSm) k_raster(con
             if (g < total) {
                 while (a.tri_prefix[r + 1] <= g) ++r;  // ranks without triangles are stepped over
                 const uint32_t k = row_at_rank(a, order, r);
+                // the instance first: where any of its triangles can land and how near (k_raster_keys); one that covers no
+                // sample, or that lies behind the coarse depth of everything it can touch, is done with here, before a
+                // single index or vertex of it is read
+                const uint4 bd = a.bound[k];
+                inst = bd.w;
+                const int bx0 = (int)(bd.x & 0xFFFFu), bx1 = (int)(bd.x >> 16), by0 = (int)(bd.y & 0xFFFFu), by1 = (int)(bd.y >> 16);
+                bool hidden = bx0 > bx1;
+                if (!hidden && a.hiz) {
+                    const unsigned long long inst_floor = ((unsigned long long)bd.z << 32) | inst;
+                    if ((bx1 - bx0 + 1) * (by1 - by0 + 1) <= 16) {
+                        unsigned long long far = 0;
+                        for (int cy = by0; cy <= by1; ++cy)
+                            for (int cx = bx0; cx <= bx1; ++cx) far = max(far, __ldg(a.hiz + (size_t)cy * a.hiz_w + cx));
+                        hidden = inst_floor > far;
+                    } else if (((bx1 >> 3) - (bx0 >> 3) + 1) * ((by1 >> 3) - (by0 >> 3) + 1) <= 16) {
+                        unsigned long long far = 0;
+                        for (int ty = by0 >> 3; ty <= (by1 >> 3); ++ty)
+                            for (int tx = bx0 >> 3; tx <= (bx1 >> 3); ++tx) far = max(far, __ldg(a.hiz2 + (size_t)ty * a.hiz2_w + tx));
+                        hidden = inst_floor > far;
+                    }
+                }
+                RSTAT(9, hidden);
+                if (!hidden) {
                 const ss_draw_cmd dc = a.draws[a.draw_of[k]];
                 const uint32_t tI = (uint32_t)(g - a.tri_prefix[r]);
                 const float4 r0 = a.rows[(size_t)k * 3 + 0], r1 = a.rows[(size_t)k * 3 + 1], r2 = a.rows[(size_t)k * 3 + 2];
-                inst = a.idx[k];
                 // 1: the triangle in clip space
                 float c[3][4], dd[3];
                 bool in_range = true;
@@ -617,6 +750,7 @@ __global__ void __launch_bounds__(kRasterThreads, kRasterCtasPerSm) k_raster(con
                     } else {
                         cut_and_queue(c, dd, inst, a);
                     }
+                }
                 }
             }
             r_warp = __shfl_sync(0xffffffffu, r, 31);  // where the next 32 pairs start looking
@@ -792,14 +926,14 @@ size_t raster_hiz_words(uint32_t width, uint32_t height)
     return (size_t)((width + 7) >> kCellShift) * ((height + 7) >> kCellShift) + (size_t)((width + 63) >> 6) * ((height + 63) >> 6);
 }
 
-size_t raster_order_bytes(uint32_t n)
+size_t raster_order_bytes(uint32_t n, uint32_t max_draws)
 {
     auto up = [](size_t x) { return (x + 255) & ~size_t(255); };
     const size_t n1 = (size_t)(n ? n : 1);
-    return 2 * up(n1 * 8) + up((n1 + 1) * 8) + 2 * up(n1 * 4) + up(((n1 + kScanTile - 1) / kScanTile) * 8) + up(sort_scratch_bytes(n1));
+    return 2 * up(n1 * 8) + up((n1 + 1) * 8) + 2 * up(n1 * 4) + up(n1 * 16) + up(((size_t)max_draws + 1) * 24) + up(((n1 + kScanTile - 1) / kScanTile) * 8) + up(sort_scratch_bytes(n1));
 }
 
-void raster_order_carve(void* blob, uint32_t n, RasterArgs* a)
+void raster_order_carve(void* blob, uint32_t n, uint32_t max_draws, RasterArgs* a)
 {
     auto up = [](size_t x) { return (x + 255) & ~size_t(255); };
     const size_t n1 = (size_t)(n ? n : 1);
@@ -809,6 +943,8 @@ void raster_order_carve(void* blob, uint32_t n, RasterArgs* a)
     a->tri_prefix = reinterpret_cast<unsigned long long*>(p); p += up((n1 + 1) * 8);
     a->draw_of = reinterpret_cast<uint32_t*>(p); p += up(n1 * 4);
     a->row_of = reinterpret_cast<uint32_t*>(p); p += up(n1 * 4);
+    a->bound = reinterpret_cast<uint4*>(p); p += up(n1 * 16);
+    a->draw_aabb = reinterpret_cast<float*>(p); p += up(((size_t)max_draws + 1) * 24);
     a->block_sums = reinterpret_cast<unsigned long long*>(p); p += up(((n1 + kScanTile - 1) / kScanTile) * 8);
     a->sort_scratch = p;
 }
@@ -825,6 +961,7 @@ void launch_raster(const RasterArgs& a_in, cudaStream_t st)
     const unsigned scan_grid = (a.visible + kScanTile - 1) / kScanTile;
     const int sort_begin = (a.flags & SS_RASTER_DEPTH_CLAMP) ? 0 : 32;
     a.sort_passes = sort_num_passes(sort_begin, 64);
+    k_raster_draw_bounds<<<(unsigned)std::min<uint32_t>(std::max<uint32_t>(a.max_draws, 1u), (uint32_t)sms * 16u), 128, 0, st>>>(a);
     k_raster_keys<<<row_grid, 256, 0, st>>>(a);
     int sort_launches = 0;
     sort_async(reinterpret_cast<uint64_t*>(a.order_a), nullptr, reinterpret_cast<uint64_t*>(a.order_b), nullptr, a.visible, sort_begin, 64,
@@ -873,8 +1010,8 @@ void launch_raster(const RasterArgs& a_in, cudaStream_t st)
                 fprintf(stderr, "  hiz before the next phase: %zu cells, %zu open, %zu at depth 0, %zu at depth 1; no floor %llu\n", cells, ones, zeros, one_f, h[8]);
             }
             fprintf(stderr, "raster phase %2d [%5u, %5u): pairs %llu with_samples %llu small_rejected %llu balanced_samples %llu coop_tris %llu "
-                            "cells %llu alive %llu puts %llu queued %u tiles %u\n", ph, a.phase_lo, a.phase_hi, h[0], h[1], h[2], h[3], h[4],
-                    h[5], h[6], h[7], qc[0], qc[1]);
+                            "cells %llu alive %llu puts %llu hidden_at_instance_level %llu queued %u tiles %u\n", ph, a.phase_lo, a.phase_hi, h[0], h[1],
+                    h[2], h[3], h[4], h[5], h[6], h[7], h[9], qc[0], qc[1]);
         }
 #endif
     }

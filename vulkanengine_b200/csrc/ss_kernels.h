@@ -238,6 +238,9 @@ struct RasterArgs {
     void* sort_scratch;
     int sort_passes;
     uint32_t* draw_of;
+    float* draw_aabb;          // [max_draws][6] bounds of the vertices each draw's index range names (min > max: none valid)
+    uint4* bound;              // [visible] per row: cells {x0 | x1 << 16, y0 | y1 << 16} its samples can lie in (x0 > x1: none),
+                               // depth floor bits, instance
     uint32_t* row_of;          // [n_instances], DepthClamp passes: the sort word carries the instance, this maps it back to its row
     unsigned long long* tri_prefix;
     unsigned long long* block_sums;
@@ -263,8 +266,8 @@ struct RasterArgs {
     uint32_t phase_lo, phase_hi;
 };
 size_t raster_hiz_words(uint32_t width, uint32_t height);
-size_t raster_order_bytes(uint32_t n_instances);  // one allocation, carved up by raster_order_carve
-void raster_order_carve(void* blob, uint32_t n_instances, RasterArgs* a);
+size_t raster_order_bytes(uint32_t n_instances, uint32_t max_draws);  // one allocation, carved up by raster_order_carve
+void raster_order_carve(void* blob, uint32_t n_instances, uint32_t max_draws, RasterArgs* a);
 int device_sm_count();  // SMs of the current device, cached per device
 void launch_raster_clear(unsigned long long* target, size_t n, cudaStream_t st);
 void launch_raster(const RasterArgs& a, cudaStream_t st);
