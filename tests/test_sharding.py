@@ -152,6 +152,8 @@ def test_merge_views_equals_single_context(shards, pipe):
     mg = S.Merger(shards, n_views, max_draws_per_rank=1 << 12, max_visible_per_view=n_total)
     for _ in range(2):  # twice: the tables are reused
         mg.merge(peers)
+    stage = mg.stage_ms()  # ss_merge_stage_ms: CUDA-event times of the four kernels
+    assert set(stage) == {"fetch", "rank", "segments", "place"} and all(0.0 <= x < 1e3 for x in stage.values()), stage
     for v in range(n_views):
         o = mg.map(v)
         assert o.visible == len(ref[v]["idx"]) and o.n_draws == len(ref[v]["draws"]), v
