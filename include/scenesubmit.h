@@ -339,7 +339,10 @@ SS_API ss_status ss_set_geometry(ss_ctx* ctx, const float* positions_xyz, uint32
                                  const uint32_t* indices, uint32_t n_indices);
 /* Rasterises view `view` of the frame in `slot` with that view's view_proj into the library's target of that
    view (width x height words, cleared to SS_RASTER_EMPTY first; every view keeps its own size).  Asynchronous on
-   the frame stream. */
+   the frame stream.  The pass draws front to back against a coarse depth buffer it rebuilds as it goes (DESIGN.md
+   section 7); the image is the same whatever the order.  The first call allocates the pass's scratch once per
+   context: 48 bytes per instance of the context (sort words, triangle prefix, per-row bounds) + the sort's own
+   scratch + 24 bytes per draw; the coarse depth (16 bytes per 64 samples) grows with the largest target. */
 SS_API ss_status ss_raster_view(ss_ctx* ctx, uint32_t slot, uint32_t view, uint32_t width, uint32_t height,
                                 uint32_t flags);
 /* Device pointer of view `view`'s target, at the size of its last ss_raster_view (fences the stream), or a copy
