@@ -641,13 +641,15 @@ __device__ __noinline__ void cut_and_queue(const float c[3][4], const float dd[3
     }
 }
 
-// One thread per (instance, triangle) pair of the view, pairs numbered draw by draw, instance by instance: a warp
-// holds 32 consecutive triangles (of one instance of a large mesh, or of a few instances of a small one), whatever the
-// mix of meshes.  A warp finds the draw of its first pair by bisection over the draws' prefix, its lanes walk on from
-// there.  What a triangle costs decides who samples it: a few samples (the common case at scene scale) — its thread;
-// up to 16 K samples — its warp, lanes striding over the bounds; more, or anything cut by the near plane or not
-// snappable — the queue, so that a view whose instances cover thousands of pixels each (the near shadow cascades)
-// is spread over the whole grid.
+// One thread per (instance, triangle) pair of the view, pairs numbered rank by rank of the front-to-back order: a warp
+// takes a chunk of the phase's pairs, finds its first rank by bisection, and goes through the chunk's ranks 32 at a time
+// — one instance-level test per lane — before the triangles of the ranks that survive are set up, one per thread, 32
+// at a time whoever's they are (so a 12-triangle box scene and a 9 K-triangle vase load the lanes alike, and a phase
+// in which nearly everything is hidden costs a few coalesced loads per instance: id pass of cfg 3 3.3 -> 2.4 ms,
+// far cascade 21.3 -> 16.3 ms against testing pair by pair).  What a triangle costs decides who samples it: a few
+// samples (the common case at scene scale) — its thread, balanced over the warp; up to 16 K samples — its warp, cell by
+// cell; more, or anything cut by the near plane or not snappable — the queue, so that a view whose instances cover
+// thousands of pixels each (the near shadow cascades) is spread over the whole grid.
 // 8 CTAs of 128 threads per SM (64 registers): the per-triangle set-up is a chain of dependent loads, and with most
 // triangles dropped by the coarse depth it is what the pass spends its time on; measured on cfg 3's far cascade
 // (199 M triangles) 31.8 ms at 4 CTAs, 26.4 at 6, 23.4 at 8.
@@ -656,6 +658,8 @@ __global__ void __launch_bounds__(kRasterThreads, kRasterCtasPerSm) k_raster(con
 {
     __shared__ __align__(16) uint32_t s_rec[kRasterThreads / 32][32][20];  // per lane: x, y, dx, dy, zn, fa, x0, y0, width, instance
     __shared__ uint32_t s_pre[kRasterThreads / 32][32];                     // samples before each lane's
+    __shared__ uint4 s_ent[kRasterThreads / 32][32];                         // the round's ranks: row, instance, first triangle, draw
+    __shared__ uint32_t s_epre[kRasterThreads / 32][32];                    // live pairs before each of them
     const int lane = threadIdx.x & 31;
     const unsigned long long* order = sorted_order(a);
     const unsigned long long all_pairs = a.tri_prefix[a.visible];
@@ -690,26 +694,24 @@ __global__ void __launch_bounds__(kRasterThreads, kRasterCtasPerSm) k_raster(con
             }
             r_warp = lo;
         }
-        for (unsigned long long g0 = c0; g0 < total; g0 += 32ull) {
-            const unsigned long long g = g0 + (unsigned long long)lane;
-            Work t;
-            t.mode = -1;
-            t.x0 = t.y0 = 0;
-            t.x1 = t.y1 = -1;
-            uint32_t inst = 0;
-            uint32_t r = r_warp;
-            if (g < total) {
-                while (a.tri_prefix[r + 1] <= g) ++r;  // ranks without triangles are stepped over
+        // The ranks of the chunk 32 at a time, one per lane: the instance first — where any of its triangles can land and how
+        // near (k_raster_keys); one that covers no sample, or that lies behind the coarse depth of everything it can
+        // touch, is done with here, before a single index or vertex of it is read.  The triangles of the ranks that are
+        // left are numbered through (exclusive prefix in shared memory) and taken 32 at a time, whoever's they are.
+        for (uint32_t rb = r_warp;; rb += 32u) {
+            const uint32_t r = rb + (uint32_t)lane;
+            const unsigned long long p0 = r < a.visible ? a.tri_prefix[r] : all_pairs;
+            const unsigned long long p1 = r < a.visible ? a.tri_prefix[r + 1] : all_pairs;
+            uint32_t cnt = 0;
+            uint4 ent = make_uint4(0u, 0u, 0u, 0u);  // row, instance, first triangle of the rank in this chunk, draw
+            if (r < a.visible && p0 < total && p1 > c0) {
+                const unsigned long long lo = max(p0, c0), hi = min(p1, total);
                 const uint32_t k = row_at_rank(a, order, r);
-                // the instance first: where any of its triangles can land and how near (k_raster_keys); one that covers no
-                // sample, or that lies behind the coarse depth of everything it can touch, is done with here, before a
-                // single index or vertex of it is read
                 const uint4 bd = a.bound[k];
-                inst = bd.w;
                 const int bx0 = (int)(bd.x & 0xFFFFu), bx1 = (int)(bd.x >> 16), by0 = (int)(bd.y & 0xFFFFu), by1 = (int)(bd.y >> 16);
                 bool hidden = bx0 > bx1;
                 if (!hidden && a.hiz) {
-                    const unsigned long long inst_floor = ((unsigned long long)bd.z << 32) | inst;
+                    const unsigned long long inst_floor = ((unsigned long long)bd.z << 32) | bd.w;
                     if ((bx1 - bx0 + 1) * (by1 - by0 + 1) <= 16) {
                         unsigned long long far = 0;
                         for (int cy = by0; cy <= by1; ++cy)
@@ -722,159 +724,194 @@ __global__ void __launch_bounds__(kRasterThreads, kRasterCtasPerSm) k_raster(con
                         hidden = inst_floor > far;
                     }
                 }
-                RSTAT(9, hidden);
+                RSTAT(9, hidden ? hi - lo : 0);
                 if (!hidden) {
-                const ss_draw_cmd dc = a.draws[a.draw_of[k]];
-                const uint32_t tI = (uint32_t)(g - a.tri_prefix[r]);
-                const float4 r0 = a.rows[(size_t)k * 3 + 0], r1 = a.rows[(size_t)k * 3 + 1], r2 = a.rows[(size_t)k * 3 + 2];
-                // 1: the triangle in clip space
-                float c[3][4], dd[3];
-                bool in_range = true;
-    #pragma unroll
-                for (int v = 0; v < 3; ++v) {
-                    const uint64_t ii = (uint64_t)dc.first_index + (uint64_t)tI * 3u + (uint64_t)v;
-                    if (ii >= a.n_indices) { in_range = false; break; }
-                    const int64_t vi = (int64_t)dc.vertex_offset + (int64_t)a.indices[ii];
-                    if (vi < 0 || vi >= (int64_t)a.n_vertices) { in_range = false; break; }
-                    clip_of(a.vp, r0, r1, r2, a.positions + (size_t)vi * 3, c[v]);
-                }
-                if (in_range) {  // a table that points outside the geometry draws nothing
-    #pragma unroll
-                    for (int v = 0; v < 3; ++v) dd[v] = clamp_depth ? c[v][3] - 1e-5f : c[v][2];
-                    if (dd[0] >= 0.f && dd[1] >= 0.f && dd[2] >= 0.f) {
-                        t = setup(c, (int)a.width, (int)a.height);
-                        if (t.mode == 1) {  // not snappable: never sampled here
-                            queue_or_walk(t, inst, a);
-                            t.mode = -1;
-                        }
-                    } else {
-                        cut_and_queue(c, dd, inst, a);
-                    }
-                }
+                    cnt = (uint32_t)(hi - lo);
+                    ent = make_uint4(k, bd.w, (uint32_t)(lo - p0), a.draw_of[k]);
                 }
             }
-            r_warp = __shfl_sync(0xffffffffu, r, 31);  // where the next 32 pairs start looking
-            // from here on: uncut, snapped triangles only
-            long long samples = t.mode == 0 ? (long long)(t.x1 - t.x0 + 1) * (t.y1 - t.y0 + 1) : 0;
-            const unsigned long long floor_word = ((unsigned long long)work_depth_floor(t, clamp_depth) << 32) | inst;
-            // a large triangle that lies behind the coarse depth of every 64 x 64 tile it touches is dropped here
-            if (a.hiz2 && samples > kCoopSamples) {
-                const int tx0 = t.x0 >> 6, tx1 = t.x1 >> 6, ty0 = t.y0 >> 6, ty1 = t.y1 >> 6;
-                if ((tx1 - tx0 + 1) * (ty1 - ty0 + 1) <= 16) {
-                    unsigned long long far = 0;
-                    for (int ty = ty0; ty <= ty1; ++ty)
-                        for (int tx = tx0; tx <= tx1; ++tx) far = max(far, __ldg(a.hiz2 + (size_t)ty * a.hiz2_w + tx));
-                    if (floor_word > far) {
-                        t.mode = -1;
-                        samples = 0;
-                    }
-                }
+            uint32_t incl_p = cnt;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const uint32_t y = __shfl_up_sync(0xffffffffu, incl_p, o);
+                if (lane >= o) incl_p += y;
             }
-            if (samples > huge_samples) {
-                queue_or_walk(t, inst, a);
+            const uint32_t live = __shfl_sync(0xffffffffu, incl_p, 31);
+            const bool chunk_done = __any_sync(0xffffffffu, r >= a.visible || p1 >= total);
+            __syncwarp();  // the entries of the round before have been read
+            s_ent[threadIdx.x >> 5][lane] = ent;
+            s_epre[threadIdx.x >> 5][lane] = incl_p - cnt;
+            __syncwarp();
+            for (uint32_t j0 = 0; j0 < live; j0 += 32u) {
+                const uint32_t jp = j0 + (uint32_t)lane;
+                const bool g_ok = jp < live;
+                Work t;
                 t.mode = -1;
-                samples = 0;
-            }
-            // a small triangle that lies behind the coarse depth of every cell it touches is dropped here (the others are
-            // sorted out cell by cell where they are sampled)
-            if (a.hiz && samples > 0 && samples <= kCoopSamples) {
-                const int cx0 = t.x0 >> kCellShift, cx1 = t.x1 >> kCellShift, cy0 = t.y0 >> kCellShift, cy1 = t.y1 >> kCellShift;
-                if ((cx1 - cx0 + 1) * (cy1 - cy0 + 1) <= 16) {
-                    unsigned long long far = 0;
-                    for (int cy = cy0; cy <= cy1; ++cy)
-                        for (int cx = cx0; cx <= cx1; ++cx) far = max(far, __ldg(a.hiz + (size_t)cy * a.hiz_w + cx));
-                    RSTAT(2, floor_word > far);
-                    if (floor_word > far) {
-                        t.mode = -1;
-                        samples = 0;
+                t.x0 = t.y0 = 0;
+                t.x1 = t.y1 = -1;
+                uint32_t inst = 0;
+                if (g_ok) {
+                    // the last entry whose first pair is <= jp (entries without pairs share their successor's start)
+                    int owner = 0;
+#pragma unroll
+                    for (int step = 16; step > 0; step >>= 1)
+                        if (s_epre[threadIdx.x >> 5][owner + step] <= jp) owner += step;
+                    const uint4 en = s_ent[threadIdx.x >> 5][owner];
+                    const uint32_t k = en.x;
+                    inst = en.y;
+                    {
+                    const ss_draw_cmd dc = a.draws[en.w];
+                    const uint32_t tI = en.z + (jp - s_epre[threadIdx.x >> 5][owner]);
+                    const float4 r0 = a.rows[(size_t)k * 3 + 0], r1 = a.rows[(size_t)k * 3 + 1], r2 = a.rows[(size_t)k * 3 + 2];
+                    // 1: the triangle in clip space
+                    float c[3][4], dd[3];
+                    bool in_range = true;
+#pragma unroll
+                    for (int v = 0; v < 3; ++v) {
+                        const uint64_t ii = (uint64_t)dc.first_index + (uint64_t)tI * 3u + (uint64_t)v;
+                        if (ii >= a.n_indices) { in_range = false; break; }
+                        const int64_t vi = (int64_t)dc.vertex_offset + (int64_t)a.indices[ii];
+                        if (vi < 0 || vi >= (int64_t)a.n_vertices) { in_range = false; break; }
+                        clip_of(a.vp, r0, r1, r2, a.positions + (size_t)vi * 3, c[v]);
+                    }
+                    if (in_range) {  // a table that points outside the geometry draws nothing
+#pragma unroll
+                        for (int v = 0; v < 3; ++v) dd[v] = clamp_depth ? c[v][3] - 1e-5f : c[v][2];
+                        if (dd[0] >= 0.f && dd[1] >= 0.f && dd[2] >= 0.f) {
+                            t = setup(c, (int)a.width, (int)a.height);
+                            if (t.mode == 1) {  // not snappable: never sampled here
+                                queue_or_walk(t, inst, a);
+                                t.mode = -1;
+                            }
+                        } else {
+                            cut_and_queue(c, dd, inst, a);
+                        }
+                    }
                     }
                 }
-            }
-            // The samples of the warp's 32 triangles, dealt out evenly: each lane leaves its triangle's record in shared
-            // memory and the lanes then take the samples of all bounds 32 at a time, whoever's they are.  (Sampling one's
-            // own triangle would cost the warp as many rounds as its largest triangle has samples, with most lanes idle:
-            // measured 14 of 32 lanes busy and 10 K instructions per 32 triangles on the camera view of cfg 3.)
-            // A triangle of more than kCoopSamples keeps the warp to itself instead (its record is broadcast once and the
-            // lanes stride over its bounds: no owner search and no division per sample).
-            const bool coop = t.mode == 0 && samples > kCoopSamples;
-            RSTAT(0, g < total);
-            RSTAT(1, t.mode == 0 && samples > 0);
-            if (t.mode == 0 && !coop) RSTAT(3, samples);
-            RSTAT(4, coop);
-            RSTAT(8, t.mode == 0 && samples > 0 && (floor_word >> 32) == 0u);
-            const uint32_t count = (t.mode == 0 && !coop) ? (uint32_t)samples : 0u;
-            uint32_t todo = __ballot_sync(0xffffffffu, coop);
-            while (todo) {
-                const int src = __ffs(todo) - 1;
-                todo &= todo - 1;
-                Work w;
-    #pragma unroll
-                for (int q = 0; q < 9; ++q) w.w[q] = __shfl_sync(0xffffffffu, t.w[q], src);
-                w.x0 = __shfl_sync(0xffffffffu, t.x0, src);
-                w.x1 = __shfl_sync(0xffffffffu, t.x1, src);
-                w.y0 = __shfl_sync(0xffffffffu, t.y0, src);
-                w.y1 = __shfl_sync(0xffffffffu, t.y1, src);
-                w.mode = 0;
-                const uint32_t w_inst = __shfl_sync(0xffffffffu, inst, src);
-                const Prep p = prepare(w);
-                warp_sample_rect(p, 0, w.x0, w.x1, w.y0, w.y1, __shfl_sync(0xffffffffu, floor_word, src), clamp_depth, w_inst, a, lane);
-            }
-            const uint32_t most = __reduce_max_sync(0xffffffffu, count);
-            if (most <= 2u) {  // nothing to balance
+                // from here on: uncut, snapped triangles only
+                long long samples = t.mode == 0 ? (long long)(t.x1 - t.x0 + 1) * (t.y1 - t.y0 + 1) : 0;
+                const unsigned long long floor_word = ((unsigned long long)work_depth_floor(t, clamp_depth) << 32) | inst;
+                // a large triangle that lies behind the coarse depth of every 64 x 64 tile it touches is dropped here
+                if (a.hiz2 && samples > kCoopSamples) {
+                    const int tx0 = t.x0 >> 6, tx1 = t.x1 >> 6, ty0 = t.y0 >> 6, ty1 = t.y1 >> 6;
+                    if ((tx1 - tx0 + 1) * (ty1 - ty0 + 1) <= 16) {
+                        unsigned long long far = 0;
+                        for (int ty = ty0; ty <= ty1; ++ty)
+                            for (int tx = tx0; tx <= tx1; ++tx) far = max(far, __ldg(a.hiz2 + (size_t)ty * a.hiz2_w + tx));
+                        if (floor_word > far) {
+                            t.mode = -1;
+                            samples = 0;
+                        }
+                    }
+                }
+                if (samples > huge_samples) {
+                    queue_or_walk(t, inst, a);
+                    t.mode = -1;
+                    samples = 0;
+                }
+                // a small triangle that lies behind the coarse depth of every cell it touches is dropped here (the others are
+                // sorted out cell by cell where they are sampled)
+                if (a.hiz && samples > 0 && samples <= kCoopSamples) {
+                    const int cx0 = t.x0 >> kCellShift, cx1 = t.x1 >> kCellShift, cy0 = t.y0 >> kCellShift, cy1 = t.y1 >> kCellShift;
+                    if ((cx1 - cx0 + 1) * (cy1 - cy0 + 1) <= 16) {
+                        unsigned long long far = 0;
+                        for (int cy = cy0; cy <= cy1; ++cy)
+                            for (int cx = cx0; cx <= cx1; ++cx) far = max(far, __ldg(a.hiz + (size_t)cy * a.hiz_w + cx));
+                        RSTAT(2, floor_word > far);
+                        if (floor_word > far) {
+                            t.mode = -1;
+                            samples = 0;
+                        }
+                    }
+                }
+                // The samples of the warp's 32 triangles, dealt out evenly: each lane leaves its triangle's record in shared
+                // memory and the lanes then take the samples of all bounds 32 at a time, whoever's they are.  (Sampling one's
+                // own triangle would cost the warp as many rounds as its largest triangle has samples, with most lanes idle:
+                // measured 14 of 32 lanes busy and 10 K instructions per 32 triangles on the camera view of cfg 3.)
+                // A triangle of more than kCoopSamples keeps the warp to itself instead (its record is broadcast once and the
+                // lanes stride over its bounds: no owner search and no division per sample).
+                const bool coop = t.mode == 0 && samples > kCoopSamples;
+                RSTAT(0, g_ok);
+                RSTAT(1, t.mode == 0 && samples > 0);
+                if (t.mode == 0 && !coop) RSTAT(3, samples);
+                RSTAT(4, coop);
+                RSTAT(8, t.mode == 0 && samples > 0 && (floor_word >> 32) == 0u);
+                const uint32_t count = (t.mode == 0 && !coop) ? (uint32_t)samples : 0u;
+                uint32_t todo = __ballot_sync(0xffffffffu, coop);
+                while (todo) {
+                    const int src = __ffs(todo) - 1;
+                    todo &= todo - 1;
+                    Work w;
+#pragma unroll
+                    for (int q = 0; q < 9; ++q) w.w[q] = __shfl_sync(0xffffffffu, t.w[q], src);
+                    w.x0 = __shfl_sync(0xffffffffu, t.x0, src);
+                    w.x1 = __shfl_sync(0xffffffffu, t.x1, src);
+                    w.y0 = __shfl_sync(0xffffffffu, t.y0, src);
+                    w.y1 = __shfl_sync(0xffffffffu, t.y1, src);
+                    w.mode = 0;
+                    const uint32_t w_inst = __shfl_sync(0xffffffffu, inst, src);
+                    const Prep p = prepare(w);
+                    warp_sample_rect(p, 0, w.x0, w.x1, w.y0, w.y1, __shfl_sync(0xffffffffu, floor_word, src), clamp_depth, w_inst, a, lane);
+                }
+                const uint32_t most = __reduce_max_sync(0xffffffffu, count);
+                if (most <= 2u) {  // nothing to balance
+                    if (count) {
+                        const Prep p = prepare(t);
+                        for (int j = t.y0; j <= t.y1; ++j)
+                            for (int i = t.x0; i <= t.x1; ++i) shade(p, 0, i, j, clamp_depth, inst, a.target, a.width);
+                    }
+                    continue;
+                }
+                uint32_t incl = count;
+#pragma unroll
+                for (int o = 1; o < 32; o <<= 1) {
+                    const uint32_t y = __shfl_up_sync(0xffffffffu, incl, o);
+                    if (lane >= o) incl += y;
+                }
+                const uint32_t all = __shfl_sync(0xffffffffu, incl, 31);
+                uint32_t* rec = s_rec[threadIdx.x >> 5][lane];
+                uint32_t* pre = s_pre[threadIdx.x >> 5];
+                pre[lane] = incl - count;
                 if (count) {
                     const Prep p = prepare(t);
-                    for (int j = t.y0; j <= t.y1; ++j)
-                        for (int i = t.x0; i <= t.x1; ++i) shade(p, 0, i, j, clamp_depth, inst, a.target, a.width);
+#pragma unroll
+                    for (int q = 0; q < 3; ++q) {
+                        rec[q] = (uint32_t)p.x[q];
+                        rec[3 + q] = (uint32_t)p.y[q];
+                        rec[6 + q] = (uint32_t)p.dx[q];
+                        rec[9 + q] = (uint32_t)p.dy[q];
+                        rec[12 + q] = __float_as_uint(p.zn[q]);
+                    }
+                    rec[15] = __float_as_uint(p.fa);
+                    rec[16] = (uint32_t)t.x0;
+                    rec[17] = (uint32_t)t.y0;
+                    rec[18] = (uint32_t)(t.x1 - t.x0 + 1);
+                    rec[19] = inst;
                 }
-                continue;
-            }
-            uint32_t incl = count;
-    #pragma unroll
-            for (int o = 1; o < 32; o <<= 1) {
-                const uint32_t y = __shfl_up_sync(0xffffffffu, incl, o);
-                if (lane >= o) incl += y;
-            }
-            const uint32_t all = __shfl_sync(0xffffffffu, incl, 31);
-            uint32_t* rec = s_rec[threadIdx.x >> 5][lane];
-            uint32_t* pre = s_pre[threadIdx.x >> 5];
-            pre[lane] = incl - count;
-            if (count) {
-                const Prep p = prepare(t);
-    #pragma unroll
-                for (int q = 0; q < 3; ++q) {
-                    rec[q] = (uint32_t)p.x[q];
-                    rec[3 + q] = (uint32_t)p.y[q];
-                    rec[6 + q] = (uint32_t)p.dx[q];
-                    rec[9 + q] = (uint32_t)p.dy[q];
-                    rec[12 + q] = __float_as_uint(p.zn[q]);
+                __syncwarp();
+                for (uint32_t sIdx = lane; sIdx < all; sIdx += 32) {
+                    // the last lane whose first sample is <= sIdx (lanes without samples share their successor's start)
+                    int owner = 0;
+#pragma unroll
+                    for (int step = 16; step > 0; step >>= 1)
+                        if (pre[owner + step] <= sIdx) owner += step;
+                    const uint4* r4 = reinterpret_cast<const uint4*>(s_rec[threadIdx.x >> 5][owner]);
+                    const uint4 q0 = r4[0], q1 = r4[1], q2 = r4[2], q3 = r4[3], q4 = r4[4];
+                    Prep p;
+                    p.x[0] = (int)q0.x; p.x[1] = (int)q0.y; p.x[2] = (int)q0.z;
+                    p.y[0] = (int)q0.w; p.y[1] = (int)q1.x; p.y[2] = (int)q1.y;
+                    p.dx[0] = (int)q1.z; p.dx[1] = (int)q1.w; p.dx[2] = (int)q2.x;
+                    p.dy[0] = (int)q2.y; p.dy[1] = (int)q2.z; p.dy[2] = (int)q2.w;
+                    p.zn[0] = __uint_as_float(q3.x); p.zn[1] = __uint_as_float(q3.y); p.zn[2] = __uint_as_float(q3.z);
+                    p.fa = __uint_as_float(q3.w);
+                    const uint32_t local = sIdx - pre[owner], bw = q4.z;
+                    const uint32_t row = local / bw;
+                    shade(p, 0, (int)(q4.x + (local - row * bw)), (int)(q4.y + row), clamp_depth, q4.w, a.target, a.width);
                 }
-                rec[15] = __float_as_uint(p.fa);
-                rec[16] = (uint32_t)t.x0;
-                rec[17] = (uint32_t)t.y0;
-                rec[18] = (uint32_t)(t.x1 - t.x0 + 1);
-                rec[19] = inst;
+                __syncwarp();  // the records are rewritten on the next round
             }
-            __syncwarp();
-            for (uint32_t sIdx = lane; sIdx < all; sIdx += 32) {
-                // the last lane whose first sample is <= sIdx (lanes without samples share their successor's start)
-                int owner = 0;
-    #pragma unroll
-                for (int step = 16; step > 0; step >>= 1)
-                    if (pre[owner + step] <= sIdx) owner += step;
-                const uint4* r4 = reinterpret_cast<const uint4*>(s_rec[threadIdx.x >> 5][owner]);
-                const uint4 q0 = r4[0], q1 = r4[1], q2 = r4[2], q3 = r4[3], q4 = r4[4];
-                Prep p;
-                p.x[0] = (int)q0.x; p.x[1] = (int)q0.y; p.x[2] = (int)q0.z;
-                p.y[0] = (int)q0.w; p.y[1] = (int)q1.x; p.y[2] = (int)q1.y;
-                p.dx[0] = (int)q1.z; p.dx[1] = (int)q1.w; p.dx[2] = (int)q2.x;
-                p.dy[0] = (int)q2.y; p.dy[1] = (int)q2.z; p.dy[2] = (int)q2.w;
-                p.zn[0] = __uint_as_float(q3.x); p.zn[1] = __uint_as_float(q3.y); p.zn[2] = __uint_as_float(q3.z);
-                p.fa = __uint_as_float(q3.w);
-                const uint32_t local = sIdx - pre[owner], bw = q4.z;
-                const uint32_t row = local / bw;
-                shade(p, 0, (int)(q4.x + (local - row * bw)), (int)(q4.y + row), clamp_depth, q4.w, a.target, a.width);
-            }
-            __syncwarp();  // the records are rewritten on the next round
+            if (chunk_done) break;
         }
     }
 }
