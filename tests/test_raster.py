@@ -206,3 +206,19 @@ def test_heavy_overdraw_is_drawn_in_phases(flags_name):
         assert np.array_equal(img, want), f"view {v}: {np.count_nonzero(img != want)} samples differ"
         assert np.count_nonzero(img != np.uint64(S.RASTER_EMPTY)) > 160 * 120 // 2
     ctx.close()
+
+
+@pytest.mark.parametrize("flags_name", ["default", "depth_clamp"])
+def test_large_target_exercises_tiles_and_the_queue(flags_name):
+    """A 512 x 384 target seen from inside the cloud: triangles of tens of thousands of samples go through the tile queue,
+    whose entries are filtered against the 64 x 64 level of the coarse depth as they are queued, the middle sizes are
+    sampled cell by cell; several phases.  Bit-equal to the restatement."""
+    flags = S.RASTER_DEPTH_CLAMP if flags_name == "depth_clamp" else 0
+    sc, pos, ind = close_up_scene(2400, spread=30.0, seed_shift=91)
+    views = synth.fibonacci_cameras(lambda *a: O.camera_view_proj(*a), 1, radius=8.0, seed=synth.SEED_BASE + 91)
+    ctx, slot, out = run(sc, pos, ind, views, 512, 384, lambda v: flags)
+    img, want, got_view = out[0]
+    assert len(got_view["idx"]) >= 256
+    assert np.array_equal(img, want), f"{np.count_nonzero(img != want)} samples differ"
+    assert np.count_nonzero(img != np.uint64(S.RASTER_EMPTY)) > 512 * 384 // 2
+    ctx.close()
