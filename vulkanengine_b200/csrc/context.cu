@@ -1327,12 +1327,12 @@ SS_API ss_status ss_raster_view(ss_ctx* c, uint32_t slot, uint32_t view, uint32_
     ra.max_draws = c->max_draws;
     if (!c->d_raster_order) SS_CUDA(c, cudaMalloc(&c->d_raster_order, raster_order_bytes(c->n_instances, c->max_draws)));
     raster_order_carve(c->d_raster_order, c->n_instances, c->max_draws, &ra);
-    constexpr uint32_t kRasterQueueWorks = 1u << 19, kRasterQueueTiles = 1u << 23;  // 40 MB + 32 MB, on first use
+    constexpr uint32_t kRasterQueueWorks = 1u << 19, kRasterQueueTiles = 1u << 23;  // 40 MB + 64 MB (two words per entry), on first use
     if (!c->d_raster_queue)
-        SS_CUDA(c, cudaMalloc(&c->d_raster_queue, ((size_t)kRasterQueueWorks * 20 + kRasterQueueTiles + 4) * sizeof(uint32_t)));
+        SS_CUDA(c, cudaMalloc(&c->d_raster_queue, ((size_t)kRasterQueueWorks * 20 + 2 * (size_t)kRasterQueueTiles + 4) * sizeof(uint32_t)));
     ra.queue_works = c->d_raster_queue;
     ra.queue_tiles = c->d_raster_queue + (size_t)kRasterQueueWorks * 20;
-    ra.queue_counts = ra.queue_tiles + kRasterQueueTiles;
+    ra.queue_counts = ra.queue_tiles + 2 * (size_t)kRasterQueueTiles;
     ra.queue_work_cap = kRasterQueueWorks;
     ra.queue_tile_cap = kRasterQueueTiles;
     ra.positions = c->d_positions;

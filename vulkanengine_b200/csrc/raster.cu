@@ -570,33 +570,46 @@ __global__ void __launch_bounds__(kScanThreads) k_raster_scan_apply(const __grid
 __device__ __noinline__ void queue_or_walk(const Work& t, uint32_t inst, const RasterArgs& a)
 {
     const bool clamp_depth = (a.flags & SS_RASTER_DEPTH_CLAMP) != 0;
+    const Prep p = prepare(t);
     if (a.queue_works) {
+        // Only the tiles that can matter get an entry: not those that already lie in front of everything the triangle
+        // can store (64 x 64 level of the coarse depth), nor those wholly outside one of its edges.
         const int tx0 = t.x0 >> 6, ty0 = t.y0 >> 6;
-        const uint32_t n_tiles = (uint32_t)(((t.x1 >> 6) - tx0 + 1) * ((t.y1 >> 6) - ty0 + 1));
+        const uint32_t tnx = (uint32_t)((t.x1 >> 6) - tx0 + 1);
+        const uint32_t n_tiles = tnx * (uint32_t)((t.y1 >> 6) - ty0 + 1);
+        const unsigned long long floor_word = ((unsigned long long)work_depth_floor(t, clamp_depth) << 32) | inst;
+        auto matters = [&](uint32_t k) {
+            const int ty = ty0 + (int)(k / tnx), tx = tx0 + (int)(k % tnx);
+            if (a.hiz2 && floor_word > __ldg(a.hiz2 + (size_t)ty * a.hiz2_w + tx)) return false;
+            if (t.mode == 0 && rect_outside(p, max(t.x0, tx << 6), min(t.x1, (tx << 6) + 63), max(t.y0, ty << 6), min(t.y1, (ty << 6) + 63)))
+                return false;
+            return true;
+        };
+        uint32_t n_alive = 0;
+        for (uint32_t k = 0; k < n_tiles; ++k) n_alive += matters(k) ? 1u : 0u;
+        if (n_alive == 0) return;
         const uint32_t slot_w = atomicAdd(a.queue_counts + 0, 1u);
         if (slot_w < a.queue_work_cap) {
-            const uint32_t base_t = atomicAdd(a.queue_counts + 1, n_tiles);
-            if ((unsigned long long)base_t + n_tiles <= a.queue_tile_cap) {
+            const uint32_t base_t = atomicAdd(a.queue_counts + 1, n_alive);
+            if ((unsigned long long)base_t + n_alive <= a.queue_tile_cap) {
                 uint32_t* rec = a.queue_works + (size_t)slot_w * kWorkWords;
 #pragma unroll
                 for (int q = 0; q < 13; ++q) rec[q] = t.w[q];
                 rec[13] = (uint32_t)t.x0; rec[14] = (uint32_t)t.x1; rec[15] = (uint32_t)t.y0; rec[16] = (uint32_t)t.y1;
-                rec[17] = (uint32_t)t.mode; rec[18] = inst; rec[19] = base_t;
-                // an entry whose tile already lies in front of everything the triangle can store is nobody's
-                const unsigned long long floor_word = ((unsigned long long)work_depth_floor(t, clamp_depth) << 32) | inst;
-                const uint32_t tnx = (uint32_t)((t.x1 >> 6) - tx0 + 1);
-                for (uint32_t k = 0; k < n_tiles; ++k) {
-                    const uint32_t ty = (uint32_t)ty0 + k / tnx, tx = (uint32_t)tx0 + k % tnx;
-                    const bool hidden = a.hiz2 && floor_word > __ldg(a.hiz2 + (size_t)ty * a.hiz2_w + tx);
-                    a.queue_tiles[base_t + k] = hidden ? 0xFFFFFFFFu : slot_w;
-                }
+                rec[17] = (uint32_t)t.mode; rec[18] = inst; rec[19] = 0u;
+                uint32_t at = base_t;
+                for (uint32_t k = 0; k < n_tiles; ++k)
+                    if (matters(k)) {
+                        a.queue_tiles[2 * (size_t)at] = slot_w;
+                        a.queue_tiles[2 * (size_t)at + 1] = k;
+                        ++at;
+                    }
                 return;
             }
             // the tile list is full: the part of the range that exists is marked as nobody's
-            for (unsigned long long k = base_t; k < a.queue_tile_cap; ++k) a.queue_tiles[k] = 0xFFFFFFFFu;
+            for (unsigned long long k = base_t; k < a.queue_tile_cap; ++k) a.queue_tiles[2 * k] = 0xFFFFFFFFu;
         }
     }
-    const Prep p = prepare(t);
     for (int j = t.y0; j <= t.y1; ++j)
         for (int i = t.x0; i <= t.x1; ++i) shade(p, t.mode, i, j, clamp_depth, inst, a.target, a.width);
 }
@@ -927,7 +940,7 @@ __global__ void __launch_bounds__(kRasterThreads) k_raster_tiles(const __grid_co
     const uint32_t warps = (gridDim.x * kRasterThreads) >> 5;
     const uint32_t warp_id = (blockIdx.x * kRasterThreads + threadIdx.x) >> 5;
     for (uint32_t e = warp_id; e < n_entries; e += warps) {
-        const uint32_t owner = a.queue_tiles[e];
+        const uint32_t owner = a.queue_tiles[2 * (size_t)e];
         if (owner == 0xFFFFFFFFu) continue;
         const uint32_t* rec = a.queue_works + (size_t)owner * kWorkWords;
         Work w;
@@ -937,7 +950,7 @@ __global__ void __launch_bounds__(kRasterThreads) k_raster_tiles(const __grid_co
         w.mode = (int)rec[17];
         const uint32_t inst = rec[18];
         const int tx0 = w.x0 >> 6, ty0 = w.y0 >> 6, tnx = (w.x1 >> 6) - tx0 + 1;
-        const int local = (int)(e - rec[19]);
+        const int local = (int)a.queue_tiles[2 * (size_t)e + 1];
         const int tx = tx0 + local % tnx, ty = ty0 + local / tnx;
         // the tile's samples that lie inside the triangle's bounds
         const int x0 = max(w.x0, tx << 6), x1 = min(w.x1, (tx << 6) + 63), y0 = max(w.y0, ty << 6), y1 = min(w.y1, (ty << 6) + 63);
@@ -1024,8 +1037,8 @@ void launch_raster(const RasterArgs& a_in, cudaStream_t st)
         a.phase_hi = hi;
         lo = hi;
         cudaMemsetAsync(a.queue_counts, 0, 4 * sizeof(uint32_t), st);  // queue fill and the next chunk of pairs
-        k_raster<<<sms * 3 * kRasterCtasPerSm, kRasterThreads, 0, st>>>(a);  // persistent warps taking chunks of the phase's pairs
-        if (a.queue_works) k_raster_tiles<<<sms * 12, kRasterThreads, 0, st>>>(a);  // ... and striding over the queued tiles
+        k_raster<<<sms * kRasterCtasPerSm, kRasterThreads, 0, st>>>(a);  // persistent warps taking chunks of the phase's pairs
+        if (a.queue_works) k_raster_tiles<<<sms * 8, kRasterThreads, 0, st>>>(a);  // ... and striding over the queued tiles
         if (a.hiz && ph + 1 < phases) {
             const size_t want = (cells + 255) / 256;
             k_raster_hiz<<<(unsigned)std::min<size_t>(want, (size_t)sms * 8), 256, 0, st>>>(a.target, a.width, a.height, a.hiz, a.hiz_w, a.hiz_h);

@@ -254,7 +254,7 @@ struct RasterArgs {
     unsigned long long* target;  // [height][width] words [depth bits | instance], SS_RASTER_EMPTY where untouched
     // queue of huge triangles (nullptr: none, they are walked where they are found)
     uint32_t* queue_works;     // [queue_work_cap][20]
-    uint32_t* queue_tiles;     // [queue_tile_cap] owner work of each 64 x 64 tile entry
+    uint32_t* queue_tiles;     // [queue_tile_cap][2] {work, which 64 x 64 tile of its bounds} of each entry
     uint32_t* queue_counts;    // {works, tile entries, next chunk of pairs, unused}
     uint32_t queue_work_cap, queue_tile_cap;
     // coarse depth: per 8 x 8-sample cell an upper bound of the words its samples hold (all ones: unknown), refreshed
