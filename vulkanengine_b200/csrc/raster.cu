@@ -296,31 +296,45 @@ __device__ __forceinline__ void warp_sample_rect(const Prep& p, int mode, int x0
 
 // hiz[cell] = the largest word among the cell's samples (all ones while any of them is empty).  The target's words
 // only ever fall, so the value stays an upper bound for as long as it is used.
+// a warp takes four cells next to each other: lane = 4 row + cell, so the lanes of a row read 256 contiguous bytes
 __global__ void __launch_bounds__(256) k_raster_hiz(const unsigned long long* __restrict__ target, uint32_t width, uint32_t height,
                                                     unsigned long long* __restrict__ hiz, uint32_t hiz_w, uint32_t hiz_h)
 {
-    const uint32_t n = hiz_w * hiz_h;
-    for (uint32_t c = blockIdx.x * blockDim.x + threadIdx.x; c < n; c += gridDim.x * blockDim.x) {
-        const uint32_t cy = c / hiz_w, cx = c - cy * hiz_w;
-        const uint32_t x0 = cx << kCellShift, y0 = cy << kCellShift;
+    const uint32_t groups_x = (hiz_w + 3) / 4, n_groups = groups_x * hiz_h;
+    const uint32_t lane = threadIdx.x & 31u, warps = (gridDim.x * blockDim.x) >> 5;
+    const uint32_t row = lane >> 2, cl = lane & 3u;
+    for (uint32_t g = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; g < n_groups; g += warps) {
+        const uint32_t cy = g / groups_x, cx = (g - cy * groups_x) * 4 + cl;
+        const uint32_t x0 = cx << kCellShift, y = (cy << kCellShift) + row;
         unsigned long long m = 0;
-        const uint32_t x1 = min(x0 + 8u, width), y1 = min(y0 + 8u, height);
-        for (uint32_t j = y0; j < y1; ++j)
-            for (uint32_t i = x0; i < x1; ++i) m = max(m, __ldcg(target + (size_t)j * width + i));
-        hiz[c] = m;
+        if (cx < hiz_w && y < height) {
+            const uint32_t x1 = min(x0 + 8u, width);
+            for (uint32_t i = x0; i < x1; ++i) m = max(m, __ldcg(target + (size_t)y * width + i));
+        }
+        m = max(m, __shfl_xor_sync(0xffffffffu, m, 4));
+        m = max(m, __shfl_xor_sync(0xffffffffu, m, 8));
+        m = max(m, __shfl_xor_sync(0xffffffffu, m, 16));
+        if (row == 0 && cx < hiz_w) hiz[(size_t)cy * hiz_w + cx] = m;
     }
 }
 
+// one warp per tile: its 8 x 8 cells two per lane
 __global__ void __launch_bounds__(256) k_raster_hiz2(const unsigned long long* __restrict__ hiz, uint32_t hiz_w, uint32_t hiz_h,
                                                      unsigned long long* __restrict__ hiz2, uint32_t hiz2_w, uint32_t hiz2_h)
 {
     const uint32_t n = hiz2_w * hiz2_h;
-    for (uint32_t c = blockIdx.x * blockDim.x + threadIdx.x; c < n; c += gridDim.x * blockDim.x) {
+    const uint32_t lane = threadIdx.x & 31u, warps = (gridDim.x * blockDim.x) >> 5;
+    for (uint32_t c = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; c < n; c += warps) {
         const uint32_t ty = c / hiz2_w, tx = c - ty * hiz2_w;
         unsigned long long m = 0;
-        for (uint32_t cy = ty * 8; cy < min(ty * 8 + 8u, hiz_h); ++cy)
-            for (uint32_t cx = tx * 8; cx < min(tx * 8 + 8u, hiz_w); ++cx) m = max(m, hiz[(size_t)cy * hiz_w + cx]);
-        hiz2[c] = m;
+#pragma unroll
+        for (uint32_t h = 0; h < 2; ++h) {
+            const uint32_t q = lane + 32u * h, cy = ty * 8 + (q >> 3), cx = tx * 8 + (q & 7u);
+            if (cy < hiz_h && cx < hiz_w) m = max(m, hiz[(size_t)cy * hiz_w + cx]);
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) m = max(m, __shfl_xor_sync(0xffffffffu, m, o));
+        if (lane == 0) hiz2[c] = m;
     }
 }
 
@@ -1040,9 +1054,9 @@ void launch_raster(const RasterArgs& a_in, cudaStream_t st)
         k_raster<<<sms * kRasterCtasPerSm, kRasterThreads, 0, st>>>(a);  // persistent warps taking chunks of the phase's pairs
         if (a.queue_works) k_raster_tiles<<<sms * 8, kRasterThreads, 0, st>>>(a);  // ... and striding over the queued tiles
         if (a.hiz && ph + 1 < phases) {
-            const size_t want = (cells + 255) / 256;
+            const size_t want = ((size_t)((a.hiz_w + 3) / 4) * a.hiz_h + 7) / 8;  // a warp per four cells
             k_raster_hiz<<<(unsigned)std::min<size_t>(want, (size_t)sms * 8), 256, 0, st>>>(a.target, a.width, a.height, a.hiz, a.hiz_w, a.hiz_h);
-            k_raster_hiz2<<<(unsigned)((tiles + 255) / 256), 256, 0, st>>>(a.hiz, a.hiz_w, a.hiz_h, a.hiz2, a.hiz2_w, a.hiz2_h);
+            k_raster_hiz2<<<(unsigned)std::min<size_t>((tiles + 7) / 8, (size_t)sms * 8), 256, 0, st>>>(a.hiz, a.hiz_w, a.hiz_h, a.hiz2, a.hiz2_w, a.hiz2_h);
         }
 #ifdef SS_RASTER_STATS
         {
