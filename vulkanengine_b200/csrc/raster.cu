@@ -475,13 +475,22 @@ __global__ void __launch_bounds__(256) k_raster_keys(const __grid_constant__ Ras
         uint32_t low = k;
         if (a.flags & SS_RASTER_DEPTH_CLAMP) {
             // everything in front of the near plane is stored at depth 0 and the lowest instance wins there: those rows
-            // are drawn in instance order (the sort then runs over all 64 bits)
+            // are drawn in instance order (the sort then runs over the instance bits too)
             key = key > 0.f ? fminf(key, 1.0f) : 0.f;
             low = a.idx[k];
             a.row_of[low] = k;
         }
-        const uint32_t bits = __float_as_uint(key);
-        const uint32_t sortable = bits ^ ((bits >> 31) ? 0xFFFFFFFFu : 0x80000000u);
+        uint32_t sortable;
+        if (a.flags & SS_RASTER_DEPTH_CLAMP) {
+            sortable = __float_as_uint(key);  // in [0, 1]: the bits order like the values
+        } else {
+            // 16 bits of key are enough for an order that only decides how much can be skipped: the upper half of the
+            // float bits of 1 - depth, reversed — for a perspective view that is 1 / distance in steps of 0.8 %.  Two
+            // sort passes instead of four.  (An orthographic DepthClamp pass keeps all 32 bits: with 16, steps of 0.4 %
+            // of the depth range, cascade 2 of cfg 3 went from 3.6 to 4.6 ms.)
+            const float gap = fmaxf(1.0f - key, 1e-30f);  // > 1 in front of the near plane, tiny at and beyond the far one
+            sortable = 0xFFFFu - (__float_as_uint(gap) >> 16);
+        }
         a.order_a[k] = ((unsigned long long)sortable << 32) | low;
         a.draw_of[k] = d;
         const uint32_t inst = a.idx[k];
@@ -1024,11 +1033,12 @@ void launch_raster(const RasterArgs& a_in, cudaStream_t st)
     const unsigned row_grid = (unsigned)std::min<size_t>(((size_t)a.visible + 255) / 256, (size_t)sms * 8);
     const unsigned scan_grid = (a.visible + kScanTile - 1) / kScanTile;
     const int sort_begin = (a.flags & SS_RASTER_DEPTH_CLAMP) ? 0 : 32;
-    a.sort_passes = sort_num_passes(sort_begin, 64);
+    const int sort_end = (a.flags & SS_RASTER_DEPTH_CLAMP) ? 64 : 48;
+    a.sort_passes = sort_num_passes(sort_begin, sort_end);
     k_raster_draw_bounds<<<(unsigned)std::min<uint32_t>(std::max<uint32_t>(a.max_draws, 1u), (uint32_t)sms * 16u), 128, 0, st>>>(a);
     k_raster_keys<<<row_grid, 256, 0, st>>>(a);
     int sort_launches = 0;
-    sort_async(reinterpret_cast<uint64_t*>(a.order_a), nullptr, reinterpret_cast<uint64_t*>(a.order_b), nullptr, a.visible, sort_begin, 64,
+    sort_async(reinterpret_cast<uint64_t*>(a.order_a), nullptr, reinterpret_cast<uint64_t*>(a.order_b), nullptr, a.visible, sort_begin, sort_end,
                a.sort_scratch, st, &sort_launches, false);
     k_raster_scan_sums<<<scan_grid, kScanThreads, 0, st>>>(a);
     k_raster_scan_top<<<1, kScanThreads, 0, st>>>(a.block_sums, scan_grid);
